@@ -1,0 +1,125 @@
+"""Generate tests/golden/*.npz by running the REFERENCE'S OWN FILES (unmodified, imported
+from /root/reference over oracle/shims — see oracle/refbridge.py) on the reference's own
+cleaned CSVs.  Runs only in the build container; the fixtures travel, the reference does not.
+
+    python -m oracle.make_golden            # writes tests/golden/ref_modeR_L{2,8,21}.npz, ref_helpers.npz, ...
+
+Inputs that the reference would draw from TensorFlow's RNG (initial kernels, shuffles) are
+explicit and stored in the fixture, so the CUDA path and oracle/ae_oracle.py can be given the
+very same ones.
+"""
+from __future__ import annotations
+
+import os
+import sys
+
+import numpy as np
+import pandas as pd
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.dirname(HERE))
+
+from oracle import fitcore, refbridge  # noqa: E402
+
+OUT = os.path.join(os.path.dirname(HERE), "tests", "golden")
+
+
+def run_reference_AE(ae_mod, keras, data, L, seed, perm=None, patience=5, epochs=None, grads_at=(0, 1, 100)):
+    etf, hfd, rf = data
+    from sklearn.model_selection import train_test_split
+    X_train, X_test, Y_train, Y_test = train_test_split(etf, hfd, shuffle=False, test_size=.5)   # ipynb:112
+    We0, Wd0 = fitcore.initial_weights(seed, etf.shape[1], L)
+    feed = iter([We0, Wd0])
+    keras.CONTROL.update(w0=lambda i, o: next(feed), perm=perm, record_grads_at=tuple(grads_at),
+                         fit_overrides=({} if epochs is None else {"epochs": epochs}))
+    with refbridge.positional_series_getitem():
+        ae = ae_mod.AE(X_train, Y_train, X_test, Y_test, L)                      # ipynb:159
+        ae.train(patience=patience, verbose=0, plot=False)                       # ipynb:160
+        fit = keras.CONTROL["last_fit"]
+        res = dict(
+            We0=We0, Wd0=Wd0, We=fit["We"], Wd=fit["Wd"], loss=fit["loss"], val_loss=fit["val_loss"],
+            epochs_run=np.int32(fit["epochs_run"]), x_train_scaled=np.asarray(ae._x_train),
+            is_r2=ae.model_IS_r2(), is_rmse=ae.model_IS_RMSE(),                  # ipynb:162-163
+            oos_r2=np.array(ae.model_OOS_r2()), oos_rmse=np.array(ae.model_OOS_RMSE()),   # ipynb:164-165
+        )
+        for t, (gWe, gWd) in fit["grads"].items():
+            res[f"grad_We_step{t}"], res[f"grad_Wd_step{t}"] = gWe, gWd
+        ante = ae.ante(rf, hfd)                                                  # ipynb:899
+        from cleaned_names import hfd_fullname
+        turn = ae.turnover(hfd_fullname)                                         # ipynb:900
+        post = ae.post(etf)                                                      # ipynb:901
+        res.update(ante=ante.values, post=post.values, turnover=turn["Turnover"].values,
+                   weights=np.array([w.values for w in ae.strat_weight_on_etf]),            # (144, 22, 13)
+                   reshaped0=ae.reshape_strat_weight_on_etf[0].values,
+                   latent=ae.autoencoder.encoder.predict(ae._x_test.values if hasattr(ae._x_test, "values") else ae._x_test),
+                   ante_index0=str(ante.index[0].date()), ante_columns=np.array(list(ante.columns)))
+    keras.CONTROL.update(w0=None, perm=None, record_grads_at=(), fit_overrides={})
+    return res
+
+
+def helper_vectors(helper):
+    """Outputs of the reference's numeric helpers on seeded random inputs."""
+    import random
+    rng = np.random.default_rng(7)
+    out = {}
+    Y, X, beta = rng.normal(size=(24, 13)) * .02, rng.normal(size=(24, 5)) * .03, rng.normal(size=(5, 13))
+    out.update(norm_Y=Y, norm_X=X, norm_beta=beta, norm_out=helper.normalization(Y, X, beta, 24))
+    old, new = rng.normal(size=22), rng.normal(size=22)
+    A = rng.normal(size=(24, 22)) * .04
+    cov = pd.DataFrame(A).cov()
+    out.update(tc_old=old, tc_new=new, tc_window=A, tc_out=helper.transaction_cost(old, new, cov),
+               pi_out=helper.price_impact(old, new, cov))
+    frames = [pd.DataFrame(rng.normal(size=(22, 13))) for _ in range(6)]
+    out["cab_in"] = np.array([f.values for f in frames])
+    out["cab_out"] = np.array([f.values for f in helper.reshape_cab(frames)])
+    arr = rng.normal(size=(4, 168, 36)).astype(np.float32)
+    fa, hf = helper.factor_hf_split(arr, 22)
+    out.update(split_in=arr, split_factor=fa, split_hf=hf)
+    data = rng.normal(size=(337, 35))
+    random.seed(123)
+    samp = helper.random_sampling(data, 16, 48)
+    random.seed(123)
+    starts = np.array([random.randint(0, 337 - 48) for _ in range(16)], np.int32)
+    out.update(rs_in=data, rs_out=samp, rs_starts=starts)
+    # ex_post_return on small synthetic inputs: T=10 months, window 6, 3 funds, 5 ETFs
+    T, w, Fn, E = 10, 6, 3, 5
+    ante = pd.DataFrame(rng.normal(size=(T, Fn)) * .01)
+    strat = [pd.DataFrame(rng.normal(size=(T, E))) for _ in range(Fn)]
+    etf = pd.DataFrame(rng.normal(size=(T + w, E)) * .03)
+    with refbridge.positional_series_getitem():
+        post = helper.ex_post_return(ante, w, strat, etf)
+    out.update(epr_ante=ante.values, epr_strat=np.array([s.values for s in strat]), epr_etf=etf.values,
+               epr_window=np.int32(w), epr_out=post.values)
+    return out
+
+
+def main():
+    os.makedirs(OUT, exist_ok=True)
+    ae_mod, helper, keras = refbridge.load()
+    etf, hfd, rf = refbridge.read_reference_data()
+    names = helper.dic_read(os.path.join(refbridge.REFERENCE_ROOT, "cleaned_data", "hfd_fullname.pkl"))
+    mod = type(sys)("cleaned_names")
+    mod.hfd_fullname = names
+    sys.modules["cleaned_names"] = mod
+
+    np.savez_compressed(os.path.join(OUT, "ref_inputs.npz"), etf=etf.values, hfd=hfd.values, rf=rf.values,
+                        etf_columns=np.array(list(etf.columns)), hfd_columns=np.array(list(hfd.columns)),
+                        dates=np.array([str(d.date()) for d in etf.index]),
+                        hfd_fullname=np.array(list(names.values())))
+    for L in (2, 8, 21):
+        res = run_reference_AE(ae_mod, keras, (etf, hfd, rf), L, seed=123)
+        np.savez_compressed(os.path.join(OUT, f"ref_modeR_L{L}.npz"), **res)
+        print(f"L={L}: epochs_run={res['epochs_run']} is_r2={res['is_r2']:.4f} loss[-1]={res['loss'][-1]:.6g} "
+              f"turnover[0]={res['turnover'][0]:.3f}")
+    # shuffled order + early stopping: per-epoch permutations from the documented stream
+    perm = fitcore.make_perm(123, 1000, 126)
+    res = run_reference_AE(ae_mod, keras, (etf, hfd, rf), 8, seed=124, perm=perm, patience=5)
+    res["perm_seed"] = np.int32(123)
+    np.savez_compressed(os.path.join(OUT, "ref_modeR_L8_shuffled.npz"), **res)
+    print(f"L=8 shuffled: epochs_run={res['epochs_run']} is_r2={res['is_r2']:.4f}")
+    np.savez_compressed(os.path.join(OUT, "ref_helpers.npz"), **helper_vectors(helper))
+    refbridge.unload()
+
+
+if __name__ == "__main__":
+    main()
