@@ -1,0 +1,492 @@
+// Kernel (c): fused out-of-sample predict + rolling-window OLS + replica + ex-post + metrics.
+// One trained autoencoder (task) per CTA of 256 threads; everything between the trained kernels
+// and the scored replica series happens in one launch, intermediate results in shared memory.
+//
+// Replaces, in this order (reference lines in Autoencoder_encapsulate.py unless noted):
+//   quality   model_IS_r2/RMSE :107-113, model_OOS_r2/RMSE :115-131 (167 expanding MinMax prefixes)
+//   latent    encoder.predict on the raw test block :140
+//   ols       OLS(Y, X).fit().params for window 0 :148-156 + helper.normalization helper.py:10-17
+//   weights   LeakyReLU mask + beta_0/norm_0 mapping :158-169, pop last :179-180
+//   ante      replica returns :183-193
+//   post      helper.ex_post_return / transaction_cost / price_impact helper.py:65-92,112-131
+//   turnover  :210-224
+//   metrics   annualized_sharpe_ratio autoencoder_v4.ipynb:715-721; tracking error / correlation (ours, App. A.9)
+//
+// Precision follows the reference: network forward passes in float32 (Keras), everything else
+// float64 (numpy/pandas/statsmodels).  OLS = Householder QR in float64 (the reference's pinv-OLS is
+// the same least-squares solution for full-rank windows; rank deficiency is reported in status).
+#include "common.cuh"
+
+#include <cmath>
+
+namespace hfrep {
+
+constexpr int NTH_EVAL = 256;
+constexpr int WS = 24;            // stride of We / Wd / M rows in shared memory (floats)
+
+struct EvalParams {
+    const double* Xtr; const double* Xte; const double* Yte; const double* rf; const double* sigma;
+    const int* task_L; const float* W;
+    double* ante; double* post; double* turnover; double* metrics; double* quality;
+    unsigned char* mask; double* weights; double* beta; double* norm; int* status;
+    int n_tasks, w_stride, E, F, T_train, T_test, window, want_oos, n_oos, n_pre, acols;
+    int off_float;        // byte offset of the float32 region inside dynamic shared memory (16-byte aligned)
+    float alpha;
+    double cost_param, phi;
+};
+
+// float32 forward pass of one row held in registers: y = lrelu(lrelu(x We) Wd)   (:32-35, predict)
+__device__ __forceinline__ void forward_row(const float (&x)[HFREP_MAX_E], float (&y)[HFREP_MAX_E],
+                                            const float* We, const float* Wd, int E, int L, float alpha) {
+    float h[HFREP_MAX_L];
+#pragma unroll
+    for (int l = 0; l < HFREP_MAX_L; ++l) h[l] = 0.f;
+#pragma unroll
+    for (int e = 0; e < HFREP_MAX_E; ++e) {
+        if (e < E) {
+            const float xe = x[e];
+#pragma unroll
+            for (int l4 = 0; l4 < HFREP_MAX_L / 4; ++l4) {
+                if (l4 * 4 < L) {
+                    const float4 w = *reinterpret_cast<const float4*>(We + e * WS + l4 * 4);
+                    h[l4 * 4 + 0] = fmaf(xe, w.x, h[l4 * 4 + 0]);
+                    h[l4 * 4 + 1] = fmaf(xe, w.y, h[l4 * 4 + 1]);
+                    h[l4 * 4 + 2] = fmaf(xe, w.z, h[l4 * 4 + 2]);
+                    h[l4 * 4 + 3] = fmaf(xe, w.w, h[l4 * 4 + 3]);
+                }
+            }
+        }
+    }
+#pragma unroll
+    for (int e = 0; e < HFREP_MAX_E; ++e) y[e] = 0.f;
+#pragma unroll
+    for (int l = 0; l < HFREP_MAX_L; ++l) {
+        if (l < L) {
+            const float hl = lrelu(h[l], alpha);
+#pragma unroll
+            for (int e4 = 0; e4 < HFREP_MAX_E / 4; ++e4) {
+                const float4 w = *reinterpret_cast<const float4*>(Wd + l * WS + e4 * 4);
+                y[e4 * 4 + 0] = fmaf(hl, w.x, y[e4 * 4 + 0]);
+                y[e4 * 4 + 1] = fmaf(hl, w.y, y[e4 * 4 + 1]);
+                y[e4 * 4 + 2] = fmaf(hl, w.z, y[e4 * 4 + 2]);
+                y[e4 * 4 + 3] = fmaf(hl, w.w, y[e4 * 4 + 3]);
+            }
+        }
+    }
+#pragma unroll
+    for (int e = 0; e < HFREP_MAX_E; ++e) y[e] = lrelu(y[e], alpha);
+}
+
+// r2_score (uniform average, sklearn's zero-denominator rule) and per-column-RMSE mean of one block of
+// `n` rows, rows strided over the lanes of one warp.  scaled row = x*scale + shift (MinMaxScaler), all f64.
+// cstat: per-warp shared scratch [3][HFREP_MAX_E] doubles = scale, shift, mean of the scaled column.
+__device__ void block_quality(const double* x, int n, int E, int L, const double* cstat, const float* We,
+                              const float* Wd, float alpha, int lane, double& r2, double& rmse) {
+    double ssr[HFREP_MAX_E], sst[HFREP_MAX_E];
+#pragma unroll
+    for (int e = 0; e < HFREP_MAX_E; ++e) ssr[e] = sst[e] = 0.;
+    for (int r = lane; r < n; r += 32) {
+        float xf[HFREP_MAX_E], yf[HFREP_MAX_E];
+        double xs[HFREP_MAX_E];
+#pragma unroll
+        for (int e = 0; e < HFREP_MAX_E; ++e) {
+            xs[e] = e < E ? x[(size_t)r * E + e] * cstat[e] + cstat[HFREP_MAX_E + e] : 0.;
+            xf[e] = (float)xs[e];
+        }
+        forward_row(xf, yf, We, Wd, E, L, alpha);
+#pragma unroll
+        for (int e = 0; e < HFREP_MAX_E; ++e) {
+            if (e < E) {
+                const double d = xs[e] - (double)yf[e];
+                const double c = xs[e] - cstat[2 * HFREP_MAX_E + e];
+                ssr[e] += d * d;
+                sst[e] += c * c;
+            }
+        }
+    }
+    double r2s = 0., rms = 0.;
+#pragma unroll
+    for (int e = 0; e < HFREP_MAX_E; ++e) {
+        if (e < E) {
+            const double num = warp_sum(ssr[e]), den = warp_sum(sst[e]);
+            r2s += den != 0. ? 1. - num / den : (num != 0. ? 0. : 1.);
+            rms += sqrt(num / n);
+        }
+    }
+    r2 = r2s / E;
+    rmse = rms / E;
+}
+
+__global__ void __launch_bounds__(NTH_EVAL) eval_kernel(const EvalParams p) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int task = blockIdx.x;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    constexpr int NW = NTH_EVAL / 32;
+    const int E = p.E, F = p.F, L = p.task_L[task], window = p.window, n_oos = p.n_oos, T_test = p.T_test;
+    const float alpha = p.alpha;
+
+    // ---- shared memory carve-up (doubles first)
+    double* A = reinterpret_cast<double*>(smem_raw);              // [window][acols]  QR workspace [M_w | Y_w]
+    double* betaS = A + (size_t)window * p.acols;                 // [HFREP_MAX_L][F]
+    double* G = betaS + HFREP_MAX_L * F;                          // [F][E]
+    double* normS = G + F * E;                                    // [F]
+    double* anteS = normS + F;                                    // [n_oos][F]
+    double* postS = anteS + (size_t)n_oos * F;                    // [n_oos][F]
+    double* turnS = postS + (size_t)n_oos * F;                    // [n_oos][F]
+    double* cstat = turnS + (size_t)n_oos * F;                    // [NW][3][HFREP_MAX_E]
+    double* vhh = cstat + NW * 3 * HFREP_MAX_E;                   // [window] Householder vector
+    float* We = reinterpret_cast<float*>(smem_raw + p.off_float); // [E][WS]
+    float* Wd = We + HFREP_MAX_E * WS;                            // [L][WS]
+    float* M = Wd + HFREP_MAX_L * WS;                             // [T_test][WS] latent factors
+    unsigned char* maskS = reinterpret_cast<unsigned char*>(M + (size_t)T_test * WS);   // [n_oos][E]
+    __shared__ int s_status;
+
+    const float* w = p.W + (size_t)task * p.w_stride;
+    for (int idx = tid; idx < HFREP_MAX_E * WS; idx += NTH_EVAL) {
+        const int e = idx / WS, l = idx - e * WS;
+        We[idx] = (e < E && l < L) ? w[e * L + l] : 0.f;
+    }
+    for (int idx = tid; idx < HFREP_MAX_L * WS; idx += NTH_EVAL) {
+        const int l = idx / WS, e = idx - l * WS;
+        Wd[idx] = (l < L && e < E) ? w[E * L + l * E + e] : 0.f;
+    }
+    if (tid == 0) s_status = 0;
+    __syncthreads();
+
+    // ---- quality: in-sample block (warp 0) and the expanding prefixes (all warps, incremental column stats)
+    if (p.quality) {
+        double* q = p.quality + (size_t)task * (2 + 2 * p.n_pre);
+        double* cs = cstat + warp * 3 * HFREP_MAX_E;
+        if (warp == 0) {
+            if (lane < HFREP_MAX_E) {
+                double s = 0.;
+                if (lane < E) for (int r = 0; r < p.T_train; ++r) s += p.Xtr[(size_t)r * E + lane];
+                cs[lane] = 1.; cs[HFREP_MAX_E + lane] = 0.; cs[2 * HFREP_MAX_E + lane] = s / p.T_train;
+            }
+            __syncwarp();
+            double r2, rmse;
+            block_quality(p.Xtr, p.T_train, E, L, cs, We, Wd, alpha, lane, r2, rmse);
+            if (lane == 0) { q[0] = r2; q[1] = rmse; }
+            __syncwarp();
+        }
+        if (p.want_oos) {
+            double lo = INFINITY, hi = -INFINITY, sum = 0.;
+            int seen = 0;                                         // rows [0, seen) folded into lo/hi/sum (lane = column)
+            for (int j = warp; j < p.n_pre; j += NW) {
+                const int n = j + 2;                              // prefix x_test[:n]
+                if (lane < E)
+                    for (; seen < n; ++seen) {
+                        const double v = p.Xte[(size_t)seen * E + lane];
+                        lo = fmin(lo, v); hi = fmax(hi, v); sum += v;
+                    }
+                seen = n;
+                if (lane < HFREP_MAX_E) {
+                    double scale = 1., shift = 0., mean = 0.;
+                    if (lane < E) {
+                        double rng = hi - lo;
+                        if (rng == 0.) rng = 1.;
+                        scale = 1. / rng;                         // MinMaxScaler: scale_ = 1/range, min_ = -min*scale_
+                        shift = 0. - lo * scale;
+                        mean = (sum / n) * scale + shift;
+                    }
+                    cs[lane] = scale; cs[HFREP_MAX_E + lane] = shift; cs[2 * HFREP_MAX_E + lane] = mean;
+                }
+                __syncwarp();
+                double r2, rmse;
+                block_quality(p.Xte, n, E, L, cs, We, Wd, alpha, lane, r2, rmse);
+                if (lane == 0) { q[2 + j] = r2; q[2 + p.n_pre + j] = rmse; }
+                __syncwarp();
+            }
+        }
+    }
+
+    // ---- latent factors of the raw test block, float32 (:140)
+    for (int idx = tid; idx < T_test * WS; idx += NTH_EVAL) {
+        const int r = idx / WS, l = idx - r * WS;
+        float acc = 0.f;
+        if (l < L)
+            for (int e = 0; e < E; ++e) acc = fmaf((float)p.Xte[(size_t)r * E + e], We[e * WS + l], acc);
+        M[idx] = lrelu(acc, alpha);
+    }
+    __syncthreads();
+
+    // ---- LeakyReLU masks of the decoder pre-activation, float32 (:163-166), months 0..n_oos-1
+    for (int idx = tid; idx < n_oos * E; idx += NTH_EVAL) {
+        const int k = idx / E, e = idx - k * E;
+        float acc = 0.f;
+        for (int l = 0; l < L; ++l) acc = fmaf(M[(window + k) * WS + l], Wd[l * WS + e], acc);
+        maskS[idx] = acc < 0.f ? 1 : 0;
+    }
+
+    // ---- OLS on window 0 (:148-156): Householder QR of [M_0 | Y_0] in float64, warp 0, lane = column
+    const int ncol = L + F;
+    if (warp == 0) {
+        for (int idx = lane; idx < window * ncol; idx += 32) {
+            const int r = idx / ncol, c = idx - r * ncol;
+            A[r * p.acols + c] = c < L ? (double)M[r * WS + c] : p.Yte[(size_t)r * F + (c - L)];
+        }
+        __syncwarp();
+        double dmax = 0., dmin = INFINITY;
+        for (int k = 0; k < L; ++k) {
+            // column k below the diagonal -> Householder vector v (all lanes compute the same scalars)
+            double s = 0.;
+            for (int r = k; r < window; ++r) { const double a = A[r * p.acols + k]; s += a * a; }
+            const double akk = A[k * p.acols + k];
+            const double nrm = sqrt(s);
+            const double alph = akk > 0. ? -nrm : nrm;
+            const double vtv = s - 2. * akk * alph + alph * alph;      // |x - alph e1|^2
+            dmax = fmax(dmax, fabs(alph)); dmin = fmin(dmin, fabs(alph));
+            __syncwarp();
+            for (int r = k + lane; r < window; r += 32) vhh[r] = A[r * p.acols + k] - (r == k ? alph : 0.);
+            __syncwarp();
+            if (vtv > 0.) {
+                const double bh = 2. / vtv;
+                for (int c = k + 1 + lane; c < ncol; c += 32) {
+                    double wj = 0.;
+                    for (int r = k; r < window; ++r) wj += vhh[r] * A[r * p.acols + c];
+                    wj *= bh;
+                    for (int r = k; r < window; ++r) A[r * p.acols + c] -= vhh[r] * wj;
+                }
+            }
+            __syncwarp();
+            if (lane == 0) {
+                A[k * p.acols + k] = alph;
+                for (int r = k + 1; r < window; ++r) A[r * p.acols + k] = 0.;
+            }
+            __syncwarp();
+        }
+        if (!(dmin > 1e-13 * dmax)) { if (lane == 0) s_status = 2; }
+        // back substitution, lane = fund
+        for (int f = lane; f < F; f += 32) {
+            for (int l = L - 1; l >= 0; --l) {
+                double acc = A[l * p.acols + L + f];
+                for (int j = l + 1; j < L; ++j) acc -= A[l * p.acols + j] * betaS[j * F + f];
+                betaS[l * F + f] = acc / A[l * p.acols + l];
+            }
+            // helper.normalization (helper.py:10-17): sd(Y)/sd(M beta), ddof = 1
+            double my = 0., mr = 0.;
+            for (int r = 0; r < window; ++r) {
+                double rh = 0.;
+                for (int l = 0; l < L; ++l) rh += (double)M[r * WS + l] * betaS[l * F + f];
+                mr += rh; my += p.Yte[(size_t)r * F + f];
+            }
+            mr /= window; my /= window;
+            double vr = 0., vy = 0.;
+            for (int r = 0; r < window; ++r) {
+                double rh = 0.;
+                for (int l = 0; l < L; ++l) rh += (double)M[r * WS + l] * betaS[l * F + f];
+                const double dy = p.Yte[(size_t)r * F + f] - my;
+                vr += (rh - mr) * (rh - mr) / (window - 1);
+                vy += dy * dy / (window - 1);
+            }
+            normS[f] = sqrt(vy) / sqrt(vr);
+        }
+    }
+    __syncthreads();
+
+    // ---- G = beta_0^T Wd  (F x E), float64 (:167)
+    for (int idx = tid; idx < F * E; idx += NTH_EVAL) {
+        const int f = idx / E, e = idx - f * E;
+        double acc = 0.;
+        for (int l = 0; l < L; ++l) acc += betaS[l * F + f] * (double)Wd[l * WS + e];
+        G[idx] = acc;
+    }
+    __syncthreads();
+
+    // ---- per (month, fund): weights, delta, ante (:167-168, :188-190), ex-post penalty (helper.py:120-129), |dw|
+    const double scale_c = p.cost_param, phi = p.phi;
+    for (int idx = tid; idx < n_oos * F; idx += NTH_EVAL) {
+        const int k = idx / F, f = idx - k * F;
+        const double nf = normS[f];
+        const int row = window + 1 + k;                           // test-block row of OOS month k (App. B.3)
+        double sumw = 0., dot = 0., pen = 0., dabs = 0.;
+        for (int e = 0; e < E; ++e) {
+            const double g = G[f * E + e];
+            const double wk = g * (maskS[k * E + e] ? .2 : 1.) * nf;
+            sumw += wk;
+            dot += p.Xte[(size_t)row * E + e] * wk;
+            if (p.weights) p.weights[(((size_t)task * n_oos + k) * E + e) * F + f] = wk;
+            if (k >= 1 && p.sigma) {                              // transaction_cost + price_impact, helper.py:65-92
+                const double old = g * (maskS[(k - 1) * E + e] ? .2 : 1.) * nf;
+                const double sg = p.sigma[(size_t)(k - 1) * E + e] * scale_c;
+                const double d = old - wk;
+                const double tc = .5 * d * d * sg;
+                const double pi = phi * wk * sg * d - old * sg * d - .5 * d * d * sg;
+                pen += tc + pi;
+            }
+            if (k + 1 < n_oos) {
+                const double nxt = g * (maskS[(k + 1) * E + e] ? .2 : 1.) * nf;
+                dabs += fabs(wk - nxt);
+            }
+        }
+        const double a = (1. - sumw) * p.rf[row] + dot;
+        anteS[idx] = a;
+        postS[idx] = a + pen;                                     // post[0] = ante[0] (pen = 0)
+        turnS[idx] = dabs;
+    }
+    __syncthreads();
+
+    // ---- stores + per-fund reductions (warp per fund)
+    if (p.ante) for (int idx = tid; idx < n_oos * F; idx += NTH_EVAL) p.ante[(size_t)task * n_oos * F + idx] = anteS[idx];
+    if (p.post) for (int idx = tid; idx < n_oos * F; idx += NTH_EVAL) p.post[(size_t)task * n_oos * F + idx] = postS[idx];
+    if (p.mask) for (int idx = tid; idx < n_oos * E; idx += NTH_EVAL) p.mask[(size_t)task * n_oos * E + idx] = maskS[idx];
+    if (p.beta) for (int idx = tid; idx < HFREP_MAX_L * F; idx += NTH_EVAL)
+        p.beta[(size_t)task * HFREP_MAX_L * F + idx] = idx < L * F ? betaS[idx] : 0.;
+    if (p.norm) for (int idx = tid; idx < F; idx += NTH_EVAL) p.norm[(size_t)task * F + idx] = normS[idx];
+
+    double rfm = 0.;
+    for (int k = lane; k < n_oos; k += 32) rfm += p.rf[window + 1 + k];
+    rfm = warp_sum(rfm) / n_oos;
+    for (int f = warp; f < F; f += NW) {
+        double ts = 0.;
+        for (int k = lane; k < n_oos; k += 32) ts += turnS[k * F + f];
+        ts = warp_sum(ts);
+        if (lane == 0 && p.turnover) p.turnover[(size_t)task * F + f] = ts / (n_oos / 12.);     // :216
+        if (p.metrics) {
+#pragma unroll
+            for (int which = 0; which < 2; ++which) {
+                const double* s = which ? postS : anteS;
+                double sr = 0., sy = 0.;
+                for (int k = lane; k < n_oos; k += 32) { sr += s[k * F + f]; sy += p.Yte[(size_t)(window + 1 + k) * F + f]; }
+                const double mr = warp_sum(sr) / n_oos, my = warp_sum(sy) / n_oos;
+                double vrr = 0., vyy = 0., vry = 0., sd = 0.;
+                for (int k = lane; k < n_oos; k += 32) {
+                    const double a = s[k * F + f] - mr, b = p.Yte[(size_t)(window + 1 + k) * F + f] - my;
+                    vrr += a * a; vyy += b * b; vry += a * b; sd += (a - b) * (a - b);
+                }
+                vrr = warp_sum(vrr); vyy = warp_sum(vyy); vry = warp_sum(vry); sd = warp_sum(sd);
+                if (lane == 0) {
+                    double* m = p.metrics + (size_t)task * 6 * F + which * 3 * F;
+                    m[0 * F + f] = (mr - rfm) / sqrt(vrr / n_oos) * sqrt(12.);          // ipynb:721 (np.std ddof=0)
+                    m[1 * F + f] = sqrt(sd / (n_oos - 1)) * sqrt(12.);                  // tracking error, ddof=1
+                    m[2 * F + f] = vry / sqrt(vrr * vyy);                               // Pearson correlation
+                }
+            }
+        }
+    }
+    if (tid == 0 && p.status) p.status[task] = s_status;
+}
+
+// Forward pass of arbitrary rows, one thread per row; weights staged in shared memory.
+__global__ void __launch_bounds__(128) forward_kernel(const float* __restrict__ W, int E, int L, const float* __restrict__ x,
+                                                      int n, int encode_only, float alpha, float* __restrict__ out) {
+    __shared__ __align__(16) float We[HFREP_MAX_E * WS];
+    __shared__ __align__(16) float Wd[HFREP_MAX_L * WS];
+    for (int idx = threadIdx.x; idx < HFREP_MAX_E * WS; idx += blockDim.x) {
+        const int e = idx / WS, l = idx - e * WS;
+        We[idx] = (e < E && l < L) ? W[e * L + l] : 0.f;
+    }
+    for (int idx = threadIdx.x; idx < HFREP_MAX_L * WS; idx += blockDim.x) {
+        const int l = idx / WS, e = idx - l * WS;
+        Wd[idx] = (l < L && e < E) ? W[E * L + l * E + e] : 0.f;
+    }
+    __syncthreads();
+    const int r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= n) return;
+    if (encode_only) {
+        for (int l = 0; l < L; ++l) {
+            float acc = 0.f;
+            for (int e = 0; e < E; ++e) acc = fmaf(x[(size_t)r * E + e], We[e * WS + l], acc);
+            out[(size_t)r * L + l] = lrelu(acc, alpha);
+        }
+    } else {
+        float xf[HFREP_MAX_E], yf[HFREP_MAX_E];
+#pragma unroll
+        for (int e = 0; e < HFREP_MAX_E; ++e) xf[e] = e < E ? x[(size_t)r * E + e] : 0.f;
+        forward_row(xf, yf, We, Wd, E, L, alpha);
+#pragma unroll
+        for (int e = 0; e < HFREP_MAX_E; ++e)
+            if (e < E) out[(size_t)r * E + e] = yf[e];
+    }
+}
+
+// Stand-alone series statistics: one warp per fund.
+__global__ void series_metrics_kernel(const double* s, const double* y, const double* rf, int n, int F, double* out) {
+    const int lane = threadIdx.x & 31;
+    const int f = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (f >= F) return;
+    double sr = 0., sy = 0., sf = 0.;
+    for (int k = lane; k < n; k += 32) { sr += s[(size_t)k * F + f]; sy += y[(size_t)k * F + f]; sf += rf[k]; }
+    const double mr = warp_sum(sr) / n, my = warp_sum(sy) / n, rfm = warp_sum(sf) / n;
+    double vrr = 0., vyy = 0., vry = 0., sd = 0.;
+    for (int k = lane; k < n; k += 32) {
+        const double a = s[(size_t)k * F + f] - mr, b = y[(size_t)k * F + f] - my;
+        vrr += a * a; vyy += b * b; vry += a * b; sd += (a - b) * (a - b);
+    }
+    vrr = warp_sum(vrr); vyy = warp_sum(vyy); vry = warp_sum(vry); sd = warp_sum(sd);
+    if (lane == 0) {
+        out[0 * F + f] = (mr - rfm) / sqrt(vrr / n) * sqrt(12.);
+        out[1 * F + f] = sqrt(sd / (n - 1)) * sqrt(12.);
+        out[2 * F + f] = vry / sqrt(vrr * vyy);
+    }
+}
+
+}  // namespace hfrep
+
+using namespace hfrep;
+
+extern "C" void hfrep_eval_cfg_default(hfrep_eval_cfg* c) {
+    memset(c, 0, sizeof(*c));
+    c->E = 22; c->F = 13; c->T_train = 168; c->T_test = 169; c->window = 24;     // autoencoder_v4.ipynb:112, :133
+    c->beta_rolling = 0; c->want_oos = 1; c->alpha = .2f; c->cost_param = .05; c->phi = .5;   // helper.py:65,83
+}
+
+extern "C" int hfrep_predict_metrics(const hfrep_eval_cfg* c, const double* Xtr, const double* Xte, const double* Yte,
+                                     const double* rf, const double* sigma, int n_tasks, const int32_t* task_L,
+                                     const float* W, int w_stride, double* ante, double* post, double* turnover,
+                                     double* metrics, double* quality, uint8_t* mask, double* weights, double* beta,
+                                     double* norm, int32_t* status, void* stream) {
+    HFREP_REQUIRE(c && Xte && Yte && rf && task_L && W, "predict_metrics: null argument");
+    HFREP_REQUIRE(n_tasks >= 0, "predict_metrics: n_tasks=%d", n_tasks);
+    if (n_tasks == 0) return HFREP_OK;
+    HFREP_REQUIRE(c->E >= 1 && c->E <= HFREP_MAX_E, "predict_metrics: E=%d outside 1..%d", c->E, HFREP_MAX_E);
+    HFREP_REQUIRE(c->F >= 1 && c->F <= HFREP_MAX_F, "predict_metrics: F=%d outside 1..%d", c->F, HFREP_MAX_F);
+    HFREP_REQUIRE(c->window >= 2 && c->window <= 64, "predict_metrics: window=%d outside 2..64", c->window);
+    HFREP_REQUIRE(c->T_test >= c->window + 2, "predict_metrics: T_test=%d needs at least window+2 rows", c->T_test);
+    HFREP_REQUIRE(w_stride >= 2 * c->E, "predict_metrics: w_stride=%d", w_stride);
+    HFREP_REQUIRE(c->beta_rolling == 0, "predict_metrics: beta_rolling=1 is not available in this build");
+    HFREP_REQUIRE(!quality || Xtr, "predict_metrics: quality needs Xtr");
+    HFREP_REQUIRE(!(post) || sigma, "predict_metrics: post needs sigma");
+
+    EvalParams p;
+    p.Xtr = Xtr; p.Xte = Xte; p.Yte = Yte; p.rf = rf; p.sigma = sigma; p.task_L = task_L; p.W = W;
+    p.ante = ante; p.post = post; p.turnover = turnover; p.metrics = metrics; p.quality = quality; p.mask = mask;
+    p.weights = weights; p.beta = beta; p.norm = norm; p.status = status;
+    p.n_tasks = n_tasks; p.w_stride = w_stride; p.E = c->E; p.F = c->F; p.T_train = c->T_train; p.T_test = c->T_test;
+    p.window = c->window; p.want_oos = c->want_oos; p.n_oos = c->T_test - c->window - 1; p.n_pre = c->T_test - 2;
+    p.acols = HFREP_MAX_L + c->F + 1;       // odd-ish stride keeps the column walks off a single bank
+    p.alpha = c->alpha; p.cost_param = c->cost_param; p.phi = c->phi;
+
+    size_t dbl = (size_t)c->window * p.acols + HFREP_MAX_L * c->F + (size_t)c->F * c->E + c->F +
+                 3 * (size_t)p.n_oos * c->F + (NTH_EVAL / 32) * 3 * HFREP_MAX_E + c->window;
+    dbl = (dbl + 1) & ~(size_t)1;           // float region starts 16-byte aligned
+    p.off_float = (int)(dbl * 8);
+    const size_t flt = (size_t)HFREP_MAX_E * WS + (size_t)HFREP_MAX_L * WS + (size_t)c->T_test * WS;
+    const size_t smem = dbl * 8 + flt * 4 + (size_t)p.n_oos * c->E + 16;
+    HFREP_REQUIRE(smem <= 227 * 1024, "predict_metrics: %zu bytes of shared memory needed (T_test=%d too long)", smem,
+                  c->T_test);
+    HFREP_CUDA_OK(cudaFuncSetAttribute(eval_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    eval_kernel<<<n_tasks, NTH_EVAL, smem, (cudaStream_t)stream>>>(p);
+    HFREP_CUDA_OK(cudaGetLastError());
+    return HFREP_OK;
+}
+
+extern "C" int hfrep_series_metrics(const double* series, const double* fund, const double* rf, int n, int F,
+                                    double* out, void* stream) {
+    HFREP_REQUIRE(series && fund && rf && out, "series_metrics: null argument");
+    HFREP_REQUIRE(n >= 2 && F >= 1, "series_metrics: n=%d F=%d", n, F);
+    const int wpb = 4;
+    series_metrics_kernel<<<(F + wpb - 1) / wpb, wpb * 32, 0, (cudaStream_t)stream>>>(series, fund, rf, n, F, out);
+    HFREP_CUDA_OK(cudaGetLastError());
+    return HFREP_OK;
+}
+
+extern "C" int hfrep_forward(const float* W, int E, int L, const float* x, int n, int encode_only, float alpha,
+                             float* out, void* stream) {
+    HFREP_REQUIRE(W && x && out, "forward: null argument");
+    HFREP_REQUIRE(E >= 1 && E <= HFREP_MAX_E && L >= 1 && L <= HFREP_MAX_L, "forward: E=%d L=%d", E, L);
+    if (n <= 0) return HFREP_OK;
+    forward_kernel<<<(n + 127) / 128, 128, 0, (cudaStream_t)stream>>>(W, E, L, x, n, encode_only, alpha, out);
+    HFREP_CUDA_OK(cudaGetLastError());
+    return HFREP_OK;
+}

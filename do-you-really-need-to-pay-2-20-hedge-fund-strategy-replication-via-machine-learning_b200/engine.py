@@ -1,0 +1,311 @@
+"""Host side of the batched replication path: prepares inputs the way the reference does
+(autoencoder_v4.ipynb:112, Autoencoder_encapsulate.py:62-67), moves them to the GPU and drives
+the three CUDA kernels through the C ABI (include/hfrep.h).  PyTorch is used for device
+memory and streams only.
+
+A *task* is one independent autoencoder fit plus its evaluation (Mode R):
+task = (latent_dim L, initial kernels W0[, per-epoch row orders]).
+"""
+from __future__ import annotations
+
+import ctypes as C
+import dataclasses
+
+import numpy as np
+import torch
+
+from . import _lib
+from ._lib import lib, check, ptr, stream_ptr
+
+
+# ------------------------------------------------------------------------------------ host prep
+def minmax_scale(x: np.ndarray) -> np.ndarray:
+    """MinMaxScaler().fit_transform in float64 (Autoencoder_encapsulate.py:62-65): scale = 1/(max-min)
+    (1 where the range is zero), out = x*scale + (0 - min*scale)."""
+    x = np.asarray(x, dtype=np.float64)
+    lo = x.min(axis=0)
+    rng = x.max(axis=0) - lo
+    rng[rng == 0.] = 1.
+    scale = 1. / rng
+    return x * scale + (0. - lo * scale)
+
+
+def split_rows(n: int, test_size: float = .5):
+    """train_test_split(shuffle=False, test_size) row counts (autoencoder_v4.ipynb:112): n_test = ceil(test_size*n)."""
+    n_test = int(np.ceil(test_size * n))
+    return n - n_test, n_test
+
+
+def glorot_limit(fan_in: int, fan_out: int) -> float:
+    return float(np.sqrt(6. / (fan_in + fan_out)))
+
+
+def initial_weights(seed: int, E: int, L: int):
+    """GlorotUniform kernels (Dense default, Autoencoder_encapsulate.py:24,28) from numpy's Philox
+    generator: encoder stream keyed 2*seed, decoder stream 2*seed+1, U(-l, l) drawn in float64 and
+    rounded to float32.  (Keras draws from TensorFlow's RNG, which is not reproducible here.)"""
+    out = []
+    for key, (fi, fo) in ((2 * seed, (E, L)), (2 * seed + 1, (L, E))):
+        rng = np.random.Generator(np.random.Philox(key=int(key)))
+        lim = glorot_limit(fi, fo)
+        out.append(rng.uniform(-lim, lim, (fi, fo)).astype(np.float32))
+    return out[0], out[1]
+
+
+def epoch_permutations(seed: int, epochs: int, n_fit: int) -> np.ndarray:
+    """Per-epoch row orders standing in for Keras' shuffle=True (int32 [epochs][n_fit])."""
+    rng = np.random.Generator(np.random.Philox(key=int(seed)))
+    return np.stack([rng.permutation(n_fit) for _ in range(epochs)]).astype(np.int32)
+
+
+def pack_weights(pairs, E: int, w_stride: int) -> np.ndarray:
+    """[(We (E,L), Wd (L,E)), ...] -> f32 [n][w_stride] in the C ABI's packing."""
+    out = np.zeros((len(pairs), w_stride), np.float32)
+    for i, (We, Wd) in enumerate(pairs):
+        L = We.shape[1]
+        assert We.shape == (E, L) and Wd.shape == (L, E)
+        out[i, :E * L] = np.asarray(We, np.float32).ravel()
+        out[i, E * L:2 * E * L] = np.asarray(Wd, np.float32).ravel()
+    return out
+
+
+def unpack_weights(row: np.ndarray, E: int, L: int):
+    return row[:E * L].reshape(E, L).copy(), row[E * L:2 * E * L].reshape(L, E).copy()
+
+
+def window_index(kind: str, T: int, window: int):
+    """Bit-exact window tables from the C ABI: returns (starts, lens) int32."""
+    k = {"rolling": 0, "expanding": 1, "expost": 2}[kind]
+    n = check(lib.hfrep_window_index(k, T, window, None, None, 0))
+    starts, lens = np.zeros(n, np.int32), np.zeros(n, np.int32)
+    check(lib.hfrep_window_index(k, T, window, ptr(starts), ptr(lens), n))
+    return starts, lens
+
+
+# ------------------------------------------------------------------------------------ device helpers
+def _dev(device=None):
+    if not torch.cuda.is_available():
+        raise _lib.HfrepError("no CUDA device: this package has no CPU fallback")
+    return torch.device(device if device is not None else f"cuda:{torch.cuda.current_device()}")
+
+
+def to_device(a: np.ndarray, device, dtype=None) -> torch.Tensor:
+    """Host array -> pinned staging -> device (async on the current stream)."""
+    t = torch.from_numpy(np.ascontiguousarray(a))
+    if dtype is not None:
+        t = t.to(dtype)
+    return t.pin_memory().to(device, non_blocking=True)
+
+
+_SCHED_CACHE: dict = {}
+
+
+def nadam_schedule(cfg: _lib.FitCfg, n_steps: int, device) -> torch.Tensor:
+    key = (cfg.lr, cfg.beta_1, cfg.beta_2, cfg.epsilon, cfg.schedule_decay, cfg.decay_base, n_steps, str(device))
+    t = _SCHED_CACHE.get(key)
+    if t is None:
+        host = np.zeros((n_steps, 4), np.float32)
+        check(lib.hfrep_nadam_schedule(C.byref(cfg), n_steps, ptr(host)))
+        t = torch.from_numpy(host).to(device)
+        _SCHED_CACHE[key] = t
+    return t
+
+
+@dataclasses.dataclass
+class FitResult:
+    W: torch.Tensor            # f32 [n][w_stride]
+    loss: torch.Tensor         # f32 [n][max_epochs]
+    val_loss: torch.Tensor
+    epochs_run: torch.Tensor   # i32 [n]
+    status: torch.Tensor
+    grads: torch.Tensor | None
+    w_stride: int
+
+
+_SIDE_STREAMS: dict = {}
+
+
+def _side_streams(device, n):
+    pool = _SIDE_STREAMS.setdefault(str(device), [])
+    while len(pool) < n:
+        pool.append(torch.cuda.Stream(device=device))
+    return pool[:n]
+
+
+def fit_batched(X: torch.Tensor, task_L, W0: torch.Tensor, *, E: int, T: int, n_fit: int | None = None,
+                perm: torch.Tensor | None = None, task_x: torch.Tensor | None = None, dump_step: int | None = None,
+                warps_per_task: int = 0, bucket: bool = True, **cfg_kw) -> FitResult:
+    """Kernel (b) for a batch of tasks.  X f32 [n_x][T][E] (device, scaled); task_L sequence of ints;
+    W0 f32 [n][w_stride] (device).  Tasks are grouped by padded latent width (multiples of 4) and each
+    group is launched on its own stream, so a sweep over L runs concurrently."""
+    device = X.device
+    task_L = np.asarray(task_L, np.int32)
+    n = len(task_L)
+    w_stride = W0.shape[1]
+    n_x = X.shape[0] if X.dim() == 3 else 1
+    if n_fit is None:
+        n_fit = int(np.floor(T * .75))                       # validation_split=.25, Autoencoder_encapsulate.py:89
+    cfg = _lib.fit_cfg(E=E, T=T, n_fit=n_fit, n_x=n_x, warps_per_task=warps_per_task,
+                       dump_step=(dump_step or 0), **cfg_kw)
+    if n == 0:
+        z = lambda *shape, dt=torch.float32: torch.zeros(shape, dtype=dt, device=device)
+        return FitResult(z(0, w_stride), z(0, cfg.max_epochs), z(0, cfg.max_epochs), z(0, dt=torch.int32),
+                         z(0, dt=torch.int32), None, w_stride)
+    steps = cfg.max_epochs * ((n_fit + cfg.batch - 1) // cfg.batch)
+    sched = nadam_schedule(cfg, steps, device)
+    # order tasks by padded width, widest (slowest) first
+    order = np.argsort(-((task_L + 3) // 4), kind="stable") if bucket else np.arange(n)
+    inv = np.empty(n, np.int64)
+    inv[order] = np.arange(n)
+    L_sorted = task_L[order]
+    order_t = torch.from_numpy(order).to(device)
+    tL = torch.from_numpy(L_sorted).to(device)
+    W0s = W0.index_select(0, order_t).contiguous()
+    tx = task_x.index_select(0, order_t).contiguous() if task_x is not None else None
+    per_task_perm = perm is not None and perm.dim() == 3
+    perms = perm.index_select(0, order_t).contiguous() if per_task_perm else perm
+    perm_stride = perms.shape[1] * perms.shape[2] if per_task_perm else 0
+
+    W_out = torch.empty_like(W0s)
+    loss = torch.full((n, cfg.max_epochs), float("nan"), dtype=torch.float32, device=device)
+    val = torch.full((n, cfg.max_epochs), float("nan"), dtype=torch.float32, device=device)
+    epochs_run = torch.zeros(n, dtype=torch.int32, device=device)
+    status = torch.zeros(n, dtype=torch.int32, device=device)
+    grads = torch.zeros_like(W0s) if dump_step is not None else None
+
+    LP = (L_sorted + 3) // 4 * 4
+    bounds = [0] + [i for i in range(1, n) if LP[i] != LP[i - 1]] + [n] if bucket else [0, n]
+    groups = [(bounds[i], bounds[i + 1]) for i in range(len(bounds) - 1)]
+    main = torch.cuda.current_stream(device)
+    streams = _side_streams(device, len(groups)) if len(groups) > 1 else [main]
+    ready = torch.cuda.Event()
+    ready.record(main)
+    for (a, b), s in zip(groups, streams):
+        if s is not main:
+            s.wait_event(ready)
+        with torch.cuda.stream(s):
+            cfg.L_max = int(L_sorted[a:b].max())
+            off = lambda t, a=a: None if t is None else C.c_void_p(t.data_ptr() + a * t.stride(0) * t.element_size())
+            check(lib.hfrep_fit_batched(
+                C.byref(cfg), ptr(X), b - a, off(tL), off(tx), off(W0s), w_stride,
+                off(perms) if per_task_perm else ptr(perms), perm_stride, ptr(sched), off(W_out), off(loss),
+                off(val), off(epochs_run), off(status), off(grads), C.c_void_p(s.cuda_stream)))
+        if s is not main:
+            done = torch.cuda.Event()
+            done.record(s)
+            main.wait_event(done)
+    inv_t = torch.from_numpy(inv).to(device)
+    sel = lambda t: None if t is None else t.index_select(0, inv_t)
+    return FitResult(sel(W_out), sel(loss), sel(val), sel(epochs_run), sel(status), sel(grads), w_stride)
+
+
+@dataclasses.dataclass
+class EvalResult:
+    ante: torch.Tensor         # f64 [n][n_oos][F]
+    post: torch.Tensor
+    turnover: torch.Tensor     # f64 [n][F]
+    metrics: torch.Tensor      # f64 [n][6][F]   sharpe/te/corr of ante, then of post
+    quality: torch.Tensor      # f64 [n][2+2*n_pre]
+    mask: torch.Tensor         # u8  [n][n_oos][E]
+    beta: torch.Tensor         # f64 [n][MAX_L][F]
+    norm: torch.Tensor         # f64 [n][F]
+    status: torch.Tensor
+    weights: torch.Tensor | None
+
+
+def rolling_sigma(R64: torch.Tensor, starts: torch.Tensor, window: int) -> torch.Tensor:
+    T, E = R64.shape
+    out = torch.empty((len(starts), E), dtype=torch.float64, device=R64.device)
+    check(lib.hfrep_rolling_sigma(ptr(R64), T, E, ptr(starts), len(starts), window, ptr(out), stream_ptr()))
+    return out
+
+
+def predict_metrics(Xtr64, Xte64, Yte64, rf64, sigma, task_L, W, *, window=24, want_oos=True,
+                    want_weights=False, alpha=.2, cost_param=.05, phi=.5) -> EvalResult:
+    """Kernel (c) for a batch of trained tasks (all tensors on the device, float64 unless noted)."""
+    device = Xte64.device
+    n = len(task_L)
+    T_test, E = Xte64.shape
+    F = Yte64.shape[1]
+    cfg = _lib.eval_cfg(E=E, F=F, T_train=Xtr64.shape[0], T_test=T_test, window=window,
+                        want_oos=int(want_oos), alpha=alpha, cost_param=cost_param, phi=phi)
+    n_oos, n_pre = T_test - window - 1, T_test - 2
+    tL = task_L if isinstance(task_L, torch.Tensor) else torch.from_numpy(np.asarray(task_L, np.int32)).to(device)
+    f64 = dict(dtype=torch.float64, device=device)
+    r = EvalResult(
+        ante=torch.empty((n, n_oos, F), **f64), post=torch.empty((n, n_oos, F), **f64),
+        turnover=torch.empty((n, F), **f64), metrics=torch.empty((n, 6, F), **f64),
+        quality=torch.full((n, 2 + 2 * n_pre), float("nan"), **f64),
+        mask=torch.empty((n, n_oos, E), dtype=torch.uint8, device=device),
+        beta=torch.empty((n, _lib.MAX_L, F), **f64), norm=torch.empty((n, F), **f64),
+        status=torch.zeros(n, dtype=torch.int32, device=device),
+        weights=torch.empty((n, n_oos, E, F), **f64) if want_weights else None)
+    check(lib.hfrep_predict_metrics(
+        C.byref(cfg), ptr(Xtr64), ptr(Xte64), ptr(Yte64), ptr(rf64), ptr(sigma), n, ptr(tL), ptr(W), W.shape[1],
+        ptr(r.ante), ptr(r.post), ptr(r.turnover), ptr(r.metrics), ptr(r.quality), ptr(r.mask), ptr(r.weights),
+        ptr(r.beta), ptr(r.norm), ptr(r.status), stream_ptr()))
+    return r
+
+
+def window_gather(R: torch.Tensor, starts, length: int, col_lo: int = 0, ncols: int | None = None,
+                  minmax: bool = False) -> torch.Tensor:
+    """Kernel (a): out[w] = R[starts[w]:starts[w]+length, col_lo:col_lo+ncols] (f32, device)."""
+    T, Cc = R.shape
+    ncols = Cc - col_lo if ncols is None else ncols
+    st = starts if isinstance(starts, torch.Tensor) else torch.from_numpy(np.asarray(starts, np.int32)).to(R.device)
+    if len(st) and (int(st.min()) < 0 or int(st.max()) + length > T):
+        raise _lib.HfrepError("window_gather: a window reaches outside the returns matrix")
+    out = torch.empty((len(st), length, ncols), dtype=torch.float32, device=R.device)
+    check(lib.hfrep_window_gather(ptr(R), T, Cc, ptr(st), len(st), length, col_lo, ncols, int(minmax), ptr(out),
+                                  stream_ptr()))
+    return out
+
+
+# ------------------------------------------------------------------------------------ Mode R front-end
+class ReplicationData:
+    """The reference's data split, resident on one GPU: train/test halves of the ETF and fund
+    matrices (autoencoder_v4.ipynb:112), the MinMax-scaled train block (Autoencoder_encapsulate.py:65),
+    the raw test block (:67), rf aligned with the test block and the rolling ex-post volatilities of
+    the last n_oos+window ETF rows (helper.py:121; task-independent, computed once)."""
+
+    def __init__(self, etf, hfd, rf, window: int = 24, device=None, test_size: float = .5):
+        self.device = _dev(device)
+        etf, hfd = np.asarray(etf, np.float64), np.asarray(hfd, np.float64)
+        rf = np.asarray(rf, np.float64).reshape(-1)
+        assert len(etf) == len(hfd) == len(rf)
+        self.n_train, self.n_test = split_rows(len(etf), test_size)
+        self.E, self.F, self.window = etf.shape[1], hfd.shape[1], window
+        self.n_oos = self.n_test - window - 1
+        with torch.cuda.device(self.device):
+            self.Xtr64 = to_device(minmax_scale(etf[:self.n_train]), self.device)
+            self.Xtr32 = self.Xtr64.to(torch.float32).reshape(1, self.n_train, self.E).contiguous()
+            self.Xte64 = to_device(etf[self.n_train:], self.device)
+            self.Yte64 = to_device(hfd[self.n_train:], self.device)
+            self.rf64 = to_device(rf[self.n_train:], self.device)
+            tail = to_device(etf[len(etf) - self.n_oos - window:], self.device)        # Autoencoder_encapsulate.py:206
+            starts, _ = window_index("expost", self.n_oos + window, window)               # helper.py:120
+            self.sigma = rolling_sigma(tail, torch.from_numpy(starts).to(self.device), window)
+        self.h2d_bytes = (etf.nbytes + hfd.nbytes + rf.nbytes)
+
+
+def run_mode_r(data: ReplicationData, latent_dims, seeds=(123,), *, W0=None, perm=None, want_oos=True,
+               want_weights=False, warps_per_task=0, **fit_kw):
+    """The notebook's sweep (autoencoder_v4.ipynb:158-165, :896-901) as one batched GPU pass:
+    for every (L, seed): fit, IS/OOS quality, ante, turnover, post, metrics.
+    Returns (tasks, FitResult, EvalResult); tasks[i] = (L, seed)."""
+    tasks = [(int(L), int(s)) for s in seeds for L in latent_dims]
+    E = data.E
+    L_max = max(L for L, _ in tasks)
+    w_stride = 2 * E * L_max
+    with torch.cuda.device(data.device):
+        if W0 is None:
+            W0 = pack_weights([initial_weights(s, E, L) for L, s in tasks], E, w_stride)
+        W0d = to_device(np.asarray(W0, np.float32), data.device)
+        permd = None if perm is None else to_device(np.asarray(perm, np.int32), data.device)
+        task_L = [L for L, _ in tasks]
+        fit = fit_batched(data.Xtr32, task_L, W0d, E=E, T=data.n_train, perm=permd,
+                          warps_per_task=warps_per_task, **fit_kw)
+        ev = predict_metrics(data.Xtr64, data.Xte64, data.Yte64, data.rf64, data.sigma, task_L, fit.W,
+                             window=data.window, want_oos=want_oos, want_weights=want_weights,
+                             alpha=fit_kw.get("alpha", .2))
+    return tasks, fit, ev

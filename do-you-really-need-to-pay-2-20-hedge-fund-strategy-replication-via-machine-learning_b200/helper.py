@@ -1,0 +1,217 @@
+"""Drop-in for the reference's ``helper.py`` — same names, argument order and defaults
+(helper.py:10-162) — with the array work done by the CUDA library (kernel (a) window
+gather, rolling volatility + ex-post penalty kernels, series metrics).  Importing it
+requires the built library; there is no CPU fallback for the GPU-backed functions.
+
+`normalization`, `transaction_cost` and `price_impact` are one-line formulas on a handful of
+values; as stand-alone helpers they stay host arithmetic (inside ``AE.ante``/``AE.post`` the
+same formulas run fused in kernel (c) / the ex-post kernel).
+"""
+from __future__ import annotations
+
+import os
+import pickle
+import random
+
+import numpy as np
+import pandas as pd
+import torch
+
+from . import engine
+from ._lib import lib, check, ptr, stream_ptr
+
+_STATE = {"seed": 123, "draws": 0}
+
+
+def normalization(Y, X, beta, window):
+    """helper.py:10-17: sqrt(var(Y)) / sqrt(var(X beta)), ddof = window-1 ... per fund."""
+    Y, X, beta = np.array(Y), np.array(X), np.array(beta)
+    R_hat = X @ beta
+    denominator = np.sum((R_hat - np.mean(R_hat, axis=0)) ** 2 / (window - 1), axis=0)
+    numerator = np.sum((Y - np.mean(Y, axis=0)) ** 2 / (window - 1), axis=0)
+    return np.sqrt(numerator) / np.sqrt(denominator)
+
+
+def read_csv(loc, date=True):
+    """helper.py:18-23."""
+    df = pd.read_csv(loc)
+    if date:
+        df['Date'] = pd.to_datetime(df['Date'])
+        df.set_index('Date', inplace=True)
+    return df
+
+
+def dic_read(loc):
+    """helper.py:26-29."""
+    with open(loc, "rb") as f:
+        return pickle.load(f)
+
+
+def set_seed(seed_value=123):
+    """helper.py:32-41 seeds python/numpy/TensorFlow and pins TF to one thread.  Here it seeds
+    python's and numpy's global generators the same way and restarts the Philox streams from which
+    ``AE.train`` draws initial kernels and epoch permutations."""
+    os.environ['PYTHONHASHSEED'] = str(seed_value)
+    np.random.seed(seed_value)
+    random.seed(seed_value)
+    _STATE["seed"], _STATE["draws"] = int(seed_value), 0
+
+
+def next_stream_seed() -> int:
+    """Seed for the next model built after set_seed (successive models get distinct streams,
+    as successive Keras models do)."""
+    s = _STATE["seed"] + 1000003 * _STATE["draws"]
+    _STATE["draws"] += 1
+    return s
+
+
+def _as_words(a: np.ndarray):
+    """View a float32/float64 C-contiguous 2-D array as 32-bit words so kernel (a) moves it bit-exactly."""
+    a = np.ascontiguousarray(a)
+    if a.dtype == np.float32:
+        return a, 1
+    if a.dtype != np.float64:
+        a = a.astype(np.float64)
+    return a.view(np.float32), 2
+
+
+def random_sampling(dataset, n_sample, window):
+    """helper.py:44-62: n_sample windows dataset[s:s+window] with s = random.randint(0, T-window)
+    (inclusive, python's global generator) -> array (n_sample, window, cols).  Starts are drawn on
+    the host exactly as the reference draws them; the gather runs on the GPU (kernel (a))."""
+    isinstance(dataset, np.ndarray)
+    starts = np.array([random.randint(0, dataset.shape[0] - window) for _ in range(n_sample)], np.int32)
+    data = np.asarray(dataset)
+    if data.ndim != 2:
+        raise ValueError("random_sampling expects a 2-D array")
+    words, k = _as_words(data)
+    dev = engine._dev()
+    R = engine.to_device(words, dev)
+    out = engine.window_gather(R, starts, window)
+    res = out.cpu().numpy()
+    if k == 2:
+        res = res.view(np.float64)
+    return res.astype(data.dtype, copy=False)
+
+
+def transaction_cost(old_x, new_x, covMatrix, param=0.05):
+    """helper.py:65-80."""
+    isinstance(param, float)
+    sigma = np.sqrt(np.diag(np.asarray(covMatrix))) * param
+    delta_x = np.array(old_x) - np.array(new_x)
+    return 0.5 * delta_x ** 2 * sigma
+
+
+def price_impact(old_x, new_x, covMatrix, param=0.05, phi=0.5):
+    """helper.py:83-92."""
+    isinstance(param, float)
+    isinstance(phi, float)
+    sigma = np.sqrt(np.diag(np.asarray(covMatrix))) * param
+    old_x, new_x = np.array(old_x), np.array(new_x)
+    delta_x = old_x - new_x
+    return phi * new_x * sigma * delta_x - old_x * sigma * delta_x - 0.5 * delta_x ** 2 * sigma
+
+
+def reshape_cab(df_list):
+    """helper.py:94-110: list of A frames (B x C) -> C frames (A x B); a stride change, done in one
+    transpose instead of A*C row appends."""
+    assert isinstance(df_list, list)
+    assert isinstance(df_list[0], pd.DataFrame)
+    cube = np.stack([df.values for df in df_list])            # (A, B, C)
+    cols, rows = df_list[0].columns, df_list[0].index
+    out = []
+    for i in range(cube.shape[2]):
+        out.append(pd.DataFrame(cube[:, :, i], index=[cols[i]] * cube.shape[0], columns=rows))
+    return out
+
+
+def ex_post_return(ex_ante, window, strat_weight, factor_etf):
+    """helper.py:112-131 on the GPU: rolling ddof=1 volatilities of factor_etf (rows [i, i+window),
+    i = 1..T-1) then post[0] = ante[0], post[t] = ante[t] + sum_e(tc + pi)(w[t-1], w[t])."""
+    assert isinstance(ex_ante, pd.DataFrame)
+    assert isinstance(factor_etf, pd.DataFrame)
+    T, F = ex_ante.shape
+    E = factor_etf.shape[1]
+    dev = engine._dev()
+    with torch.cuda.device(dev):
+        etf = engine.to_device(np.asarray(factor_etf.values, np.float64), dev)
+        starts, _ = engine.window_index("expost", len(factor_etf), window)
+        n_pen = len(starts)                                       # len(factor_etf) - window - 1
+        if n_pen < T - 1:
+            raise IndexError("list index out of range")           # what helper.py:129 would raise
+        sigma = engine.rolling_sigma(etf, torch.from_numpy(starts).to(dev), window)
+        w = np.stack([np.asarray(sw.values if hasattr(sw, "values") else sw, np.float64)[:T] for sw in strat_weight])
+        wd = engine.to_device(w, dev)                             # (F, T, E)
+        ante = engine.to_device(np.asarray(ex_ante.values, np.float64), dev)
+        post = torch.empty_like(ante)
+        check(lib.hfrep_ex_post_return(ptr(ante), ptr(wd), ptr(sigma), T, F, E, 0.05, 0.5, ptr(post), stream_ptr()))
+        res = post.cpu().numpy()
+    return pd.DataFrame(res.T, columns=ex_ante.index, index=ex_ante.columns).T
+
+
+def factor_hf_split(arr, split_pos, reshape=True):
+    """helper.py:133-153: (n, T, C) -> factor (n, T, split_pos) and hf (n, T, C-split_pos), flattened
+    to (n*T, .) when reshape.  Two column-range gathers of kernel (a)."""
+    assert isinstance(arr, np.ndarray)
+    assert isinstance(split_pos, int)
+    assert arr.ndim == 3
+    assert 0 < split_pos < arr.shape[2]
+    n, T, Cc = arr.shape
+    words, k = _as_words(arr.reshape(n * T, Cc))
+    dev = engine._dev()
+    R = engine.to_device(words, dev)
+    starts = (np.arange(n, dtype=np.int64) * T).astype(np.int32)
+    fa = engine.window_gather(R, starts, T, 0, split_pos * k).cpu().numpy()
+    hf = engine.window_gather(R, starts, T, split_pos * k, (Cc - split_pos) * k).cpu().numpy()
+    if k == 2:
+        fa, hf = fa.view(np.float64), hf.view(np.float64)
+    fa, hf = fa.astype(arr.dtype, copy=False), hf.astype(arr.dtype, copy=False)
+    if reshape:
+        fa = fa.reshape(n * T, split_pos)
+        hf = hf.reshape(n * T, Cc - split_pos)
+    return fa, hf
+
+
+def dic_save(dic, loc):
+    """helper.py:155-162."""
+    with open(loc, 'wb') as f:
+        pickle.dump(dic, f)
+    output = dic_read(loc)
+    print('stored dictionary:\n')
+    print(output)
+
+
+# ---- additive API (not in the reference's helper.py) ------------------------------
+def replica_metrics(series, fund, rf):
+    """GPU series statistics: returns (sharpe, tracking_error, correlation), each (F,).
+    sharpe = autoencoder_v4.ipynb:715-721; tracking error = std(series-fund, ddof=1)*sqrt(12);
+    correlation = Pearson.  series/fund (n, F), rf (n,)."""
+    s = np.asarray(series, np.float64)
+    y = np.asarray(fund, np.float64)
+    if s.ndim == 1:
+        s, y = s[:, None], y[:, None]
+    r = np.asarray(rf, np.float64).reshape(-1)
+    dev = engine._dev()
+    with torch.cuda.device(dev):
+        sd, yd, rd = (engine.to_device(a, dev) for a in (s, y, r))
+        out = torch.empty((3, s.shape[1]), dtype=torch.float64, device=dev)
+        check(lib.hfrep_series_metrics(ptr(sd), ptr(yd), ptr(rd), s.shape[0], s.shape[1], ptr(out), stream_ptr()))
+        o = out.cpu().numpy()
+    return o[0], o[1], o[2]
+
+
+def annualized_sharpe_ratio(ret, rf=0):
+    """autoencoder_v4.ipynb:715-721 for one series."""
+    ret = np.asarray(ret, np.float64).reshape(-1)
+    rfv = np.broadcast_to(np.asarray(rf, np.float64).reshape(-1), ret.shape) if np.ndim(rf) else np.full(ret.shape, float(rf))
+    return float(replica_metrics(ret, ret, rfv)[0][0])
+
+
+def tracking_error(replica, fund):
+    r = np.asarray(replica, np.float64).reshape(-1)
+    return float(replica_metrics(r, np.asarray(fund, np.float64).reshape(-1), np.zeros_like(r))[1][0])
+
+
+def correlation(replica, fund):
+    r = np.asarray(replica, np.float64).reshape(-1)
+    return float(replica_metrics(r, np.asarray(fund, np.float64).reshape(-1), np.zeros_like(r))[2][0])

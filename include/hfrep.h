@@ -1,0 +1,180 @@
+/*
+ * hfrep.h — C ABI of the B200-native replication hot path (libhfrep.so, sm_100a).
+ *
+ * This is the drop-in boundary underneath the Python entry points of the reference's
+ * Autoencoder_encapsulate.py / helper.py (the reference has no FFI of its own; its
+ * "interface" is those Python signatures).  Every entry point below names
+ * the reference lines whose arithmetic it replaces.  Plain C: caller-owned buffers, sizes
+ * and a CUDA stream handle (cudaStream_t passed as void*); no torch / C++ types.
+ *
+ * Conventions
+ *   - all pointers are DEVICE pointers unless the parameter name ends in _host;
+ *   - matrices are row-major; "f32"/"f64" = IEEE float/double; indices are int32;
+ *   - every call is asynchronous on `stream` and allocates nothing (every buffer, scratch
+ *     included, is passed in by the caller);
+ *   - return value 0 = ok, <0 = error; hfrep_last_error() returns a thread-local message;
+ *   - no CPU fallback exists: without a CUDA device the calls return HFREP_ERR_CUDA.
+ */
+#ifndef HFREP_H
+#define HFREP_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define HFREP_OK 0
+#define HFREP_ERR_ARG (-1)    /* bad argument / unsupported shape */
+#define HFREP_ERR_CUDA (-2)   /* CUDA runtime error (message has the CUDA string) */
+
+#define HFREP_MAX_E 24        /* ETF width handled by the narrow kernels (reference: 22) */
+#define HFREP_MAX_L 24        /* latent width (reference sweep: 1..21) */
+#define HFREP_MAX_F 32        /* funds per evaluation (reference: 13) */
+
+const char* hfrep_last_error(void);
+int hfrep_version(void);
+
+/* ---------------------------------------------------------------------------------------
+ * Window index tables (host side, bit-exact int32).
+ *   kind 0 rolling   : start=i, len=window, i=0..T-window           (Autoencoder_encapsulate.py:145-156; count T-window)
+ *   kind 1 expanding : start=0, len=i,      i=2..T-1               (Autoencoder_encapsulate.py:117,126; count T-2)
+ *   kind 2 expost    : start=i, len=window, i=1..T-window-1         (helper.py:120-121; count T-window-1)
+ * Writes up to `cap` entries to starts_host/lens_host and returns the count (or <0).
+ * Random windows (helper.py:55-58) come from python's `random.randint`; the Python facade draws
+ * them and passes the table in — there is nothing to compute natively.
+ */
+int hfrep_window_index(int kind, int T, int window, int32_t* starts_host, int32_t* lens_host, int cap);
+
+/* ---------------------------------------------------------------------------------------
+ * Kernel (a): window gather.  out[w][r][c] = R[starts[w]+r][col_lo+c], r<len, c<ncols, for
+ * n windows of equal length `len`; replaces the python slicing loops of helper.random_sampling
+ * (helper.py:55-58), helper.factor_hf_split (helper.py:145-152) and the window slices of
+ * Autoencoder_encapsulate.py:149-150.  If `minmax` != 0 every window is MinMax-scaled per
+ * column on the fly exactly as MinMaxScaler().fit_transform does (Autoencoder_encapsulate.py:62-65):
+ * (x-min)*(1/(max-min)) in float64, zero range -> scale 1, rounded to f32.
+ *   R   f32 [T][C]      starts int32 [n]      out f32 [n][len][ncols]
+ */
+int hfrep_window_gather(const float* R, int T, int C, const int32_t* starts, int n, int len,
+                        int col_lo, int ncols, int minmax, float* out, void* stream);
+
+/* Rolling ex-post volatility (helper.py:121 + :75/:87): sigma[i][e] = sqrt(var(R[start_i..start_i+window), e], ddof=1)),
+ * f64 in / f64 out.  R f64 [T][E], starts int32 [n], sigma f64 [n][E]. */
+int hfrep_rolling_sigma(const double* R, int T, int E, const int32_t* starts, int n, int window,
+                        double* sigma, void* stream);
+
+/* ---------------------------------------------------------------------------------------
+ * Kernel (b): batched autoencoder fit.  Replaces Autoencoder (Autoencoder_encapsulate.py:19-35)
+ * + AE.train (Autoencoder_encapsulate.py:72-96), i.e. Keras Dense(no bias)/LeakyReLU/MSE/Nadam/
+ * fit(validation_split, batch_size)/EarlyStopping, for n_tasks independent tasks in one launch.
+ */
+typedef struct hfrep_fit_cfg {
+    int32_t E;            /* ETF columns (22), <= HFREP_MAX_E */
+    int32_t L_max;        /* largest latent width among the tasks of this call, <= HFREP_MAX_L */
+    int32_t T;            /* rows per training block (168) */
+    int32_t n_fit;        /* floor(T*(1-validation_split)) = 126: rows [0,n_fit) train, [n_fit,T) validate */
+    int32_t batch;        /* 48 */
+    int32_t max_epochs;   /* 1000 */
+    int32_t patience;     /* 5 */
+    int32_t early_stop;   /* 1 = EarlyStopping(val_loss, patience), 0 = run max_epochs */
+    float alpha;          /* LeakyReLU slope .2 */
+    float lr, beta_1, beta_2, epsilon, schedule_decay, decay_base;  /* Nadam(): 1e-3,.9,.999,1e-7,.004,.96 */
+    int32_t n_x;          /* number of training blocks in X; 1 = all tasks share block 0 */
+    int32_t warps_per_task; /* 0 = choose from n_tasks; 1 = throughput mapping; 4 = latency mapping */
+    int32_t dump_step;    /* global step (0-based) whose gradients go to grad_out, if grad_out != NULL */
+} hfrep_fit_cfg;
+
+void hfrep_fit_cfg_default(hfrep_fit_cfg* cfg);
+
+/* Nadam's scalar schedule is task-independent: fill sched f32 [n_steps][4] (host) with
+ * {(1-mu_t)/(1-m_sched_t), mu_{t+1}/(1-m_sched_{t+1}), 1/(1-beta_2^t), mu_t}, t=1..n_steps. */
+int hfrep_nadam_schedule(const hfrep_fit_cfg* cfg, int n_steps, float* sched_host);
+
+/*   X        f32 [n_x][T][E]        training blocks, already MinMax-scaled
+ *   task_L   int32 [n_tasks]        latent width of each task (<= L_max)
+ *   task_x   int32 [n_tasks]|NULL   block of each task (NULL: block 0)
+ *   W0       f32 [n_tasks][w_stride] initial kernels: We (E x L) then Wd (L x E), packed with the task's own L
+ *   perm     int32 [.. ][epochs][n_fit] per-epoch row order; NULL = no shuffling; perm_task_stride
+ *            (in int32 elements) = 0 shares one table between all tasks
+ *   sched    f32 [>= max_epochs*ceil(n_fit/batch)][4]  from hfrep_nadam_schedule, on the device
+ *   W_out    f32 [n_tasks][w_stride]       final kernels, same packing
+ *   loss_hist/val_hist f32 [n_tasks][max_epochs]   history.history['loss'|'val_loss']
+ *   epochs_run int32 [n_tasks];  status int32 [n_tasks] (0 ok, 1 non-finite loss)
+ *   grad_out f32 [n_tasks][w_stride] | NULL   gradients (dWe, dWd) of step cfg->dump_step
+ */
+int hfrep_fit_batched(const hfrep_fit_cfg* cfg, const float* X, int n_tasks, const int32_t* task_L,
+                      const int32_t* task_x, const float* W0, int w_stride, const int32_t* perm,
+                      int64_t perm_task_stride, const float* sched, float* W_out, float* loss_hist,
+                      float* val_hist, int32_t* epochs_run, int32_t* status, float* grad_out, void* stream);
+
+/* ---------------------------------------------------------------------------------------
+ * Kernel (c): fused out-of-sample predict + rolling OLS + replica + ex-post + metrics, one
+ * task (= one trained autoencoder) per CTA.  Replaces AE.model_IS_r2/RMSE (:107-113),
+ * AE.model_OOS_r2/RMSE (:115-131), AE.ante (:133-201) with helper.normalization (helper.py:10-17),
+ * AE.post (:203-208) with helper.ex_post_return/transaction_cost/price_impact (helper.py:65-92,112-131),
+ * AE.turnover (:210-224), annualized_sharpe_ratio (autoencoder_v4.ipynb:715-721) and the two
+ * metrics the reference does not have (tracking error, correlation).
+ */
+typedef struct hfrep_eval_cfg {
+    int32_t E, F;         /* ETF columns, fund columns (<= HFREP_MAX_F) */
+    int32_t T_train;      /* rows of Xtr (168) */
+    int32_t T_test;       /* rows of the test block (169) */
+    int32_t window;       /* OLS / ex-post window (24), <= 64 */
+    int32_t beta_rolling; /* 0 = reference behaviour (window 0's beta/norm for every month, :167); 1 = window i */
+    int32_t want_oos;     /* 1 = also the expanding-prefix quality loops (:115-131) */
+    float alpha;          /* LeakyReLU slope */
+    double cost_param;    /* .05  (helper.py:65,83) */
+    double phi;           /* .5   (helper.py:83) */
+} hfrep_eval_cfg;
+
+void hfrep_eval_cfg_default(hfrep_eval_cfg* cfg);
+
+/* n_oos = T_test - window - 1 replica months (144); n_pre = T_test - 2 expanding prefixes (167).
+ *   Xtr    f64 [T_train][E]  MinMax-scaled train block (as AE.__init__ stores it, :65)
+ *   Xte    f64 [T_test][E]   raw test ETF rows (:67);  Yte f64 [T_test][F] test fund rows
+ *   rf     f64 [T_test]      risk-free rows aligned with the test block
+ *   sigma  f64 [n_oos-1][E]  from hfrep_rolling_sigma over the last n_oos+window ETF rows, starts 1..n_oos-1
+ *   W      f32 [n_tasks][w_stride], task_L int32 [n_tasks]: trained kernels from hfrep_fit_batched
+ * outputs (any may be NULL to skip the store):
+ *   ante, post f64 [n_tasks][n_oos][F];  turnover f64 [n_tasks][F]
+ *   metrics f64 [n_tasks][6][F]: sharpe, tracking error, correlation of ante; then of post
+ *   quality f64 [n_tasks][2 + 2*n_pre]: IS r2, IS rmse, OOS r2[n_pre], OOS rmse[n_pre]
+ *   mask u8 [n_tasks][n_oos][E]  (1 = LeakyReLU slope applied, i.e. pre-activation < 0, :164-166)
+ *   weights f64 [n_tasks][n_oos][E][F]  strat_weight_on_etf (:167); large — facade use only
+ *   beta f64 [n_tasks][L_stride=HFREP_MAX_L][F] window-0 OLS coefficients; norm f64 [n_tasks][F]
+ *   status int32 [n_tasks] (0 ok, 2 rank-deficient OLS window)
+ */
+int hfrep_predict_metrics(const hfrep_eval_cfg* cfg, const double* Xtr, const double* Xte, const double* Yte,
+                          const double* rf, const double* sigma, int n_tasks, const int32_t* task_L,
+                          const float* W, int w_stride, double* ante, double* post, double* turnover,
+                          double* metrics, double* quality, uint8_t* mask, double* weights, double* beta,
+                          double* norm, int32_t* status, void* stream);
+
+/* Network forward pass for arbitrary rows (Autoencoder.call :32-35, Model.predict, encoder.predict :140):
+ * x f32 [n][E]; W f32 packed We (E x L), Wd (L x E); encode_only != 0 -> out f32 [n][L] = lrelu(x We),
+ * else out f32 [n][E] = lrelu(lrelu(x We) Wd). */
+int hfrep_forward(const float* W, int E, int L, const float* x, int n, int encode_only, float alpha, float* out,
+                  void* stream);
+
+/* Stand-alone replica statistics for any (n, F) return block (autoencoder_v4.ipynb:715-721 + App. A.9):
+ * out f64 [3][F] = sharpe(series, rf), tracking error and correlation against `fund`. */
+int hfrep_series_metrics(const double* series, const double* fund, const double* rf, int n, int F,
+                         double* out, void* stream);
+
+/* helper.ex_post_return (helper.py:112-131) for arbitrary weights: post[0][f] = ante[0][f];
+ * post[t][f] = ante[t][f] + sum_e(transaction_cost + price_impact)(w[f][t-1], w[f][t], sigma[t-1]*param), t >= 1.
+ *   ante f64 [T][F]; weights f64 [F][T][E] (the reshape_cab layout, helper.py:94-110);
+ *   sigma f64 [T-1][E] from hfrep_rolling_sigma (starts 1..T-1 over the T+window ETF rows); post f64 [T][F]. */
+int hfrep_ex_post_return(const double* ante, const double* weights, const double* sigma, int T, int F, int E,
+                         double param, double phi, double* post, void* stream);
+
+/* FP32-FFMA peak micro-benchmark used as the roofline denominator of kernel (b) (MEASURED_PEAKS.json
+ * has no FP32 figure).  Runs `iters` dependent-chain-free FFMAs per thread on a full grid and returns
+ * the flop count through *flops_host; time it with CUDA events on `stream`. sink f32 [>=1]. */
+int hfrep_ffma_peak(int iters, float* sink, double* flops_host, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* HFREP_H */

@@ -103,11 +103,16 @@ class Nadam:
         nxt = F32(self.t + 2)
         base = F32(c.decay_base)
         dec = F32(c.schedule_decay)
-        mu_t = b1 * (F32(1.) - F32(.5) * np.power(base, dec * t, dtype=F32))
-        mu_t1 = b1 * (F32(1.) - F32(.5) * np.power(base, dec * nxt, dtype=F32))
+        # float32 pow = the correctly rounded value (evaluated in float64, then rounded): numpy's own
+        # float32 power is SIMD code whose last bit depends on the CPU, and 1 - beta_2^t amplifies it
+        # 100x during the first steps.
+        def pw(x, y):
+            return F32(np.power(np.float64(x), np.float64(y)))
+        mu_t = b1 * (F32(1.) - F32(.5) * pw(base, dec * t))
+        mu_t1 = b1 * (F32(1.) - F32(.5) * pw(base, dec * nxt))
         ms_new = F32(self.m_cache * mu_t)
         ms_next = F32(ms_new * mu_t1)
-        vden = F32(1.) - np.power(b2, t, dtype=F32)
+        vden = F32(1.) - pw(b2, t)
         return mu_t, mu_t1, ms_new, ms_next, vden
 
     def step(self, params, grads):

@@ -1,0 +1,284 @@
+"""Parity of the CUDA path (through the C ABI) against the committed golden fixtures — outputs of
+the REFERENCE'S OWN FILES run over shims (oracle/make_golden.py) — and against the portable CPU
+oracle on seeded synthetic inputs.  Tolerance (BASELINE.json north_star): window indices and
+LeakyReLU masks bit-exact; per-epoch losses, gradients, final kernels and replica returns within
+1e-5 relative in FP32.  All tests here need a GPU."""
+import numpy as np
+import pytest
+import torch
+
+from conftest import load_golden, rel_err
+
+pytestmark = pytest.mark.gpu
+
+TOL = 1e-5
+
+
+@pytest.fixture(scope="module")
+def hf():
+    import hfrep
+    assert torch.cuda.is_available()
+    return hfrep
+
+
+@pytest.fixture(scope="module")
+def data(hf, ref_inputs):
+    return hf.ReplicationData(ref_inputs["etf"], ref_inputs["hfd"], ref_inputs["rf"], window=24, device="cuda:0")
+
+
+def _fit_golden(hf, data, g, **kw):
+    E = data.E
+    L = g["We0"].shape[1]
+    W0 = hf.engine.pack_weights([(g["We0"], g["Wd0"])], E, 2 * E * L)
+    W0d = hf.engine.to_device(W0, data.device)
+    return hf.fit_batched(data.Xtr32, [L], W0d, E=E, T=data.n_train, **kw), L
+
+
+@pytest.mark.parametrize("L", [2, 8, 21])
+@pytest.mark.parametrize("wpt", [1, 4])
+def test_fit_matches_reference_run(hf, data, L, wpt):
+    """Full 1000-epoch fit, deterministic order: history and final kernels vs the reference run."""
+    g = load_golden(f"ref_modeR_L{L}")
+    res, _ = _fit_golden(hf, data, g, warps_per_task=wpt)
+    n = int(res.epochs_run[0])
+    assert n == int(g["epochs_run"]) == 1000
+    assert int(res.status[0]) == 0
+    loss, val = res.loss[0, :n].cpu().numpy(), res.val_loss[0, :n].cpu().numpy()
+    assert np.max(np.abs(loss - g["loss"]) / g["loss"]) < TOL
+    assert np.max(np.abs(val - g["val_loss"]) / g["val_loss"]) < TOL
+    We, Wd = hf.engine.unpack_weights(res.W[0].cpu().numpy(), data.E, L)
+    assert rel_err(We, g["We"]) < TOL and rel_err(Wd, g["Wd"]) < TOL
+
+
+@pytest.mark.parametrize("L", [2, 8, 21])
+@pytest.mark.parametrize("step", [0, 1, 100])
+def test_gradients_match_reference_run(hf, data, L, step):
+    g = load_golden(f"ref_modeR_L{L}")
+    res, _ = _fit_golden(hf, data, g, dump_step=step, max_epochs=step // 3 + 1, early_stop=0)
+    gWe, gWd = hf.engine.unpack_weights(res.grads[0].cpu().numpy(), data.E, L)
+    assert rel_err(gWe, g[f"grad_We_step{step}"]) < TOL
+    assert rel_err(gWd, g[f"grad_Wd_step{step}"]) < TOL
+
+
+def test_shuffled_fit_with_early_stopping(hf, data):
+    """Explicit per-epoch permutations + EarlyStopping(patience=5): the stop epoch must match exactly."""
+    g = load_golden("ref_modeR_L8_shuffled")
+    perm = hf.engine.epoch_permutations(int(g["perm_seed"]), 1000, 126)
+    permd = hf.engine.to_device(perm, data.device)
+    for wpt in (1, 4):
+        res, L = _fit_golden(hf, data, g, perm=permd, warps_per_task=wpt, patience=5)
+        n = int(res.epochs_run[0])
+        assert n == int(g["epochs_run"])
+        assert np.max(np.abs(res.loss[0, :n].cpu().numpy() - g["loss"]) / g["loss"]) < TOL
+        assert np.max(np.abs(res.val_loss[0, :n].cpu().numpy() - g["val_loss"]) / g["val_loss"]) < TOL
+        We, Wd = hf.engine.unpack_weights(res.W[0].cpu().numpy(), data.E, L)
+        assert rel_err(We, g["We"]) < TOL and rel_err(Wd, g["Wd"]) < TOL
+        assert torch.isnan(res.loss[0, n:]).all()          # history holds one entry per epoch run
+
+
+@pytest.mark.parametrize("name", ["ref_modeR_L2", "ref_modeR_L8", "ref_modeR_L21", "ref_modeR_L8_shuffled"])
+def test_eval_matches_reference_run(hf, data, name):
+    """Kernel (c) on the reference run's own trained kernels: quality, ante, post, turnover, weights."""
+    g = load_golden(name)
+    E, L = data.E, g["We"].shape[1]
+    W = hf.engine.to_device(hf.engine.pack_weights([(g["We"], g["Wd"])], E, 2 * E * L), data.device)
+    ev = hf.predict_metrics(data.Xtr64, data.Xte64, data.Yte64, data.rf64, data.sigma, [L], W,
+                            window=24, want_oos=True, want_weights=True)
+    q = ev.quality[0].cpu().numpy()
+    n_pre = 167
+    assert abs(q[0] - g["is_r2"]) < TOL * abs(g["is_r2"]) and abs(q[1] - g["is_rmse"]) < TOL * g["is_rmse"]
+    assert rel_err(q[2:2 + n_pre], g["oos_r2"]) < TOL
+    assert rel_err(q[2 + n_pre:], g["oos_rmse"]) < TOL
+    w_ref = g["weights"]                                   # (144, 22, 13)
+    got_w = ev.weights[0].cpu().numpy()
+    assert rel_err(got_w, w_ref) < TOL
+    assert rel_err(ev.ante[0].cpu().numpy(), g["ante"]) < TOL
+    assert rel_err(ev.post[0].cpu().numpy(), g["post"]) < TOL
+    assert rel_err(ev.turnover[0].cpu().numpy(), g["turnover"]) < TOL
+    assert int(ev.status[0]) == 0
+    # masks bit-exact: recompute the reference's mask from its float32 latent block and decoder kernel
+    lat = g["latent"].astype(np.float32)
+    ref_mask = ((lat[24:24 + 144] @ g["Wd"]) < 0).astype(np.uint8)
+    assert np.array_equal(ev.mask[0].cpu().numpy(), ref_mask)
+
+
+def test_mode_r_end_to_end(hf, data, ref_inputs):
+    """Fit + evaluation in one pass (three widths at once, bucketed launches) vs the reference runs."""
+    gs = {L: load_golden(f"ref_modeR_L{L}") for L in (2, 8, 21)}
+    E = data.E
+    W0 = hf.engine.pack_weights([(gs[L]["We0"], gs[L]["Wd0"]) for L in (2, 8, 21)], E, 2 * E * 21)
+    tasks, fit, ev = hf.run_mode_r(data, [2, 8, 21], seeds=(123,), W0=W0)
+    for i, L in enumerate((2, 8, 21)):
+        g = gs[L]
+        assert int(fit.epochs_run[i]) == 1000
+        assert rel_err(ev.ante[i].cpu().numpy(), g["ante"]) < TOL
+        assert rel_err(ev.post[i].cpu().numpy(), g["post"]) < TOL
+        assert rel_err(ev.turnover[i].cpu().numpy(), g["turnover"]) < TOL
+        assert abs(float(ev.quality[i, 0]) - g["is_r2"]) < TOL
+    # metrics against the oracle's definitions on the reference's replica
+    from oracle import ae_oracle
+    rf_oos = ref_inputs["rf"].reshape(-1)[-144:]
+    hfd_oos = ref_inputs["hfd"][-144:]
+    m = ev.metrics[1].cpu().numpy()
+    for f in range(13):
+        assert abs(m[0, f] - ae_oracle.annualized_sharpe_ratio(gs[8]["ante"][:, f], rf_oos)) < 1e-5 * abs(m[0, f]) + 1e-9
+        assert abs(m[1, f] - ae_oracle.tracking_error(gs[8]["ante"][:, f], hfd_oos[:, f])) < 1e-5 * m[1, f]
+        assert abs(m[2, f] - ae_oracle.correlation(gs[8]["ante"][:, f], hfd_oos[:, f])) < 1e-5
+        assert abs(m[3, f] - ae_oracle.annualized_sharpe_ratio(gs[8]["post"][:, f], rf_oos)) < 1e-5 * abs(m[3, f]) + 1e-9
+
+
+def test_known_answer_sharpe_table(hf, ref_inputs):
+    """hfd_res of autoencoder_v4.ipynb:1015 (deterministic): Sharpe of the 13 real indices, last 144 months."""
+    expect = [0.725028, 0.763790, 0.390113, 0.164249, 0.372265, 0.578300, 0.287477, 0.593060, 1.183535,
+              0.932520, 0.541682, 0.214612, 1.204837]
+    hfd, rf = ref_inputs["hfd"][-144:], ref_inputs["rf"].reshape(-1)[-144:]
+    sh, te, co = hf.helper.replica_metrics(hfd, hfd, rf)
+    assert np.allclose(sh, expect, atol=5e-7)
+    assert np.allclose(co, 1.) and np.allclose(te, 0.)
+
+
+@pytest.mark.parametrize("E,L,T,batch", [(22, 5, 168, 48), (10, 3, 64, 16), (24, 24, 100, 32), (22, 1, 57, 48),
+                                          (7, 13, 90, 25)])
+def test_fit_vs_oracle_synthetic(hf, E, L, T, batch):
+    """Ragged shapes (L not a multiple of 4, E != 22, partial batches, odd validation tails)."""
+    from oracle import fitcore
+    rng = np.random.default_rng(E * 100 + L)
+    x = rng.uniform(0, 1, (T, E))
+    cfg = fitcore.FitConfig(epochs=40, batch_size=batch, early_stop=False)
+    We0, Wd0 = fitcore.initial_weights(11, E, L)
+    o = fitcore.fit(x, We0, Wd0, cfg)
+    dev = torch.device("cuda:0")
+    X = hf.engine.to_device(x.astype(np.float32)[None], dev)
+    W0 = hf.engine.to_device(hf.engine.pack_weights([(We0, Wd0)], E, 2 * E * L), dev)
+    for wpt in (1, 4):
+        res = hf.fit_batched(X, [L], W0, E=E, T=T, max_epochs=40, batch=batch, early_stop=0, warps_per_task=wpt)
+        assert np.max(np.abs(res.loss[0, :40].cpu().numpy() - o["loss"]) / o["loss"]) < TOL
+        assert np.max(np.abs(res.val_loss[0, :40].cpu().numpy() - o["val_loss"]) / o["val_loss"]) < TOL
+        We, Wd = hf.engine.unpack_weights(res.W[0].cpu().numpy(), E, L)
+        assert rel_err(We, o["We"]) < TOL and rel_err(Wd, o["Wd"]) < TOL
+
+
+def test_per_task_blocks_and_perms(hf):
+    """n_x > 1 (each task its own training block, cfg-5 style) with per-task permutation tables."""
+    from oracle import fitcore
+    rng = np.random.default_rng(3)
+    n, T, E, L = 5, 60, 22, 6
+    xs = rng.uniform(0, 1, (n, T, E)).astype(np.float32)
+    n_fit = int(np.floor(T * .75))
+    perms = np.stack([fitcore.make_perm(50 + i, 12, n_fit) for i in range(n)])
+    pairs = [fitcore.initial_weights(20 + i, E, L) for i in range(n)]
+    dev = torch.device("cuda:0")
+    res = hf.fit_batched(hf.engine.to_device(xs, dev), [L] * n,
+                         hf.engine.to_device(hf.engine.pack_weights(pairs, E, 2 * E * L), dev), E=E, T=T,
+                         task_x=torch.arange(n, dtype=torch.int32, device=dev),
+                         perm=hf.engine.to_device(perms, dev), max_epochs=12, early_stop=0)
+    for i in range(n):
+        o = fitcore.fit(xs[i], *pairs[i], fitcore.FitConfig(epochs=12, early_stop=False), perm=perms[i])
+        assert np.max(np.abs(res.loss[i, :12].cpu().numpy() - o["loss"]) / o["loss"]) < TOL
+        We, Wd = hf.engine.unpack_weights(res.W[i].cpu().numpy(), E, L)
+        assert rel_err(We, o["We"]) < TOL and rel_err(Wd, o["Wd"]) < TOL
+
+
+def test_full_size_grid_properties(hf, data):
+    """cfg-3 size (21 widths x 64 seeds = 1344 tasks, 60 epochs): results do not depend on where a task
+    sits in the batch or on the thread mapping, and a rerun is bit-identical."""
+    E = data.E
+    Ls = list(range(1, 22))
+    seeds = list(range(123, 123 + 64))
+    tasks, fit, ev = hf.run_mode_r(data, Ls, seeds=seeds, max_epochs=60, early_stop=0, want_oos=False)
+    assert len(tasks) == 1344 and int(fit.status.abs().sum()) == 0 and int(ev.status.abs().sum()) == 0
+    assert bool(torch.isfinite(ev.ante).all()) and bool(torch.isfinite(ev.post).all())
+    tasks2, fit2, ev2 = hf.run_mode_r(data, Ls, seeds=seeds, max_epochs=60, early_stop=0, want_oos=False)
+    assert torch.equal(fit.W, fit2.W) and torch.equal(ev.ante, ev2.ante)
+    # a 3-task call containing the same (L, seed) pairs must reproduce the big batch (other mapping: 4 warps/task)
+    pick = [tasks.index((L, 150)) for L in (4, 9, 21)]
+    _, fit3, ev3 = hf.run_mode_r(data, [4, 9, 21], seeds=(150,), max_epochs=60, early_stop=0, want_oos=False)
+    for j, i in enumerate(pick):
+        assert rel_err(fit3.loss[j, :60].cpu().numpy(), fit.loss[i, :60].cpu().numpy()) < TOL
+        assert rel_err(ev3.ante[j].cpu().numpy(), ev.ante[i].cpu().numpy()) < 1e-4
+
+
+def test_window_gather(hf):
+    rng = np.random.default_rng(1)
+    R = rng.normal(size=(337, 36)).astype(np.float32)
+    dev = torch.device("cuda:0")
+    Rd = hf.engine.to_device(R, dev)
+    starts, lens = hf.window_index("rolling", 337, 48)
+    out = hf.window_gather(Rd, starts, 48).cpu().numpy()
+    assert np.array_equal(out, np.stack([R[s:s + 48] for s in starts]))            # bit-exact, float4 path
+    out = hf.window_gather(Rd, starts[:7], 48, col_lo=22, ncols=13).cpu().numpy()  # ragged column range
+    assert np.array_equal(out, np.stack([R[s:s + 48, 22:35] for s in starts[:7]]))
+    assert hf.window_gather(Rd, np.zeros(0, np.int32), 48).shape == (0, 48, 36)    # empty
+    from oracle import ae_oracle
+    out = hf.window_gather(Rd, starts[:9], 48, col_lo=0, ncols=22, minmax=True).cpu().numpy()
+    ref = np.stack([ae_oracle.minmax_fit_transform(R[s:s + 48, :22]).astype(np.float32) for s in starts[:9]])
+    assert np.array_equal(out, ref)
+    with pytest.raises(hf._lib.HfrepError):
+        hf.window_gather(Rd, np.array([300], np.int32), 48)
+
+
+def test_helper_functions_match_reference(hf):
+    import random
+    import pandas as pd
+    g = load_golden("ref_helpers")
+    h = hf.helper
+    random.seed(123)
+    assert np.array_equal(h.random_sampling(g["rs_in"], 16, 48), g["rs_out"])      # same randint stream, bit-exact
+    fa, hfm = h.factor_hf_split(g["split_in"], 22)
+    assert np.array_equal(fa, g["split_factor"]) and np.array_equal(hfm, g["split_hf"])
+    frames = [pd.DataFrame(a) for a in g["cab_in"]]
+    assert np.array_equal(np.array([f.values for f in h.reshape_cab(frames)]), g["cab_out"])
+    assert np.allclose(h.normalization(g["norm_Y"], g["norm_X"], g["norm_beta"], 24), g["norm_out"], rtol=1e-12)
+    cov = pd.DataFrame(g["tc_window"]).cov()
+    assert np.allclose(h.transaction_cost(g["tc_old"], g["tc_new"], cov), g["tc_out"], rtol=1e-12)
+    assert np.allclose(h.price_impact(g["tc_old"], g["tc_new"], cov), g["pi_out"], rtol=1e-12)
+    post = h.ex_post_return(pd.DataFrame(g["epr_ante"]), int(g["epr_window"]),
+                            [pd.DataFrame(s) for s in g["epr_strat"]], pd.DataFrame(g["epr_etf"]))
+    assert rel_err(post.values, g["epr_out"]) < 1e-12
+
+
+def test_facade_matches_reference_run(hf, ref_inputs, monkeypatch):
+    """The drop-in AE class, called the way autoencoder_v4.ipynb calls it, against the reference run."""
+    import pandas as pd
+    g = load_golden("ref_modeR_L8")
+    idx = pd.to_datetime(ref_inputs["dates"])
+    etf = pd.DataFrame(ref_inputs["etf"], index=idx, columns=ref_inputs["etf_columns"])
+    hfd = pd.DataFrame(ref_inputs["hfd"], index=idx, columns=ref_inputs["hfd_columns"])
+    rf = pd.DataFrame(ref_inputs["rf"], index=idx, columns=["RF"])
+    names = dict(zip(ref_inputs["hfd_columns"], ref_inputs["hfd_fullname"]))
+    monkeypatch.setattr(hf.engine, "initial_weights", lambda seed, E, L: (g["We0"].copy(), g["Wd0"].copy()))
+    monkeypatch.setattr(hf.config, "shuffle", False)
+    hf.helper.set_seed()
+    ae = hf.AE(etf.iloc[:168], hfd.iloc[:168], etf.iloc[168:], hfd.iloc[168:], 8)       # ipynb:159
+    ae.train(verbose=0, plot=False)                                                    # ipynb:160
+    assert len(ae.history.history["loss"]) == 1000
+    assert rel_err(ae.history.history["val_loss"], g["val_loss"]) < TOL
+    assert abs(ae.model_IS_r2() - g["is_r2"]) < TOL and abs(ae.model_IS_RMSE() - g["is_rmse"]) < TOL
+    assert rel_err(ae.model_OOS_r2(), g["oos_r2"]) < TOL and rel_err(ae.model_OOS_RMSE(), g["oos_rmse"]) < TOL
+    with pytest.raises(Exception, match="please execute ante before turnover"):
+        ae.turnover(names)
+    with pytest.raises(AssertionError):
+        ae.ante(rf.values, hfd)
+    ante = ae.ante(rf, hfd)                                                             # ipynb:899
+    turn = ae.turnover(names)                                                           # ipynb:900
+    post = ae.post(etf)                                                                 # ipynb:901
+    assert ante.shape == (144, 13) and str(ante.index[0].date()) == str(g["ante_index0"]) == "2010-05-31"
+    assert list(ante.columns) == list(g["ante_columns"])
+    assert rel_err(ante.values, g["ante"]) < TOL and rel_err(post.values, g["post"]) < TOL
+    assert rel_err(turn["Turnover"].values, g["turnover"]) < TOL and turn.index.name == "Real_AE"
+    assert len(ae.strat_weight_on_etf) == 144 and ae.strat_weight_on_etf[0].shape == (22, 13)
+    assert rel_err(ae.reshape_strat_weight_on_etf[0].values, g["reshaped0"]) < TOL
+    assert rel_err(ae.autoencoder.encoder.predict(etf.iloc[168:].values), g["latent"]) < TOL
+    assert rel_err(ae.autoencoder.decoder.get_weights()[0], g["Wd"]) < TOL
+
+
+def test_errors_and_empty(hf, data):
+    dev = data.device
+    E = data.E
+    W0 = torch.zeros((1, 2 * E * 8), dtype=torch.float32, device=dev)
+    with pytest.raises(hf._lib.HfrepError, match="L_max"):
+        hf.fit_batched(data.Xtr32, [30], W0, E=E, T=168)
+    with pytest.raises(hf._lib.HfrepError, match="w_stride"):
+        hf.fit_batched(data.Xtr32, [21], W0, E=E, T=168)
+    res = hf.fit_batched(data.Xtr32, [], torch.zeros((0, 2 * E * 8), dtype=torch.float32, device=dev), E=E, T=168)
+    assert res.W.shape[0] == 0

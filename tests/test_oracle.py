@@ -1,0 +1,109 @@
+"""CPU tests of the oracle itself (test infrastructure): the portable restatement against the
+golden fixtures produced by the reference's own files, the deterministic known-answer table of
+the notebook, and the Nadam restatement against torch.optim.NAdam."""
+import os
+
+import numpy as np
+import pytest
+
+from conftest import load_golden, rel_err
+from oracle import ae_oracle, fitcore, refbridge
+
+
+@pytest.mark.parametrize("name", ["ref_modeR_L2", "ref_modeR_L8_shuffled"])
+def test_portable_oracle_matches_reference_run(ref_inputs, name):
+    g = load_golden(name)
+    etf, hfd, rf = ref_inputs["etf"], ref_inputs["hfd"], ref_inputs["rf"]
+    L = g["We0"].shape[1]
+    perm = fitcore.make_perm(int(g["perm_seed"]), 1000, 126) if "perm_seed" in g else None
+    o = ae_oracle.run_task(etf[:168], hfd[:168], etf[168:], hfd[168:], rf, etf, L, g["We0"], g["Wd0"], perm=perm)
+    assert o["epochs_run"] == int(g["epochs_run"])
+    for k in ("We", "Wd", "loss", "val_loss"):
+        assert np.array_equal(o[k], g[k]), k                 # same float32 arithmetic -> bit-identical
+    for k in ("is_r2", "is_rmse", "oos_r2", "oos_rmse", "ante", "post", "turnover"):
+        assert rel_err(o[k], g[k]) < 1e-10, k
+
+
+def test_structural_constants(ref_inputs):
+    """Window bookkeeping pinned by the notebook."""
+    g = load_golden("ref_modeR_L2")
+    assert ref_inputs["etf"].shape == (337, 22) and ref_inputs["hfd"].shape == (337, 13)
+    assert g["x_train_scaled"].shape == (168, 22)            # 168/169 split, autoencoder_v4.ipynb:112
+    assert g["oos_r2"].shape == (167,)                       # 167 expanding prefixes, :319
+    assert g["ante"].shape == (144, 13) and str(g["ante_index0"]) == "2010-05-31"   # :929
+    assert fitcore.split_at(168, .25) == 126 and fitcore.split_at(1848, .25) == 1386
+
+
+def test_known_answer_table(ref_inputs):
+    """hfd_res (autoencoder_v4.ipynb:1015): deterministic statistics of the real indices, last 144 months."""
+    hfd, rf = ref_inputs["hfd"][-144:], ref_inputs["rf"][-144:]
+    sharpe = [ae_oracle.annualized_sharpe_ratio(hfd[:, f], rf) for f in range(13)]
+    expect = [0.725028, 0.763790, 0.390113, 0.164249, 0.372265, 0.578300, 0.287477, 0.593060, 1.183535,
+              0.932520, 0.541682, 0.214612, 1.204837]
+    assert np.allclose(sharpe, expect, atol=5e-7)
+    h = hfd[:, 0]
+    got = [ae_oracle.omega_ratio(h, 0), ae_oracle.omega_ratio(h, .1), ae_oracle.historical_cvar(h),
+           ae_oracle.ceq(h, rf, 2), ae_oracle.skewness(h), ae_oracle.kurtosis(h)]
+    assert np.allclose(got, [1.908581, 0.593268, -0.031864, 0.033211, -1.321605, 6.283068], atol=5e-7)
+
+
+def test_helper_restatements_match_reference():
+    g = load_golden("ref_helpers")
+    assert np.allclose(ae_oracle.normalization(g["norm_Y"], g["norm_X"], g["norm_beta"], 24), g["norm_out"], rtol=1e-13)
+    cov = np.cov(g["tc_window"], rowvar=False, ddof=1)
+    assert np.allclose(ae_oracle.transaction_cost(g["tc_old"], g["tc_new"], cov), g["tc_out"], rtol=1e-12)
+    assert np.allclose(ae_oracle.price_impact(g["tc_old"], g["tc_new"], cov), g["pi_out"], rtol=1e-12)
+    fa, hf = ae_oracle.factor_hf_split(g["split_in"], 22)
+    assert np.array_equal(fa, g["split_factor"]) and np.array_equal(hf, g["split_hf"])
+    assert np.array_equal(ae_oracle.random_window_starts(337, 16, 48, 123), g["rs_starts"])
+    assert np.array_equal(ae_oracle.random_sampling(g["rs_in"], g["rs_starts"], 48), g["rs_out"])
+    post = ae_oracle.ex_post_return(g["epr_ante"], int(g["epr_window"]), g["epr_strat"], g["epr_etf"])
+    assert rel_err(post, g["epr_out"]) < 1e-12
+    assert np.array_equal(np.transpose(g["cab_in"], (2, 0, 1)), g["cab_out"])     # reshape_cab is a transpose
+
+
+def test_nadam_against_torch():
+    """torch.optim.NAdam(eps=1e-7, momentum_decay=4e-3) is formula-identical to Keras 2.7 Nadam (App. A.4)."""
+    import torch
+    rng = np.random.default_rng(0)
+    w0 = rng.normal(size=(22, 8)).astype(np.float32)
+    grads = [rng.normal(size=(22, 8)).astype(np.float32) * .01 for _ in range(200)]
+    w = w0.copy()
+    opt = fitcore.Nadam(fitcore.FitConfig(), [w.shape])
+    for gr in grads:
+        opt.step([w], [gr])
+    tw = torch.tensor(w0.astype(np.float64), requires_grad=True)
+    topt = torch.optim.NAdam([tw], lr=1e-3, betas=(.9, .999), eps=1e-7, momentum_decay=4e-3)
+    for gr in grads:
+        tw.grad = torch.tensor(gr.astype(np.float64))
+        topt.step()
+    assert rel_err(w, tw.detach().numpy()) < 2e-6
+
+
+def test_early_stopping_rule():
+    """App. A.6: strict '<', wait counted before the comparison, never stops at epoch 0."""
+    rng = np.random.default_rng(1)
+    x = rng.uniform(0, 1, (64, 6))
+    We0, Wd0 = fitcore.initial_weights(3, 6, 2)
+    perm = fitcore.make_perm(9, 400, 48)
+    out = fitcore.fit(x, We0, Wd0, fitcore.FitConfig(epochs=400, batch_size=16, patience=2), perm=perm)
+    v = out["val_loss"]
+    n = out["epochs_run"]
+    assert n == len(v) == len(out["loss"])
+    if n < 400:
+        best_before = np.min(v[:n - 2])
+        assert not (v[n - 2] < best_before) and not (v[n - 1] < min(best_before, v[n - 2]))
+    out0 = fitcore.fit(x, We0, Wd0, fitcore.FitConfig(epochs=5, batch_size=16, patience=0))
+    assert out0["epochs_run"] == 2          # patience 0 still needs epoch > 0
+
+
+@pytest.mark.skipif(not refbridge.available(), reason="reference checkout not present on this machine")
+def test_reference_import_is_unmodified_source():
+    ae_mod, helper, keras = refbridge.load()
+    try:
+        assert ae_mod.__file__ == os.path.join(refbridge.REFERENCE_ROOT, "Autoencoder_encapsulate.py")
+        assert helper.__file__ == os.path.join(refbridge.REFERENCE_ROOT, "helper.py")
+        g = load_golden("ref_helpers")
+        assert np.allclose(helper.normalization(g["norm_Y"], g["norm_X"], g["norm_beta"], 24), g["norm_out"])
+    finally:
+        refbridge.unload()
