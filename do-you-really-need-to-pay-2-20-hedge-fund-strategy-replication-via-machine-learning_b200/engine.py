@@ -166,7 +166,7 @@ def fit_batched(X: torch.Tensor, task_L, W0: torch.Tensor, *, E: int, T: int, n_
     perms = perm.index_select(0, order_t).contiguous() if per_task_perm else perm
     perm_stride = perms.shape[1] * perms.shape[2] if per_task_perm else 0
 
-    W_out = torch.empty_like(W0s)
+    W_out = torch.zeros_like(W0s)          # rows are packed with each task's own L; the tail stays zero
     loss = torch.full((n, cfg.max_epochs), float("nan"), dtype=torch.float32, device=device)
     val = torch.full((n, cfg.max_epochs), float("nan"), dtype=torch.float32, device=device)
     epochs_run = torch.zeros(n, dtype=torch.int32, device=device)
