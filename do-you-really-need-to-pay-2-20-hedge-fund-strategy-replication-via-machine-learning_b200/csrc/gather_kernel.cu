@@ -112,12 +112,12 @@ using namespace hfrep;
 
 extern "C" int hfrep_window_gather(const float* R, int T, int C, const int32_t* starts, int n, int len, int col_lo,
                                    int ncols, int minmax, float* out, void* stream) {
-    HFREP_REQUIRE(R && starts && out, "window_gather: null argument");
     HFREP_REQUIRE(n >= 0 && len >= 0, "window_gather: n=%d len=%d", n, len);
+    if (n == 0 || len == 0) return HFREP_OK;             // empty batch: nothing to read or write
+    HFREP_REQUIRE(R && starts && out, "window_gather: null argument");
     HFREP_REQUIRE(col_lo >= 0 && ncols >= 1 && col_lo + ncols <= C, "window_gather: columns [%d,%d) outside 0..%d", col_lo,
                   col_lo + ncols, C);
     HFREP_REQUIRE(len <= T, "window_gather: len=%d exceeds T=%d", len, T);
-    if (n == 0 || len == 0) return HFREP_OK;
     const int vec4 = !minmax && (ncols % 4 == 0) && (C % 4 == 0) && (col_lo % 4 == 0) &&
                      (((uintptr_t)R | (uintptr_t)out) & 15) == 0;
     const size_t smem = minmax ? sizeof(double) * 2 * ncols : 0;
