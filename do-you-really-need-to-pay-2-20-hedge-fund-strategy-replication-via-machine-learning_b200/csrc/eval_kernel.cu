@@ -90,7 +90,7 @@ __device__ void block_quality(const double* x, int n, int E, int L, const double
         double xs[HFREP_MAX_E];
 #pragma unroll
         for (int e = 0; e < HFREP_MAX_E; ++e) {
-            xs[e] = e < E ? x[(size_t)r * E + e] * cstat[e] + cstat[HFREP_MAX_E + e] : 0.;
+            xs[e] = e < E ? __dadd_rn(__dmul_rn(x[(size_t)r * E + e], cstat[e]), cstat[HFREP_MAX_E + e]) : 0.;   // X *= scale; X += min_
             xf[e] = (float)xs[e];
         }
         forward_row(xf, yf, We, Wd, E, L, alpha);
@@ -186,7 +186,7 @@ __global__ void __launch_bounds__(NTH_EVAL) eval_kernel(const EvalParams p) {
                         double rng = hi - lo;
                         if (rng == 0.) rng = 1.;
                         scale = 1. / rng;                         // MinMaxScaler: scale_ = 1/range, min_ = -min*scale_
-                        shift = 0. - lo * scale;
+                        shift = __dsub_rn(0., __dmul_rn(lo, scale));
                         mean = (sum / n) * scale + shift;
                     }
                     cs[lane] = scale; cs[HFREP_MAX_E + lane] = shift; cs[2 * HFREP_MAX_E + lane] = mean;

@@ -1,19 +1,25 @@
 // Kernel (b): batched autoencoder fit — one task (E -> L -> E bias-free LeakyReLU autoencoder,
-// MSE, Nadam, validation tail, early stopping) per warp team, whole training run in one launch.
+// MSE, Nadam, validation tail, early stopping) per team of NW warps, whole training run in one launch.
 //
 // Replaces Autoencoder (Autoencoder_encapsulate.py:19-35) and AE.train (:72-96) of the reference,
 // i.e. the Keras fit loop; semantics restated in SURVEY.md App. A.1-A.6.
 //
-// Data layout (per team, shared memory, floats; every row start 16-byte aligned):
-//   Xs  [(T+1)][XS=28]   scaled training block, columns >= E zero, row T all zero (padding rows point at it)
-//   We  [EP=24][LP]      encoder kernel (in x out), LP = L rounded up to 4, padding zero (stays zero: its gradient is 0)
-//   Wd  [LP][WDS=28]     decoder kernel
-//   H   [BP][HS]         h = lrelu(x We) of the current mini-batch (position-major)
-//   dZy [BP][XS]         dLoss/d(decoder pre-activation)
-//   dZh [BP][HS]         dLoss/d(encoder pre-activation)
-// Nadam's m and v never leave registers: each thread owns a fixed set of 4x4 weight tiles.
-// Every contraction is a 4x4 register-tiled FP32 FFMA mini-GEMM fed by 128-bit shared loads
-// (8 LDS.128 per 64 FFMA); strides 28 / LP+4 keep 8 consecutive rows on distinct bank groups.
+// Per mini-batch step, three phases separated by team barriers:
+//   rows    one lane per batch row (CS=2: a lane pair per row, each half of the columns): the row's
+//           zh -> h -> zy -> y, squared error, dzy -> dzh accumulate in REGISTERS; weights are read as
+//           warp-broadcast 128-bit shared loads (1 LDS.128 per 4 FFMA) in rolled k4-loops (small code,
+//           few live registers).  h, dzy, dzh rows are parked in shared memory for the weight gradients.
+//   grads   dWd = H^T dZy and dWe = X_b^T dZh as 4x4 register tiles (outer products, 2 LDS.128 per 16
+//           FFMA); the batch rows are split over the team's warps (split-K), partial tiles go to
+//           shared memory in tile-major order.
+//   update  element-wise over the 48*LP weight slots: sum the NW partials in fixed order, Nadam (m, v in
+//           shared memory next to the weights), write the weight back.
+// Shared memory (floats, rows 16-byte aligned).  Per CTA: Xs [(T+1)][28] (shared by the CTA's teams when all
+// tasks train on the same block; cols >= E zero, row T zero), woff [48*LP] (tile-major slot -> weight offset).
+// Per team: We [24][LP], Wd [LP][28], H [BP+1][HS], dZh [BP+1][HS], dZy [BP+1][28] (row BP = scratch row for
+// idle lanes), part [NW][48*LP], mv [48*LP] float2, xoff [BP] (row offsets of the current batch: the fused
+// window gather — shuffled orders cost nothing extra).
+// LP = L rounded up to 4; zero padding is exactly neutral (zero activations, zero gradients, Nadam(0)=0).
 #include "common.cuh"
 
 #include <cmath>
@@ -21,7 +27,7 @@
 namespace hfrep {
 
 constexpr int EP = 24;    // padded ETF width
-constexpr int XS = 28;    // row stride of Xs and dZy
+constexpr int XS = 28;    // row stride of Xs and dZy (8 consecutive rows -> 8 distinct 16-byte bank groups)
 constexpr int WDS = 28;   // row stride of Wd
 
 struct FitParams {
@@ -46,33 +52,36 @@ template <int LP>
 struct Lay {
     static constexpr int HS = (LP % 8 == 4) ? LP : LP + 4;
     static constexpr int CT = LP / 4;
-    __host__ __device__ static size_t team_floats(int BP) {
-        return (size_t)EP * LP + (size_t)LP * WDS + (size_t)BP * HS * 2 + (size_t)BP * XS + BP + 32;
+    static constexpr int NT5 = 12 * CT;        // weight tiles: dWd (CT x 6) then dWe (6 x CT)
+    static constexpr int NEL = NT5 * 16;       // = 48*LP weight slots, tile-major
+    __host__ __device__ static size_t team_floats(int BP, int NW) {
+        return (size_t)EP * LP + (size_t)LP * WDS + (size_t)(BP + 1) * HS * 2 + (size_t)(BP + 1) * XS +
+               (size_t)NW * NEL + 2 * (size_t)NEL + BP + 32;
     }
+    __host__ __device__ static size_t cta_floats(int T) { return (size_t)(T + 1) * XS + NEL; }
 };
-__host__ __device__ inline size_t x_floats(int T) { return (size_t)(T + 1) * XS; }
 
-template <int WPT>
+template <int NW>
 __device__ __forceinline__ void team_sync(int team) {
-    if constexpr (WPT == 1) {
+    if constexpr (NW == 1) {
         __syncwarp();
     } else {
-        asm volatile("bar.sync %0, %1;" ::"r"(team + 1), "n"(WPT * 32) : "memory");
+        asm volatile("bar.sync %0, %1;" ::"r"(team + 1), "n"(NW * 32) : "memory");
     }
 }
 
-template <int WPT>
-__device__ __forceinline__ float team_sum(float v, float* red, int team, int tid) {
+template <int NW>
+__device__ __forceinline__ float team_sum(float v, float* red, int team, int tl) {
     v = warp_sum(v);
-    if constexpr (WPT == 1) {
+    if constexpr (NW == 1) {
         return v;
     } else {
-        if ((tid & 31) == 0) red[tid >> 5] = v;
-        team_sync<WPT>(team);
+        if ((tl & 31) == 0) red[tl >> 5] = v;
+        team_sync<NW>(team);
         float s = 0.f;
 #pragma unroll
-        for (int w = 0; w < WPT; ++w) s += red[w];
-        team_sync<WPT>(team);
+        for (int w = 0; w < NW; ++w) s += red[w];
+        team_sync<NW>(team);
         return s;
     }
 }
@@ -80,311 +89,344 @@ __device__ __forceinline__ float team_sum(float v, float* red, int team, int tid
 __device__ __forceinline__ float4 ld4(const float* p) { return *reinterpret_cast<const float4*>(p); }
 __device__ __forceinline__ void st4(float* p, float4 v) { *reinterpret_cast<float4*>(p) = v; }
 
-// acc[i][j] += sum_kk a[i][kk] * b[kk][j]      (A rows along k, B rows along n)
-__device__ __forceinline__ void mma_nn(float (&acc)[4][4], const float4 (&a)[4], const float4 (&b)[4]) {
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-        const float av[4] = {a[i].x, a[i].y, a[i].z, a[i].w};
-#pragma unroll
-        for (int kk = 0; kk < 4; ++kk) {
-            acc[i][0] = fmaf(av[kk], b[kk].x, acc[i][0]);
-            acc[i][1] = fmaf(av[kk], b[kk].y, acc[i][1]);
-            acc[i][2] = fmaf(av[kk], b[kk].z, acc[i][2]);
-            acc[i][3] = fmaf(av[kk], b[kk].w, acc[i][3]);
-        }
-    }
-}
-// acc[i][j] += sum_kk a[i][kk] * b[j][kk]      (both operands along k)
-__device__ __forceinline__ void mma_nt(float (&acc)[4][4], const float4 (&a)[4], const float4 (&b)[4]) {
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            acc[i][j] = fmaf(a[i].x, b[j].x, acc[i][j]);
-            acc[i][j] = fmaf(a[i].y, b[j].y, acc[i][j]);
-            acc[i][j] = fmaf(a[i].z, b[j].z, acc[i][j]);
-            acc[i][j] = fmaf(a[i].w, b[j].w, acc[i][j]);
-        }
-    }
-}
-// acc[i][j] += a[i] * b[j]                     (outer product, one k)
-__device__ __forceinline__ void mma_tn(float (&acc)[4][4], const float4& a, const float4& b) {
-    const float av[4] = {a.x, a.y, a.z, a.w};
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-        acc[i][0] = fmaf(av[i], b.x, acc[i][0]);
-        acc[i][1] = fmaf(av[i], b.y, acc[i][1]);
-        acc[i][2] = fmaf(av[i], b.z, acc[i][2]);
-        acc[i][3] = fmaf(av[i], b.w, acc[i][3]);
-    }
+__device__ __forceinline__ float2 ld2(const float* p) { return *reinterpret_cast<const float2*>(p); }
+__device__ __forceinline__ void st2(float* p, float2 v) { *reinterpret_cast<float2*>(p) = v; }
+__device__ __forceinline__ float fast_sqrt(float x) {      // MUFU.SQRT, 1 ulp; exact 0 for 0
+    float r;
+    asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
 }
 
-template <int LP, int WPT, int TPC>
-__global__ void __launch_bounds__(32 * WPT * TPC) fit_kernel(const FitParams p) {
+// LP: padded latent width; NW: warps per team; CS: lanes per batch row (1, or 2 = a lane pair splits the columns);
+// TPC: teams per CTA; FULL: fully unroll the k-loops of the rows phase (latency mapping: one warp per scheduler,
+// registers are free, the compiler software-pipelines the shared loads) instead of rolling them (throughput mapping)
+template <int LP, int NW, int CS, int TPC, bool FULL>
+__global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
     extern __shared__ __align__(16) float smem[];
-    constexpr int NTH = 32 * WPT;
+    constexpr int NTH = 32 * NW;
     constexpr int HS = Lay<LP>::HS;
     constexpr int CT = Lay<LP>::CT;
-    constexpr int NT5 = 2 * 6 * CT;                    // weight tiles: dWd (CT x 6) then dWe (6 x CT)
-    constexpr int MAXT5 = (NT5 + NTH - 1) / NTH;       // tiles owned per thread
-
+    constexpr int NT5 = Lay<LP>::NT5;
+    constexpr int NEL = Lay<LP>::NEL;
+    // Column split of the rows phase (CS == 2): the pair shares a row; lane `part` owns the float4 column groups
+    // g = 2i+part of the latent block (plus half of the last group when their number is odd) and the ETF columns
+    // [part*12, part*12+12).  CS == 1: a lane owns everything.
+    constexpr int NG4 = CT / CS;                   // whole float4 latent groups per lane
+    constexpr int TAIL = (CS == 2) ? (CT % 2) : 0; // 1: one extra float2 piece per lane
+    constexpr int LPC = 4 * NG4 + 2 * TAIL;        // latent columns per lane
+    constexpr int EPC = EP / CS;                   // ETF columns per lane
+    constexpr int ROWS = NTH / CS;                 // batch rows per pass
+    constexpr int UK = FULL ? EP / 4 : 2;          // unroll of the k4-loops
     const int team = threadIdx.x / NTH;
-    const int tid = threadIdx.x - team * NTH;
+    const int tl = threadIdx.x - team * NTH;       // lane within the team
+    const int warp = tl >> 5, lane = tl & 31;
     const int task = blockIdx.x * TPC + team;
     const bool active = task < p.n_tasks;
     const int T = p.T, E = p.E, BP = p.BP;
 
-    const size_t xf = x_floats(T);
-    const size_t tf = Lay<LP>::team_floats(BP);
-    float* Xs;
-    float* base;
-    if (p.shared_x) {
-        Xs = smem;
-        base = smem + xf + (size_t)team * tf;
-    } else {
-        Xs = smem + (size_t)team * (xf + tf);
-        base = Xs + xf;
-    }
+    const size_t cf = Lay<LP>::cta_floats(T);
+    const size_t tf = Lay<LP>::team_floats(BP, NW);
+    // shared training block: [Xs | woff | team 0 | team 1 ...]; own blocks (TPC == 1 then): same layout
+    float* Xs = smem;
+    int* woff = reinterpret_cast<int*>(smem + (size_t)(T + 1) * XS);
+    float* base = smem + cf + (size_t)team * tf;
     float* We = base;
     float* Wd = We + EP * LP;
     float* H = Wd + LP * WDS;
-    float* dZh = H + BP * HS;
-    float* dZy = dZh + BP * HS;
-    int* rowidx = reinterpret_cast<int*>(dZy + BP * XS);
-    float* red = reinterpret_cast<float*>(rowidx + BP);
+    float* dZh = H + (BP + 1) * HS;
+    float* dZy = dZh + (BP + 1) * HS;
+    float* part = dZy + (BP + 1) * XS;
+    float2* mv = reinterpret_cast<float2*>(part + NW * NEL);
+    int* xoff = reinterpret_cast<int*>(part + NW * NEL + 2 * NEL);
+    float* red = reinterpret_cast<float*>(xoff + BP);
 
     // ---- stage the training block (fused window load: rows of the scaled block -> padded tile)
-    if (p.shared_x) {
+    {
+        const int xb = (p.shared_x || !active || !p.task_x) ? 0 : p.task_x[task];
+        const float* xg = p.X + (size_t)xb * T * E;
         const int n = (T + 1) * XS;
         for (int idx = threadIdx.x; idx < n; idx += blockDim.x) {
             const int r = idx / XS, c = idx - r * XS;
-            Xs[idx] = (r < T && c < E) ? __ldg(p.X + (size_t)r * E + c) : 0.f;
-        }
-        __syncthreads();
-        if (!active) return;
-    } else {
-        if (!active) return;
-        const int xb = p.task_x ? p.task_x[task] : 0;
-        const float* xg = p.X + (size_t)xb * T * E;
-        const int n = (T + 1) * XS;
-        for (int idx = tid; idx < n; idx += NTH) {
-            const int r = idx / XS, c = idx - r * XS;
             Xs[idx] = (r < T && c < E) ? __ldg(xg + (size_t)r * E + c) : 0.f;
         }
+        // tile-major weight slot -> offset from We
+        for (int idx = threadIdx.x; idx < NEL; idx += blockDim.x) {
+            const int t = idx >> 4, i = (idx >> 2) & 3, jj = idx & 3;
+            int o;
+            if (t < 6 * CT) {                            // dWd tile (lt, et): Wd[lt*4+i][et*4+jj]
+                const int lt = t / 6, et = t - lt * 6;
+                o = EP * LP + (lt * 4 + i) * WDS + et * 4 + jj;
+            } else {                                     // dWe tile (et, lt): We[et*4+i][lt*4+jj]
+                const int u = t - 6 * CT;
+                const int et = u / CT, lt = u - et * CT;
+                o = (et * 4 + i) * LP + lt * 4 + jj;
+            }
+            woff[idx] = o;
+        }
     }
-
+    if (active) {
+        const int L0 = p.task_L[task];
+        const float* w0 = p.W0 + (size_t)task * p.w_stride;
+        for (int idx = tl; idx < EP * LP; idx += NTH) {
+            const int e = idx / LP, l = idx - e * LP;
+            We[idx] = (e < E && l < L0) ? w0[e * L0 + l] : 0.f;
+        }
+        for (int idx = tl; idx < LP * WDS; idx += NTH) {
+            const int l = idx / WDS, e = idx - l * WDS;
+            Wd[idx] = (l < L0 && e < E) ? w0[E * L0 + l * E + e] : 0.f;
+        }
+        for (int idx = tl; idx < NEL; idx += NTH) mv[idx] = make_float2(0.f, 0.f);
+    }
+    __syncthreads();
+    if (!active) return;
     const int L = p.task_L[task];
-    const float* w0 = p.W0 + (size_t)task * p.w_stride;
-    for (int idx = tid; idx < EP * LP; idx += NTH) {
-        const int e = idx / LP, l = idx - e * LP;
-        We[idx] = (e < E && l < L) ? w0[e * L + l] : 0.f;
-    }
-    for (int idx = tid; idx < LP * WDS; idx += NTH) {
-        const int l = idx / WDS, e = idx - l * WDS;
-        Wd[idx] = (l < L && e < E) ? w0[E * L + l * E + e] : 0.f;
-    }
-
-    float mom[MAXT5][16], vel[MAXT5][16];
-#pragma unroll
-    for (int j = 0; j < MAXT5; ++j)
-#pragma unroll
-        for (int q = 0; q < 16; ++q) mom[j][q] = vel[j][q] = 0.f;
 
     const int* perm_t = p.perm ? p.perm + (size_t)task * p.perm_task_stride : nullptr;
     const float alpha = p.alpha;
     const float omb1 = 1.f - p.b1, omb2 = 1.f - p.b2;
+    const int part_id = (CS == 1) ? 0 : (tl & (CS - 1));      // which column part this lane handles
+    const int row_in_pass = tl / CS;
 
-    // ---------------------------------------------------------------- phases
-    // P1: H = lrelu(X_b We)            [nb x 24] . [24 x LP]
-    auto fwd_encode = [&](int RT) {
-        const int ntiles = RT * CT;
-        for (int t = tid; t < ntiles; t += NTH) {
-            const int ct = t / RT, rt = t - ct * RT;
-            const float* ar[4];
-#pragma unroll
-            for (int i = 0; i < 4; ++i) ar[i] = Xs + rowidx[rt + RT * i] * XS;
-            const float* bp = We + ct * 4;
-            float acc[4][4] = {};
-#pragma unroll
-            for (int k4 = 0; k4 < EP / 4; ++k4) {
-                float4 a[4], b[4];
-#pragma unroll
-                for (int i = 0; i < 4; ++i) a[i] = ld4(ar[i] + 4 * k4);
-#pragma unroll
-                for (int kk = 0; kk < 4; ++kk) b[kk] = ld4(bp + (4 * k4 + kk) * LP);
-                mma_nn(acc, a, b);
-            }
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                float4 h;
-                h.x = lrelu(acc[i][0], alpha);
-                h.y = lrelu(acc[i][1], alpha);
-                h.z = lrelu(acc[i][2], alpha);
-                h.w = lrelu(acc[i][3], alpha);
-                st4(H + (rt + RT * i) * HS + ct * 4, h);
-            }
-        }
-    };
-    // P2: Zy = H Wd, y = lrelu(Zy), squared error, dZy   [nb x LP] . [LP x 24]
-    auto fwd_decode = [&](int RT, bool train, float coef) -> float {
+    // ---------------------------------------------------------------- rows phase
+    // Forward (and backward to dZh) of the batch rows, one row per lane (pair).  Returns the lane's share of the
+    // squared error.  Lanes without a row work on the all-zero row T and park their (all-zero) results in
+    // scratch row BP, so the phase needs no predication and pairs stay converged.
+    auto rows_phase = [&](int nb, bool train, float coef) -> float {
         float sse = 0.f;
-        const int ntiles = RT * (EP / 4);
-        for (int t = tid; t < ntiles; t += NTH) {
-            const int ct = t / RT, rt = t - ct * RT;
-            const float* bp = Wd + ct * 4;
-            float acc[4][4] = {};
+#pragma unroll 1
+        for (int r0 = 0; r0 < nb; r0 += ROWS) {
+            const int r = r0 + row_in_pass;
+            const bool valid = r < nb;
+            const float* xr = Xs + (valid ? xoff[r] : T * XS);
+            const int rs = valid ? r : BP;
+            float* hrow = H + rs * HS;
+            float* yrow = dZy + rs * XS;
+            // own latent columns: float4 groups at 4*(CS*i+part_id), tail float2 at 4*(CT-1)+2*part_id
+            const int lcol0 = 4 * part_id;
+            const int ltail = 4 * (CT - 1) + 2 * part_id;
+            // ---- zh (own columns) = x . We[:, cols]
+            float zh[LPC];
 #pragma unroll
-            for (int k4 = 0; k4 < CT; ++k4) {
-                float4 a[4], b[4];
+            for (int l = 0; l < LPC; ++l) zh[l] = 0.f;
+#pragma unroll (UK)
+            for (int e4 = 0; e4 < EP / 4; ++e4) {
+                const float4 xv = ld4(xr + 4 * e4);
+                const float xe[4] = {xv.x, xv.y, xv.z, xv.w};
 #pragma unroll
-                for (int i = 0; i < 4; ++i) a[i] = ld4(H + (rt + RT * i) * HS + 4 * k4);
+                for (int k = 0; k < 4; ++k) {
+                    const float* wrow = We + (4 * e4 + k) * LP;
 #pragma unroll
-                for (int kk = 0; kk < 4; ++kk) b[kk] = ld4(bp + (4 * k4 + kk) * WDS);
-                mma_nn(acc, a, b);
+                    for (int i = 0; i < NG4; ++i) {
+                        const float4 w = ld4(wrow + lcol0 + 4 * CS * i);
+                        zh[4 * i + 0] = fmaf(xe[k], w.x, zh[4 * i + 0]);
+                        zh[4 * i + 1] = fmaf(xe[k], w.y, zh[4 * i + 1]);
+                        zh[4 * i + 2] = fmaf(xe[k], w.z, zh[4 * i + 2]);
+                        zh[4 * i + 3] = fmaf(xe[k], w.w, zh[4 * i + 3]);
+                    }
+                    if constexpr (TAIL) {
+                        const float2 w = ld2(wrow + ltail);
+                        zh[4 * NG4 + 0] = fmaf(xe[k], w.x, zh[4 * NG4 + 0]);
+                        zh[4 * NG4 + 1] = fmaf(xe[k], w.y, zh[4 * NG4 + 1]);
+                    }
+                }
             }
 #pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                const int pos = rt + RT * i;
-                const float4 x = ld4(Xs + rowidx[pos] * XS + ct * 4);
-                const float xv[4] = {x.x, x.y, x.z, x.w};
-                float g[4];
+            for (int i = 0; i < NG4; ++i)
+                st4(hrow + lcol0 + 4 * CS * i, make_float4(lrelu(zh[4 * i], alpha), lrelu(zh[4 * i + 1], alpha),
+                                                           lrelu(zh[4 * i + 2], alpha), lrelu(zh[4 * i + 3], alpha)));
+            if constexpr (TAIL) st2(hrow + ltail, make_float2(lrelu(zh[4 * NG4], alpha), lrelu(zh[4 * NG4 + 1], alpha)));
+            if constexpr (CS > 1) __syncwarp();
+            // ---- zy (own EPC columns) = h . Wd[:, cols]; h re-read from the row (written by the pair)
+            float zy[EPC];
 #pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    const float zy = acc[i][j];
-                    const float d = lrelu(zy, alpha) - xv[j];
-                    sse = fmaf(d, d, sse);
-                    g[j] = lrelu_grad(zy, coef * d, alpha);
+            for (int e = 0; e < EPC; ++e) zy[e] = 0.f;
+            const float* wdp = Wd + part_id * EPC;
+#pragma unroll (UK)
+            for (int l4 = 0; l4 < CT; ++l4) {
+                const float4 hv = ld4(hrow + 4 * l4);
+                const float hl[4] = {hv.x, hv.y, hv.z, hv.w};
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+#pragma unroll
+                    for (int e4 = 0; e4 < EPC / 4; ++e4) {
+                        const float4 w = ld4(wdp + (4 * l4 + k) * WDS + 4 * e4);
+                        zy[4 * e4 + 0] = fmaf(hl[k], w.x, zy[4 * e4 + 0]);
+                        zy[4 * e4 + 1] = fmaf(hl[k], w.y, zy[4 * e4 + 1]);
+                        zy[4 * e4 + 2] = fmaf(hl[k], w.z, zy[4 * e4 + 2]);
+                        zy[4 * e4 + 3] = fmaf(hl[k], w.w, zy[4 * e4 + 3]);
+                    }
                 }
-                if (train) st4(dZy + pos * XS + ct * 4, make_float4(g[0], g[1], g[2], g[3]));
+            }
+            // ---- squared error and dLoss/dzy on the lane's columns
+#pragma unroll
+            for (int e4 = 0; e4 < EPC / 4; ++e4) {
+                const float4 xv = ld4(xr + part_id * EPC + 4 * e4);
+                const float xe[4] = {xv.x, xv.y, xv.z, xv.w};
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    const float z = zy[4 * e4 + k];
+                    const float d = lrelu(z, alpha) - xe[k];
+                    sse = fmaf(d, d, sse);
+                    zy[4 * e4 + k] = lrelu_grad(z, coef * d, alpha);      // zy now holds dzy
+                }
+            }
+            if (train) {
+#pragma unroll
+                for (int e4 = 0; e4 < EPC / 4; ++e4)
+                    st4(yrow + part_id * EPC + 4 * e4, make_float4(zy[4 * e4], zy[4 * e4 + 1], zy[4 * e4 + 2], zy[4 * e4 + 3]));
+                float dzy[EP];
+                if constexpr (CS > 1) {
+                    __syncwarp();
+#pragma unroll
+                    for (int e4 = 0; e4 < EP / 4; ++e4) {
+                        const float4 v = ld4(yrow + 4 * e4);
+                        dzy[4 * e4] = v.x; dzy[4 * e4 + 1] = v.y; dzy[4 * e4 + 2] = v.z; dzy[4 * e4 + 3] = v.w;
+                    }
+                } else {
+#pragma unroll
+                    for (int e = 0; e < EP; ++e) dzy[e] = zy[e];
+                }
+                // ---- dzh (own columns) = (dzy . Wd[l, :]) * lrelu'(zh); 4 partial sums per column keep the chains short
+                float* grow = dZh + rs * HS;
+                auto dzh_col = [&](int l, float hsign) -> float {
+                    const float* wr = Wd + l * WDS;
+                    float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+#pragma unroll
+                    for (int e4 = 0; e4 < EP / 4; ++e4) {
+                        const float4 w = ld4(wr + 4 * e4);
+                        a0 = fmaf(dzy[4 * e4 + 0], w.x, a0);
+                        a1 = fmaf(dzy[4 * e4 + 1], w.y, a1);
+                        a2 = fmaf(dzy[4 * e4 + 2], w.z, a2);
+                        a3 = fmaf(dzy[4 * e4 + 3], w.w, a3);
+                    }
+                    return lrelu_grad(hsign, (a0 + a1) + (a2 + a3), alpha);   // sign(h) == sign(zh) for alpha > 0
+                };
+#pragma unroll (FULL ? (NG4 > 0 ? NG4 : 1) : 1)
+                for (int i = 0; i < NG4; ++i) {
+                    const int l0 = lcol0 + 4 * CS * i;
+                    const float4 hv = ld4(hrow + l0);
+                    st4(grow + l0, make_float4(dzh_col(l0, hv.x), dzh_col(l0 + 1, hv.y), dzh_col(l0 + 2, hv.z),
+                                               dzh_col(l0 + 3, hv.w)));
+                }
+                if constexpr (TAIL) {
+                    const float2 hv = ld2(hrow + ltail);
+                    st2(grow + ltail, make_float2(dzh_col(ltail, hv.x), dzh_col(ltail + 1, hv.y)));
+                }
             }
         }
         return sse;
     };
-    // P4: dZh = (dZy Wd^T) o lrelu'(Zh)   [nb x 24] . [24 x LP]
-    auto bwd_hidden = [&](int RT) {
-        const int ntiles = RT * CT;
-        for (int t = tid; t < ntiles; t += NTH) {
-            const int ct = t / RT, rt = t - ct * RT;
+
+    // ---------------------------------------------------------------- weight-gradient phase (split-K over warps)
+    auto grads_phase = [&](int nb) {
+        float* mypart = part + warp * NEL;
+#pragma unroll 1
+        for (int t = lane; t < NT5; t += 32) {
+            const bool dec = t < 6 * CT;
+            int a0, b0, bstr;
+            if (dec) {                                   // dWd tile: A = H[:, lt*4..], B = dZy[:, et*4..]
+                const int lt = t / 6, et = t - lt * 6;
+                a0 = (int)(H - Xs) + lt * 4; b0 = (int)(dZy - Xs) + et * 4; bstr = XS;
+            } else {                                     // dWe tile: A = X_b[:, et*4..], B = dZh[:, lt*4..]
+                const int u = t - 6 * CT;
+                const int et = u / CT, lt = u - et * CT;
+                a0 = et * 4; b0 = (int)(dZh - Xs) + lt * 4; bstr = HS;
+            }
             float acc[4][4] = {};
-#pragma unroll
-            for (int k4 = 0; k4 < EP / 4; ++k4) {
-                float4 a[4], b[4];
-#pragma unroll
-                for (int i = 0; i < 4; ++i) a[i] = ld4(dZy + (rt + RT * i) * XS + 4 * k4);
-#pragma unroll
-                for (int j = 0; j < 4; ++j) b[j] = ld4(Wd + (ct * 4 + j) * WDS + 4 * k4);
-                mma_nt(acc, a, b);
-            }
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                const int pos = rt + RT * i;
-                const float4 h = ld4(H + pos * HS + ct * 4);     // sign(h) == sign(zh) for alpha > 0
-                float4 g;
-                g.x = lrelu_grad(h.x, acc[i][0], alpha);
-                g.y = lrelu_grad(h.y, acc[i][1], alpha);
-                g.z = lrelu_grad(h.z, acc[i][2], alpha);
-                g.w = lrelu_grad(h.w, acc[i][3], alpha);
-                st4(dZh + pos * HS + ct * 4, g);
-            }
-        }
-    };
-    // P5: dWd = H^T dZy, dWe = X_b^T dZh, then the Nadam update of the owned tiles
-    auto grads_and_update = [&](int nb, int step) {
-        const float4 sc = __ldg(p.sched + step);
-        const bool dump = p.grad_out != nullptr && step == p.dump_step;
-#pragma unroll
-        for (int j = 0; j < MAXT5; ++j) {
-            const int t = tid + j * NTH;
-            if (t < NT5) {
-                float acc[4][4] = {};
-                float* wt;
-                int wstride, r0, c0;
-                const bool dec = t < 6 * CT;
-                if (dec) {                                   // dWd tile: rows l (lt), cols e (et)
-                    const int lt = t / 6, et = t - lt * 6;
-                    const float* ap = H + lt * 4;
-                    const float* bp = dZy + et * 4;
 #pragma unroll 4
-                    for (int q = 0; q < nb; ++q) mma_tn(acc, ld4(ap + q * HS), ld4(bp + q * XS));
-                    wt = Wd + (lt * 4) * WDS + et * 4;
-                    wstride = WDS; r0 = lt * 4; c0 = et * 4;
-                } else {                                     // dWe tile: rows e (et), cols l (lt)
-                    const int u = t - 6 * CT;
-                    const int et = u / CT, lt = u - et * CT;
-                    const float* ap = Xs + et * 4;
-                    const float* bp = dZh + lt * 4;
-#pragma unroll 4
-                    for (int q = 0; q < nb; ++q) mma_tn(acc, ld4(ap + rowidx[q] * XS), ld4(bp + q * HS));
-                    wt = We + (et * 4) * LP + lt * 4;
-                    wstride = LP; r0 = et * 4; c0 = lt * 4;
-                }
+            for (int q = warp; q < nb; q += NW) {
+                const int ao = dec ? q * HS : xoff[q];
+                const float4 a = ld4(Xs + a0 + ao);
+                const float4 b = ld4(Xs + b0 + q * bstr);
+                const float av[4] = {a.x, a.y, a.z, a.w};
 #pragma unroll
                 for (int i = 0; i < 4; ++i) {
-                    float4 w4 = ld4(wt + i * wstride);
-                    float wv[4] = {w4.x, w4.y, w4.z, w4.w};
-#pragma unroll
-                    for (int jj = 0; jj < 4; ++jj) {
-                        const float g = acc[i][jj];
-                        float& m = mom[j][i * 4 + jj];
-                        float& v = vel[j][i * 4 + jj];
-                        m = p.b1 * m + omb1 * g;
-                        v = p.b2 * v + omb2 * (g * g);
-                        const float m_bar = sc.x * g + sc.y * m;
-                        wv[jj] -= p.lr * m_bar / (sqrtf(v * sc.z) + p.eps);
-                    }
-                    st4(wt + i * wstride, make_float4(wv[0], wv[1], wv[2], wv[3]));
+                    acc[i][0] = fmaf(av[i], b.x, acc[i][0]);
+                    acc[i][1] = fmaf(av[i], b.y, acc[i][1]);
+                    acc[i][2] = fmaf(av[i], b.z, acc[i][2]);
+                    acc[i][3] = fmaf(av[i], b.w, acc[i][3]);
                 }
-                if (dump) {
-                    float* go = p.grad_out + (size_t)task * p.w_stride;
+            }
 #pragma unroll
-                    for (int i = 0; i < 4; ++i)
+            for (int i = 0; i < 4; ++i)
+                st4(mypart + t * 16 + i * 4, make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]));
+        }
+    };
+
+    // ---------------------------------------------------------------- update phase (Nadam, element-wise)
+    auto update_phase = [&](int step) {
+        const float4 sc = __ldg(p.sched + step);
+        const bool dump = p.grad_out != nullptr && step == p.dump_step;
+#pragma unroll 2
+        for (int idx = tl; idx < NEL; idx += NTH) {
+            float g = part[idx];
 #pragma unroll
-                        for (int jj = 0; jj < 4; ++jj) {
-                            const int r = r0 + i, c = c0 + jj;
-                            if (dec) { if (r < L && c < E) go[E * L + r * E + c] = acc[i][jj]; }
-                            else     { if (r < E && c < L) go[r * L + c] = acc[i][jj]; }
-                        }
+            for (int w = 1; w < NW; ++w) g += part[w * NEL + idx];
+            float2 s2 = mv[idx];
+            s2.x = p.b1 * s2.x + omb1 * g;
+            s2.y = p.b2 * s2.y + omb2 * (g * g);
+            mv[idx] = s2;
+            const float m_bar = sc.x * g + sc.y * s2.x;
+            const int o = woff[idx];
+            We[o] -= __fdividef(p.lr * m_bar, fast_sqrt(s2.y * sc.z) + p.eps);
+            if (dump) {
+                float* go = p.grad_out + (size_t)task * p.w_stride;
+                if (o >= EP * LP) {
+                    const int r = (o - EP * LP) / WDS, c = (o - EP * LP) - r * WDS;
+                    if (r < L && c < E) go[E * L + r * E + c] = g;
+                } else {
+                    const int r = o / LP, c = o - r * LP;
+                    if (r < E && c < L) go[r * L + c] = g;
                 }
             }
         }
     };
 
     // ---------------------------------------------------------------- training run
+    // An epoch is a list of segments: the train mini-batches, then the validation chunks.  One loop (one
+    // call site per phase keeps the code small and the phases inlined).
     const int n_fit = p.n_fit, n_val = p.n_val, batch = p.batch;
+    const int n_tb = (n_fit + batch - 1) / batch, n_vb = (n_val + batch - 1) / batch, n_seg = n_tb + n_vb;
     int step = 0, wait = 0, epochs_run = 0, st = 0;
     float best = INFINITY;
+    auto set_rows = [&](int epoch, int seg) {
+        const bool val = seg >= n_tb;
+        const int lo = (val ? seg - n_tb : seg) * batch;
+        const int nb = min(batch, (val ? n_val : n_fit) - lo);
+        for (int q = tl; q < nb; q += NTH) {
+            const int row = val ? n_fit + lo + q : (perm_t ? __ldg(perm_t + (size_t)epoch * n_fit + lo + q) : lo + q);
+            xoff[q] = row * XS;
+        }
+    };
+    set_rows(0, 0);
+    team_sync<NW>(team);
     for (int epoch = 0; epoch < p.max_epochs; ++epoch) {
-        float lsum = 0.f;
-        for (int lo = 0; lo < n_fit; lo += batch) {
-            const int nb = min(batch, n_fit - lo);
-            const int RT = (nb + 3) >> 2;
-            for (int q = tid; q < 4 * RT; q += NTH)
-                rowidx[q] = q < nb ? (perm_t ? __ldg(perm_t + (size_t)epoch * n_fit + lo + q) : lo + q) : T;
-            team_sync<WPT>(team);
-            fwd_encode(RT);
-            team_sync<WPT>(team);
-            lsum += fwd_decode(RT, true, 2.f / (float)(nb * E));
-            team_sync<WPT>(team);
-            bwd_hidden(RT);
-            team_sync<WPT>(team);
-            grads_and_update(nb, step);
-            ++step;
-            team_sync<WPT>(team);
+        float lsum = 0.f, vsum = 0.f;
+#pragma unroll 1
+        for (int seg = 0; seg < n_seg; ++seg) {
+            const bool train = seg < n_tb;
+            const int lo = (train ? seg : seg - n_tb) * batch;
+            const int nb = min(batch, (train ? n_fit : n_val) - lo);
+            const float sse = rows_phase(nb, train, 2.f / (float)(nb * E));
+            if (train) {
+                lsum += sse;
+                team_sync<NW>(team);
+                grads_phase(nb);
+                team_sync<NW>(team);
+                update_phase(step);
+                ++step;
+            } else {
+                vsum += sse;
+                team_sync<NW>(team);
+            }
+            // row offsets of the next segment (next epoch's first batch after the last one)
+            if (seg + 1 < n_seg) set_rows(epoch, seg + 1);
+            else set_rows(epoch + 1 < p.max_epochs ? epoch + 1 : epoch, 0);
+            team_sync<NW>(team);
         }
-        float vsum = 0.f;
-        for (int lo = 0; lo < n_val; lo += batch) {
-            const int nb = min(batch, n_val - lo);
-            const int RT = (nb + 3) >> 2;
-            for (int q = tid; q < 4 * RT; q += NTH) rowidx[q] = q < nb ? n_fit + lo + q : T;
-            team_sync<WPT>(team);
-            fwd_encode(RT);
-            team_sync<WPT>(team);
-            vsum += fwd_decode(RT, false, 0.f);
-            team_sync<WPT>(team);
-        }
-        const float loss = team_sum<WPT>(lsum, red, team, tid) / (float)(E * n_fit);
-        const float val = n_val > 0 ? team_sum<WPT>(vsum, red, team, tid) / (float)(E * n_val) : NAN;
-        if (tid == 0) {
+        const float loss = team_sum<NW>(lsum, red, team, tl) / (float)(E * n_fit);
+        const float val = n_val > 0 ? team_sum<NW>(vsum, red, team, tl) / (float)(E * n_val) : NAN;
+        if (tl == 0) {
             p.loss_hist[(size_t)task * p.max_epochs + epoch] = loss;
             p.val_hist[(size_t)task * p.max_epochs + epoch] = val;
         }
@@ -398,39 +440,61 @@ __global__ void __launch_bounds__(32 * WPT * TPC) fit_kernel(const FitParams p) 
     }
 
     float* wo = p.W_out + (size_t)task * p.w_stride;
-    for (int idx = tid; idx < E * L; idx += NTH) {
+    for (int idx = tl; idx < E * L; idx += NTH) {
         const int e = idx / L, l = idx - e * L;
         wo[idx] = We[e * LP + l];
     }
-    for (int idx = tid; idx < L * E; idx += NTH) {
+    for (int idx = tl; idx < L * E; idx += NTH) {
         const int l = idx / E, e = idx - l * E;
         wo[E * L + idx] = Wd[l * WDS + e];
     }
-    if (tid == 0) {
+    if (tl == 0) {
         p.epochs_run[task] = epochs_run;
         p.status[task] = st;
     }
 }
 
 // ---------------------------------------------------------------------------------- host side
-template <int LP, int WPT, int TPC>
+constexpr size_t kMaxSmem = 227 * 1024;
+
+template <int LP, int NW, int TPC>
+static size_t fit_smem_bytes(const FitParams& p) {
+    return sizeof(float) * (Lay<LP>::cta_floats(p.T) + TPC * Lay<LP>::team_floats(p.BP, NW));
+}
+
+template <int LP, int NW, int CS, int TPC, bool FULL>
 static int launch_fit(const FitParams& p, cudaStream_t stream) {
-    const size_t xf = x_floats(p.T), tf = Lay<LP>::team_floats(p.BP);
-    const size_t smem = sizeof(float) * (p.shared_x ? xf + TPC * tf : TPC * (xf + tf));
-    HFREP_REQUIRE(smem <= 227 * 1024, "fit: %zu bytes of shared memory needed (T=%d too long for the narrow kernel)",
-                  smem, p.T);
-    auto kern = fit_kernel<LP, WPT, TPC>;
+    const size_t smem = fit_smem_bytes<LP, NW, TPC>(p);
+    HFREP_REQUIRE(smem <= kMaxSmem, "fit: %zu bytes of shared memory needed (T=%d / batch=%d too large for the narrow kernel)",
+                  smem, p.T, p.batch);
+    auto kern = fit_kernel<LP, NW, CS, TPC, FULL>;
     HFREP_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const int grid = (p.n_tasks + TPC - 1) / TPC;
-    kern<<<grid, 32 * WPT * TPC, smem, stream>>>(p);
+    kern<<<grid, 32 * NW * TPC, smem, stream>>>(p);
     HFREP_CUDA_OK(cudaGetLastError());
     return HFREP_OK;
 }
 
+// Teams of one CTA share the staged training block, so several teams per CTA need n_x == 1; take the
+// largest team count whose shared memory fits.
+template <int LP, int NW, int CS, int TPC>
+static int launch_fit_packed(const FitParams& p, cudaStream_t stream) {
+    if constexpr (TPC > 1) {
+        if (!p.shared_x || fit_smem_bytes<LP, NW, TPC>(p) > kMaxSmem) return launch_fit_packed<LP, NW, CS, TPC / 2>(p, stream);
+    }
+    return launch_fit<LP, NW, CS, TPC, false>(p, stream);
+}
+
+// warps per task:
+//   1  one warp per task, lane pairs share a row (16 rows per pass): most work per issued instruction, for grids
+//      with thousands of tasks;
+//   3  three warps per task, lane pairs share a row (48 rows per pass = one batch): the default;
+//   4  = 3 with the k-loops fully unrolled: latency mapping for a handful of tasks (one warp per scheduler).
 template <int LP>
 static int dispatch_mapping(const FitParams& p, int wpt, cudaStream_t stream) {
-    if (wpt == 1) return p.shared_x ? launch_fit<LP, 1, 8>(p, stream) : launch_fit<LP, 1, 1>(p, stream);
-    return launch_fit<LP, 4, 1>(p, stream);
+    if (wpt == 1) return launch_fit_packed<LP, 1, 2, 8>(p, stream);
+    if (wpt == 3) return launch_fit_packed<LP, 3, 2, 2>(p, stream);
+    return launch_fit<LP, 3, 2, 1, true>(p, stream);
 }
 
 int fit_dispatch(const FitParams& p, int L_max, int wpt, cudaStream_t stream) {
@@ -509,7 +573,10 @@ extern "C" int hfrep_fit_batched(const hfrep_fit_cfg* c, const float* X, int n_t
     p.alpha = c->alpha; p.lr = c->lr; p.b1 = c->beta_1; p.b2 = c->beta_2; p.eps = c->epsilon;
 
     int wpt = c->warps_per_task;
-    if (wpt == 0) wpt = (n_tasks >= 4 * sm_count()) ? 1 : 4;    // few tasks: spend 4 warps on each to cut latency
-    HFREP_REQUIRE(wpt == 1 || wpt == 4, "fit_batched: warps_per_task=%d (0, 1 or 4)", wpt);
+    if (wpt == 0) {                                  // pick the mapping from the amount of parallel work
+        const int sms = sm_count();
+        wpt = n_tasks <= sms ? 4 : (n_tasks < 24 * sms ? 3 : 1);
+    }
+    HFREP_REQUIRE(wpt == 1 || wpt == 3 || wpt == 4, "fit_batched: warps_per_task=%d (0, 1, 3 or 4)", wpt);
     return fit_dispatch(p, c->L_max, wpt, (cudaStream_t)stream);
 }

@@ -32,12 +32,12 @@ __global__ void __launch_bounds__(256) window_gather_kernel(const float* __restr
                 if (rng == 0.) rng = 1.;
                 const double scale = 1. / rng;
                 cst[c] = scale;
-                cst[ncols + c] = 0. - (double)lo * scale;
+                cst[ncols + c] = __dsub_rn(0., __dmul_rn((double)lo, scale));
             }
             __syncthreads();
             for (int idx = threadIdx.x; idx < len * ncols; idx += blockDim.x) {
                 const int r = idx / ncols, c = idx - r * ncols;
-                dst[idx] = (float)((double)__ldg(src + (size_t)r * C + c) * cst[c] + cst[ncols + c]);
+                dst[idx] = (float)__dadd_rn(__dmul_rn((double)__ldg(src + (size_t)r * C + c), cst[c]), cst[ncols + c]);   // X *= scale; X += min_ (no FMA contraction)
             }
         } else if (vec4) {
             const int q = ncols >> 2;
