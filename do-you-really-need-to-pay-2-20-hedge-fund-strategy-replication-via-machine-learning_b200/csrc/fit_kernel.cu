@@ -17,12 +17,13 @@
 // Shared memory (floats, rows 16-byte aligned).  Per CTA: Xs [(T+1)][28] (shared by the CTA's teams when all
 // tasks train on the same block; cols >= E zero, row T zero), woff [48*LP] (tile-major slot -> weight offset).
 // Per team: We [24][LP], Wd [LP][28], H [BP+1][HS], dZh [BP+1][HS], dZy [BP+1][28] (row BP = scratch row for
-// idle lanes), part [NW][48*LP], mv [48*LP] float2, xoff [BP] (row offsets of the current batch: the fused
+// idle lanes), part [NW][48*LP], mv [48*LP] float2, xoff [2][BP] (row offsets of the current / next batch: the fused
 // window gather — shuffled orders cost nothing extra).
 // LP = L rounded up to 4; zero padding is exactly neutral (zero activations, zero gradients, Nadam(0)=0).
 #include "common.cuh"
 
 #include <cmath>
+#include <cstdlib>
 
 namespace hfrep {
 
@@ -45,6 +46,7 @@ struct FitParams {
     float* grad_out;
     long long perm_task_stride;
     int n_tasks, E, T, n_fit, n_val, batch, BP, max_epochs, patience, early_stop, w_stride, shared_x, dump_step;
+    int debug_skip;      // profiling only (env HFREP_DEBUG_SKIP): bit0 rows, bit1 grads, bit2 update phases skipped
     float alpha, lr, b1, b2, eps;
 };
 
@@ -56,7 +58,7 @@ struct Lay {
     static constexpr int NEL = NT5 * 16;       // = 48*LP weight slots, tile-major
     __host__ __device__ static size_t team_floats(int BP, int NW) {
         return (size_t)EP * LP + (size_t)LP * WDS + (size_t)(BP + 1) * HS * 2 + (size_t)(BP + 1) * XS +
-               (size_t)NW * NEL + 2 * (size_t)NEL + BP + 32;
+               (size_t)NW * NEL + 2 * (size_t)NEL + 2 * BP + 64;
     }
     __host__ __device__ static size_t cta_floats(int T) { return (size_t)(T + 1) * XS + NEL; }
 };
@@ -111,9 +113,11 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
     // Column split of the rows phase (CS == 2): the pair shares a row; lane `part` owns the float4 column groups
     // g = 2i+part of the latent block (plus half of the last group when their number is odd) and the ETF columns
     // [part*12, part*12+12).  CS == 1: a lane owns everything.
-    constexpr int NG4 = CT / CS;                   // whole float4 latent groups per lane
+    // CS == 4 (latency mapping, LP % 8 == 0): a lane quad shares a row; lane `part` owns the float2 pieces at
+    // columns 8j + 2*part of both the latent and the ETF block (see rows_phase_quad).
+    constexpr int NG4 = (CS == 4) ? 0 : CT / CS;   // whole float4 latent groups per lane
     constexpr int TAIL = (CS == 2) ? (CT % 2) : 0; // 1: one extra float2 piece per lane
-    constexpr int LPC = 4 * NG4 + 2 * TAIL;        // latent columns per lane
+    constexpr int LPC = (CS == 4) ? LP / 4 : 4 * NG4 + 2 * TAIL;   // latent columns per lane
     constexpr int EPC = EP / CS;                   // ETF columns per lane
     constexpr int ROWS = NTH / CS;                 // batch rows per pass
     constexpr int UK = FULL ? EP / 4 : 2;          // unroll of the k4-loops
@@ -137,8 +141,8 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
     float* dZy = dZh + (BP + 1) * HS;
     float* part = dZy + (BP + 1) * XS;
     float2* mv = reinterpret_cast<float2*>(part + NW * NEL);
-    int* xoff = reinterpret_cast<int*>(part + NW * NEL + 2 * NEL);
-    float* red = reinterpret_cast<float*>(xoff + BP);
+    int* xoff_tab = reinterpret_cast<int*>(part + NW * NEL + 2 * NEL);   // [2][BP], double-buffered per segment
+    float* red = reinterpret_cast<float*>(xoff_tab + 2 * BP);          // [2][32], double-buffered per epoch
 
     // ---- stage the training block (fused window load: rows of the scaled block -> padded tile)
     {
@@ -191,7 +195,7 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
     // Forward (and backward to dZh) of the batch rows, one row per lane (pair).  Returns the lane's share of the
     // squared error.  Lanes without a row work on the all-zero row T and park their (all-zero) results in
     // scratch row BP, so the phase needs no predication and pairs stay converged.
-    auto rows_phase = [&](int nb, bool train, float coef) -> float {
+    auto rows_phase = [&](const int* xoff, int nb, bool train, float coef) -> float {
         float sse = 0.f;
 #pragma unroll 1
         for (int r0 = 0; r0 < nb; r0 += ROWS) {
@@ -208,25 +212,63 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
             float zh[LPC];
 #pragma unroll
             for (int l = 0; l < LPC; ++l) zh[l] = 0.f;
-#pragma unroll (UK)
-            for (int e4 = 0; e4 < EP / 4; ++e4) {
-                const float4 xv = ld4(xr + 4 * e4);
-                const float xe[4] = {xv.x, xv.y, xv.z, xv.w};
+            if constexpr (FULL) {
+                // explicit double buffering: the weights of k4-group e4+1 are in flight while group e4 is multiplied
+                float4 wq[2][4][NG4 > 0 ? NG4 : 1];
+                float2 wt[2][4];
+                float4 xq[2];
+                auto load_group = [&](int b, int e4) {
+                    xq[b] = ld4(xr + 4 * e4);
 #pragma unroll
-                for (int k = 0; k < 4; ++k) {
-                    const float* wrow = We + (4 * e4 + k) * LP;
+                    for (int k = 0; k < 4; ++k) {
+                        const float* wrow = We + (4 * e4 + k) * LP;
 #pragma unroll
-                    for (int i = 0; i < NG4; ++i) {
-                        const float4 w = ld4(wrow + lcol0 + 4 * CS * i);
-                        zh[4 * i + 0] = fmaf(xe[k], w.x, zh[4 * i + 0]);
-                        zh[4 * i + 1] = fmaf(xe[k], w.y, zh[4 * i + 1]);
-                        zh[4 * i + 2] = fmaf(xe[k], w.z, zh[4 * i + 2]);
-                        zh[4 * i + 3] = fmaf(xe[k], w.w, zh[4 * i + 3]);
+                        for (int i = 0; i < NG4; ++i) wq[b][k][i] = ld4(wrow + lcol0 + 4 * CS * i);
+                        if constexpr (TAIL) wt[b][k] = ld2(wrow + ltail);
                     }
-                    if constexpr (TAIL) {
-                        const float2 w = ld2(wrow + ltail);
-                        zh[4 * NG4 + 0] = fmaf(xe[k], w.x, zh[4 * NG4 + 0]);
-                        zh[4 * NG4 + 1] = fmaf(xe[k], w.y, zh[4 * NG4 + 1]);
+                };
+                load_group(0, 0);
+#pragma unroll
+                for (int e4 = 0; e4 < EP / 4; ++e4) {
+                    const int b = e4 & 1;
+                    if (e4 + 1 < EP / 4) load_group(b ^ 1, e4 + 1);
+                    const float xe[4] = {xq[b].x, xq[b].y, xq[b].z, xq[b].w};
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+#pragma unroll
+                        for (int i = 0; i < NG4; ++i) {
+                            zh[4 * i + 0] = fmaf(xe[k], wq[b][k][i].x, zh[4 * i + 0]);
+                            zh[4 * i + 1] = fmaf(xe[k], wq[b][k][i].y, zh[4 * i + 1]);
+                            zh[4 * i + 2] = fmaf(xe[k], wq[b][k][i].z, zh[4 * i + 2]);
+                            zh[4 * i + 3] = fmaf(xe[k], wq[b][k][i].w, zh[4 * i + 3]);
+                        }
+                        if constexpr (TAIL) {
+                            zh[4 * NG4 + 0] = fmaf(xe[k], wt[b][k].x, zh[4 * NG4 + 0]);
+                            zh[4 * NG4 + 1] = fmaf(xe[k], wt[b][k].y, zh[4 * NG4 + 1]);
+                        }
+                    }
+                }
+            } else {
+    #pragma unroll (UK)
+                for (int e4 = 0; e4 < EP / 4; ++e4) {
+                    const float4 xv = ld4(xr + 4 * e4);
+                    const float xe[4] = {xv.x, xv.y, xv.z, xv.w};
+    #pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        const float* wrow = We + (4 * e4 + k) * LP;
+    #pragma unroll
+                        for (int i = 0; i < NG4; ++i) {
+                            const float4 w = ld4(wrow + lcol0 + 4 * CS * i);
+                            zh[4 * i + 0] = fmaf(xe[k], w.x, zh[4 * i + 0]);
+                            zh[4 * i + 1] = fmaf(xe[k], w.y, zh[4 * i + 1]);
+                            zh[4 * i + 2] = fmaf(xe[k], w.z, zh[4 * i + 2]);
+                            zh[4 * i + 3] = fmaf(xe[k], w.w, zh[4 * i + 3]);
+                        }
+                        if constexpr (TAIL) {
+                            const float2 w = ld2(wrow + ltail);
+                            zh[4 * NG4 + 0] = fmaf(xe[k], w.x, zh[4 * NG4 + 0]);
+                            zh[4 * NG4 + 1] = fmaf(xe[k], w.y, zh[4 * NG4 + 1]);
+                        }
                     }
                 }
             }
@@ -241,19 +283,47 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
 #pragma unroll
             for (int e = 0; e < EPC; ++e) zy[e] = 0.f;
             const float* wdp = Wd + part_id * EPC;
-#pragma unroll (UK)
-            for (int l4 = 0; l4 < CT; ++l4) {
-                const float4 hv = ld4(hrow + 4 * l4);
-                const float hl[4] = {hv.x, hv.y, hv.z, hv.w};
+            if constexpr (FULL) {
+                float4 wq[2][4][EPC / 4];
+                float4 hq[2];
+                auto load_group = [&](int b, int l4) {
+                    hq[b] = ld4(hrow + 4 * l4);
 #pragma unroll
-                for (int k = 0; k < 4; ++k) {
+                    for (int k = 0; k < 4; ++k)
 #pragma unroll
-                    for (int e4 = 0; e4 < EPC / 4; ++e4) {
-                        const float4 w = ld4(wdp + (4 * l4 + k) * WDS + 4 * e4);
-                        zy[4 * e4 + 0] = fmaf(hl[k], w.x, zy[4 * e4 + 0]);
-                        zy[4 * e4 + 1] = fmaf(hl[k], w.y, zy[4 * e4 + 1]);
-                        zy[4 * e4 + 2] = fmaf(hl[k], w.z, zy[4 * e4 + 2]);
-                        zy[4 * e4 + 3] = fmaf(hl[k], w.w, zy[4 * e4 + 3]);
+                        for (int e4 = 0; e4 < EPC / 4; ++e4) wq[b][k][e4] = ld4(wdp + (4 * l4 + k) * WDS + 4 * e4);
+                };
+                load_group(0, 0);
+#pragma unroll
+                for (int l4 = 0; l4 < CT; ++l4) {
+                    const int b = l4 & 1;
+                    if (l4 + 1 < CT) load_group(b ^ 1, l4 + 1);
+                    const float hl[4] = {hq[b].x, hq[b].y, hq[b].z, hq[b].w};
+#pragma unroll
+                    for (int k = 0; k < 4; ++k)
+#pragma unroll
+                        for (int e4 = 0; e4 < EPC / 4; ++e4) {
+                            zy[4 * e4 + 0] = fmaf(hl[k], wq[b][k][e4].x, zy[4 * e4 + 0]);
+                            zy[4 * e4 + 1] = fmaf(hl[k], wq[b][k][e4].y, zy[4 * e4 + 1]);
+                            zy[4 * e4 + 2] = fmaf(hl[k], wq[b][k][e4].z, zy[4 * e4 + 2]);
+                            zy[4 * e4 + 3] = fmaf(hl[k], wq[b][k][e4].w, zy[4 * e4 + 3]);
+                        }
+                }
+            } else {
+    #pragma unroll (UK)
+                for (int l4 = 0; l4 < CT; ++l4) {
+                    const float4 hv = ld4(hrow + 4 * l4);
+                    const float hl[4] = {hv.x, hv.y, hv.z, hv.w};
+    #pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+    #pragma unroll
+                        for (int e4 = 0; e4 < EPC / 4; ++e4) {
+                            const float4 w = ld4(wdp + (4 * l4 + k) * WDS + 4 * e4);
+                            zy[4 * e4 + 0] = fmaf(hl[k], w.x, zy[4 * e4 + 0]);
+                            zy[4 * e4 + 1] = fmaf(hl[k], w.y, zy[4 * e4 + 1]);
+                            zy[4 * e4 + 2] = fmaf(hl[k], w.z, zy[4 * e4 + 2]);
+                            zy[4 * e4 + 3] = fmaf(hl[k], w.w, zy[4 * e4 + 3]);
+                        }
                     }
                 }
             }
@@ -301,16 +371,170 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
                     }
                     return lrelu_grad(hsign, (a0 + a1) + (a2 + a3), alpha);   // sign(h) == sign(zh) for alpha > 0
                 };
-#pragma unroll (FULL ? (NG4 > 0 ? NG4 : 1) : 1)
-                for (int i = 0; i < NG4; ++i) {
-                    const int l0 = lcol0 + 4 * CS * i;
-                    const float4 hv = ld4(hrow + l0);
-                    st4(grow + l0, make_float4(dzh_col(l0, hv.x), dzh_col(l0 + 1, hv.y), dzh_col(l0 + 2, hv.z),
-                                               dzh_col(l0 + 3, hv.w)));
+                if constexpr (FULL) {
+                    // own columns two at a time, the next pair's decoder rows in flight (double buffer)
+                    float hs[LPC], out[LPC];
+#pragma unroll
+                    for (int i = 0; i < NG4; ++i) {
+                        const float4 hv = ld4(hrow + lcol0 + 4 * CS * i);
+                        hs[4 * i] = hv.x; hs[4 * i + 1] = hv.y; hs[4 * i + 2] = hv.z; hs[4 * i + 3] = hv.w;
+                    }
+                    if constexpr (TAIL) {
+                        const float2 hv = ld2(hrow + ltail);
+                        hs[4 * NG4] = hv.x; hs[4 * NG4 + 1] = hv.y;
+                    }
+                    auto col_of = [&](int c) { return c < 4 * NG4 ? lcol0 + 4 * CS * (c >> 2) + (c & 3) : ltail + (c - 4 * NG4); };
+                    float4 wq[2][2][EP / 4];
+                    auto load_pair = [&](int b, int c) {
+#pragma unroll
+                        for (int u = 0; u < 2; ++u) {
+                            const float* wr = Wd + col_of(c + u) * WDS;
+#pragma unroll
+                            for (int e4 = 0; e4 < EP / 4; ++e4) wq[b][u][e4] = ld4(wr + 4 * e4);
+                        }
+                    };
+                    load_pair(0, 0);
+#pragma unroll
+                    for (int c = 0; c < LPC; c += 2) {
+                        const int b = (c >> 1) & 1;
+                        if (c + 2 < LPC) load_pair(b ^ 1, c + 2);
+#pragma unroll
+                        for (int u = 0; u < 2; ++u) {
+                            float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+#pragma unroll
+                            for (int e4 = 0; e4 < EP / 4; ++e4) {
+                                a0 = fmaf(dzy[4 * e4 + 0], wq[b][u][e4].x, a0);
+                                a1 = fmaf(dzy[4 * e4 + 1], wq[b][u][e4].y, a1);
+                                a2 = fmaf(dzy[4 * e4 + 2], wq[b][u][e4].z, a2);
+                                a3 = fmaf(dzy[4 * e4 + 3], wq[b][u][e4].w, a3);
+                            }
+                            out[c + u] = lrelu_grad(hs[c + u], (a0 + a1) + (a2 + a3), alpha);
+                        }
+                    }
+#pragma unroll
+                    for (int i = 0; i < NG4; ++i)
+                        st4(grow + lcol0 + 4 * CS * i, make_float4(out[4 * i], out[4 * i + 1], out[4 * i + 2], out[4 * i + 3]));
+                    if constexpr (TAIL) st2(grow + ltail, make_float2(out[4 * NG4], out[4 * NG4 + 1]));
+                } else {
+    #pragma unroll 1
+                    for (int i = 0; i < NG4; ++i) {
+                        const int l0 = lcol0 + 4 * CS * i;
+                        const float4 hv = ld4(hrow + l0);
+                        st4(grow + l0, make_float4(dzh_col(l0, hv.x), dzh_col(l0 + 1, hv.y), dzh_col(l0 + 2, hv.z),
+                                                   dzh_col(l0 + 3, hv.w)));
+                    }
+                    if constexpr (TAIL) {
+                        const float2 hv = ld2(hrow + ltail);
+                        st2(grow + ltail, make_float2(dzh_col(ltail, hv.x), dzh_col(ltail + 1, hv.y)));
+                    }
                 }
-                if constexpr (TAIL) {
-                    const float2 hv = ld2(hrow + ltail);
-                    st2(grow + ltail, make_float2(dzh_col(ltail, hv.x), dzh_col(ltail + 1, hv.y)));
+            }
+        }
+        return sse;
+    };
+
+    // ---------------------------------------------------------------- rows phase, quad variant (CS == 4)
+    // Same arithmetic as rows_phase with a row spread over four lanes: every lane owns the float2 pieces at
+    // columns 8j + 2*part (j < LP/8 latent pieces, 3 ETF pieces).  A quarter of the FMAs per lane, twice the
+    // warps: the latency mapping for a handful of tasks.  Rows are exchanged through the shared rows + __syncwarp.
+    auto rows_phase_quad = [&](const int* xoff, int nb, bool train, float coef) -> float {
+        constexpr int NPL = LP >= 8 ? LP / 8 : 1;  // latent float2 pieces per lane (only instantiated for LP % 8 == 0)
+        constexpr int NPE = EP / 8;                // ETF float2 pieces per lane (3)
+        float sse = 0.f;
+#pragma unroll 1
+        for (int r0 = 0; r0 < nb; r0 += ROWS) {
+            const int r = r0 + row_in_pass;
+            const bool valid = r < nb;
+            const float* xr = Xs + (valid ? xoff[r] : T * XS);
+            const int rs = valid ? r : BP;
+            float* hrow = H + rs * HS;
+            float* yrow = dZy + rs * XS;
+            float* grow = dZh + rs * HS;
+            const int c0 = 2 * part_id;            // own pieces start at column 8j + c0
+            // ---- zh pieces = x . We[:, own columns]
+            float zh[2 * NPL];
+#pragma unroll
+            for (int l = 0; l < 2 * NPL; ++l) zh[l] = 0.f;
+#pragma unroll
+            for (int e4 = 0; e4 < EP / 4; ++e4) {
+                const float4 xv = ld4(xr + 4 * e4);
+                const float xe[4] = {xv.x, xv.y, xv.z, xv.w};
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    const float* wrow = We + (4 * e4 + k) * LP + c0;
+#pragma unroll
+                    for (int j = 0; j < NPL; ++j) {
+                        const float2 w = ld2(wrow + 8 * j);
+                        zh[2 * j + 0] = fmaf(xe[k], w.x, zh[2 * j + 0]);
+                        zh[2 * j + 1] = fmaf(xe[k], w.y, zh[2 * j + 1]);
+                    }
+                }
+            }
+#pragma unroll
+            for (int j = 0; j < NPL; ++j)
+                st2(hrow + 8 * j + c0, make_float2(lrelu(zh[2 * j], alpha), lrelu(zh[2 * j + 1], alpha)));
+            __syncwarp();
+            // ---- zy pieces = h . Wd[:, own columns]
+            float zy[2 * NPE];
+#pragma unroll
+            for (int e = 0; e < 2 * NPE; ++e) zy[e] = 0.f;
+#pragma unroll
+            for (int l4 = 0; l4 < CT; ++l4) {
+                const float4 hv = ld4(hrow + 4 * l4);
+                const float hl[4] = {hv.x, hv.y, hv.z, hv.w};
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    const float* wrow = Wd + (4 * l4 + k) * WDS + c0;
+#pragma unroll
+                    for (int j = 0; j < NPE; ++j) {
+                        const float2 w = ld2(wrow + 8 * j);
+                        zy[2 * j + 0] = fmaf(hl[k], w.x, zy[2 * j + 0]);
+                        zy[2 * j + 1] = fmaf(hl[k], w.y, zy[2 * j + 1]);
+                    }
+                }
+            }
+            // ---- squared error and dLoss/dzy on the lane's columns
+#pragma unroll
+            for (int j = 0; j < NPE; ++j) {
+                const float2 xv = ld2(xr + 8 * j + c0);
+                const float xe[2] = {xv.x, xv.y};
+#pragma unroll
+                for (int k = 0; k < 2; ++k) {
+                    const float z = zy[2 * j + k];
+                    const float d = lrelu(z, alpha) - xe[k];
+                    sse = fmaf(d, d, sse);
+                    zy[2 * j + k] = lrelu_grad(z, coef * d, alpha);
+                }
+            }
+            if (train) {
+#pragma unroll
+                for (int j = 0; j < NPE; ++j) st2(yrow + 8 * j + c0, make_float2(zy[2 * j], zy[2 * j + 1]));
+                __syncwarp();
+                float dzy[EP];
+#pragma unroll
+                for (int e4 = 0; e4 < EP / 4; ++e4) {
+                    const float4 v = ld4(yrow + 4 * e4);
+                    dzy[4 * e4] = v.x; dzy[4 * e4 + 1] = v.y; dzy[4 * e4 + 2] = v.z; dzy[4 * e4 + 3] = v.w;
+                }
+                // ---- dzh pieces = (dzy . Wd[l, :]) * lrelu'(zh) for the own latent columns
+#pragma unroll
+                for (int j = 0; j < NPL; ++j) {
+                    float out[2];
+#pragma unroll
+                    for (int k = 0; k < 2; ++k) {
+                        const float* wr = Wd + (8 * j + c0 + k) * WDS;
+                        float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+#pragma unroll
+                        for (int e4 = 0; e4 < EP / 4; ++e4) {
+                            const float4 w = ld4(wr + 4 * e4);
+                            a0 = fmaf(dzy[4 * e4 + 0], w.x, a0);
+                            a1 = fmaf(dzy[4 * e4 + 1], w.y, a1);
+                            a2 = fmaf(dzy[4 * e4 + 2], w.z, a2);
+                            a3 = fmaf(dzy[4 * e4 + 3], w.w, a3);
+                        }
+                        out[k] = lrelu_grad(zh[2 * j + k], (a0 + a1) + (a2 + a3), alpha);
+                    }
+                    st2(grow + 8 * j + c0, make_float2(out[0], out[1]));
                 }
             }
         }
@@ -318,7 +542,7 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
     };
 
     // ---------------------------------------------------------------- weight-gradient phase (split-K over warps)
-    auto grads_phase = [&](int nb) {
+    auto grads_phase = [&](const int* xoff, int nb) {
         float* mypart = part + warp * NEL;
 #pragma unroll 1
         for (int t = lane; t < NT5; t += 32) {
@@ -384,12 +608,14 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
 
     // ---------------------------------------------------------------- training run
     // An epoch is a list of segments: the train mini-batches, then the validation chunks.  One loop (one
-    // call site per phase keeps the code small and the phases inlined).
+    // call site per phase keeps the code small and the phases inlined).  The row-offset table of segment
+    // s+1 is written while segment s runs (double buffer), so a train step costs three team barriers and
+    // a validation chunk one.
     const int n_fit = p.n_fit, n_val = p.n_val, batch = p.batch;
     const int n_tb = (n_fit + batch - 1) / batch, n_vb = (n_val + batch - 1) / batch, n_seg = n_tb + n_vb;
-    int step = 0, wait = 0, epochs_run = 0, st = 0;
+    int step = 0, wait = 0, epochs_run = 0, st = 0, cur = 0;
     float best = INFINITY;
-    auto set_rows = [&](int epoch, int seg) {
+    auto set_rows = [&](int* xoff, int epoch, int seg) {
         const bool val = seg >= n_tb;
         const int lo = (val ? seg - n_tb : seg) * batch;
         const int nb = min(batch, (val ? n_val : n_fit) - lo);
@@ -398,7 +624,7 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
             xoff[q] = row * XS;
         }
     };
-    set_rows(0, 0);
+    set_rows(xoff_tab, 0, 0);
     team_sync<NW>(team);
     for (int epoch = 0; epoch < p.max_epochs; ++epoch) {
         float lsum = 0.f, vsum = 0.f;
@@ -407,25 +633,46 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
             const bool train = seg < n_tb;
             const int lo = (train ? seg : seg - n_tb) * batch;
             const int nb = min(batch, (train ? n_fit : n_val) - lo);
-            const float sse = rows_phase(nb, train, 2.f / (float)(nb * E));
+            const int* xoff = xoff_tab + cur * BP;
+            int* xnext = xoff_tab + (cur ^ 1) * BP;
+            // row offsets of the next segment (next epoch's first batch after the last one)
+            if (seg + 1 < n_seg) set_rows(xnext, epoch, seg + 1);
+            else set_rows(xnext, epoch + 1 < p.max_epochs ? epoch + 1 : epoch, 0);
+            float sse = 0.f;
+            if (!(p.debug_skip & 1)) {
+                if constexpr (CS == 4) sse = rows_phase_quad(xoff, nb, train, 2.f / (float)(nb * E));
+                else sse = rows_phase(xoff, nb, train, 2.f / (float)(nb * E));
+            }
             if (train) {
                 lsum += sse;
                 team_sync<NW>(team);
-                grads_phase(nb);
+                if (!(p.debug_skip & 2)) grads_phase(xoff, nb);
                 team_sync<NW>(team);
-                update_phase(step);
+                if (!(p.debug_skip & 4)) update_phase(step);
                 ++step;
             } else {
                 vsum += sse;
-                team_sync<NW>(team);
             }
-            // row offsets of the next segment (next epoch's first batch after the last one)
-            if (seg + 1 < n_seg) set_rows(epoch, seg + 1);
-            else set_rows(epoch + 1 < p.max_epochs ? epoch + 1 : epoch, 0);
+            cur ^= 1;
             team_sync<NW>(team);
         }
-        const float loss = team_sum<NW>(lsum, red, team, tl) / (float)(E * n_fit);
-        const float val = n_val > 0 ? team_sum<NW>(vsum, red, team, tl) / (float)(E * n_val) : NAN;
+        // epoch losses: one barrier; the scratch alternates between epochs so no second barrier is needed
+        float loss, val;
+        {
+            const float l1 = warp_sum(lsum), v1 = warp_sum(vsum);
+            if constexpr (NW == 1) {
+                loss = l1; val = v1;
+            } else {
+                float* rd = red + (epoch & 1) * 32;
+                if (lane == 0) { rd[warp] = l1; rd[8 + warp] = v1; }
+                team_sync<NW>(team);
+                loss = 0.f; val = 0.f;
+#pragma unroll
+                for (int w = 0; w < NW; ++w) { loss += rd[w]; val += rd[8 + w]; }
+            }
+        }
+        loss = loss / (float)(E * n_fit);
+        val = n_val > 0 ? val / (float)(E * n_val) : NAN;
         if (tl == 0) {
             p.loss_hist[(size_t)task * p.max_epochs + epoch] = loss;
             p.val_hist[(size_t)task * p.max_epochs + epoch] = val;
@@ -489,16 +736,19 @@ static int launch_fit_packed(const FitParams& p, cudaStream_t stream) {
 //   1  one warp per task, lane pairs share a row (16 rows per pass): most work per issued instruction, for grids
 //      with thousands of tasks;
 //   3  three warps per task, lane pairs share a row (48 rows per pass = one batch): the default;
-//   4  = 3 with the k-loops fully unrolled: latency mapping for a handful of tasks (one warp per scheduler).
+//   6  six warps per task, lane quads share a row, k-loops fully unrolled: the latency mapping for a handful of
+//      tasks (LP padded to a multiple of 8).
 template <int LP>
 static int dispatch_mapping(const FitParams& p, int wpt, cudaStream_t stream) {
     if (wpt == 1) return launch_fit_packed<LP, 1, 2, 8>(p, stream);
     if (wpt == 3) return launch_fit_packed<LP, 3, 2, 2>(p, stream);
-    return launch_fit<LP, 3, 2, 1, true>(p, stream);
+    if constexpr (LP % 8 == 0) return launch_fit<LP, 6, 4, 1, true>(p, stream);
+    else return set_err(HFREP_ERR_ARG, "fit: internal: the quad mapping needs LP %% 8 == 0");
 }
 
 int fit_dispatch(const FitParams& p, int L_max, int wpt, cudaStream_t stream) {
-    const int LP = (L_max + 3) & ~3;
+    // the latency mapping (6 warps, a lane quad per row) splits the columns in float2 pieces of 8-column groups
+    const int LP = (wpt == 6) ? ((L_max + 7) & ~7) : ((L_max + 3) & ~3);
     switch (LP) {
         case 4: return dispatch_mapping<4>(p, wpt, stream);
         case 8: return dispatch_mapping<8>(p, wpt, stream);
@@ -570,13 +820,14 @@ extern "C" int hfrep_fit_batched(const hfrep_fit_cfg* c, const float* X, int n_t
     p.n_tasks = n_tasks; p.E = c->E; p.T = c->T; p.n_fit = c->n_fit; p.n_val = c->T - c->n_fit; p.batch = c->batch;
     p.BP = (c->batch + 3) & ~3; p.max_epochs = c->max_epochs; p.patience = c->patience; p.early_stop = c->early_stop;
     p.w_stride = w_stride; p.shared_x = (c->n_x == 1); p.dump_step = c->dump_step;
+    { const char* dbg = getenv("HFREP_DEBUG_SKIP"); p.debug_skip = dbg ? atoi(dbg) : 0; }
     p.alpha = c->alpha; p.lr = c->lr; p.b1 = c->beta_1; p.b2 = c->beta_2; p.eps = c->epsilon;
 
     int wpt = c->warps_per_task;
     if (wpt == 0) {                                  // pick the mapping from the amount of parallel work
         const int sms = sm_count();
-        wpt = n_tasks <= sms ? 4 : (n_tasks < 24 * sms ? 3 : 1);
+        wpt = n_tasks <= sms ? 6 : (n_tasks < 24 * sms ? 3 : 1);
     }
-    HFREP_REQUIRE(wpt == 1 || wpt == 3 || wpt == 4, "fit_batched: warps_per_task=%d (0, 1, 3 or 4)", wpt);
+    HFREP_REQUIRE(wpt == 1 || wpt == 3 || wpt == 6, "fit_batched: warps_per_task=%d (0, 1, 3 or 6)", wpt);
     return fit_dispatch(p, c->L_max, wpt, (cudaStream_t)stream);
 }

@@ -202,7 +202,7 @@ def fit_batched(X: torch.Tensor, task_L, W0: torch.Tensor, *, E: int, T: int, n_
 @dataclasses.dataclass
 class EvalResult:
     ante: torch.Tensor         # f64 [n][n_oos][F]
-    post: torch.Tensor
+    post: torch.Tensor | None  # None when no sigma was given
     turnover: torch.Tensor     # f64 [n][F]
     metrics: torch.Tensor      # f64 [n][6][F]   sharpe/te/corr of ante, then of post
     quality: torch.Tensor      # f64 [n][2+2*n_pre]
@@ -233,7 +233,7 @@ def predict_metrics(Xtr64, Xte64, Yte64, rf64, sigma, task_L, W, *, window=24, w
     tL = task_L if isinstance(task_L, torch.Tensor) else torch.from_numpy(np.asarray(task_L, np.int32)).to(device)
     f64 = dict(dtype=torch.float64, device=device)
     r = EvalResult(
-        ante=torch.empty((n, n_oos, F), **f64), post=torch.empty((n, n_oos, F), **f64),
+        ante=torch.empty((n, n_oos, F), **f64), post=torch.empty((n, n_oos, F), **f64) if sigma is not None else None,
         turnover=torch.empty((n, F), **f64), metrics=torch.empty((n, 6, F), **f64),
         quality=torch.full((n, 2 + 2 * n_pre), float("nan"), **f64),
         mask=torch.empty((n, n_oos, E), dtype=torch.uint8, device=device),
