@@ -164,7 +164,7 @@ def gpu_arm(args):
     etf, hfd, rf = synthetic_returns()
     seeds = [123 + rank * args.seeds + s for s in range(args.seeds)]
     data = hfrep.ReplicationData(etf, hfd, rf, window=WINDOW, device=dev)
-    tasks = [(L, s) for s in seeds for L in LATENTS]
+    tasks = sorted(((L, s) for s in seeds for L in LATENTS), key=lambda t: -((t[0] + 3) // 4))   # widest first
     n_tasks = len(tasks)
     w_stride = 2 * E * max(LATENTS)
     W0_host = engine.pack_weights([engine.initial_weights(s, E, L) for L, s in tasks], E, w_stride)
@@ -190,7 +190,7 @@ def gpu_arm(args):
     def e2e_step():
         """Through the public API with HOST buffers: H2D of the returns + initial kernels, D2H of the results."""
         d = hfrep.ReplicationData(etf, hfd, rf, window=WINDOW, device=dev)
-        _, fit, ev = hfrep.run_mode_r(d, LATENTS, seeds=seeds, W0=W0_host)
+        _, fit, ev = hfrep.run_mode_r(d, LATENTS, seeds=seeds, W0=W0_host)      # same widest-first task order as W0_host
         out = [t.cpu() for t in (ev.ante, ev.post, ev.turnover, ev.metrics, ev.quality, fit.epochs_run)]
         h2d = d.h2d_bytes + W0_host.nbytes
         return h2d, sum(t.numel() * t.element_size() for t in out)
@@ -277,7 +277,7 @@ def gpu_arm(args):
     ens = None
     if args.ensemble_seeds > 0:
         es = [1000 + s for s in range(args.ensemble_seeds)]
-        et = [(L, s) for s in es for L in LATENTS]
+        et = sorted(((L, s) for s in es for L in LATENTS), key=lambda t: -((t[0] + 3) // 4))
         eW0 = engine.to_device(engine.pack_weights([engine.initial_weights(s, E, L) for L, s in et], E, w_stride), dev)
         eL = [L for L, _ in et]
         times = []

@@ -30,6 +30,7 @@ struct EvalParams {
     double* ante; double* post; double* turnover; double* metrics; double* quality;
     unsigned char* mask; double* weights; double* beta; double* norm; int* status;
     int n_tasks, w_stride, E, F, T_train, T_test, window, want_oos, n_oos, n_pre, acols;
+    int qsplit;           // CTAs per task: CTA (task, part) scores prefixes part, part+qsplit, ...; part 0 also builds the replica
     int off_float;        // byte offset of the float32 region inside dynamic shared memory (16-byte aligned)
     float alpha;
     double cost_param, phi;
@@ -119,7 +120,7 @@ __device__ void block_quality(const double* x, int n, int E, int L, const double
 
 __global__ void __launch_bounds__(NTH_EVAL) eval_kernel(const EvalParams p) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    const int task = blockIdx.x;
+    const int task = blockIdx.x / p.qsplit, qpart = blockIdx.x - task * p.qsplit;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     constexpr int NW = NTH_EVAL / 32;
     const int E = p.E, F = p.F, L = p.task_L[task], window = p.window, n_oos = p.n_oos, T_test = p.T_test;
@@ -157,7 +158,7 @@ __global__ void __launch_bounds__(NTH_EVAL) eval_kernel(const EvalParams p) {
     if (p.quality) {
         double* q = p.quality + (size_t)task * (2 + 2 * p.n_pre);
         double* cs = cstat + warp * 3 * HFREP_MAX_E;
-        if (warp == 0) {
+        if (warp == 0 && qpart == 0) {
             if (lane < HFREP_MAX_E) {
                 double s = 0.;
                 if (lane < E) for (int r = 0; r < p.T_train; ++r) s += p.Xtr[(size_t)r * E + lane];
@@ -172,7 +173,7 @@ __global__ void __launch_bounds__(NTH_EVAL) eval_kernel(const EvalParams p) {
         if (p.want_oos) {
             double lo = INFINITY, hi = -INFINITY, sum = 0.;
             int seen = 0;                                         // rows [0, seen) folded into lo/hi/sum (lane = column)
-            for (int j = warp; j < p.n_pre; j += NW) {
+            for (int j = qpart * NW + warp; j < p.n_pre; j += NW * p.qsplit) {
                 const int n = j + 2;                              // prefix x_test[:n]
                 if (lane < E)
                     for (; seen < n; ++seen) {
@@ -199,6 +200,8 @@ __global__ void __launch_bounds__(NTH_EVAL) eval_kernel(const EvalParams p) {
             }
         }
     }
+
+    if (qpart != 0) return;          // the other CTAs of this task only score expanding prefixes
 
     // ---- latent factors of the raw test block, float32 (:140)
     for (int idx = tid; idx < T_test * WS; idx += NTH_EVAL) {
@@ -466,7 +469,13 @@ extern "C" int hfrep_predict_metrics(const hfrep_eval_cfg* c, const double* Xtr,
     HFREP_REQUIRE(smem <= 227 * 1024, "predict_metrics: %zu bytes of shared memory needed (T_test=%d too long)", smem,
                   c->T_test);
     HFREP_CUDA_OK(cudaFuncSetAttribute(eval_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    eval_kernel<<<n_tasks, NTH_EVAL, smem, (cudaStream_t)stream>>>(p);
+    // few tasks: spread each task's 167 expanding-prefix evaluations over several CTAs so the whole GPU works
+    p.qsplit = 1;
+    if (quality && c->want_oos) {
+        const int sms = sm_count();
+        while (p.qsplit < 16 && n_tasks * p.qsplit * 2 <= 2 * sms) p.qsplit *= 2;
+    }
+    eval_kernel<<<n_tasks * p.qsplit, NTH_EVAL, smem, (cudaStream_t)stream>>>(p);
     HFREP_CUDA_OK(cudaGetLastError());
     return HFREP_OK;
 }

@@ -123,6 +123,19 @@ class FitResult:
 
 
 _SIDE_STREAMS: dict = {}
+_INT_CACHE: dict = {}
+
+
+def _device_ints(a: np.ndarray, device) -> torch.Tensor:
+    """Small int32 task tables live on the device once per distinct content (sweeps reuse them every step)."""
+    key = (str(device), a.tobytes())
+    t = _INT_CACHE.get(key)
+    if t is None:
+        if len(_INT_CACHE) > 64:
+            _INT_CACHE.clear()
+        t = torch.from_numpy(np.ascontiguousarray(a, np.int32)).to(device)
+        _INT_CACHE[key] = t
+    return t
 
 
 def _side_streams(device, n):
@@ -158,12 +171,16 @@ def fit_batched(X: torch.Tensor, task_L, W0: torch.Tensor, *, E: int, T: int, n_
     inv = np.empty(n, np.int64)
     inv[order] = np.arange(n)
     L_sorted = task_L[order]
-    order_t = torch.from_numpy(order).to(device)
-    tL = torch.from_numpy(L_sorted).to(device)
-    W0s = W0.index_select(0, order_t).contiguous()
-    tx = task_x.index_select(0, order_t).contiguous() if task_x is not None else None
+    identity = bool(np.array_equal(order, np.arange(n)))      # already widest-first: no gather / scatter needed
+    tL = _device_ints(L_sorted, device)
     per_task_perm = perm is not None and perm.dim() == 3
-    perms = perm.index_select(0, order_t).contiguous() if per_task_perm else perm
+    if identity:
+        W0s, tx, perms = W0.contiguous(), task_x, perm
+    else:
+        order_t = torch.from_numpy(order).to(device)
+        W0s = W0.index_select(0, order_t).contiguous()
+        tx = task_x.index_select(0, order_t).contiguous() if task_x is not None else None
+        perms = perm.index_select(0, order_t).contiguous() if per_task_perm else perm
     perm_stride = perms.shape[1] * perms.shape[2] if per_task_perm else 0
 
     W_out = torch.zeros_like(W0s)          # rows are packed with each task's own L; the tail stays zero
@@ -194,8 +211,11 @@ def fit_batched(X: torch.Tensor, task_L, W0: torch.Tensor, *, E: int, T: int, n_
             done = torch.cuda.Event()
             done.record(s)
             main.wait_event(done)
-    inv_t = torch.from_numpy(inv).to(device)
-    sel = lambda t: None if t is None else t.index_select(0, inv_t)
+    if identity:
+        sel = lambda t: t
+    else:
+        inv_t = torch.from_numpy(inv).to(device)
+        sel = lambda t: None if t is None else t.index_select(0, inv_t)
     return FitResult(sel(W_out), sel(loss), sel(val), sel(epochs_run), sel(status), sel(grads), w_stride)
 
 
@@ -230,7 +250,7 @@ def predict_metrics(Xtr64, Xte64, Yte64, rf64, sigma, task_L, W, *, window=24, w
     cfg = _lib.eval_cfg(E=E, F=F, T_train=Xtr64.shape[0], T_test=T_test, window=window,
                         want_oos=int(want_oos), alpha=alpha, cost_param=cost_param, phi=phi)
     n_oos, n_pre = T_test - window - 1, T_test - 2
-    tL = task_L if isinstance(task_L, torch.Tensor) else torch.from_numpy(np.asarray(task_L, np.int32)).to(device)
+    tL = task_L if isinstance(task_L, torch.Tensor) else _device_ints(np.asarray(task_L, np.int32), device)
     f64 = dict(dtype=torch.float64, device=device)
     r = EvalResult(
         ante=torch.empty((n, n_oos, F), **f64), post=torch.empty((n, n_oos, F), **f64) if sigma is not None else None,
@@ -293,7 +313,8 @@ def run_mode_r(data: ReplicationData, latent_dims, seeds=(123,), *, W0=None, per
     """The notebook's sweep (autoencoder_v4.ipynb:158-165, :896-901) as one batched GPU pass:
     for every (L, seed): fit, IS/OOS quality, ante, turnover, post, metrics.
     Returns (tasks, FitResult, EvalResult); tasks[i] = (L, seed)."""
-    tasks = [(int(L), int(s)) for s in seeds for L in latent_dims]
+    # widest (slowest) tasks first: that is the launch order of the width buckets, and it spares a gather
+    tasks = sorted(((int(L), int(s)) for s in seeds for L in latent_dims), key=lambda t: -((t[0] + 3) // 4))
     E = data.E
     L_max = max(L for L, _ in tasks)
     w_stride = 2 * E * L_max

@@ -106,9 +106,10 @@ def test_mode_r_end_to_end(hf, data, ref_inputs):
     """Fit + evaluation in one pass (three widths at once, bucketed launches) vs the reference runs."""
     gs = {L: load_golden(f"ref_modeR_L{L}") for L in (2, 8, 21)}
     E = data.E
-    W0 = hf.engine.pack_weights([(gs[L]["We0"], gs[L]["Wd0"]) for L in (2, 8, 21)], E, 2 * E * 21)
-    tasks, fit, ev = hf.run_mode_r(data, [2, 8, 21], seeds=(123,), W0=W0)
-    for i, L in enumerate((2, 8, 21)):
+    W0 = hf.engine.pack_weights([(gs[L]["We0"], gs[L]["Wd0"]) for L in (21, 8, 2)], E, 2 * E * 21)
+    tasks, fit, ev = hf.run_mode_r(data, [21, 8, 2], seeds=(123,), W0=W0)
+    assert [L for L, _ in tasks] == [21, 8, 2]
+    for i, L in enumerate((21, 8, 2)):
         g = gs[L]
         assert int(fit.epochs_run[i]) == 1000
         assert rel_err(ev.ante[i].cpu().numpy(), g["ante"]) < TOL
@@ -119,7 +120,7 @@ def test_mode_r_end_to_end(hf, data, ref_inputs):
     from oracle import ae_oracle
     rf_oos = ref_inputs["rf"].reshape(-1)[-144:]
     hfd_oos = ref_inputs["hfd"][-144:]
-    m = ev.metrics[1].cpu().numpy()
+    m = ev.metrics[[L for L, _ in tasks].index(8)].cpu().numpy()
     for f in range(13):
         assert abs(m[0, f] - ae_oracle.annualized_sharpe_ratio(gs[8]["ante"][:, f], rf_oos)) < 1e-5 * abs(m[0, f]) + 1e-9
         assert abs(m[1, f] - ae_oracle.tracking_error(gs[8]["ante"][:, f], hfd_oos[:, f])) < 1e-5 * m[1, f]
@@ -191,8 +192,8 @@ def test_full_size_grid_properties(hf, data):
     tasks2, fit2, ev2 = hf.run_mode_r(data, Ls, seeds=seeds, max_epochs=60, early_stop=0, want_oos=False)
     assert torch.equal(fit.W, fit2.W) and torch.equal(ev.ante, ev2.ante)
     # a 3-task call containing the same (L, seed) pairs must reproduce the big batch (other mapping: 4 warps/task)
-    pick = [tasks.index((L, 150)) for L in (4, 9, 21)]
-    _, fit3, ev3 = hf.run_mode_r(data, [4, 9, 21], seeds=(150,), max_epochs=60, early_stop=0, want_oos=False)
+    tasks3, fit3, ev3 = hf.run_mode_r(data, [4, 9, 21], seeds=(150,), max_epochs=60, early_stop=0, want_oos=False)
+    pick = [tasks.index(t3) for t3 in tasks3]
     for j, i in enumerate(pick):
         assert rel_err(fit3.loss[j, :60].cpu().numpy(), fit.loss[i, :60].cpu().numpy()) < TOL
         assert rel_err(ev3.ante[j].cpu().numpy(), ev.ante[i].cpu().numpy()) < 1e-4
