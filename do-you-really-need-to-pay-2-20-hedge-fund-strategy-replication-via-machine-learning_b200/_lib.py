@@ -37,7 +37,7 @@ class EvalCfg(C.Structure):
 
 
 EXPORTS = ("hfrep_last_error", "hfrep_version", "hfrep_window_index", "hfrep_window_gather",
-           "hfrep_rolling_sigma", "hfrep_fit_cfg_default", "hfrep_nadam_schedule", "hfrep_fit_batched",
+           "hfrep_rolling_sigma", "hfrep_fit_cfg_default", "hfrep_nadam_schedule", "hfrep_fit_batched", "hfrep_fit_windows_workspace", "hfrep_fit_windows",
            "hfrep_eval_cfg_default", "hfrep_predict_metrics", "hfrep_series_metrics", "hfrep_ex_post_return", "hfrep_forward",
            "hfrep_ffma_peak")
 
@@ -61,17 +61,21 @@ def _load():
     lib.hfrep_nadam_schedule.argtypes = [C.POINTER(FitCfg), C.c_int, vp]
     lib.hfrep_fit_batched.argtypes = [C.POINTER(FitCfg), vp, C.c_int, vp, vp, vp, C.c_int, vp, i64, vp, vp, vp, vp,
                                       vp, vp, vp, vp]
+    lib.hfrep_fit_windows_workspace.argtypes = [C.c_int, C.c_int, C.c_int]
+    lib.hfrep_fit_windows.argtypes = [C.POINTER(FitCfg), vp, C.c_int, C.c_int, C.c_int, vp, C.c_int, C.c_int, vp, vp, vp,
+                                      C.c_int, vp, i64, vp, vp, C.c_size_t, vp, vp, vp, vp, vp, vp]
     lib.hfrep_eval_cfg_default.argtypes = [C.POINTER(EvalCfg)]
     lib.hfrep_eval_cfg_default.restype = None
-    lib.hfrep_predict_metrics.argtypes = [C.POINTER(EvalCfg), vp, vp, vp, vp, vp, C.c_int, vp, vp, C.c_int] + [vp] * 11
+    lib.hfrep_predict_metrics.argtypes = [C.POINTER(EvalCfg), vp, vp, vp, vp, vp, C.c_int, vp, vp, vp, C.c_int] + [vp] * 11
     lib.hfrep_series_metrics.argtypes = [vp, vp, vp, C.c_int, C.c_int, vp, vp]
     lib.hfrep_ex_post_return.argtypes = [vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_double, C.c_double, vp, vp]
     lib.hfrep_forward.argtypes = [vp, C.c_int, C.c_int, vp, C.c_int, C.c_int, C.c_float, vp, vp]
     lib.hfrep_ffma_peak.argtypes = [C.c_int, vp, C.POINTER(C.c_double), vp]
     for name in EXPORTS:
         fn = getattr(lib, name)
-        if name not in ("hfrep_last_error", "hfrep_fit_cfg_default", "hfrep_eval_cfg_default"):
+        if name not in ("hfrep_last_error", "hfrep_fit_cfg_default", "hfrep_eval_cfg_default", "hfrep_fit_windows_workspace"):
             fn.restype = C.c_int
+    lib.hfrep_fit_windows_workspace.restype = C.c_size_t
     return lib
 
 

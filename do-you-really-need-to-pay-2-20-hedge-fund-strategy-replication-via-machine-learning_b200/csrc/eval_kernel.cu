@@ -26,7 +26,7 @@ constexpr int WS = 24;            // stride of We / Wd / M rows in shared memory
 
 struct EvalParams {
     const double* Xtr; const double* Xte; const double* Yte; const double* rf; const double* sigma;
-    const int* task_L; const float* W;
+    const int* task_L; const int* task_row0; const float* W;
     double* ante; double* post; double* turnover; double* metrics; double* quality;
     unsigned char* mask; double* weights; double* beta; double* norm; int* status;
     int n_tasks, w_stride, E, F, T_train, T_test, window, want_oos, n_oos, n_pre, acols;
@@ -125,6 +125,11 @@ __global__ void __launch_bounds__(NTH_EVAL) eval_kernel(const EvalParams p) {
     constexpr int NW = NTH_EVAL / 32;
     const int E = p.E, F = p.F, L = p.task_L[task], window = p.window, n_oos = p.n_oos, T_test = p.T_test;
     const float alpha = p.alpha;
+    // rolling refit: every task evaluates its own T_test rows of the full matrices, starting at task_row0[task]
+    const int row0 = p.task_row0 ? p.task_row0[task] : 0;
+    const double* Xte = p.Xte + (size_t)row0 * E;
+    const double* Yte = p.Yte + (size_t)row0 * F;
+    const double* rfv = p.rf + row0;
 
     // ---- shared memory carve-up (doubles first)
     double* A = reinterpret_cast<double*>(smem_raw);              // [window][acols]  QR workspace [M_w | Y_w]
@@ -177,7 +182,7 @@ __global__ void __launch_bounds__(NTH_EVAL) eval_kernel(const EvalParams p) {
                 const int n = j + 2;                              // prefix x_test[:n]
                 if (lane < E)
                     for (; seen < n; ++seen) {
-                        const double v = p.Xte[(size_t)seen * E + lane];
+                        const double v = Xte[(size_t)seen * E + lane];
                         lo = fmin(lo, v); hi = fmax(hi, v); sum += v;
                     }
                 seen = n;
@@ -194,7 +199,7 @@ __global__ void __launch_bounds__(NTH_EVAL) eval_kernel(const EvalParams p) {
                 }
                 __syncwarp();
                 double r2, rmse;
-                block_quality(p.Xte, n, E, L, cs, We, Wd, alpha, lane, r2, rmse);
+                block_quality(Xte, n, E, L, cs, We, Wd, alpha, lane, r2, rmse);
                 if (lane == 0) { q[2 + j] = r2; q[2 + p.n_pre + j] = rmse; }
                 __syncwarp();
             }
@@ -208,7 +213,7 @@ __global__ void __launch_bounds__(NTH_EVAL) eval_kernel(const EvalParams p) {
         const int r = idx / WS, l = idx - r * WS;
         float acc = 0.f;
         if (l < L)
-            for (int e = 0; e < E; ++e) acc = fmaf((float)p.Xte[(size_t)r * E + e], We[e * WS + l], acc);
+            for (int e = 0; e < E; ++e) acc = fmaf((float)Xte[(size_t)r * E + e], We[e * WS + l], acc);
         M[idx] = lrelu(acc, alpha);
     }
     __syncthreads();
@@ -226,7 +231,7 @@ __global__ void __launch_bounds__(NTH_EVAL) eval_kernel(const EvalParams p) {
     if (warp == 0) {
         for (int idx = lane; idx < window * ncol; idx += 32) {
             const int r = idx / ncol, c = idx - r * ncol;
-            A[r * p.acols + c] = c < L ? (double)M[r * WS + c] : p.Yte[(size_t)r * F + (c - L)];
+            A[r * p.acols + c] = c < L ? (double)M[r * WS + c] : Yte[(size_t)r * F + (c - L)];
         }
         __syncwarp();
         double dmax = 0., dmin = INFINITY;
@@ -271,14 +276,14 @@ __global__ void __launch_bounds__(NTH_EVAL) eval_kernel(const EvalParams p) {
             for (int r = 0; r < window; ++r) {
                 double rh = 0.;
                 for (int l = 0; l < L; ++l) rh += (double)M[r * WS + l] * betaS[l * F + f];
-                mr += rh; my += p.Yte[(size_t)r * F + f];
+                mr += rh; my += Yte[(size_t)r * F + f];
             }
             mr /= window; my /= window;
             double vr = 0., vy = 0.;
             for (int r = 0; r < window; ++r) {
                 double rh = 0.;
                 for (int l = 0; l < L; ++l) rh += (double)M[r * WS + l] * betaS[l * F + f];
-                const double dy = p.Yte[(size_t)r * F + f] - my;
+                const double dy = Yte[(size_t)r * F + f] - my;
                 vr += (rh - mr) * (rh - mr) / (window - 1);
                 vy += dy * dy / (window - 1);
             }
@@ -307,7 +312,7 @@ __global__ void __launch_bounds__(NTH_EVAL) eval_kernel(const EvalParams p) {
             const double g = G[f * E + e];
             const double wk = g * (maskS[k * E + e] ? .2 : 1.) * nf;
             sumw += wk;
-            dot += p.Xte[(size_t)row * E + e] * wk;
+            dot += Xte[(size_t)row * E + e] * wk;
             if (p.weights) p.weights[(((size_t)task * n_oos + k) * E + e) * F + f] = wk;
             if (k >= 1 && p.sigma) {                              // transaction_cost + price_impact, helper.py:65-92
                 const double old = g * (maskS[(k - 1) * E + e] ? .2 : 1.) * nf;
@@ -322,7 +327,7 @@ __global__ void __launch_bounds__(NTH_EVAL) eval_kernel(const EvalParams p) {
                 dabs += fabs(wk - nxt);
             }
         }
-        const double a = (1. - sumw) * p.rf[row] + dot;
+        const double a = (1. - sumw) * rfv[row] + dot;
         anteS[idx] = a;
         postS[idx] = a + pen;                                     // post[0] = ante[0] (pen = 0)
         turnS[idx] = dabs;
@@ -338,7 +343,7 @@ __global__ void __launch_bounds__(NTH_EVAL) eval_kernel(const EvalParams p) {
     if (p.norm) for (int idx = tid; idx < F; idx += NTH_EVAL) p.norm[(size_t)task * F + idx] = normS[idx];
 
     double rfm = 0.;
-    for (int k = lane; k < n_oos; k += 32) rfm += p.rf[window + 1 + k];
+    for (int k = lane; k < n_oos; k += 32) rfm += rfv[window + 1 + k];
     rfm = warp_sum(rfm) / n_oos;
     for (int f = warp; f < F; f += NW) {
         double ts = 0.;
@@ -350,11 +355,11 @@ __global__ void __launch_bounds__(NTH_EVAL) eval_kernel(const EvalParams p) {
             for (int which = 0; which < 2; ++which) {
                 const double* s = which ? postS : anteS;
                 double sr = 0., sy = 0.;
-                for (int k = lane; k < n_oos; k += 32) { sr += s[k * F + f]; sy += p.Yte[(size_t)(window + 1 + k) * F + f]; }
+                for (int k = lane; k < n_oos; k += 32) { sr += s[k * F + f]; sy += Yte[(size_t)(window + 1 + k) * F + f]; }
                 const double mr = warp_sum(sr) / n_oos, my = warp_sum(sy) / n_oos;
                 double vrr = 0., vyy = 0., vry = 0., sd = 0.;
                 for (int k = lane; k < n_oos; k += 32) {
-                    const double a = s[k * F + f] - mr, b = p.Yte[(size_t)(window + 1 + k) * F + f] - my;
+                    const double a = s[k * F + f] - mr, b = Yte[(size_t)(window + 1 + k) * F + f] - my;
                     vrr += a * a; vyy += b * b; vry += a * b; sd += (a - b) * (a - b);
                 }
                 vrr = warp_sum(vrr); vyy = warp_sum(vyy); vry = warp_sum(vry); sd = warp_sum(sd);
@@ -436,7 +441,7 @@ extern "C" void hfrep_eval_cfg_default(hfrep_eval_cfg* c) {
 
 extern "C" int hfrep_predict_metrics(const hfrep_eval_cfg* c, const double* Xtr, const double* Xte, const double* Yte,
                                      const double* rf, const double* sigma, int n_tasks, const int32_t* task_L,
-                                     const float* W, int w_stride, double* ante, double* post, double* turnover,
+                                     const int32_t* task_row0, const float* W, int w_stride, double* ante, double* post, double* turnover,
                                      double* metrics, double* quality, uint8_t* mask, double* weights, double* beta,
                                      double* norm, int32_t* status, void* stream) {
     HFREP_REQUIRE(c && Xte && Yte && rf && task_L && W, "predict_metrics: null argument");
@@ -452,7 +457,7 @@ extern "C" int hfrep_predict_metrics(const hfrep_eval_cfg* c, const double* Xtr,
     HFREP_REQUIRE(!(post) || sigma, "predict_metrics: post needs sigma");
 
     EvalParams p;
-    p.Xtr = Xtr; p.Xte = Xte; p.Yte = Yte; p.rf = rf; p.sigma = sigma; p.task_L = task_L; p.W = W;
+    p.Xtr = Xtr; p.Xte = Xte; p.Yte = Yte; p.rf = rf; p.sigma = sigma; p.task_L = task_L; p.task_row0 = task_row0; p.W = W;
     p.ante = ante; p.post = post; p.turnover = turnover; p.metrics = metrics; p.quality = quality; p.mask = mask;
     p.weights = weights; p.beta = beta; p.norm = norm; p.status = status;
     p.n_tasks = n_tasks; p.w_stride = w_stride; p.E = c->E; p.F = c->F; p.T_train = c->T_train; p.T_test = c->T_test;

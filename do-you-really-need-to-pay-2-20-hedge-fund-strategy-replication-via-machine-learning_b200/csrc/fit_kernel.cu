@@ -794,7 +794,7 @@ extern "C" int hfrep_nadam_schedule(const hfrep_fit_cfg* c, int n_steps, float* 
     return HFREP_OK;
 }
 
-extern "C" int hfrep_fit_batched(const hfrep_fit_cfg* c, const float* X, int n_tasks, const int32_t* task_L,
+static int fit_batched_impl(const hfrep_fit_cfg* c, const float* X, int n_tasks, const int32_t* task_L,
                                  const int32_t* task_x, const float* W0, int w_stride, const int32_t* perm,
                                  int64_t perm_task_stride, const float* sched, float* W_out, float* loss_hist,
                                  float* val_hist, int32_t* epochs_run, int32_t* status, float* grad_out,
@@ -830,4 +830,40 @@ extern "C" int hfrep_fit_batched(const hfrep_fit_cfg* c, const float* X, int n_t
     }
     HFREP_REQUIRE(wpt == 1 || wpt == 3 || wpt == 6, "fit_batched: warps_per_task=%d (0, 1, 3 or 6)", wpt);
     return fit_dispatch(p, c->L_max, wpt, (cudaStream_t)stream);
+}
+
+extern "C" int hfrep_fit_batched(const hfrep_fit_cfg* c, const float* X, int n_tasks, const int32_t* task_L,
+                                 const int32_t* task_x, const float* W0, int w_stride, const int32_t* perm,
+                                 int64_t perm_task_stride, const float* sched, float* W_out, float* loss_hist,
+                                 float* val_hist, int32_t* epochs_run, int32_t* status, float* grad_out,
+                                 void* stream) {
+    return fit_batched_impl(c, X, n_tasks, task_L, task_x, W0, w_stride, perm, perm_task_stride, sched, W_out, loss_hist,
+                            val_hist, epochs_run, status, grad_out, stream);
+}
+
+// Rolling refit (Mode W): kernel (a) builds every window's MinMax-scaled training block into the caller's workspace,
+// kernel (b) fits the tasks on them.
+extern "C" size_t hfrep_fit_windows_workspace(int n_windows, int T_win, int E) {
+    if (n_windows <= 0 || T_win <= 0 || E <= 0) return 0;
+    return sizeof(float) * (size_t)n_windows * T_win * E;
+}
+
+extern "C" int hfrep_fit_windows(const hfrep_fit_cfg* c, const float* R, int T_all, int C, int col_lo,
+                                 const int32_t* win_starts, int n_windows, int n_tasks, const int32_t* task_L,
+                                 const int32_t* task_win, const float* W0, int w_stride, const int32_t* perm,
+                                 int64_t perm_task_stride, const float* sched, void* ws, size_t ws_bytes, float* W_out,
+                                 float* loss_hist, float* val_hist, int32_t* epochs_run, int32_t* status, void* stream) {
+    HFREP_REQUIRE(c && R && win_starts && task_win, "fit_windows: null argument");
+    HFREP_REQUIRE(n_windows >= 1, "fit_windows: n_windows=%d", n_windows);
+    const size_t need = hfrep_fit_windows_workspace(n_windows, c->T, c->E);
+    HFREP_REQUIRE(ws && ws_bytes >= need, "fit_windows: workspace of %zu bytes needed, %zu given", need, ws_bytes);
+    HFREP_REQUIRE(((uintptr_t)ws & 15) == 0, "fit_windows: workspace must be 16-byte aligned");
+    float* blocks = static_cast<float*>(ws);
+    int rc = launch_window_gather(R, T_all, C, win_starts, n_windows, c->T, col_lo, c->E, /*minmax=*/1, blocks,
+                                  (cudaStream_t)stream);
+    if (rc != HFREP_OK) return rc;
+    hfrep_fit_cfg cc = *c;
+    cc.n_x = n_windows > 1 ? n_windows : 2;          // every task trains on its own block: one team per CTA
+    return fit_batched_impl(&cc, blocks, n_tasks, task_L, task_win, W0, w_stride, perm, perm_task_stride, sched, W_out,
+                            loss_hist, val_hist, epochs_run, status, nullptr, stream);
 }

@@ -110,8 +110,9 @@ __global__ void __launch_bounds__(256) ffma_peak_kernel(int iters, float* sink) 
 
 using namespace hfrep;
 
-extern "C" int hfrep_window_gather(const float* R, int T, int C, const int32_t* starts, int n, int len, int col_lo,
-                                   int ncols, int minmax, float* out, void* stream) {
+namespace hfrep {
+int launch_window_gather(const float* R, int T, int C, const int32_t* starts, int n, int len, int col_lo, int ncols,
+                         int minmax, float* out, cudaStream_t stream) {
     HFREP_REQUIRE(n >= 0 && len >= 0, "window_gather: n=%d len=%d", n, len);
     if (n == 0 || len == 0) return HFREP_OK;             // empty batch: nothing to read or write
     HFREP_REQUIRE(R && starts && out, "window_gather: null argument");
@@ -124,9 +125,15 @@ extern "C" int hfrep_window_gather(const float* R, int T, int C, const int32_t* 
     HFREP_REQUIRE(smem <= 48 * 1024, "window_gather: ncols=%d too wide for the minmax path", ncols);
     const int sms = sm_count();
     const int grid = n < 8 * sms ? n : 8 * sms;      // whole multiples of the SM count once there is enough work
-    window_gather_kernel<<<grid, 256, smem, (cudaStream_t)stream>>>(R, C, starts, n, len, col_lo, ncols, minmax, vec4, out);
+    window_gather_kernel<<<grid, 256, smem, stream>>>(R, C, starts, n, len, col_lo, ncols, minmax, vec4, out);
     HFREP_CUDA_OK(cudaGetLastError());
     return HFREP_OK;
+}
+}  // namespace hfrep
+
+extern "C" int hfrep_window_gather(const float* R, int T, int C, const int32_t* starts, int n, int len, int col_lo,
+                                   int ncols, int minmax, float* out, void* stream) {
+    return launch_window_gather(R, T, C, starts, n, len, col_lo, ncols, minmax, out, (cudaStream_t)stream);
 }
 
 extern "C" int hfrep_rolling_sigma(const double* R, int T, int E, const int32_t* starts, int n, int window,

@@ -241,13 +241,15 @@ def rolling_sigma(R64: torch.Tensor, starts: torch.Tensor, window: int) -> torch
 
 
 def predict_metrics(Xtr64, Xte64, Yte64, rf64, sigma, task_L, W, *, window=24, want_oos=True,
-                    want_weights=False, alpha=.2, cost_param=.05, phi=.5) -> EvalResult:
+                    want_weights=False, alpha=.2, cost_param=.05, phi=.5, task_row0=None, T_test=None,
+                    want_quality=True) -> EvalResult:
     """Kernel (c) for a batch of trained tasks (all tensors on the device, float64 unless noted)."""
     device = Xte64.device
     n = len(task_L)
-    T_test, E = Xte64.shape
+    E = Xte64.shape[1]
+    T_test = Xte64.shape[0] if T_test is None else T_test      # rolling refit: rows per task, not the history
     F = Yte64.shape[1]
-    cfg = _lib.eval_cfg(E=E, F=F, T_train=Xtr64.shape[0], T_test=T_test, window=window,
+    cfg = _lib.eval_cfg(E=E, F=F, T_train=(Xtr64.shape[0] if Xtr64 is not None else 0), T_test=T_test, window=window,
                         want_oos=int(want_oos), alpha=alpha, cost_param=cost_param, phi=phi)
     n_oos, n_pre = T_test - window - 1, T_test - 2
     tL = task_L if isinstance(task_L, torch.Tensor) else _device_ints(np.asarray(task_L, np.int32), device)
@@ -255,13 +257,13 @@ def predict_metrics(Xtr64, Xte64, Yte64, rf64, sigma, task_L, W, *, window=24, w
     r = EvalResult(
         ante=torch.empty((n, n_oos, F), **f64), post=torch.empty((n, n_oos, F), **f64) if sigma is not None else None,
         turnover=torch.empty((n, F), **f64), metrics=torch.empty((n, 6, F), **f64),
-        quality=torch.full((n, 2 + 2 * n_pre), float("nan"), **f64),
+        quality=torch.full((n, 2 + 2 * n_pre), float("nan"), **f64) if want_quality else None,
         mask=torch.empty((n, n_oos, E), dtype=torch.uint8, device=device),
         beta=torch.empty((n, _lib.MAX_L, F), **f64), norm=torch.empty((n, F), **f64),
         status=torch.zeros(n, dtype=torch.int32, device=device),
         weights=torch.empty((n, n_oos, E, F), **f64) if want_weights else None)
     check(lib.hfrep_predict_metrics(
-        C.byref(cfg), ptr(Xtr64), ptr(Xte64), ptr(Yte64), ptr(rf64), ptr(sigma), n, ptr(tL), ptr(W), W.shape[1],
+        C.byref(cfg), ptr(Xtr64), ptr(Xte64), ptr(Yte64), ptr(rf64), ptr(sigma), n, ptr(tL), ptr(task_row0), ptr(W), W.shape[1],
         ptr(r.ante), ptr(r.post), ptr(r.turnover), ptr(r.metrics), ptr(r.quality), ptr(r.mask), ptr(r.weights),
         ptr(r.beta), ptr(r.norm), ptr(r.status), stream_ptr()))
     return r
@@ -330,3 +332,67 @@ def run_mode_r(data: ReplicationData, latent_dims, seeds=(123,), *, W0=None, per
                              window=data.window, want_oos=want_oos, want_weights=want_weights,
                              alpha=fit_kw.get("alpha", .2))
     return tasks, fit, ev
+
+
+# ------------------------------------------------------------------------------------ Mode W front-end
+def fit_windows(R32: torch.Tensor, win_starts, T_win: int, task_L, task_win, W0: torch.Tensor, *, E: int, col_lo: int = 0,
+                perm: torch.Tensor | None = None, warps_per_task: int = 0, **cfg_kw):
+    """hfrep_fit_windows: kernel (a) gathers + MinMax-scales every training window into a scratch buffer, kernel (b)
+    fits task i on window task_win[i].  Returns (FitResult, scratch blocks f32 [n_windows][T_win][E])."""
+    device = R32.device
+    T_all, Cc = R32.shape
+    task_L = np.asarray(task_L, np.int32)
+    n = len(task_L)
+    n_fit = int(np.floor(T_win * .75))
+    cfg = _lib.fit_cfg(E=E, T=T_win, n_fit=n_fit, L_max=int(task_L.max()), warps_per_task=warps_per_task, **cfg_kw)
+    steps = cfg.max_epochs * ((n_fit + cfg.batch - 1) // cfg.batch)
+    sched = nadam_schedule(cfg, steps, device)
+    starts = _device_ints(np.asarray(win_starts, np.int32), device)
+    n_win = len(starts)
+    ws_bytes = lib.hfrep_fit_windows_workspace(n_win, T_win, E)
+    ws = torch.empty(ws_bytes // 4, dtype=torch.float32, device=device)
+    tL, tw = _device_ints(task_L, device), _device_ints(np.asarray(task_win, np.int32), device)
+    W_out = torch.zeros_like(W0)
+    loss = torch.full((n, cfg.max_epochs), float("nan"), dtype=torch.float32, device=device)
+    val = torch.full((n, cfg.max_epochs), float("nan"), dtype=torch.float32, device=device)
+    epochs_run = torch.zeros(n, dtype=torch.int32, device=device)
+    status = torch.zeros(n, dtype=torch.int32, device=device)
+    per_task_perm = perm is not None and perm.dim() == 3
+    check(lib.hfrep_fit_windows(C.byref(cfg), ptr(R32), T_all, Cc, col_lo, ptr(starts), n_win, n, ptr(tL), ptr(tw),
+                                ptr(W0), W0.shape[1], ptr(perm), perm.shape[1] * perm.shape[2] if per_task_perm else 0,
+                                ptr(sched), ptr(ws), ws_bytes, ptr(W_out), ptr(loss), ptr(val), ptr(epochs_run),
+                                ptr(status), stream_ptr()))
+    return FitResult(W_out, loss, val, epochs_run, status, None, W0.shape[1]), ws.view(n_win, T_win, E)
+
+
+def run_mode_w(etf, hfd, rf, *, train_window: int, latent_dim: int, seeds=(123,), ols_window: int = 24, device=None,
+               W0=None, **fit_kw):
+    """Rolling refit (north_star's per-(window, seed) task; SURVEY §8d Mode W — an extension, the reference fits once):
+    for t = train_window .. T-2 fit the autoencoder on rows [t-train_window, t) (MinMax on those rows, 75/25 split),
+    then follow the reference's own alignment (Autoencoder_encapsulate.py:149-150,164,183): OLS on rows [t-ols_window, t),
+    mask from row t, replica for row t+1.  Returns dict(t, replica [seed][window][F], weights, fit)."""
+    dev = _dev(device)
+    etf = np.asarray(etf, np.float64)
+    hfd = np.asarray(hfd, np.float64)
+    rf = np.asarray(rf, np.float64).reshape(-1)
+    T, E = etf.shape
+    assert train_window >= ols_window and T >= train_window + 2
+    ts = np.arange(train_window, T - 1)
+    n_win = len(ts)
+    tasks = [(wi, int(s)) for s in seeds for wi in range(n_win)]
+    task_L = [latent_dim] * len(tasks)
+    w_stride = 2 * E * latent_dim
+    with torch.cuda.device(dev):
+        R32 = to_device(etf.astype(np.float32), dev)
+        if W0 is None:
+            W0 = pack_weights([initial_weights(s * 100003 + wi, E, latent_dim) for wi, s in tasks], E, w_stride)
+        W0d = to_device(np.asarray(W0, np.float32), dev)
+        fit, blocks = fit_windows(R32, ts - train_window, train_window, task_L, [wi for wi, _ in tasks], W0d, E=E, **fit_kw)
+        row0 = _device_ints((ts - ols_window)[[wi for wi, _ in tasks]].astype(np.int32), dev)
+        ev = predict_metrics(None, to_device(etf, dev), to_device(hfd, dev), to_device(rf, dev), None, task_L, fit.W,
+                             window=ols_window, want_oos=False, want_quality=False, want_weights=True,
+                             task_row0=row0, T_test=ols_window + 2, alpha=fit_kw.get("alpha", .2))
+        F = hfd.shape[1]
+        replica = ev.ante.view(len(seeds), n_win, F)
+        weights = ev.weights.view(len(seeds), n_win, E, F)
+    return dict(t=ts, replica=replica, weights=weights, fit=fit, eval=ev, blocks=blocks, tasks=tasks)

@@ -108,6 +108,18 @@ int hfrep_fit_batched(const hfrep_fit_cfg* cfg, const float* X, int n_tasks, con
                       int64_t perm_task_stride, const float* sched, float* W_out, float* loss_hist,
                       float* val_hist, int32_t* epochs_run, int32_t* status, float* grad_out, void* stream);
 
+/* Rolling refit (the north_star's per-window task; SURVEY §8d "Mode W", not in the reference): task i trains on the
+ * window R[win_starts[task_win[i]] .. +cfg->T)[col_lo .. col_lo+cfg->E), MinMax-scaled per window exactly as
+ * AE.__init__ scales its training half (Autoencoder_encapsulate.py:62-65).  Kernel (a) writes the scaled blocks
+ * into the caller's workspace `ws` (f32 [n_windows][cfg->T][cfg->E], size from hfrep_fit_windows_workspace, 16-byte
+ * aligned), kernel (b) fits on them.  Other arguments as hfrep_fit_batched. */
+size_t hfrep_fit_windows_workspace(int n_windows, int T_win, int E);
+int hfrep_fit_windows(const hfrep_fit_cfg* cfg, const float* R, int T_all, int C, int col_lo,
+                      const int32_t* win_starts, int n_windows, int n_tasks, const int32_t* task_L,
+                      const int32_t* task_win, const float* W0, int w_stride, const int32_t* perm,
+                      int64_t perm_task_stride, const float* sched, void* ws, size_t ws_bytes, float* W_out,
+                      float* loss_hist, float* val_hist, int32_t* epochs_run, int32_t* status, void* stream);
+
 /* ---------------------------------------------------------------------------------------
  * Kernel (c): fused out-of-sample predict + rolling OLS + replica + ex-post + metrics, one
  * task (= one trained autoencoder) per CTA.  Replaces AE.model_IS_r2/RMSE (:107-113),
@@ -136,6 +148,8 @@ void hfrep_eval_cfg_default(hfrep_eval_cfg* cfg);
  *   rf     f64 [T_test]      risk-free rows aligned with the test block
  *   sigma  f64 [n_oos-1][E]  from hfrep_rolling_sigma over the last n_oos+window ETF rows, starts 1..n_oos-1
  *   W      f32 [n_tasks][w_stride], task_L int32 [n_tasks]: trained kernels from hfrep_fit_batched
+ *   task_row0 int32 [n_tasks] | NULL: rolling refit (one autoencoder per window): task i evaluates rows
+ *          [task_row0[i], task_row0[i]+T_test) of Xte/Yte/rf, which then hold the whole history (NULL: row 0)
  * outputs (any may be NULL to skip the store):
  *   ante, post f64 [n_tasks][n_oos][F];  turnover f64 [n_tasks][F]
  *   metrics f64 [n_tasks][6][F]: sharpe, tracking error, correlation of ante; then of post
@@ -147,7 +161,7 @@ void hfrep_eval_cfg_default(hfrep_eval_cfg* cfg);
  */
 int hfrep_predict_metrics(const hfrep_eval_cfg* cfg, const double* Xtr, const double* Xte, const double* Yte,
                           const double* rf, const double* sigma, int n_tasks, const int32_t* task_L,
-                          const float* W, int w_stride, double* ante, double* post, double* turnover,
+                          const int32_t* task_row0, const float* W, int w_stride, double* ante, double* post, double* turnover,
                           double* metrics, double* quality, uint8_t* mask, double* weights, double* beta,
                           double* norm, int32_t* status, void* stream);
 

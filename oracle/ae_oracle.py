@@ -304,3 +304,15 @@ def run_task(x_train, y_train, x_test, y_test, rf, etf_all, L, We0, Wd0, perm=No
         sh, te, co = ae.metrics(out[name])
         out[f"sharpe_{name}"], out[f"te_{name}"], out[f"corr_{name}"] = sh, te, co
     return out
+
+
+def run_mode_w_window(etf_train, etf, hfd, rf, t, train_window, L, We0, Wd0, ols_window=24, cfg=None):
+    """One task of the rolling refit (SURVEY §8d Mode W; OUR extension — the reference fits once): the reference's `AE`
+    restatement called on train block rows [t-train_window, t) and test block rows [t-ols_window, t+2), `ante(window)`
+    -> one replica row (for row t+1).  etf_train: the matrix the training windows are cut from."""
+    lo = t - ols_window
+    ae = AEOracle(etf_train[t - train_window:t], hfd[t - train_window:t], etf[lo:t + 2], hfd[lo:t + 2], L)
+    ae.train(We0, Wd0, cfg=cfg)
+    ante = ae.ante(np.asarray(rf).reshape(-1)[lo:t + 2], window=ols_window)
+    assert ante.shape[0] == 1
+    return ante[0], ae.weights[0]

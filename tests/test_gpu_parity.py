@@ -283,3 +283,35 @@ def test_errors_and_empty(hf, data):
         hf.fit_batched(data.Xtr32, [21], W0, E=E, T=168)
     res = hf.fit_batched(data.Xtr32, [], torch.zeros((0, 2 * E * 8), dtype=torch.float32, device=dev), E=E, T=168)
     assert res.W.shape[0] == 0
+
+
+def test_mode_w_rolling_refit(hf):
+    """Rolling refit (window gather + MinMax into scratch -> fit per window -> one replica row per window) against the
+    Mode-W oracle, which calls the reference's AE restatement once per window."""
+    from oracle import ae_oracle, fitcore
+    rng = np.random.default_rng(5)
+    T, E, F, W, L, ols = 70, 22, 5, 40, 3, 12
+    fac = rng.normal(size=(T, 3)) * .03
+    etf = fac @ rng.normal(size=(3, E)) + rng.normal(size=(T, E)) * .01
+    hfd = etf @ (rng.normal(size=(E, F)) * .1) + rng.normal(size=(T, F)) * .004
+    rf = np.full(T, 1e-3)
+    seeds = (7, 8)
+    out = hf.run_mode_w(etf, hfd, rf, train_window=W, latent_dim=L, seeds=seeds, ols_window=ols, device="cuda:0",
+                        max_epochs=25, early_stop=0)
+    ts = out["t"]
+    assert np.array_equal(ts, np.arange(W, T - 1)) and out["replica"].shape == (2, len(ts), F)
+    assert int(out["fit"].status.abs().sum()) == 0 and int(out["eval"].status.abs().sum()) == 0
+    etf32 = etf.astype(np.float32).astype(np.float64)          # kernel (a) cuts the training windows from the f32 matrix
+    # scratch blocks = MinMax of each window, bit-exact
+    blocks = out["blocks"].cpu().numpy()
+    for wi in (0, len(ts) - 1):
+        t = ts[wi]
+        assert np.array_equal(blocks[wi], ae_oracle.minmax_fit_transform(etf32[t - W:t]).astype(np.float32))
+    cfg = fitcore.FitConfig(epochs=25, early_stop=False)
+    rep = out["replica"].cpu().numpy()
+    for si, s in enumerate(seeds):
+        for wi in (0, 7, len(ts) - 1):
+            t = int(ts[wi])
+            We0, Wd0 = hf.engine.initial_weights(s * 100003 + wi, E, L)
+            want, _ = ae_oracle.run_mode_w_window(etf32, etf, hfd, rf, t, W, L, We0, Wd0, ols_window=ols, cfg=cfg)
+            assert rel_err(rep[si, wi], want) < TOL, (s, wi)

@@ -103,7 +103,7 @@ def test_argument_validation_without_gpu():
                                     None, None)
     assert rc == -1 and b"E=30" in _lib.lib.hfrep_last_error()
     ecfg = _lib.eval_cfg(window=100)
-    rc = _lib.lib.hfrep_predict_metrics(ctypes.byref(ecfg), one, one, one, one, one, 1, one, one, 400, *([None] * 11))
+    rc = _lib.lib.hfrep_predict_metrics(ctypes.byref(ecfg), one, one, one, one, one, 1, one, None, one, 400, *([None] * 11))
     assert rc == -1 and b"window" in _lib.lib.hfrep_last_error()
 
 
