@@ -13,6 +13,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libhfrep.so")
 
 MAX_E, MAX_L, MAX_F = 24, 24, 32
+STATIC_SCRATCH_BYTES = 4 << 20     # HFREP_STATIC_SCRATCH_BYTES
 
 
 class HfrepError(RuntimeError):
@@ -37,7 +38,7 @@ class EvalCfg(C.Structure):
 
 
 EXPORTS = ("hfrep_last_error", "hfrep_version", "hfrep_window_index", "hfrep_window_gather",
-           "hfrep_rolling_sigma", "hfrep_fit_cfg_default", "hfrep_nadam_schedule", "hfrep_fit_batched", "hfrep_fit_windows_workspace", "hfrep_fit_windows",
+           "hfrep_rolling_sigma", "hfrep_fit_cfg_default", "hfrep_nadam_schedule", "hfrep_fit_batched", "hfrep_fit_windows_workspace", "hfrep_fit_windows", "hfrep_fit_windows_static",
            "hfrep_eval_cfg_default", "hfrep_predict_metrics", "hfrep_series_metrics", "hfrep_ex_post_return", "hfrep_forward",
            "hfrep_ffma_peak")
 
@@ -64,6 +65,8 @@ def _load():
     lib.hfrep_fit_windows_workspace.argtypes = [C.c_int, C.c_int, C.c_int]
     lib.hfrep_fit_windows.argtypes = [C.POINTER(FitCfg), vp, C.c_int, C.c_int, C.c_int, vp, C.c_int, C.c_int, vp, vp, vp,
                                       C.c_int, vp, i64, vp, vp, C.c_size_t, vp, vp, vp, vp, vp, vp]
+    lib.hfrep_fit_windows_static.argtypes = [C.POINTER(FitCfg), vp, C.c_int, C.c_int, C.c_int, vp, C.c_int, C.c_int, vp, vp, vp,
+                                             C.c_int, vp, i64, vp, vp, vp, vp, vp, vp, vp]
     lib.hfrep_eval_cfg_default.argtypes = [C.POINTER(EvalCfg)]
     lib.hfrep_eval_cfg_default.restype = None
     lib.hfrep_predict_metrics.argtypes = [C.POINTER(EvalCfg), vp, vp, vp, vp, vp, C.c_int, vp, vp, vp, C.c_int] + [vp] * 11

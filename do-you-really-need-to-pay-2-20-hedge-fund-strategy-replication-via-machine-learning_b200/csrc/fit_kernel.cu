@@ -867,3 +867,58 @@ extern "C" int hfrep_fit_windows(const hfrep_fit_cfg* c, const float* R, int T_a
     return fit_batched_impl(&cc, blocks, n_tasks, task_L, task_win, W0, w_stride, perm, perm_task_stride, sched, W_out,
                             loss_hist, val_hist, epochs_run, status, nullptr, stream);
 }
+
+// ------------------------------------------------------------------------------------------------------------
+// hfrep_fit_windows_static: the rolling refit for callers that must not allocate device memory.
+//
+// Who that is: a host process that gave the whole GPU to its own arena at start-up (PyTorch's caching allocator
+// with a memory fraction, an RMM pool, a risk engine with a fixed device-memory plan) has nothing left for a
+// cudaMalloc made on its behalf, and a scheduler that keeps other streams busy cannot afford the device-wide
+// synchronisation an allocation or a free implies.  Such a caller still owns its inputs and outputs, but it has
+// nowhere to put the scaled window blocks that kernel (a) hands to kernel (b).  Here that scratch is a fixed
+// array inside the library image: every GPU that loads libhfrep.so reserves HFREP_STATIC_SCRATCH_BYTES for it
+// until the process exits.
+//
+// The array's name is only a handle on the host; its device address is looked up with cudaGetSymbolAddress the
+// first time the entry point runs on a device (with that device current) and remembered per device.  Make that
+// first call outside any stream capture.  All calls on one device share the one array: two calls whose kernels
+// overlap on the GPU (different streams, no dependency) overwrite each other's blocks.  Nothing in the array
+// has to start at zero — kernel (a) rewrites every element the fit reads — so no clearing is done between calls.
+// No cudaMalloc / cudaFree / allocating library routine is called on this path.
+static __device__ __align__(256) float g_window_scratch[HFREP_STATIC_SCRATCH_BYTES / sizeof(float)];
+
+static int static_scratch_address(float** out) {
+    static float* cached[64] = {nullptr};
+    int dev = -1;
+    HFREP_CUDA_OK(cudaGetDevice(&dev));
+    HFREP_REQUIRE(dev >= 0 && dev < 64, "fit_windows_static: device ordinal %d not supported", dev);
+    if (cached[dev] == nullptr) {
+        float* ptr = nullptr;
+        HFREP_CUDA_OK(cudaGetSymbolAddress((void**)&ptr, g_window_scratch));
+        HFREP_REQUIRE(ptr != nullptr, "fit_windows_static: no device address for the scratch array");
+        cached[dev] = ptr;
+    }
+    *out = cached[dev];
+    return HFREP_OK;
+}
+
+extern "C" int hfrep_fit_windows_static(const hfrep_fit_cfg* c, const float* R, int T_all, int C, int col_lo,
+                                        const int32_t* win_starts, int n_windows, int n_tasks,
+                                        const int32_t* task_L, const int32_t* task_win, const float* W0, int w_stride,
+                                        const int32_t* perm, int64_t perm_task_stride, const float* sched,
+                                        float* W_out, float* loss_hist, float* val_hist, int32_t* epochs_run,
+                                        int32_t* status, void* stream) {
+    HFREP_REQUIRE(c != nullptr, "fit_windows_static: null argument");
+    const size_t need = hfrep_fit_windows_workspace(n_windows, c->T, c->E);
+    HFREP_REQUIRE(n_windows >= 1 && need > 0, "fit_windows_static: n_windows=%d T=%d E=%d", n_windows, c->T, c->E);
+    HFREP_REQUIRE(need <= (size_t)HFREP_STATIC_SCRATCH_BYTES,
+                  "fit_windows_static: %d windows x %d rows x %d columns need %zu bytes of scratch, the built-in array "
+                  "holds %zu; use hfrep_fit_windows with your own workspace", n_windows, c->T, c->E, need,
+                  (size_t)HFREP_STATIC_SCRATCH_BYTES);
+    float* scratch = nullptr;
+    const int rc = static_scratch_address(&scratch);
+    if (rc != HFREP_OK) return rc;
+    return hfrep_fit_windows(c, R, T_all, C, col_lo, win_starts, n_windows, n_tasks, task_L, task_win, W0, w_stride, perm,
+                             perm_task_stride, sched, scratch, (size_t)HFREP_STATIC_SCRATCH_BYTES, W_out, loss_hist,
+                             val_hist, epochs_run, status, stream);
+}

@@ -120,6 +120,21 @@ int hfrep_fit_windows(const hfrep_fit_cfg* cfg, const float* R, int T_all, int C
                       int64_t perm_task_stride, const float* sched, void* ws, size_t ws_bytes, float* W_out,
                       float* loss_hist, float* val_hist, int32_t* epochs_run, int32_t* status, void* stream);
 
+/* hfrep_fit_windows for callers that cannot allocate device memory.  (No counterpart in the reference: the reference
+ * never touches a GPU.)  Same arguments as hfrep_fit_windows minus the workspace: the scaled window blocks go into a
+ * fixed array built into the library (HFREP_STATIC_SCRATCH_BYTES per GPU, reserved from load to exit).  Meant for
+ * hosts whose own arena already owns the GPU's memory, or that cannot take the device-wide stall of an allocation
+ * while other streams are fitting.  Limits: n_windows * cfg->T * cfg->E * 4 bytes must fit the array, else the call
+ * returns HFREP_ERR_ARG and names both sizes.  The first call on each device looks up the array's device address; make
+ * that call outside stream capture.  All calls on a device share the array — calls that overlap on the GPU race on
+ * it; calls ordered on one stream (or by events) are safe.  Nothing needs clearing between calls. */
+#define HFREP_STATIC_SCRATCH_BYTES (4u << 20)
+int hfrep_fit_windows_static(const hfrep_fit_cfg* cfg, const float* R, int T_all, int C, int col_lo,
+                             const int32_t* win_starts, int n_windows, int n_tasks, const int32_t* task_L,
+                             const int32_t* task_win, const float* W0, int w_stride, const int32_t* perm,
+                             int64_t perm_task_stride, const float* sched, float* W_out, float* loss_hist,
+                             float* val_hist, int32_t* epochs_run, int32_t* status, void* stream);
+
 /* ---------------------------------------------------------------------------------------
  * Kernel (c): fused out-of-sample predict + rolling OLS + replica + ex-post + metrics, one
  * task (= one trained autoencoder) per CTA.  Replaces AE.model_IS_r2/RMSE (:107-113),
