@@ -34,6 +34,9 @@ UNIT = "fits/s"
 T_ALL, E, F, WINDOW = 337, 22, 13, 24
 LATENTS = list(range(1, 22))
 EPOCHS = 1000
+# dram__bytes_read.sum + dram__bytes_write.sum per fit_kernel launch of the cfg2 sweep, from the committed
+# `ncu --set full` capture (profiles/r1_ncu_full_cfg2_summary.txt): the kernel is shared-memory resident.
+NCU_DRAM_BYTES_PER_FIT_LAUNCH = 68e3
 
 
 def synthetic_returns(seed=20240611):
@@ -268,8 +271,8 @@ def gpu_arm(args):
     flop = float(sum(flops_per_epoch(L) * int(n) for L, n in zip(task_L, epochs_run)))
     achieved = flop / (fit_ms_mean * 1e-3) / 1e12
     roofline = {"bound": "fp32_ffma", "kernel": "fit_kernel", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
-                "frac": achieved / peak, "traffic": None,
-                "peak_source": "measured live: hfrep_ffma_peak (8 FFMA chains/thread, full grid); MEASURED_PEAKS.json has no FP32 figure; nominal 148*128*2*1.965 GHz = 74.4",
+                "frac": achieved / peak, "traffic": NCU_DRAM_BYTES_PER_FIT_LAUNCH,
+                "peak_source": "measured live: hfrep_ffma_peak (8 packed FFMA2 chains/thread, full grid; scalar FFMA reaches 64.4 on the same box); MEASURED_PEAKS.json has no FP32 figure; nominal 148*128*2*1.965 GHz = 74.4",
                 "algorithmic_flop_per_launch": flop, "ms_per_launch": fit_ms_mean,
                 "note": f"{n_tasks} fits on {n_buckets} concurrent launches: cfg2 exposes only 21 sequential chains, so this is latency-, not FFMA-bound; see 'ensemble'"}
 

@@ -56,9 +56,11 @@ struct Lay {
     static constexpr int CT = LP / 4;
     static constexpr int NT5 = 12 * CT;        // weight tiles: dWd (CT x 6) then dWe (6 x CT)
     static constexpr int NEL = NT5 * 16;       // = 48*LP weight slots, tile-major
+    // Nadam's m, v: registers when the team has >= 3 warps (LP/2 or LP/4 slots per lane), else shared memory
+    __host__ __device__ static constexpr bool mv_in_regs(int NW) { return NW >= 3; }
     __host__ __device__ static size_t team_floats(int BP, int NW) {
         return (size_t)EP * LP + (size_t)LP * WDS + (size_t)(BP + 1) * HS * 2 + (size_t)(BP + 1) * XS +
-               (size_t)NW * NEL + 2 * (size_t)NEL + 2 * BP + 64;
+               (size_t)NW * NEL + (mv_in_regs(NW) ? 0 : 2 * (size_t)NEL) + 2 * BP + 64;
     }
     __host__ __device__ static size_t cta_floats(int T) { return (size_t)(T + 1) * XS + NEL; }
 };
@@ -100,7 +102,7 @@ __device__ __forceinline__ float fast_sqrt(float x) {      // MUFU.SQRT, 1 ulp; 
 }
 
 // LP: padded latent width; NW: warps per team; CS: lanes per batch row (1, or 2 = a lane pair splits the columns);
-// TPC: teams per CTA; FULL: fully unroll the k-loops of the rows phase (latency mapping: one warp per scheduler,
+// TPC: most teams per CTA (the launch picks blockDim.x / (32*NW) <= TPC teams from the shared-memory budget); FULL: fully unroll the k-loops of the rows phase (latency mapping: one warp per scheduler,
 // registers are free, the compiler software-pipelines the shared loads) instead of rolling them (throughput mapping)
 template <int LP, int NW, int CS, int TPC, bool FULL>
 __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
@@ -124,7 +126,7 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
     const int team = threadIdx.x / NTH;
     const int tl = threadIdx.x - team * NTH;       // lane within the team
     const int warp = tl >> 5, lane = tl & 31;
-    const int task = blockIdx.x * TPC + team;
+    const int task = blockIdx.x * (blockDim.x / NTH) + team;
     const bool active = task < p.n_tasks;
     const int T = p.T, E = p.E, BP = p.BP;
 
@@ -140,8 +142,11 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
     float* dZh = H + (BP + 1) * HS;
     float* dZy = dZh + (BP + 1) * HS;
     float* part = dZy + (BP + 1) * XS;
+    constexpr bool MVREG = Lay<LP>::mv_in_regs(NW);
+    constexpr int EPL = MVREG ? NEL / NTH : 1;     // weight slots per lane when m, v live in registers
+    static_assert(!MVREG || NEL % NTH == 0, "register-resident Nadam state needs a whole number of slots per lane");
     float2* mv = reinterpret_cast<float2*>(part + NW * NEL);
-    int* xoff_tab = reinterpret_cast<int*>(part + NW * NEL + 2 * NEL);   // [2][BP], double-buffered per segment
+    int* xoff_tab = reinterpret_cast<int*>(part + NW * NEL + (MVREG ? 0 : 2 * NEL));   // [2][BP], double-buffered per segment
     float* red = reinterpret_cast<float*>(xoff_tab + 2 * BP);          // [2][32], double-buffered per epoch
 
     // ---- stage the training block (fused window load: rows of the scaled block -> padded tile)
@@ -155,7 +160,7 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
         }
         // tile-major weight slot -> offset from We
         for (int idx = threadIdx.x; idx < NEL; idx += blockDim.x) {
-            const int t = idx >> 4, i = (idx >> 2) & 3, jj = idx & 3;
+            const int i = idx / (NT5 * 4), t = (idx - i * (NT5 * 4)) >> 2, jj = idx & 3;   // slot layout [i][tile][jj]
             int o;
             if (t < 6 * CT) {                            // dWd tile (lt, et): Wd[lt*4+i][et*4+jj]
                 const int lt = t / 6, et = t - lt * 6;
@@ -179,7 +184,8 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
             const int l = idx / WDS, e = idx - l * WDS;
             Wd[idx] = (l < L0 && e < E) ? w0[E * L0 + l * E + e] : 0.f;
         }
-        for (int idx = tl; idx < NEL; idx += NTH) mv[idx] = make_float2(0.f, 0.f);
+        if constexpr (!MVREG)
+            for (int idx = tl; idx < NEL; idx += NTH) mv[idx] = make_float2(0.f, 0.f);
     }
     __syncthreads();
     if (!active) return;
@@ -195,8 +201,10 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
     // Forward (and backward to dZh) of the batch rows, one row per lane (pair).  Returns the lane's share of the
     // squared error.  Lanes without a row work on the all-zero row T and park their (all-zero) results in
     // scratch row BP, so the phase needs no predication and pairs stay converged.
+    // All multiply-adds are packed FFMA2 (fma.rn.f32x2, sm_100): two IEEE-rounded FP32 FMAs per issue slot,
+    // bit-identical to scalar fmaf.
     auto rows_phase = [&](const int* xoff, int nb, bool train, float coef) -> float {
-        float sse = 0.f;
+        float2 sse2 = make_float2(0.f, 0.f);
 #pragma unroll 1
         for (int r0 = 0; r0 < nb; r0 += ROWS) {
             const int r = r0 + row_in_pass;
@@ -209,121 +217,49 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
             const int lcol0 = 4 * part_id;
             const int ltail = 4 * (CT - 1) + 2 * part_id;
             // ---- zh (own columns) = x . We[:, cols]
-            float zh[LPC];
+            float2 zh[LPC / 2];
 #pragma unroll
-            for (int l = 0; l < LPC; ++l) zh[l] = 0.f;
-            if constexpr (FULL) {
-                // explicit double buffering: the weights of k4-group e4+1 are in flight while group e4 is multiplied
-                float4 wq[2][4][NG4 > 0 ? NG4 : 1];
-                float2 wt[2][4];
-                float4 xq[2];
-                auto load_group = [&](int b, int e4) {
-                    xq[b] = ld4(xr + 4 * e4);
+            for (int l = 0; l < LPC / 2; ++l) zh[l] = make_float2(0.f, 0.f);
+#pragma unroll (UK)
+            for (int e4 = 0; e4 < EP / 4; ++e4) {
+                const float4 xv = ld4(xr + 4 * e4);
+                const float xe[4] = {xv.x, xv.y, xv.z, xv.w};
 #pragma unroll
-                    for (int k = 0; k < 4; ++k) {
-                        const float* wrow = We + (4 * e4 + k) * LP;
+                for (int k = 0; k < 4; ++k) {
+                    const float* wrow = We + (4 * e4 + k) * LP;
+                    const float2 xx = make_float2(xe[k], xe[k]);
 #pragma unroll
-                        for (int i = 0; i < NG4; ++i) wq[b][k][i] = ld4(wrow + lcol0 + 4 * CS * i);
-                        if constexpr (TAIL) wt[b][k] = ld2(wrow + ltail);
+                    for (int i = 0; i < NG4; ++i) {
+                        const float4 w = ld4(wrow + lcol0 + 4 * CS * i);
+                        zh[2 * i + 0] = __ffma2_rn(xx, make_float2(w.x, w.y), zh[2 * i + 0]);
+                        zh[2 * i + 1] = __ffma2_rn(xx, make_float2(w.z, w.w), zh[2 * i + 1]);
                     }
-                };
-                load_group(0, 0);
-#pragma unroll
-                for (int e4 = 0; e4 < EP / 4; ++e4) {
-                    const int b = e4 & 1;
-                    if (e4 + 1 < EP / 4) load_group(b ^ 1, e4 + 1);
-                    const float xe[4] = {xq[b].x, xq[b].y, xq[b].z, xq[b].w};
-#pragma unroll
-                    for (int k = 0; k < 4; ++k) {
-#pragma unroll
-                        for (int i = 0; i < NG4; ++i) {
-                            zh[4 * i + 0] = fmaf(xe[k], wq[b][k][i].x, zh[4 * i + 0]);
-                            zh[4 * i + 1] = fmaf(xe[k], wq[b][k][i].y, zh[4 * i + 1]);
-                            zh[4 * i + 2] = fmaf(xe[k], wq[b][k][i].z, zh[4 * i + 2]);
-                            zh[4 * i + 3] = fmaf(xe[k], wq[b][k][i].w, zh[4 * i + 3]);
-                        }
-                        if constexpr (TAIL) {
-                            zh[4 * NG4 + 0] = fmaf(xe[k], wt[b][k].x, zh[4 * NG4 + 0]);
-                            zh[4 * NG4 + 1] = fmaf(xe[k], wt[b][k].y, zh[4 * NG4 + 1]);
-                        }
-                    }
-                }
-            } else {
-    #pragma unroll (UK)
-                for (int e4 = 0; e4 < EP / 4; ++e4) {
-                    const float4 xv = ld4(xr + 4 * e4);
-                    const float xe[4] = {xv.x, xv.y, xv.z, xv.w};
-    #pragma unroll
-                    for (int k = 0; k < 4; ++k) {
-                        const float* wrow = We + (4 * e4 + k) * LP;
-    #pragma unroll
-                        for (int i = 0; i < NG4; ++i) {
-                            const float4 w = ld4(wrow + lcol0 + 4 * CS * i);
-                            zh[4 * i + 0] = fmaf(xe[k], w.x, zh[4 * i + 0]);
-                            zh[4 * i + 1] = fmaf(xe[k], w.y, zh[4 * i + 1]);
-                            zh[4 * i + 2] = fmaf(xe[k], w.z, zh[4 * i + 2]);
-                            zh[4 * i + 3] = fmaf(xe[k], w.w, zh[4 * i + 3]);
-                        }
-                        if constexpr (TAIL) {
-                            const float2 w = ld2(wrow + ltail);
-                            zh[4 * NG4 + 0] = fmaf(xe[k], w.x, zh[4 * NG4 + 0]);
-                            zh[4 * NG4 + 1] = fmaf(xe[k], w.y, zh[4 * NG4 + 1]);
-                        }
-                    }
+                    if constexpr (TAIL) zh[2 * NG4] = __ffma2_rn(xx, ld2(wrow + ltail), zh[2 * NG4]);
                 }
             }
 #pragma unroll
             for (int i = 0; i < NG4; ++i)
-                st4(hrow + lcol0 + 4 * CS * i, make_float4(lrelu(zh[4 * i], alpha), lrelu(zh[4 * i + 1], alpha),
-                                                           lrelu(zh[4 * i + 2], alpha), lrelu(zh[4 * i + 3], alpha)));
-            if constexpr (TAIL) st2(hrow + ltail, make_float2(lrelu(zh[4 * NG4], alpha), lrelu(zh[4 * NG4 + 1], alpha)));
+                st4(hrow + lcol0 + 4 * CS * i, make_float4(lrelu(zh[2 * i].x, alpha), lrelu(zh[2 * i].y, alpha),
+                                                           lrelu(zh[2 * i + 1].x, alpha), lrelu(zh[2 * i + 1].y, alpha)));
+            if constexpr (TAIL) st2(hrow + ltail, make_float2(lrelu(zh[2 * NG4].x, alpha), lrelu(zh[2 * NG4].y, alpha)));
             if constexpr (CS > 1) __syncwarp();
             // ---- zy (own EPC columns) = h . Wd[:, cols]; h re-read from the row (written by the pair)
-            float zy[EPC];
+            float2 zy[EPC / 2];
 #pragma unroll
-            for (int e = 0; e < EPC; ++e) zy[e] = 0.f;
+            for (int e = 0; e < EPC / 2; ++e) zy[e] = make_float2(0.f, 0.f);
             const float* wdp = Wd + part_id * EPC;
-            if constexpr (FULL) {
-                float4 wq[2][4][EPC / 4];
-                float4 hq[2];
-                auto load_group = [&](int b, int l4) {
-                    hq[b] = ld4(hrow + 4 * l4);
+#pragma unroll (UK)
+            for (int l4 = 0; l4 < CT; ++l4) {
+                const float4 hv = ld4(hrow + 4 * l4);
+                const float hl[4] = {hv.x, hv.y, hv.z, hv.w};
 #pragma unroll
-                    for (int k = 0; k < 4; ++k)
+                for (int k = 0; k < 4; ++k) {
+                    const float2 hh = make_float2(hl[k], hl[k]);
 #pragma unroll
-                        for (int e4 = 0; e4 < EPC / 4; ++e4) wq[b][k][e4] = ld4(wdp + (4 * l4 + k) * WDS + 4 * e4);
-                };
-                load_group(0, 0);
-#pragma unroll
-                for (int l4 = 0; l4 < CT; ++l4) {
-                    const int b = l4 & 1;
-                    if (l4 + 1 < CT) load_group(b ^ 1, l4 + 1);
-                    const float hl[4] = {hq[b].x, hq[b].y, hq[b].z, hq[b].w};
-#pragma unroll
-                    for (int k = 0; k < 4; ++k)
-#pragma unroll
-                        for (int e4 = 0; e4 < EPC / 4; ++e4) {
-                            zy[4 * e4 + 0] = fmaf(hl[k], wq[b][k][e4].x, zy[4 * e4 + 0]);
-                            zy[4 * e4 + 1] = fmaf(hl[k], wq[b][k][e4].y, zy[4 * e4 + 1]);
-                            zy[4 * e4 + 2] = fmaf(hl[k], wq[b][k][e4].z, zy[4 * e4 + 2]);
-                            zy[4 * e4 + 3] = fmaf(hl[k], wq[b][k][e4].w, zy[4 * e4 + 3]);
-                        }
-                }
-            } else {
-    #pragma unroll (UK)
-                for (int l4 = 0; l4 < CT; ++l4) {
-                    const float4 hv = ld4(hrow + 4 * l4);
-                    const float hl[4] = {hv.x, hv.y, hv.z, hv.w};
-    #pragma unroll
-                    for (int k = 0; k < 4; ++k) {
-    #pragma unroll
-                        for (int e4 = 0; e4 < EPC / 4; ++e4) {
-                            const float4 w = ld4(wdp + (4 * l4 + k) * WDS + 4 * e4);
-                            zy[4 * e4 + 0] = fmaf(hl[k], w.x, zy[4 * e4 + 0]);
-                            zy[4 * e4 + 1] = fmaf(hl[k], w.y, zy[4 * e4 + 1]);
-                            zy[4 * e4 + 2] = fmaf(hl[k], w.z, zy[4 * e4 + 2]);
-                            zy[4 * e4 + 3] = fmaf(hl[k], w.w, zy[4 * e4 + 3]);
-                        }
+                    for (int e4 = 0; e4 < EPC / 4; ++e4) {
+                        const float4 w = ld4(wdp + (4 * l4 + k) * WDS + 4 * e4);
+                        zy[2 * e4 + 0] = __ffma2_rn(hh, make_float2(w.x, w.y), zy[2 * e4 + 0]);
+                        zy[2 * e4 + 1] = __ffma2_rn(hh, make_float2(w.z, w.w), zy[2 * e4 + 1]);
                     }
                 }
             }
@@ -332,105 +268,59 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
             for (int e4 = 0; e4 < EPC / 4; ++e4) {
                 const float4 xv = ld4(xr + part_id * EPC + 4 * e4);
                 const float xe[4] = {xv.x, xv.y, xv.z, xv.w};
+                float z[4] = {zy[2 * e4].x, zy[2 * e4].y, zy[2 * e4 + 1].x, zy[2 * e4 + 1].y};
 #pragma unroll
                 for (int k = 0; k < 4; ++k) {
-                    const float z = zy[4 * e4 + k];
-                    const float d = lrelu(z, alpha) - xe[k];
-                    sse = fmaf(d, d, sse);
-                    zy[4 * e4 + k] = lrelu_grad(z, coef * d, alpha);      // zy now holds dzy
+                    const float d = lrelu(z[k], alpha) - xe[k];
+                    if (k & 1) sse2.y = fmaf(d, d, sse2.y); else sse2.x = fmaf(d, d, sse2.x);
+                    z[k] = lrelu_grad(z[k], coef * d, alpha);      // now dzy
                 }
+                zy[2 * e4] = make_float2(z[0], z[1]);
+                zy[2 * e4 + 1] = make_float2(z[2], z[3]);
             }
             if (train) {
 #pragma unroll
                 for (int e4 = 0; e4 < EPC / 4; ++e4)
-                    st4(yrow + part_id * EPC + 4 * e4, make_float4(zy[4 * e4], zy[4 * e4 + 1], zy[4 * e4 + 2], zy[4 * e4 + 3]));
-                float dzy[EP];
+                    st4(yrow + part_id * EPC + 4 * e4, make_float4(zy[2 * e4].x, zy[2 * e4].y, zy[2 * e4 + 1].x, zy[2 * e4 + 1].y));
+                float2 dzy[EP / 2];
                 if constexpr (CS > 1) {
                     __syncwarp();
 #pragma unroll
                     for (int e4 = 0; e4 < EP / 4; ++e4) {
                         const float4 v = ld4(yrow + 4 * e4);
-                        dzy[4 * e4] = v.x; dzy[4 * e4 + 1] = v.y; dzy[4 * e4 + 2] = v.z; dzy[4 * e4 + 3] = v.w;
+                        dzy[2 * e4] = make_float2(v.x, v.y); dzy[2 * e4 + 1] = make_float2(v.z, v.w);
                     }
                 } else {
 #pragma unroll
-                    for (int e = 0; e < EP; ++e) dzy[e] = zy[e];
+                    for (int e = 0; e < EP / 2; ++e) dzy[e] = zy[e];
                 }
-                // ---- dzh (own columns) = (dzy . Wd[l, :]) * lrelu'(zh); 4 partial sums per column keep the chains short
+                // ---- dzh (own columns) = (dzy . Wd[l, :]) * lrelu'(zh); two packed partial sums per column
                 float* grow = dZh + rs * HS;
                 auto dzh_col = [&](int l, float hsign) -> float {
                     const float* wr = Wd + l * WDS;
-                    float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+                    float2 a01 = make_float2(0.f, 0.f), a23 = make_float2(0.f, 0.f);
 #pragma unroll
                     for (int e4 = 0; e4 < EP / 4; ++e4) {
                         const float4 w = ld4(wr + 4 * e4);
-                        a0 = fmaf(dzy[4 * e4 + 0], w.x, a0);
-                        a1 = fmaf(dzy[4 * e4 + 1], w.y, a1);
-                        a2 = fmaf(dzy[4 * e4 + 2], w.z, a2);
-                        a3 = fmaf(dzy[4 * e4 + 3], w.w, a3);
+                        a01 = __ffma2_rn(dzy[2 * e4 + 0], make_float2(w.x, w.y), a01);
+                        a23 = __ffma2_rn(dzy[2 * e4 + 1], make_float2(w.z, w.w), a23);
                     }
-                    return lrelu_grad(hsign, (a0 + a1) + (a2 + a3), alpha);   // sign(h) == sign(zh) for alpha > 0
+                    return lrelu_grad(hsign, (a01.x + a01.y) + (a23.x + a23.y), alpha);   // sign(h) == sign(zh) for alpha > 0
                 };
-                if constexpr (FULL) {
-                    // own columns two at a time, the next pair's decoder rows in flight (double buffer)
-                    float hs[LPC], out[LPC];
-#pragma unroll
-                    for (int i = 0; i < NG4; ++i) {
-                        const float4 hv = ld4(hrow + lcol0 + 4 * CS * i);
-                        hs[4 * i] = hv.x; hs[4 * i + 1] = hv.y; hs[4 * i + 2] = hv.z; hs[4 * i + 3] = hv.w;
-                    }
-                    if constexpr (TAIL) {
-                        const float2 hv = ld2(hrow + ltail);
-                        hs[4 * NG4] = hv.x; hs[4 * NG4 + 1] = hv.y;
-                    }
-                    auto col_of = [&](int c) { return c < 4 * NG4 ? lcol0 + 4 * CS * (c >> 2) + (c & 3) : ltail + (c - 4 * NG4); };
-                    float4 wq[2][2][EP / 4];
-                    auto load_pair = [&](int b, int c) {
-#pragma unroll
-                        for (int u = 0; u < 2; ++u) {
-                            const float* wr = Wd + col_of(c + u) * WDS;
-#pragma unroll
-                            for (int e4 = 0; e4 < EP / 4; ++e4) wq[b][u][e4] = ld4(wr + 4 * e4);
-                        }
-                    };
-                    load_pair(0, 0);
-#pragma unroll
-                    for (int c = 0; c < LPC; c += 2) {
-                        const int b = (c >> 1) & 1;
-                        if (c + 2 < LPC) load_pair(b ^ 1, c + 2);
-#pragma unroll
-                        for (int u = 0; u < 2; ++u) {
-                            float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
-#pragma unroll
-                            for (int e4 = 0; e4 < EP / 4; ++e4) {
-                                a0 = fmaf(dzy[4 * e4 + 0], wq[b][u][e4].x, a0);
-                                a1 = fmaf(dzy[4 * e4 + 1], wq[b][u][e4].y, a1);
-                                a2 = fmaf(dzy[4 * e4 + 2], wq[b][u][e4].z, a2);
-                                a3 = fmaf(dzy[4 * e4 + 3], wq[b][u][e4].w, a3);
-                            }
-                            out[c + u] = lrelu_grad(hs[c + u], (a0 + a1) + (a2 + a3), alpha);
-                        }
-                    }
-#pragma unroll
-                    for (int i = 0; i < NG4; ++i)
-                        st4(grow + lcol0 + 4 * CS * i, make_float4(out[4 * i], out[4 * i + 1], out[4 * i + 2], out[4 * i + 3]));
-                    if constexpr (TAIL) st2(grow + ltail, make_float2(out[4 * NG4], out[4 * NG4 + 1]));
-                } else {
-    #pragma unroll 1
-                    for (int i = 0; i < NG4; ++i) {
-                        const int l0 = lcol0 + 4 * CS * i;
-                        const float4 hv = ld4(hrow + l0);
-                        st4(grow + l0, make_float4(dzh_col(l0, hv.x), dzh_col(l0 + 1, hv.y), dzh_col(l0 + 2, hv.z),
-                                                   dzh_col(l0 + 3, hv.w)));
-                    }
-                    if constexpr (TAIL) {
-                        const float2 hv = ld2(hrow + ltail);
-                        st2(grow + ltail, make_float2(dzh_col(ltail, hv.x), dzh_col(ltail + 1, hv.y)));
-                    }
+#pragma unroll 1
+                for (int i = 0; i < NG4; ++i) {
+                    const int l0 = lcol0 + 4 * CS * i;
+                    const float4 hv = ld4(hrow + l0);
+                    st4(grow + l0, make_float4(dzh_col(l0, hv.x), dzh_col(l0 + 1, hv.y), dzh_col(l0 + 2, hv.z),
+                                               dzh_col(l0 + 3, hv.w)));
+                }
+                if constexpr (TAIL) {
+                    const float2 hv = ld2(hrow + ltail);
+                    st2(grow + ltail, make_float2(dzh_col(ltail, hv.x), dzh_col(ltail + 1, hv.y)));
                 }
             }
         }
-        return sse;
+        return sse2.x + sse2.y;
     };
 
     // ---------------------------------------------------------------- rows phase, quad variant (CS == 4)
@@ -440,7 +330,7 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
     auto rows_phase_quad = [&](const int* xoff, int nb, bool train, float coef) -> float {
         constexpr int NPL = LP >= 8 ? LP / 8 : 1;  // latent float2 pieces per lane (only instantiated for LP % 8 == 0)
         constexpr int NPE = EP / 8;                // ETF float2 pieces per lane (3)
-        float sse = 0.f;
+        float2 sse2 = make_float2(0.f, 0.f);
 #pragma unroll 1
         for (int r0 = 0; r0 < nb; r0 += ROWS) {
             const int r = r0 + row_in_pass;
@@ -452,9 +342,9 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
             float* grow = dZh + rs * HS;
             const int c0 = 2 * part_id;            // own pieces start at column 8j + c0
             // ---- zh pieces = x . We[:, own columns]
-            float zh[2 * NPL];
+            float2 zh[NPL];
 #pragma unroll
-            for (int l = 0; l < 2 * NPL; ++l) zh[l] = 0.f;
+            for (int l = 0; l < NPL; ++l) zh[l] = make_float2(0.f, 0.f);
 #pragma unroll
             for (int e4 = 0; e4 < EP / 4; ++e4) {
                 const float4 xv = ld4(xr + 4 * e4);
@@ -462,22 +352,19 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
 #pragma unroll
                 for (int k = 0; k < 4; ++k) {
                     const float* wrow = We + (4 * e4 + k) * LP + c0;
+                    const float2 xx = make_float2(xe[k], xe[k]);
 #pragma unroll
-                    for (int j = 0; j < NPL; ++j) {
-                        const float2 w = ld2(wrow + 8 * j);
-                        zh[2 * j + 0] = fmaf(xe[k], w.x, zh[2 * j + 0]);
-                        zh[2 * j + 1] = fmaf(xe[k], w.y, zh[2 * j + 1]);
-                    }
+                    for (int j = 0; j < NPL; ++j) zh[j] = __ffma2_rn(xx, ld2(wrow + 8 * j), zh[j]);
                 }
             }
 #pragma unroll
             for (int j = 0; j < NPL; ++j)
-                st2(hrow + 8 * j + c0, make_float2(lrelu(zh[2 * j], alpha), lrelu(zh[2 * j + 1], alpha)));
+                st2(hrow + 8 * j + c0, make_float2(lrelu(zh[j].x, alpha), lrelu(zh[j].y, alpha)));
             __syncwarp();
             // ---- zy pieces = h . Wd[:, own columns]
-            float zy[2 * NPE];
+            float2 zy[NPE];
 #pragma unroll
-            for (int e = 0; e < 2 * NPE; ++e) zy[e] = 0.f;
+            for (int e = 0; e < NPE; ++e) zy[e] = make_float2(0.f, 0.f);
 #pragma unroll
             for (int l4 = 0; l4 < CT; ++l4) {
                 const float4 hv = ld4(hrow + 4 * l4);
@@ -485,36 +372,29 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
 #pragma unroll
                 for (int k = 0; k < 4; ++k) {
                     const float* wrow = Wd + (4 * l4 + k) * WDS + c0;
+                    const float2 hh = make_float2(hl[k], hl[k]);
 #pragma unroll
-                    for (int j = 0; j < NPE; ++j) {
-                        const float2 w = ld2(wrow + 8 * j);
-                        zy[2 * j + 0] = fmaf(hl[k], w.x, zy[2 * j + 0]);
-                        zy[2 * j + 1] = fmaf(hl[k], w.y, zy[2 * j + 1]);
-                    }
+                    for (int j = 0; j < NPE; ++j) zy[j] = __ffma2_rn(hh, ld2(wrow + 8 * j), zy[j]);
                 }
             }
             // ---- squared error and dLoss/dzy on the lane's columns
 #pragma unroll
             for (int j = 0; j < NPE; ++j) {
                 const float2 xv = ld2(xr + 8 * j + c0);
-                const float xe[2] = {xv.x, xv.y};
-#pragma unroll
-                for (int k = 0; k < 2; ++k) {
-                    const float z = zy[2 * j + k];
-                    const float d = lrelu(z, alpha) - xe[k];
-                    sse = fmaf(d, d, sse);
-                    zy[2 * j + k] = lrelu_grad(z, coef * d, alpha);
-                }
+                const float dx = lrelu(zy[j].x, alpha) - xv.x, dy = lrelu(zy[j].y, alpha) - xv.y;
+                sse2.x = fmaf(dx, dx, sse2.x);
+                sse2.y = fmaf(dy, dy, sse2.y);
+                zy[j] = make_float2(lrelu_grad(zy[j].x, coef * dx, alpha), lrelu_grad(zy[j].y, coef * dy, alpha));
             }
             if (train) {
 #pragma unroll
-                for (int j = 0; j < NPE; ++j) st2(yrow + 8 * j + c0, make_float2(zy[2 * j], zy[2 * j + 1]));
+                for (int j = 0; j < NPE; ++j) st2(yrow + 8 * j + c0, zy[j]);
                 __syncwarp();
-                float dzy[EP];
+                float2 dzy[EP / 2];
 #pragma unroll
                 for (int e4 = 0; e4 < EP / 4; ++e4) {
                     const float4 v = ld4(yrow + 4 * e4);
-                    dzy[4 * e4] = v.x; dzy[4 * e4 + 1] = v.y; dzy[4 * e4 + 2] = v.z; dzy[4 * e4 + 3] = v.w;
+                    dzy[2 * e4] = make_float2(v.x, v.y); dzy[2 * e4 + 1] = make_float2(v.z, v.w);
                 }
                 // ---- dzh pieces = (dzy . Wd[l, :]) * lrelu'(zh) for the own latent columns
 #pragma unroll
@@ -523,22 +403,20 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
 #pragma unroll
                     for (int k = 0; k < 2; ++k) {
                         const float* wr = Wd + (8 * j + c0 + k) * WDS;
-                        float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+                        float2 a01 = make_float2(0.f, 0.f), a23 = make_float2(0.f, 0.f);
 #pragma unroll
                         for (int e4 = 0; e4 < EP / 4; ++e4) {
                             const float4 w = ld4(wr + 4 * e4);
-                            a0 = fmaf(dzy[4 * e4 + 0], w.x, a0);
-                            a1 = fmaf(dzy[4 * e4 + 1], w.y, a1);
-                            a2 = fmaf(dzy[4 * e4 + 2], w.z, a2);
-                            a3 = fmaf(dzy[4 * e4 + 3], w.w, a3);
+                            a01 = __ffma2_rn(dzy[2 * e4 + 0], make_float2(w.x, w.y), a01);
+                            a23 = __ffma2_rn(dzy[2 * e4 + 1], make_float2(w.z, w.w), a23);
                         }
-                        out[k] = lrelu_grad(zh[2 * j + k], (a0 + a1) + (a2 + a3), alpha);
+                        out[k] = lrelu_grad(k ? zh[j].y : zh[j].x, (a01.x + a01.y) + (a23.x + a23.y), alpha);
                     }
                     st2(grow + 8 * j + c0, make_float2(out[0], out[1]));
                 }
             }
         }
-        return sse;
+        return sse2.x + sse2.y;
     };
 
     // ---------------------------------------------------------------- weight-gradient phase (split-K over warps)
@@ -556,52 +434,65 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
                 const int et = u / CT, lt = u - et * CT;
                 a0 = et * 4; b0 = (int)(dZh - Xs) + lt * 4; bstr = HS;
             }
-            float acc[4][4] = {};
+            float2 acc[4][2];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) acc[i][0] = acc[i][1] = make_float2(0.f, 0.f);
 #pragma unroll 4
             for (int q = warp; q < nb; q += NW) {
                 const int ao = dec ? q * HS : xoff[q];
                 const float4 a = ld4(Xs + a0 + ao);
                 const float4 b = ld4(Xs + b0 + q * bstr);
                 const float av[4] = {a.x, a.y, a.z, a.w};
+                const float2 b01 = make_float2(b.x, b.y), b23 = make_float2(b.z, b.w);
 #pragma unroll
                 for (int i = 0; i < 4; ++i) {
-                    acc[i][0] = fmaf(av[i], b.x, acc[i][0]);
-                    acc[i][1] = fmaf(av[i], b.y, acc[i][1]);
-                    acc[i][2] = fmaf(av[i], b.z, acc[i][2]);
-                    acc[i][3] = fmaf(av[i], b.w, acc[i][3]);
+                    const float2 aa = make_float2(av[i], av[i]);
+                    acc[i][0] = __ffma2_rn(aa, b01, acc[i][0]);
+                    acc[i][1] = __ffma2_rn(aa, b23, acc[i][1]);
                 }
             }
 #pragma unroll
             for (int i = 0; i < 4; ++i)
-                st4(mypart + t * 16 + i * 4, make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]));
+                st4(mypart + i * (NT5 * 4) + t * 4, make_float4(acc[i][0].x, acc[i][0].y, acc[i][1].x, acc[i][1].y));   // lanes -> consecutive 16 B
         }
     };
 
     // ---------------------------------------------------------------- update phase (Nadam, element-wise)
+    float2 mvr[EPL];
+#pragma unroll
+    for (int j = 0; j < EPL; ++j) mvr[j] = make_float2(0.f, 0.f);
+    auto update_slot = [&](int idx, float2& s2, const float4& sc, bool dump) {
+        float g = part[idx];
+#pragma unroll
+        for (int w = 1; w < NW; ++w) g += part[w * NEL + idx];
+        s2.x = p.b1 * s2.x + omb1 * g;
+        s2.y = p.b2 * s2.y + omb2 * (g * g);
+        const float m_bar = sc.x * g + sc.y * s2.x;
+        const int o = woff[idx];
+        We[o] -= __fdividef(p.lr * m_bar, fast_sqrt(s2.y * sc.z) + p.eps);
+        if (dump) {
+            float* go = p.grad_out + (size_t)task * p.w_stride;
+            if (o >= EP * LP) {
+                const int r = (o - EP * LP) / WDS, c = (o - EP * LP) - r * WDS;
+                if (r < L && c < E) go[E * L + r * E + c] = g;
+            } else {
+                const int r = o / LP, c = o - r * LP;
+                if (r < E && c < L) go[r * L + c] = g;
+            }
+        }
+    };
     auto update_phase = [&](int step) {
         const float4 sc = __ldg(p.sched + step);
         const bool dump = p.grad_out != nullptr && step == p.dump_step;
-#pragma unroll 2
-        for (int idx = tl; idx < NEL; idx += NTH) {
-            float g = part[idx];
+        if constexpr (MVREG) {
 #pragma unroll
-            for (int w = 1; w < NW; ++w) g += part[w * NEL + idx];
-            float2 s2 = mv[idx];
-            s2.x = p.b1 * s2.x + omb1 * g;
-            s2.y = p.b2 * s2.y + omb2 * (g * g);
-            mv[idx] = s2;
-            const float m_bar = sc.x * g + sc.y * s2.x;
-            const int o = woff[idx];
-            We[o] -= __fdividef(p.lr * m_bar, fast_sqrt(s2.y * sc.z) + p.eps);
-            if (dump) {
-                float* go = p.grad_out + (size_t)task * p.w_stride;
-                if (o >= EP * LP) {
-                    const int r = (o - EP * LP) / WDS, c = (o - EP * LP) - r * WDS;
-                    if (r < L && c < E) go[E * L + r * E + c] = g;
-                } else {
-                    const int r = o / LP, c = o - r * LP;
-                    if (r < E && c < L) go[r * L + c] = g;
-                }
+            for (int j = 0; j < EPL; ++j) update_slot(tl + j * NTH, mvr[j], sc, dump);
+        } else {
+#pragma unroll 2
+            for (int idx = tl; idx < NEL; idx += NTH) {
+                float2 s2 = mv[idx];
+                update_slot(idx, s2, sc, dump);
+                mv[idx] = s2;
             }
         }
     };
@@ -704,32 +595,28 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
 // ---------------------------------------------------------------------------------- host side
 constexpr size_t kMaxSmem = 227 * 1024;
 
-template <int LP, int NW, int TPC>
-static size_t fit_smem_bytes(const FitParams& p) {
-    return sizeof(float) * (Lay<LP>::cta_floats(p.T) + TPC * Lay<LP>::team_floats(p.BP, NW));
+template <int LP, int NW>
+static size_t fit_smem_bytes(const FitParams& p, int tpc) {
+    return sizeof(float) * (Lay<LP>::cta_floats(p.T) + tpc * Lay<LP>::team_floats(p.BP, NW));
 }
 
+// Teams of one CTA share the staged training block, so several teams per CTA need n_x == 1; the launch takes the
+// largest team count (<= TPC) whose shared memory fits.
 template <int LP, int NW, int CS, int TPC, bool FULL>
 static int launch_fit(const FitParams& p, cudaStream_t stream) {
-    const size_t smem = fit_smem_bytes<LP, NW, TPC>(p);
+    int tpc = p.shared_x ? TPC : 1;
+    while (tpc > 1 && fit_smem_bytes<LP, NW>(p, tpc) > kMaxSmem) --tpc;
+    // two half-size CTAs per SM beat one big one when both fit (finer scheduling granularity)
+    if (tpc > 1 && tpc % 2 == 0 && 2 * fit_smem_bytes<LP, NW>(p, tpc / 2) <= kMaxSmem) tpc /= 2;
+    const size_t smem = fit_smem_bytes<LP, NW>(p, tpc);
     HFREP_REQUIRE(smem <= kMaxSmem, "fit: %zu bytes of shared memory needed (T=%d / batch=%d too large for the narrow kernel)",
                   smem, p.T, p.batch);
     auto kern = fit_kernel<LP, NW, CS, TPC, FULL>;
     HFREP_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    const int grid = (p.n_tasks + TPC - 1) / TPC;
-    kern<<<grid, 32 * NW * TPC, smem, stream>>>(p);
+    const int grid = (p.n_tasks + tpc - 1) / tpc;
+    kern<<<grid, 32 * NW * tpc, smem, stream>>>(p);
     HFREP_CUDA_OK(cudaGetLastError());
     return HFREP_OK;
-}
-
-// Teams of one CTA share the staged training block, so several teams per CTA need n_x == 1; take the
-// largest team count whose shared memory fits.
-template <int LP, int NW, int CS, int TPC>
-static int launch_fit_packed(const FitParams& p, cudaStream_t stream) {
-    if constexpr (TPC > 1) {
-        if (!p.shared_x || fit_smem_bytes<LP, NW, TPC>(p) > kMaxSmem) return launch_fit_packed<LP, NW, CS, TPC / 2>(p, stream);
-    }
-    return launch_fit<LP, NW, CS, TPC, false>(p, stream);
 }
 
 // warps per task:
@@ -740,8 +627,8 @@ static int launch_fit_packed(const FitParams& p, cudaStream_t stream) {
 //      tasks (LP padded to a multiple of 8).
 template <int LP>
 static int dispatch_mapping(const FitParams& p, int wpt, cudaStream_t stream) {
-    if (wpt == 1) return launch_fit_packed<LP, 1, 2, 8>(p, stream);
-    if (wpt == 3) return launch_fit_packed<LP, 3, 2, 2>(p, stream);
+    if (wpt == 1) return launch_fit<LP, 1, 2, 8, false>(p, stream);
+    if (wpt == 3) return launch_fit<LP, 3, 2, (LP <= 8 ? 8 : 6), false>(p, stream);
     if constexpr (LP % 8 == 0) return launch_fit<LP, 6, 4, 1, true>(p, stream);
     else return set_err(HFREP_ERR_ARG, "fit: internal: the quad mapping needs LP %% 8 == 0");
 }

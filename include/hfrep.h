@@ -198,9 +198,9 @@ int hfrep_series_metrics(const double* series, const double* fund, const double*
 int hfrep_ex_post_return(const double* ante, const double* weights, const double* sigma, int T, int F, int E,
                          double param, double phi, double* post, void* stream);
 
-/* FP32-FFMA peak micro-benchmark used as the roofline denominator of kernel (b) (MEASURED_PEAKS.json
- * has no FP32 figure).  Runs `iters` dependent-chain-free FFMAs per thread on a full grid and returns
- * the flop count through *flops_host; time it with CUDA events on `stream`. sink f32 [>=1]. */
+/* FP32 peak micro-benchmark used as the roofline denominator of kernel (b) (MEASURED_PEAKS.json has no FP32
+ * figure).  Runs `iters` rounds of 8 independent packed FMAs (FFMA2, fma.rn.f32x2) per thread on a full grid and returns
+ * the flop count through *flops_host; time it with CUDA events on `stream`.  sink f32 [>=1]. */
 int hfrep_ffma_peak(int iters, float* sink, double* flops_host, void* stream);
 
 #ifdef __cplusplus

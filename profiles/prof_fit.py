@@ -14,6 +14,8 @@ seeds = int(sys.argv[1]) if len(sys.argv) > 1 else 64
 epochs = int(sys.argv[2]) if len(sys.argv) > 2 else 100
 wpt = int(sys.argv[3]) if len(sys.argv) > 3 else 0
 reps = int(sys.argv[4]) if len(sys.argv) > 4 else 2
+if os.environ.get("PROF_LATENTS"):
+    LATENTS = [int(v) for v in os.environ["PROF_LATENTS"].split(",")]
 etf, hfd, rf = synthetic_returns()
 data = hfrep.ReplicationData(etf, hfd, rf, device="cuda:0")
 tasks = [(L, s) for s in range(1000, 1000 + seeds) for L in LATENTS]
