@@ -46,6 +46,7 @@ struct FitParams {
     float* grad_out;
     long long perm_task_stride;
     int n_tasks, E, T, n_fit, n_val, batch, BP, max_epochs, patience, early_stop, w_stride, shared_x, dump_step;
+    int force_tile;      // testing: batch-tile mode even when the block could be resident (env HFREP_FORCE_TILE)
     int debug_skip;      // profiling only (env HFREP_DEBUG_SKIP): bit0 rows, bit1 grads, bit2 update phases skipped
     float alpha, lr, b1, b2, eps;
 };
@@ -58,11 +59,13 @@ struct Lay {
     static constexpr int NEL = NT5 * 16;       // = 48*LP weight slots, tile-major
     // Nadam's m, v: registers when the team has >= 3 warps (LP/2 or LP/4 slots per lane), else shared memory
     __host__ __device__ static constexpr bool mv_in_regs(int NW) { return NW >= 3; }
-    __host__ __device__ static size_t team_floats(int BP, int NW) {
+    // XT (batch-tile mode): the training block stays in global memory / L2 and only the current mini-batch's rows
+    // sit in a per-team tile [BP+1][XS], refilled with cp.async; else the whole block is resident once per CTA.
+    __host__ __device__ static size_t team_floats(int BP, int NW, bool XT) {
         return (size_t)EP * LP + (size_t)LP * WDS + (size_t)(BP + 1) * HS * 2 + (size_t)(BP + 1) * XS +
-               (size_t)NW * NEL + (mv_in_regs(NW) ? 0 : 2 * (size_t)NEL) + 2 * BP + 64;
+               (size_t)NW * NEL + (mv_in_regs(NW) ? 0 : 2 * (size_t)NEL) + 2 * BP + 64 + (XT ? (size_t)(BP + 1) * XS : 0);
     }
-    __host__ __device__ static size_t cta_floats(int T) { return (size_t)(T + 1) * XS + NEL; }
+    __host__ __device__ static size_t cta_floats(int T, bool XT) { return (XT ? 0 : (size_t)(T + 1) * XS) + NEL; }
 };
 
 template <int NW>
@@ -104,7 +107,8 @@ __device__ __forceinline__ float fast_sqrt(float x) {      // MUFU.SQRT, 1 ulp; 
 // LP: padded latent width; NW: warps per team; CS: lanes per batch row (1, or 2 = a lane pair splits the columns);
 // TPC: most teams per CTA (the launch picks blockDim.x / (32*NW) <= TPC teams from the shared-memory budget); FULL: fully unroll the k-loops of the rows phase (latency mapping: one warp per scheduler,
 // registers are free, the compiler software-pipelines the shared loads) instead of rolling them (throughput mapping)
-template <int LP, int NW, int CS, int TPC, bool FULL>
+// XT: batch-tile mode (see Lay::team_floats) — any block length T, any block per task, several teams per CTA
+template <int LP, int NW, int CS, int TPC, bool FULL, bool XT>
 __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
     extern __shared__ __align__(16) float smem[];
     constexpr int NTH = 32 * NW;
@@ -130,11 +134,10 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
     const bool active = task < p.n_tasks;
     const int T = p.T, E = p.E, BP = p.BP;
 
-    const size_t cf = Lay<LP>::cta_floats(T);
-    const size_t tf = Lay<LP>::team_floats(BP, NW);
-    // shared training block: [Xs | woff | team 0 | team 1 ...]; own blocks (TPC == 1 then): same layout
-    float* Xs = smem;
-    int* woff = reinterpret_cast<int*>(smem + (size_t)(T + 1) * XS);
+    const size_t cf = Lay<LP>::cta_floats(T, XT);
+    const size_t tf = Lay<LP>::team_floats(BP, NW, XT);
+    // [Xs (resident mode only) | woff | team 0 | team 1 ...]
+    int* woff = reinterpret_cast<int*>(smem + (XT ? 0 : (size_t)(T + 1) * XS));
     float* base = smem + cf + (size_t)team * tf;
     float* We = base;
     float* Wd = We + EP * LP;
@@ -148,15 +151,22 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
     float2* mv = reinterpret_cast<float2*>(part + NW * NEL);
     int* xoff_tab = reinterpret_cast<int*>(part + NW * NEL + (MVREG ? 0 : 2 * NEL));   // [2][BP], double-buffered per segment
     float* red = reinterpret_cast<float*>(xoff_tab + 2 * BP);          // [2][32], double-buffered per epoch
+    // Xs: what the phases address rows in — the resident block (row r at xoff[r]) or the team's batch tile (row r at r*XS)
+    float* Xs = XT ? red + 64 : smem;
+    const int zero_row = XT ? BP * XS : T * XS;      // all-zero row for idle lanes
 
     // ---- stage the training block (fused window load: rows of the scaled block -> padded tile)
+    const int xb = (!active || !p.task_x) ? 0 : p.task_x[task];
+    const float* xg = p.X + (size_t)xb * T * E;        // this task's training block in global memory
     {
-        const int xb = (p.shared_x || !active || !p.task_x) ? 0 : p.task_x[task];
-        const float* xg = p.X + (size_t)xb * T * E;
-        const int n = (T + 1) * XS;
-        for (int idx = threadIdx.x; idx < n; idx += blockDim.x) {
-            const int r = idx / XS, c = idx - r * XS;
-            Xs[idx] = (r < T && c < E) ? __ldg(xg + (size_t)r * E + c) : 0.f;
+        if constexpr (XT) {
+            for (int idx = tl; idx < (BP + 1) * XS; idx += NTH) Xs[idx] = 0.f;   // pad columns and the zero row stay 0
+        } else {
+            const int n = (T + 1) * XS;
+            for (int idx = threadIdx.x; idx < n; idx += blockDim.x) {
+                const int r = idx / XS, c = idx - r * XS;
+                Xs[idx] = (r < T && c < E) ? __ldg(xg + (size_t)r * E + c) : 0.f;
+            }
         }
         // tile-major weight slot -> offset from We
         for (int idx = threadIdx.x; idx < NEL; idx += blockDim.x) {
@@ -209,7 +219,7 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
         for (int r0 = 0; r0 < nb; r0 += ROWS) {
             const int r = r0 + row_in_pass;
             const bool valid = r < nb;
-            const float* xr = Xs + (valid ? xoff[r] : T * XS);
+            const float* xr = Xs + (valid ? (XT ? r * XS : xoff[r]) : zero_row);
             const int rs = valid ? r : BP;
             float* hrow = H + rs * HS;
             float* yrow = dZy + rs * XS;
@@ -335,7 +345,7 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
         for (int r0 = 0; r0 < nb; r0 += ROWS) {
             const int r = r0 + row_in_pass;
             const bool valid = r < nb;
-            const float* xr = Xs + (valid ? xoff[r] : T * XS);
+            const float* xr = Xs + (valid ? (XT ? r * XS : xoff[r]) : zero_row);
             const int rs = valid ? r : BP;
             float* hrow = H + rs * HS;
             float* yrow = dZy + rs * XS;
@@ -439,7 +449,7 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
             for (int i = 0; i < 4; ++i) acc[i][0] = acc[i][1] = make_float2(0.f, 0.f);
 #pragma unroll 4
             for (int q = warp; q < nb; q += NW) {
-                const int ao = dec ? q * HS : xoff[q];
+                const int ao = dec ? q * HS : (XT ? q * XS : xoff[q]);
                 const float4 a = ld4(Xs + a0 + ao);
                 const float4 b = ld4(Xs + b0 + q * bstr);
                 const float av[4] = {a.x, a.y, a.z, a.w};
@@ -510,12 +520,32 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
         const bool val = seg >= n_tb;
         const int lo = (val ? seg - n_tb : seg) * batch;
         const int nb = min(batch, (val ? n_val : n_fit) - lo);
-        for (int q = tl; q < nb; q += NTH) {
-            const int row = val ? n_fit + lo + q : (perm_t ? __ldg(perm_t + (size_t)epoch * n_fit + lo + q) : lo + q);
-            xoff[q] = row * XS;
+        if constexpr (XT) {
+            // refill the batch tile: cp.async of the rows' E floats (16-, 8- or 4-byte pieces by alignment)
+            const int pw = ((E & 3) == 0 && (((size_t)xb * T * E) & 3) == 0) ? 4 : (((E & 1) == 0 && (((size_t)xb * T * E) & 1) == 0) ? 2 : 1);
+            const int ppr = E / pw;                       // pieces per row
+            for (int idx = tl; idx < nb * ppr; idx += NTH) {
+                const int q = idx / ppr, c = (idx - q * ppr) * pw;
+                const int row = val ? n_fit + lo + q : (perm_t ? __ldg(perm_t + (size_t)epoch * n_fit + lo + q) : lo + q);
+                const float* src = xg + (size_t)row * E + c;
+                const unsigned dst = (unsigned)__cvta_generic_to_shared(Xs + q * XS + c);
+                if (pw == 4) asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
+                else if (pw == 2) asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(dst), "l"(src) : "memory");
+                else asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(src) : "memory");
+            }
+            asm volatile("cp.async.commit_group;" ::: "memory");
+        } else {
+            for (int q = tl; q < nb; q += NTH) {
+                const int row = val ? n_fit + lo + q : (perm_t ? __ldg(perm_t + (size_t)epoch * n_fit + lo + q) : lo + q);
+                xoff[q] = row * XS;
+            }
         }
     };
+    auto rows_ready = [&]() {                          // the tile refill issued by this thread has landed
+        if constexpr (XT) asm volatile("cp.async.wait_group 0;" ::: "memory");
+    };
     set_rows(xoff_tab, 0, 0);
+    rows_ready();
     team_sync<NW>(team);
     for (int epoch = 0; epoch < p.max_epochs; ++epoch) {
         float lsum = 0.f, vsum = 0.f;
@@ -526,9 +556,13 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
             const int nb = min(batch, (train ? n_fit : n_val) - lo);
             const int* xoff = xoff_tab + cur * BP;
             int* xnext = xoff_tab + (cur ^ 1) * BP;
-            // row offsets of the next segment (next epoch's first batch after the last one)
-            if (seg + 1 < n_seg) set_rows(xnext, epoch, seg + 1);
-            else set_rows(xnext, epoch + 1 < p.max_epochs ? epoch + 1 : epoch, 0);
+            // rows of the next segment (next epoch's first batch after the last one): resident mode writes the other
+            // offset table right away; tile mode refills the single tile once its last reader is done
+            auto prefetch_next = [&]() {
+                if (seg + 1 < n_seg) set_rows(xnext, epoch, seg + 1);
+                else set_rows(xnext, epoch + 1 < p.max_epochs ? epoch + 1 : epoch, 0);
+            };
+            if constexpr (!XT) prefetch_next();
             float sse = 0.f;
             if (!(p.debug_skip & 1)) {
                 if constexpr (CS == 4) sse = rows_phase_quad(xoff, nb, train, 2.f / (float)(nb * E));
@@ -539,11 +573,14 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
                 team_sync<NW>(team);
                 if (!(p.debug_skip & 2)) grads_phase(xoff, nb);
                 team_sync<NW>(team);
+                if constexpr (XT) prefetch_next();          // the copy overlaps the update phase
                 if (!(p.debug_skip & 4)) update_phase(step);
                 ++step;
             } else {
                 vsum += sse;
+                if constexpr (XT) { team_sync<NW>(team); prefetch_next(); }
             }
+            rows_ready();
             cur ^= 1;
             team_sync<NW>(team);
         }
@@ -596,27 +633,35 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
 constexpr size_t kMaxSmem = 227 * 1024;
 
 template <int LP, int NW>
-static size_t fit_smem_bytes(const FitParams& p, int tpc) {
-    return sizeof(float) * (Lay<LP>::cta_floats(p.T) + tpc * Lay<LP>::team_floats(p.BP, NW));
+static size_t fit_smem_bytes(const FitParams& p, int tpc, bool xt) {
+    return sizeof(float) * (Lay<LP>::cta_floats(p.T, xt) + tpc * Lay<LP>::team_floats(p.BP, NW, xt));
 }
 
-// Teams of one CTA share the staged training block, so several teams per CTA need n_x == 1; the launch takes the
-// largest team count (<= TPC) whose shared memory fits.
-template <int LP, int NW, int CS, int TPC, bool FULL>
-static int launch_fit(const FitParams& p, cudaStream_t stream) {
-    int tpc = p.shared_x ? TPC : 1;
-    while (tpc > 1 && fit_smem_bytes<LP, NW>(p, tpc) > kMaxSmem) --tpc;
+// Resident mode: teams of one CTA share the staged training block, so several teams per CTA need n_x == 1 and the block
+// must fit.  Batch-tile mode (own block per task, or a block too long for shared memory) has neither limit.  The launch
+// takes the largest team count (<= TPC) whose shared memory fits.
+template <int LP, int NW, int CS, int TPC, bool FULL, bool XT>
+static int launch_fit_mode(const FitParams& p, cudaStream_t stream) {
+    int tpc = TPC;
+    while (tpc > 1 && fit_smem_bytes<LP, NW>(p, tpc, XT) > kMaxSmem) --tpc;
     // two half-size CTAs per SM beat one big one when both fit (finer scheduling granularity)
-    if (tpc > 1 && tpc % 2 == 0 && 2 * fit_smem_bytes<LP, NW>(p, tpc / 2) <= kMaxSmem) tpc /= 2;
-    const size_t smem = fit_smem_bytes<LP, NW>(p, tpc);
-    HFREP_REQUIRE(smem <= kMaxSmem, "fit: %zu bytes of shared memory needed (T=%d / batch=%d too large for the narrow kernel)",
-                  smem, p.T, p.batch);
-    auto kern = fit_kernel<LP, NW, CS, TPC, FULL>;
+    if (tpc > 1 && tpc % 2 == 0 && 2 * fit_smem_bytes<LP, NW>(p, tpc / 2, XT) <= kMaxSmem) tpc /= 2;
+    const size_t smem = fit_smem_bytes<LP, NW>(p, tpc, XT);
+    HFREP_REQUIRE(smem <= kMaxSmem, "fit: %zu bytes of shared memory needed (batch=%d too large for the narrow kernel)", smem,
+                  p.batch);
+    auto kern = fit_kernel<LP, NW, CS, TPC, FULL, XT>;
     HFREP_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const int grid = (p.n_tasks + tpc - 1) / tpc;
     kern<<<grid, 32 * NW * tpc, smem, stream>>>(p);
     HFREP_CUDA_OK(cudaGetLastError());
     return HFREP_OK;
+}
+
+template <int LP, int NW, int CS, int TPC, bool FULL>
+static int launch_fit(const FitParams& p, cudaStream_t stream) {
+    const bool resident = p.shared_x && fit_smem_bytes<LP, NW>(p, 1, false) <= kMaxSmem && !p.force_tile;
+    return resident ? launch_fit_mode<LP, NW, CS, TPC, FULL, false>(p, stream)
+                    : launch_fit_mode<LP, NW, CS, TPC, FULL, true>(p, stream);
 }
 
 // warps per task:
@@ -708,6 +753,7 @@ static int fit_batched_impl(const hfrep_fit_cfg* c, const float* X, int n_tasks,
     p.BP = (c->batch + 3) & ~3; p.max_epochs = c->max_epochs; p.patience = c->patience; p.early_stop = c->early_stop;
     p.w_stride = w_stride; p.shared_x = (c->n_x == 1); p.dump_step = c->dump_step;
     { const char* dbg = getenv("HFREP_DEBUG_SKIP"); p.debug_skip = dbg ? atoi(dbg) : 0; }
+    p.force_tile = getenv("HFREP_FORCE_TILE") != nullptr;
     p.alpha = c->alpha; p.lr = c->lr; p.b1 = c->beta_1; p.b2 = c->beta_2; p.eps = c->epsilon;
 
     int wpt = c->warps_per_task;

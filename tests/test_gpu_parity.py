@@ -315,3 +315,39 @@ def test_mode_w_rolling_refit(hf):
             We0, Wd0 = hf.engine.initial_weights(s * 100003 + wi, E, L)
             want, _ = ae_oracle.run_mode_w_window(etf32, etf, hfd, rf, t, W, L, We0, Wd0, ols_window=ols, cfg=cfg)
             assert rel_err(rep[si, wi], want) < TOL, (s, wi)
+
+
+def test_batch_tile_mode_matches_resident(hf, data, monkeypatch):
+    """Batch-tile mode (training block in global memory, mini-batch rows fetched with cp.async) must give the very same
+    numbers as the resident mode: same arithmetic, different staging."""
+    g = load_golden("ref_modeR_L8_shuffled")
+    perm = hf.engine.to_device(hf.engine.epoch_permutations(int(g["perm_seed"]), 1000, 126), data.device)
+    for wpt in (1, 3, 6):
+        ref, L = _fit_golden(hf, data, g, perm=perm, warps_per_task=wpt, patience=5)
+        monkeypatch.setenv("HFREP_FORCE_TILE", "1")
+        til, _ = _fit_golden(hf, data, g, perm=perm, warps_per_task=wpt, patience=5)
+        monkeypatch.delenv("HFREP_FORCE_TILE")
+        assert int(til.epochs_run[0]) == int(ref.epochs_run[0]) == int(g["epochs_run"])
+        assert torch.equal(til.W, ref.W) and torch.equal(til.loss.nan_to_num(), ref.loss.nan_to_num())
+
+
+def test_long_training_block_stacked_rows(hf):
+    """The notebook's GAN-augmented fit stacks generated paths on top of the real rows (autoencoder_v4.ipynb:1388-1427):
+    1 848 training rows, 29 steps per epoch — too long to be resident in shared memory, so the batch-tile mode runs."""
+    from oracle import fitcore
+    rng = np.random.default_rng(21)
+    T, E, L = 1848, 22, 8
+    x = rng.uniform(0, 1, (T, E))
+    assert fitcore.split_at(T, .25) == 1386                       # SURVEY App. A.3
+    cfg = fitcore.FitConfig(epochs=6, early_stop=False)
+    We0, Wd0 = fitcore.initial_weights(4, E, L)
+    o = fitcore.fit(x, We0, Wd0, cfg)
+    dev = torch.device("cuda:0")
+    X = hf.engine.to_device(x.astype(np.float32)[None], dev)
+    W0 = hf.engine.to_device(hf.engine.pack_weights([(We0, Wd0)], E, 2 * E * L), dev)
+    for wpt in (1, 3, 6):
+        res = hf.fit_batched(X, [L], W0, E=E, T=T, max_epochs=6, early_stop=0, warps_per_task=wpt)
+        assert np.max(np.abs(res.loss[0, :6].cpu().numpy() - o["loss"]) / o["loss"]) < TOL
+        assert np.max(np.abs(res.val_loss[0, :6].cpu().numpy() - o["val_loss"]) / o["val_loss"]) < TOL
+        We, Wd = hf.engine.unpack_weights(res.W[0].cpu().numpy(), E, L)
+        assert rel_err(We, o["We"]) < TOL and rel_err(Wd, o["Wd"]) < TOL
