@@ -14,6 +14,9 @@ LIB_PATH = os.path.join(_HERE, "libhfrep.so")
 
 MAX_E, MAX_L, MAX_F = 24, 24, 32
 STATIC_SCRATCH_BYTES = 4 << 20     # HFREP_STATIC_SCRATCH_BYTES
+N_STATS = 11                       # HFREP_N_STATS
+STAT_NAMES = ("sharpe", "tracking_error", "correlation", "omega0", "omega10", "cvar5", "ceq2", "ceq5", "ceq10",
+              "skewness", "kurtosis")
 
 
 class HfrepError(RuntimeError):

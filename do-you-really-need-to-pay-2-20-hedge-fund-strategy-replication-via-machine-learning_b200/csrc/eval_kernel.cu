@@ -118,6 +118,79 @@ __device__ void block_quality(const double* x, int n, int E, int L, const double
     rmse = rms / E;
 }
 
+// The 11 per-series statistics of one return series of n values (stride ss) against a fund series y (stride ys),
+// computed by one warp; lane 0 writes out[j*ostride], j = 0..HFREP_N_STATS-1:
+//   0 Sharpe (autoencoder_v4.ipynb:715-721: (mean r - mean rf)/std(r, ddof=0)*sqrt(12))
+//   1 tracking error, 2 correlation (not in the reference)
+//   3 Omega(0 %), 4 Omega(10 %)  (ipynb:695-705, threshold de-annualised as (1+thr)^sqrt(1/252)-1)
+//   5 historical cVaR(5 %)       (ipynb:729-757: mean of r <= np.percentile(r, 5), linear interpolation)
+//   6..8 CEQ(gamma = 2, 5, 10)   (ipynb:759-770)
+//   9 skewness, 10 excess kurtosis (pandas DataFrame.skew()/kurt(), bias-corrected; ipynb:836)
+__device__ void series_stats(const double* s, int ss, const double* y, int ys, const double* rf, int n, int lane,
+                             double* out, int ostride) {
+    double sr = 0., sy = 0., sf = 0.;
+    for (int k = lane; k < n; k += 32) { sr += s[(size_t)k * ss]; sy += y[(size_t)k * ys]; sf += rf[k]; }
+    const double mr = warp_sum(sr) / n, my = warp_sum(sy) / n, rfm = warp_sum(sf) / n;
+    const double thr0 = pow(1., sqrt(1. / 252.)) - 1., thr10 = pow(1.1, sqrt(1. / 252.)) - 1.;
+    double vrr = 0., vyy = 0., vry = 0., sd = 0., m3 = 0., m4 = 0.;
+    double op0 = 0., on0 = 0., op10 = 0., on10 = 0., c2 = 0., c5 = 0., c10 = 0.;
+    for (int k = lane; k < n; k += 32) {
+        const double r = s[(size_t)k * ss];
+        const double a = r - mr, b = y[(size_t)k * ys] - my;
+        vrr += a * a; vyy += b * b; vry += a * b; sd += (a - b) * (a - b);
+        m3 += a * a * a; m4 += a * a * a * a;
+        const double e0 = r - thr0, e10 = r - thr10;
+        if (e0 > 0.) op0 += e0; else if (e0 < 0.) on0 += e0;
+        if (e10 > 0.) op10 += e10; else if (e10 < 0.) on10 += e10;
+        const double g = (1. + r) / (1. + rf[k]);
+        c2 += pow(g, -1.); c5 += pow(g, -4.); c10 += pow(g, -9.);
+    }
+    vrr = warp_sum(vrr); vyy = warp_sum(vyy); vry = warp_sum(vry); sd = warp_sum(sd);
+    m3 = warp_sum(m3); m4 = warp_sum(m4);
+    op0 = warp_sum(op0); on0 = warp_sum(on0); op10 = warp_sum(op10); on10 = warp_sum(on10);
+    c2 = warp_sum(c2); c5 = warp_sum(c5); c10 = warp_sum(c10);
+    // np.percentile(r, 5): order statistics lo, lo+1 by (stable) rank counting, then linear interpolation
+    const double pos = (n - 1) * 0.05;
+    const int lo = (int)floor(pos);
+    const double t = pos - lo;
+    double slo = 0., shi = 0.;
+    for (int i = lane; i < n; i += 32) {
+        const double v = s[(size_t)i * ss];
+        int rank = 0;
+        for (int j = 0; j < n; ++j) {
+            const double u = s[(size_t)j * ss];
+            rank += (u < v) || (u == v && j < i);
+        }
+        if (rank == lo) slo = v;
+        if (rank == min(lo + 1, n - 1)) shi = v;
+    }
+    slo = warp_sum(slo); shi = warp_sum(shi);          // exactly one lane holds each
+    const double d = shi - slo;
+    const double q = t >= .5 ? shi - d * (1. - t) : slo + d * t;     // numpy's _lerp
+    double cs = 0., cn = 0.;
+    for (int k = lane; k < n; k += 32) {
+        const double r = s[(size_t)k * ss];
+        if (r <= q) { cs += r; cn += 1.; }
+    }
+    cs = warp_sum(cs); cn = warp_sum(cn);
+    if (lane == 0) {
+        const double dn = (double)n;
+        const double m2 = vrr / dn;
+        out[0 * ostride] = (mr - rfm) / sqrt(m2) * sqrt(12.);
+        out[1 * ostride] = sqrt(sd / (dn - 1.)) * sqrt(12.);
+        out[2 * ostride] = vry / sqrt(vrr * vyy);
+        out[3 * ostride] = op0 / (-on0);
+        out[4 * ostride] = op10 / (-on10);
+        out[5 * ostride] = cs / cn;
+        out[6 * ostride] = log(c2 / dn) / ((1. - 2.) / 12.);
+        out[7 * ostride] = log(c5 / dn) / ((1. - 5.) / 12.);
+        out[8 * ostride] = log(c10 / dn) / ((1. - 10.) / 12.);
+        out[9 * ostride] = sqrt(dn * (dn - 1.)) / (dn - 2.) * (m3 / dn) / pow(m2, 1.5);
+        const double g2 = (m4 / dn) / (m2 * m2) - 3.;
+        out[10 * ostride] = (dn - 1.) / ((dn - 2.) * (dn - 3.)) * ((dn + 1.) * g2 + 6.);
+    }
+}
+
 __global__ void __launch_bounds__(NTH_EVAL) eval_kernel(const EvalParams p) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int task = blockIdx.x / p.qsplit, qpart = blockIdx.x - task * p.qsplit;
@@ -342,34 +415,16 @@ __global__ void __launch_bounds__(NTH_EVAL) eval_kernel(const EvalParams p) {
         p.beta[(size_t)task * HFREP_MAX_L * F + idx] = idx < L * F ? betaS[idx] : 0.;
     if (p.norm) for (int idx = tid; idx < F; idx += NTH_EVAL) p.norm[(size_t)task * F + idx] = normS[idx];
 
-    double rfm = 0.;
-    for (int k = lane; k < n_oos; k += 32) rfm += rfv[window + 1 + k];
-    rfm = warp_sum(rfm) / n_oos;
     for (int f = warp; f < F; f += NW) {
         double ts = 0.;
         for (int k = lane; k < n_oos; k += 32) ts += turnS[k * F + f];
         ts = warp_sum(ts);
         if (lane == 0 && p.turnover) p.turnover[(size_t)task * F + f] = ts / (n_oos / 12.);     // :216
-        if (p.metrics) {
-#pragma unroll
-            for (int which = 0; which < 2; ++which) {
-                const double* s = which ? postS : anteS;
-                double sr = 0., sy = 0.;
-                for (int k = lane; k < n_oos; k += 32) { sr += s[k * F + f]; sy += Yte[(size_t)(window + 1 + k) * F + f]; }
-                const double mr = warp_sum(sr) / n_oos, my = warp_sum(sy) / n_oos;
-                double vrr = 0., vyy = 0., vry = 0., sd = 0.;
-                for (int k = lane; k < n_oos; k += 32) {
-                    const double a = s[k * F + f] - mr, b = Yte[(size_t)(window + 1 + k) * F + f] - my;
-                    vrr += a * a; vyy += b * b; vry += a * b; sd += (a - b) * (a - b);
-                }
-                vrr = warp_sum(vrr); vyy = warp_sum(vyy); vry = warp_sum(vry); sd = warp_sum(sd);
-                if (lane == 0) {
-                    double* m = p.metrics + (size_t)task * 6 * F + which * 3 * F;
-                    m[0 * F + f] = (mr - rfm) / sqrt(vrr / n_oos) * sqrt(12.);          // ipynb:721 (np.std ddof=0)
-                    m[1 * F + f] = sqrt(sd / (n_oos - 1)) * sqrt(12.);                  // tracking error, ddof=1
-                    m[2 * F + f] = vry / sqrt(vrr * vyy);                               // Pearson correlation
-                }
-            }
+        if (p.metrics && n_oos >= 4) {
+#pragma unroll 1
+            for (int which = 0; which < 2; ++which)
+                series_stats((which ? postS : anteS) + f, F, Yte + (size_t)(window + 1) * F + f, F, rfv + window + 1, n_oos,
+                             lane, p.metrics + ((size_t)task * 2 + which) * HFREP_N_STATS * F + f, F);
         }
     }
     if (tid == 0 && p.status) p.status[task] = s_status;
@@ -413,20 +468,7 @@ __global__ void series_metrics_kernel(const double* s, const double* y, const do
     const int lane = threadIdx.x & 31;
     const int f = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (f >= F) return;
-    double sr = 0., sy = 0., sf = 0.;
-    for (int k = lane; k < n; k += 32) { sr += s[(size_t)k * F + f]; sy += y[(size_t)k * F + f]; sf += rf[k]; }
-    const double mr = warp_sum(sr) / n, my = warp_sum(sy) / n, rfm = warp_sum(sf) / n;
-    double vrr = 0., vyy = 0., vry = 0., sd = 0.;
-    for (int k = lane; k < n; k += 32) {
-        const double a = s[(size_t)k * F + f] - mr, b = y[(size_t)k * F + f] - my;
-        vrr += a * a; vyy += b * b; vry += a * b; sd += (a - b) * (a - b);
-    }
-    vrr = warp_sum(vrr); vyy = warp_sum(vyy); vry = warp_sum(vry); sd = warp_sum(sd);
-    if (lane == 0) {
-        out[0 * F + f] = (mr - rfm) / sqrt(vrr / n) * sqrt(12.);
-        out[1 * F + f] = sqrt(sd / (n - 1)) * sqrt(12.);
-        out[2 * F + f] = vry / sqrt(vrr * vyy);
-    }
+    series_stats(s + f, F, y + f, F, rf, n, lane, out + f, F);
 }
 
 }  // namespace hfrep
@@ -488,7 +530,7 @@ extern "C" int hfrep_predict_metrics(const hfrep_eval_cfg* c, const double* Xtr,
 extern "C" int hfrep_series_metrics(const double* series, const double* fund, const double* rf, int n, int F,
                                     double* out, void* stream) {
     HFREP_REQUIRE(series && fund && rf && out, "series_metrics: null argument");
-    HFREP_REQUIRE(n >= 2 && F >= 1, "series_metrics: n=%d F=%d", n, F);
+    HFREP_REQUIRE(n >= 4 && F >= 1, "series_metrics: n=%d F=%d (the bias-corrected kurtosis needs n >= 4)", n, F);
     const int wpb = 4;
     series_metrics_kernel<<<(F + wpb - 1) / wpb, wpb * 32, 0, (cudaStream_t)stream>>>(series, fund, rf, n, F, out);
     HFREP_CUDA_OK(cudaGetLastError());

@@ -224,7 +224,7 @@ class EvalResult:
     ante: torch.Tensor         # f64 [n][n_oos][F]
     post: torch.Tensor | None  # None when no sigma was given
     turnover: torch.Tensor     # f64 [n][F]
-    metrics: torch.Tensor      # f64 [n][6][F]   sharpe/te/corr of ante, then of post
+    metrics: torch.Tensor      # f64 [n][2][N_STATS][F]   _lib.STAT_NAMES of ante, then of post
     quality: torch.Tensor      # f64 [n][2+2*n_pre]
     mask: torch.Tensor         # u8  [n][n_oos][E]
     beta: torch.Tensor         # f64 [n][MAX_L][F]
@@ -256,7 +256,7 @@ def predict_metrics(Xtr64, Xte64, Yte64, rf64, sigma, task_L, W, *, window=24, w
     f64 = dict(dtype=torch.float64, device=device)
     r = EvalResult(
         ante=torch.empty((n, n_oos, F), **f64), post=torch.empty((n, n_oos, F), **f64) if sigma is not None else None,
-        turnover=torch.empty((n, F), **f64), metrics=torch.empty((n, 6, F), **f64),
+        turnover=torch.empty((n, F), **f64), metrics=torch.full((n, 2, _lib.N_STATS, F), float("nan"), **f64),
         quality=torch.full((n, 2 + 2 * n_pre), float("nan"), **f64) if want_quality else None,
         mask=torch.empty((n, n_oos, E), dtype=torch.uint8, device=device),
         beta=torch.empty((n, _lib.MAX_L, F), **f64), norm=torch.empty((n, F), **f64),

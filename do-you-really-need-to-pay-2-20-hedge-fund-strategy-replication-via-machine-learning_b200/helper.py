@@ -182,10 +182,10 @@ def dic_save(dic, loc):
 
 
 # ---- additive API (not in the reference's helper.py) ------------------------------
-def replica_metrics(series, fund, rf):
-    """GPU series statistics: returns (sharpe, tracking_error, correlation), each (F,).
-    sharpe = autoencoder_v4.ipynb:715-721; tracking error = std(series-fund, ddof=1)*sqrt(12);
-    correlation = Pearson.  series/fund (n, F), rf (n,)."""
+def series_statistics(series, fund, rf):
+    """GPU statistics of an (n, F) return block: dict name -> (F,) for _lib.STAT_NAMES (Sharpe, tracking error,
+    correlation, Omega(0 %), Omega(10 %), cVaR(5 %), CEQ(2/5/10), skewness, kurtosis; autoencoder_v4.ipynb:695-772, :836)."""
+    from ._lib import N_STATS, STAT_NAMES
     s = np.asarray(series, np.float64)
     y = np.asarray(fund, np.float64)
     if s.ndim == 1:
@@ -194,10 +194,32 @@ def replica_metrics(series, fund, rf):
     dev = engine._dev()
     with torch.cuda.device(dev):
         sd, yd, rd = (engine.to_device(a, dev) for a in (s, y, r))
-        out = torch.empty((3, s.shape[1]), dtype=torch.float64, device=dev)
+        out = torch.empty((N_STATS, s.shape[1]), dtype=torch.float64, device=dev)
         check(lib.hfrep_series_metrics(ptr(sd), ptr(yd), ptr(rd), s.shape[0], s.shape[1], ptr(out), stream_ptr()))
         o = out.cpu().numpy()
-    return o[0], o[1], o[2]
+    return dict(zip(STAT_NAMES, o))
+
+
+def replica_metrics(series, fund, rf):
+    """(sharpe, tracking_error, correlation), each (F,) — see series_statistics."""
+    st = series_statistics(series, fund, rf)
+    return st["sharpe"], st["tracking_error"], st["correlation"]
+
+
+def data_analysis(df, name, rf=None, start=None, end=None, span=None, real_data=False):
+    """The notebook's report table (autoencoder_v4.ipynb:774-849), real_data=False columns, computed on the GPU.
+    real_data=True adds Fama-French alphas and the GRS/HK tests, which the notebook runs through statsmodels and R
+    (rpy2): out of scope here and refused rather than silently dropped."""
+    if real_data:
+        raise NotImplementedError("FF3/FF5 alphas and GRS/HK tests need statsmodels and R; only real_data=False is built")
+    vals = np.asarray(df, np.float64)
+    rfv = np.zeros(len(vals)) if rf is None else np.asarray(rf, np.float64).reshape(-1)
+    st = series_statistics(vals, vals, rfv)
+    stats = pd.DataFrame({'Skewness': st["skewness"], 'Kurtosis': st["kurtosis"], 'Omega_ratio(0%)': st["omega0"],
+                          'Omega_ratio(10%)': st["omega10"], 'cVaR(95%)': st["cvar5"], 'CEQ Gamma=2': st["ceq2"],
+                          'CEQ Gamma=5': st["ceq5"], 'CEQ Gamma=10': st["ceq10"], 'Annualized_Sharpe': st["sharpe"]})
+    stats.index = name
+    return stats
 
 
 def annualized_sharpe_ratio(ret, rf=0):

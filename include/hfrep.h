@@ -32,6 +32,7 @@ extern "C" {
 #define HFREP_MAX_E 24        /* ETF width handled by the narrow kernels (reference: 22) */
 #define HFREP_MAX_L 24        /* latent width (reference sweep: 1..21) */
 #define HFREP_MAX_F 32        /* funds per evaluation (reference: 13) */
+#define HFREP_N_STATS 11      /* statistics per return series, see hfrep_series_metrics */
 
 const char* hfrep_last_error(void);
 int hfrep_version(void);
@@ -167,7 +168,8 @@ void hfrep_eval_cfg_default(hfrep_eval_cfg* cfg);
  *          [task_row0[i], task_row0[i]+T_test) of Xte/Yte/rf, which then hold the whole history (NULL: row 0)
  * outputs (any may be NULL to skip the store):
  *   ante, post f64 [n_tasks][n_oos][F];  turnover f64 [n_tasks][F]
- *   metrics f64 [n_tasks][6][F]: sharpe, tracking error, correlation of ante; then of post
+ *   metrics f64 [n_tasks][2][HFREP_N_STATS][F]: the statistics of hfrep_series_metrics for ante, then for post
+ *          (left untouched when fewer than 4 replica months exist)
  *   quality f64 [n_tasks][2 + 2*n_pre]: IS r2, IS rmse, OOS r2[n_pre], OOS rmse[n_pre]
  *   mask u8 [n_tasks][n_oos][E]  (1 = LeakyReLU slope applied, i.e. pre-activation < 0, :164-166)
  *   weights f64 [n_tasks][n_oos][E][F]  strat_weight_on_etf (:167); large — facade use only
@@ -186,8 +188,11 @@ int hfrep_predict_metrics(const hfrep_eval_cfg* cfg, const double* Xtr, const do
 int hfrep_forward(const float* W, int E, int L, const float* x, int n, int encode_only, float alpha, float* out,
                   void* stream);
 
-/* Stand-alone replica statistics for any (n, F) return block (autoencoder_v4.ipynb:715-721 + App. A.9):
- * out f64 [3][F] = sharpe(series, rf), tracking error and correlation against `fund`. */
+/* Stand-alone statistics of any (n, F) return block against `fund` (n, F) and rf (n): out f64 [HFREP_N_STATS][F], rows
+ *   0 annualised Sharpe (autoencoder_v4.ipynb:715-721)      1 tracking error, 2 correlation (not in the reference; App. A.9)
+ *   3 Omega(0 %), 4 Omega(10 %) (ipynb:695-705)              5 historical cVaR(5 %) (ipynb:729-757)
+ *   6-8 CEQ(gamma = 2, 5, 10) (ipynb:759-770)                9 skewness, 10 excess kurtosis (pandas skew()/kurt(), ipynb:836)
+ * i.e. the real_data=False columns of the notebook's data_analysis (ipynb:774-849) plus the two additive metrics. n >= 4. */
 int hfrep_series_metrics(const double* series, const double* fund, const double* rf, int n, int F,
                          double* out, void* stream);
 
