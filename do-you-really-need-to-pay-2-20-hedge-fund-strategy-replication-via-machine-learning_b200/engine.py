@@ -147,7 +147,8 @@ def _side_streams(device, n):
 
 def fit_batched(X: torch.Tensor, task_L, W0: torch.Tensor, *, E: int, T: int, n_fit: int | None = None,
                 perm: torch.Tensor | None = None, task_x: torch.Tensor | None = None, dump_step: int | None = None,
-                warps_per_task: int = 0, bucket: bool = True, **cfg_kw) -> FitResult:
+                warps_per_task: int = 0, bucket: bool = True, W_out: torch.Tensor | None = None, after_bucket=None,
+                **cfg_kw) -> FitResult:
     """Kernel (b) for a batch of tasks.  X f32 [n_x][T][E] (device, scaled); task_L sequence of ints;
     W0 f32 [n][w_stride] (device).  Tasks are grouped by padded latent width (multiples of 4) and each
     group is launched on its own stream, so a sweep over L runs concurrently."""
@@ -183,7 +184,10 @@ def fit_batched(X: torch.Tensor, task_L, W0: torch.Tensor, *, E: int, T: int, n_
         perms = perm.index_select(0, order_t).contiguous() if per_task_perm else perm
     perm_stride = perms.shape[1] * perms.shape[2] if per_task_perm else 0
 
-    W_out = torch.zeros_like(W0s)          # rows are packed with each task's own L; the tail stays zero
+    if W_out is None:
+        W_out = torch.zeros_like(W0s)      # rows are packed with each task's own L; the tail stays zero
+    if after_bucket is not None and not identity:
+        raise ValueError("after_bucket needs the tasks ordered widest-first (see run_mode_r)")
     loss = torch.full((n, cfg.max_epochs), float("nan"), dtype=torch.float32, device=device)
     val = torch.full((n, cfg.max_epochs), float("nan"), dtype=torch.float32, device=device)
     epochs_run = torch.zeros(n, dtype=torch.int32, device=device)
@@ -207,6 +211,8 @@ def fit_batched(X: torch.Tensor, task_L, W0: torch.Tensor, *, E: int, T: int, n_
                 C.byref(cfg), ptr(X), b - a, off(tL), off(tx), off(W0s), w_stride,
                 off(perms) if per_task_perm else ptr(perms), perm_stride, ptr(sched), off(W_out), off(loss),
                 off(val), off(epochs_run), off(status), off(grads), C.c_void_p(s.cuda_stream)))
+            if after_bucket is not None:
+                after_bucket(a, b, s.cuda_stream)      # e.g. this bucket's evaluation, right behind its fit
         if s is not main:
             done = torch.cuda.Event()
             done.record(s)
@@ -242,8 +248,11 @@ def rolling_sigma(R64: torch.Tensor, starts: torch.Tensor, window: int) -> torch
 
 def predict_metrics(Xtr64, Xte64, Yte64, rf64, sigma, task_L, W, *, window=24, want_oos=True,
                     want_weights=False, alpha=.2, cost_param=.05, phi=.5, task_row0=None, T_test=None,
-                    want_quality=True) -> EvalResult:
-    """Kernel (c) for a batch of trained tasks (all tensors on the device, float64 unless noted)."""
+                    want_quality=True, launch=True):
+    """Kernel (c) for a batch of trained tasks (all tensors on the device, float64 unless noted).
+    launch=False only allocates the result and returns (result, launcher): launcher(a, b, stream) scores tasks
+    [a, b) on `stream` — used to start a width bucket's evaluation right behind its fit, concurrently with the
+    other buckets' fits."""
     device = Xte64.device
     n = len(task_L)
     E = Xte64.shape[1]
@@ -262,10 +271,17 @@ def predict_metrics(Xtr64, Xte64, Yte64, rf64, sigma, task_L, W, *, window=24, w
         beta=torch.empty((n, _lib.MAX_L, F), **f64), norm=torch.empty((n, F), **f64),
         status=torch.zeros(n, dtype=torch.int32, device=device),
         weights=torch.empty((n, n_oos, E, F), **f64) if want_weights else None)
-    check(lib.hfrep_predict_metrics(
-        C.byref(cfg), ptr(Xtr64), ptr(Xte64), ptr(Yte64), ptr(rf64), ptr(sigma), n, ptr(tL), ptr(task_row0), ptr(W), W.shape[1],
-        ptr(r.ante), ptr(r.post), ptr(r.turnover), ptr(r.metrics), ptr(r.quality), ptr(r.mask), ptr(r.weights),
-        ptr(r.beta), ptr(r.norm), ptr(r.status), stream_ptr()))
+
+    def launcher(a, b, stream):
+        off = lambda t: None if t is None else C.c_void_p(t.data_ptr() + a * t.stride(0) * t.element_size())
+        check(lib.hfrep_predict_metrics(
+            C.byref(cfg), ptr(Xtr64), ptr(Xte64), ptr(Yte64), ptr(rf64), ptr(sigma), b - a, off(tL), off(task_row0), off(W),
+            W.shape[1], off(r.ante), off(r.post), off(r.turnover), off(r.metrics), off(r.quality), off(r.mask),
+            off(r.weights), off(r.beta), off(r.norm), off(r.status), C.c_void_p(stream)))
+
+    if not launch:
+        return r, launcher
+    launcher(0, n, torch.cuda.current_stream(device).cuda_stream)
     return r
 
 
@@ -310,6 +326,19 @@ class ReplicationData:
         self.h2d_bytes = (etf.nbytes + hfd.nbytes + rf.nbytes)
 
 
+def fit_and_score(data: "ReplicationData", task_L, W0d: torch.Tensor, *, perm=None, want_oos=True, want_weights=False,
+                  warps_per_task=0, **fit_kw):
+    """Kernel (b) then kernel (c) for tasks ordered widest-first: every width bucket's evaluation is queued on the
+    bucket's own stream right behind its fit, so it overlaps the fits of the other buckets."""
+    W_out = torch.zeros_like(W0d)
+    ev, score = predict_metrics(data.Xtr64, data.Xte64, data.Yte64, data.rf64, data.sigma, task_L, W_out,
+                                window=data.window, want_oos=want_oos, want_weights=want_weights,
+                                alpha=fit_kw.get("alpha", .2), launch=False)
+    fit = fit_batched(data.Xtr32, task_L, W0d, E=data.E, T=data.n_train, perm=perm, warps_per_task=warps_per_task,
+                      W_out=W_out, after_bucket=score, **fit_kw)
+    return fit, ev
+
+
 def run_mode_r(data: ReplicationData, latent_dims, seeds=(123,), *, W0=None, perm=None, want_oos=True,
                want_weights=False, warps_per_task=0, **fit_kw):
     """The notebook's sweep (autoencoder_v4.ipynb:158-165, :896-901) as one batched GPU pass:
@@ -326,11 +355,8 @@ def run_mode_r(data: ReplicationData, latent_dims, seeds=(123,), *, W0=None, per
         W0d = to_device(np.asarray(W0, np.float32), data.device)
         permd = None if perm is None else to_device(np.asarray(perm, np.int32), data.device)
         task_L = [L for L, _ in tasks]
-        fit = fit_batched(data.Xtr32, task_L, W0d, E=E, T=data.n_train, perm=permd,
-                          warps_per_task=warps_per_task, **fit_kw)
-        ev = predict_metrics(data.Xtr64, data.Xte64, data.Yte64, data.rf64, data.sigma, task_L, fit.W,
-                             window=data.window, want_oos=want_oos, want_weights=want_weights,
-                             alpha=fit_kw.get("alpha", .2))
+        fit, ev = fit_and_score(data, task_L, W0d, perm=permd, want_oos=want_oos, want_weights=want_weights,
+                                warps_per_task=warps_per_task, **fit_kw)
     return tasks, fit, ev
 
 
