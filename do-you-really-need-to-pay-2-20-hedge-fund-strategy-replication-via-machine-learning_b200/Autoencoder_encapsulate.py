@@ -165,11 +165,10 @@ class AE:
         with torch.cuda.device(dev):
             X = engine.to_device(self._x_train.astype(np.float32)[None], dev)
             W0 = engine.to_device(engine.pack_weights([(self.autoencoder.We, self.autoencoder.Wd)], E, 2 * E * L), dev)
-            perm = None
-            if config.shuffle:
-                perm = engine.to_device(engine.epoch_permutations(self.autoencoder._seed + 7, config.epochs, n_fit), dev)
-            res = engine.fit_batched(X, [L], W0, E=E, T=T, n_fit=n_fit, perm=perm, max_epochs=config.epochs,
-                                     batch=config.batch_size, patience=patience, early_stop=1)
+            # Keras fit(shuffle=True): a fresh row order every epoch, drawn on the device from the model's stream
+            shuffle_seeds = [(self.autoencoder._seed + 7) & 0xFFFFFFFF] if config.shuffle else None
+            res = engine.fit_batched(X, [L], W0, E=E, T=T, n_fit=n_fit, shuffle_seeds=shuffle_seeds,
+                                     max_epochs=config.epochs, batch=config.batch_size, patience=patience, early_stop=1)
             n = int(res.epochs_run[0])
             We, Wd = engine.unpack_weights(res.W[0].cpu().numpy(), E, L)
             loss, val = res.loss[0, :n].cpu().numpy(), res.val_loss[0, :n].cpu().numpy()

@@ -63,13 +63,13 @@ def _load():
     lib.hfrep_fit_cfg_default.argtypes = [C.POINTER(FitCfg)]
     lib.hfrep_fit_cfg_default.restype = None
     lib.hfrep_nadam_schedule.argtypes = [C.POINTER(FitCfg), C.c_int, vp]
-    lib.hfrep_fit_batched.argtypes = [C.POINTER(FitCfg), vp, C.c_int, vp, vp, vp, C.c_int, vp, i64, vp, vp, vp, vp,
+    lib.hfrep_fit_batched.argtypes = [C.POINTER(FitCfg), vp, C.c_int, vp, vp, vp, C.c_int, vp, i64, vp, vp, vp, vp, vp,
                                       vp, vp, vp, vp]
     lib.hfrep_fit_windows_workspace.argtypes = [C.c_int, C.c_int, C.c_int]
     lib.hfrep_fit_windows.argtypes = [C.POINTER(FitCfg), vp, C.c_int, C.c_int, C.c_int, vp, C.c_int, C.c_int, vp, vp, vp,
-                                      C.c_int, vp, i64, vp, vp, C.c_size_t, vp, vp, vp, vp, vp, vp]
+                                      C.c_int, vp, i64, vp, vp, vp, C.c_size_t, vp, vp, vp, vp, vp, vp]
     lib.hfrep_fit_windows_static.argtypes = [C.POINTER(FitCfg), vp, C.c_int, C.c_int, C.c_int, vp, C.c_int, C.c_int, vp, vp, vp,
-                                             C.c_int, vp, i64, vp, vp, vp, vp, vp, vp, vp]
+                                             C.c_int, vp, i64, vp, vp, vp, vp, vp, vp, vp, vp]
     lib.hfrep_eval_cfg_default.argtypes = [C.POINTER(EvalCfg)]
     lib.hfrep_eval_cfg_default.restype = None
     lib.hfrep_predict_metrics.argtypes = [C.POINTER(EvalCfg), vp, vp, vp, vp, vp, C.c_int, vp, vp, vp, C.c_int] + [vp] * 11

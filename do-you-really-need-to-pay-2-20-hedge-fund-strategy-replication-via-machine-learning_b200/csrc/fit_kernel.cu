@@ -37,6 +37,7 @@ struct FitParams {
     const int* task_x;
     const float* W0;
     const int* perm;
+    const unsigned* task_seed;   // per-task shuffle stream (device-side epoch permutations) or NULL
     const float4* sched;
     float* W_out;
     float* loss_hist;
@@ -45,6 +46,7 @@ struct FitParams {
     int* status;
     float* grad_out;
     long long perm_task_stride;
+    int PS;              // ints reserved per team for the device-side shuffle (0 or 2*n_fit rounded up to 4)
     int n_tasks, E, T, n_fit, n_val, batch, BP, max_epochs, patience, early_stop, w_stride, shared_x, dump_step;
     int force_tile;      // testing: batch-tile mode even when the block could be resident (env HFREP_FORCE_TILE)
     int debug_skip;      // profiling only (env HFREP_DEBUG_SKIP): bit0 rows, bit1 grads, bit2 update phases skipped
@@ -61,9 +63,9 @@ struct Lay {
     __host__ __device__ static constexpr bool mv_in_regs(int NW) { return NW >= 3; }
     // XT (batch-tile mode): the training block stays in global memory / L2 and only the current mini-batch's rows
     // sit in a per-team tile [BP+1][XS], refilled with cp.async; else the whole block is resident once per CTA.
-    __host__ __device__ static size_t team_floats(int BP, int NW, bool XT) {
+    __host__ __device__ static size_t team_floats(int BP, int NW, bool XT, int PS) {
         return (size_t)EP * LP + (size_t)LP * WDS + (size_t)(BP + 1) * HS * 2 + (size_t)(BP + 1) * XS +
-               (size_t)NW * NEL + (mv_in_regs(NW) ? 0 : 2 * (size_t)NEL) + 2 * BP + 64 + (XT ? (size_t)(BP + 1) * XS : 0);
+               (size_t)NW * NEL + (mv_in_regs(NW) ? 0 : 2 * (size_t)NEL) + 2 * BP + 64 + (XT ? (size_t)(BP + 1) * XS : 0) + PS;
     }
     __host__ __device__ static size_t cta_floats(int T, bool XT) { return (XT ? 0 : (size_t)(T + 1) * XS) + NEL; }
 };
@@ -135,7 +137,7 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
     const int T = p.T, E = p.E, BP = p.BP;
 
     const size_t cf = Lay<LP>::cta_floats(T, XT);
-    const size_t tf = Lay<LP>::team_floats(BP, NW, XT);
+    const size_t tf = Lay<LP>::team_floats(BP, NW, XT, p.PS);
     // [Xs (resident mode only) | woff | team 0 | team 1 ...]
     int* woff = reinterpret_cast<int*>(smem + (XT ? 0 : (size_t)(T + 1) * XS));
     float* base = smem + cf + (size_t)team * tf;
@@ -153,6 +155,8 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
     float* red = reinterpret_cast<float*>(xoff_tab + 2 * BP);          // [2][32], double-buffered per epoch
     // Xs: what the phases address rows in — the resident block (row r at xoff[r]) or the team's batch tile (row r at r*XS)
     float* Xs = XT ? red + 64 : smem;
+    unsigned* keyS = reinterpret_cast<unsigned*>(red + 64 + (XT ? (BP + 1) * XS : 0));   // [n_fit] shuffle keys
+    int* permS = reinterpret_cast<int*>(keyS) + p.PS / 2;                                  // [n_fit] this epoch's row order
     const int zero_row = XT ? BP * XS : T * XS;      // all-zero row for idle lanes
 
     // ---- stage the training block (fused window load: rows of the scaled block -> padded tile)
@@ -516,6 +520,28 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
     const int n_tb = (n_fit + batch - 1) / batch, n_vb = (n_val + batch - 1) / batch, n_seg = n_tb + n_vb;
     int step = 0, wait = 0, epochs_run = 0, st = 0, cur = 0;
     float best = INFINITY;
+    // Device-side stand-in for Keras' shuffle=True: the row order of an epoch is the stable argsort of 32-bit hash keys
+    // of (task stream, epoch, row) — a counter-based generator, so no state and no host table; oracle: fitcore.device_perm.
+    const bool dev_shuffle = p.task_seed != nullptr && perm_t == nullptr;
+    const unsigned stream_id = dev_shuffle ? p.task_seed[task] : 0u;
+    auto make_perm = [&](int epoch) {
+        for (int i = tl; i < n_fit; i += NTH) {
+            unsigned h = stream_id * 0x9E3779B1u ^ (unsigned)(epoch + 1) * 0x85EBCA77u ^ (unsigned)(i + 1) * 0xC2B2AE3Du;
+            h ^= h >> 16; h *= 0x85EBCA6Bu; h ^= h >> 13; h *= 0xC2B2AE35u; h ^= h >> 16;
+            keyS[i] = h;
+        }
+        team_sync<NW>(team);
+        for (int i = tl; i < n_fit; i += NTH) {
+            const unsigned k = keyS[i];
+            int rank = 0;
+            for (int j = 0; j < n_fit; ++j) {
+                const unsigned kj = keyS[j];
+                rank += (kj < k) || (kj == k && j < i);
+            }
+            permS[rank] = i;
+        }
+        team_sync<NW>(team);
+    };
     auto set_rows = [&](int* xoff, int epoch, int seg) {
         const bool val = seg >= n_tb;
         const int lo = (val ? seg - n_tb : seg) * batch;
@@ -526,7 +552,7 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
             const int ppr = E / pw;                       // pieces per row
             for (int idx = tl; idx < nb * ppr; idx += NTH) {
                 const int q = idx / ppr, c = (idx - q * ppr) * pw;
-                const int row = val ? n_fit + lo + q : (perm_t ? __ldg(perm_t + (size_t)epoch * n_fit + lo + q) : lo + q);
+                const int row = val ? n_fit + lo + q : (perm_t ? __ldg(perm_t + (size_t)epoch * n_fit + lo + q) : (dev_shuffle ? permS[lo + q] : lo + q));
                 const float* src = xg + (size_t)row * E + c;
                 const unsigned dst = (unsigned)__cvta_generic_to_shared(Xs + q * XS + c);
                 if (pw == 4) asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
@@ -536,7 +562,7 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
             asm volatile("cp.async.commit_group;" ::: "memory");
         } else {
             for (int q = tl; q < nb; q += NTH) {
-                const int row = val ? n_fit + lo + q : (perm_t ? __ldg(perm_t + (size_t)epoch * n_fit + lo + q) : lo + q);
+                const int row = val ? n_fit + lo + q : (perm_t ? __ldg(perm_t + (size_t)epoch * n_fit + lo + q) : (dev_shuffle ? permS[lo + q] : lo + q));
                 xoff[q] = row * XS;
             }
         }
@@ -544,6 +570,7 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
     auto rows_ready = [&]() {                          // the tile refill issued by this thread has landed
         if constexpr (XT) asm volatile("cp.async.wait_group 0;" ::: "memory");
     };
+    if (dev_shuffle) make_perm(0);
     set_rows(xoff_tab, 0, 0);
     rows_ready();
     team_sync<NW>(team);
@@ -560,7 +587,11 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
             // offset table right away; tile mode refills the single tile once its last reader is done
             auto prefetch_next = [&]() {
                 if (seg + 1 < n_seg) set_rows(xnext, epoch, seg + 1);
-                else set_rows(xnext, epoch + 1 < p.max_epochs ? epoch + 1 : epoch, 0);
+                else {
+                    const int ne = epoch + 1 < p.max_epochs ? epoch + 1 : epoch;
+                    if (dev_shuffle) make_perm(ne);       // this epoch's order is no longer needed: its last table is out
+                    set_rows(xnext, ne, 0);
+                }
             };
             if constexpr (!XT) prefetch_next();
             float sse = 0.f;
@@ -634,7 +665,7 @@ constexpr size_t kMaxSmem = 227 * 1024;
 
 template <int LP, int NW>
 static size_t fit_smem_bytes(const FitParams& p, int tpc, bool xt) {
-    return sizeof(float) * (Lay<LP>::cta_floats(p.T, xt) + tpc * Lay<LP>::team_floats(p.BP, NW, xt));
+    return sizeof(float) * (Lay<LP>::cta_floats(p.T, xt) + tpc * Lay<LP>::team_floats(p.BP, NW, xt, p.PS));
 }
 
 // Resident mode: teams of one CTA share the staged training block, so several teams per CTA need n_x == 1 and the block
@@ -727,10 +758,10 @@ extern "C" int hfrep_nadam_schedule(const hfrep_fit_cfg* c, int n_steps, float* 
 }
 
 static int fit_batched_impl(const hfrep_fit_cfg* c, const float* X, int n_tasks, const int32_t* task_L,
-                                 const int32_t* task_x, const float* W0, int w_stride, const int32_t* perm,
-                                 int64_t perm_task_stride, const float* sched, float* W_out, float* loss_hist,
-                                 float* val_hist, int32_t* epochs_run, int32_t* status, float* grad_out,
-                                 void* stream) {
+                            const int32_t* task_x, const float* W0, int w_stride, const int32_t* perm,
+                            int64_t perm_task_stride, const uint32_t* task_seed, const float* sched, float* W_out,
+                            float* loss_hist, float* val_hist, int32_t* epochs_run, int32_t* status, float* grad_out,
+                            void* stream) {
     HFREP_REQUIRE(c && X && task_L && W0 && sched && W_out && loss_hist && val_hist && epochs_run && status,
                   "fit_batched: null argument");
     HFREP_REQUIRE(n_tasks >= 0, "fit_batched: n_tasks=%d", n_tasks);
@@ -745,7 +776,8 @@ static int fit_batched_impl(const hfrep_fit_cfg* c, const float* X, int n_tasks,
     HFREP_REQUIRE(((uintptr_t)sched & 15) == 0, "fit_batched: sched must be 16-byte aligned");
 
     FitParams p;
-    p.X = X; p.task_L = task_L; p.task_x = task_x; p.W0 = W0; p.perm = perm;
+    p.X = X; p.task_L = task_L; p.task_x = task_x; p.W0 = W0; p.perm = perm; p.task_seed = task_seed;
+    p.PS = (task_seed && !perm) ? ((2 * c->n_fit + 3) & ~3) : 0;
     p.sched = reinterpret_cast<const float4*>(sched);
     p.W_out = W_out; p.loss_hist = loss_hist; p.val_hist = val_hist; p.epochs_run = epochs_run; p.status = status;
     p.grad_out = grad_out; p.perm_task_stride = perm_task_stride;
@@ -767,11 +799,11 @@ static int fit_batched_impl(const hfrep_fit_cfg* c, const float* X, int n_tasks,
 
 extern "C" int hfrep_fit_batched(const hfrep_fit_cfg* c, const float* X, int n_tasks, const int32_t* task_L,
                                  const int32_t* task_x, const float* W0, int w_stride, const int32_t* perm,
-                                 int64_t perm_task_stride, const float* sched, float* W_out, float* loss_hist,
-                                 float* val_hist, int32_t* epochs_run, int32_t* status, float* grad_out,
+                                 int64_t perm_task_stride, const uint32_t* task_seed, const float* sched, float* W_out,
+                                 float* loss_hist, float* val_hist, int32_t* epochs_run, int32_t* status, float* grad_out,
                                  void* stream) {
-    return fit_batched_impl(c, X, n_tasks, task_L, task_x, W0, w_stride, perm, perm_task_stride, sched, W_out, loss_hist,
-                            val_hist, epochs_run, status, grad_out, stream);
+    return fit_batched_impl(c, X, n_tasks, task_L, task_x, W0, w_stride, perm, perm_task_stride, task_seed, sched, W_out,
+                            loss_hist, val_hist, epochs_run, status, grad_out, stream);
 }
 
 // Rolling refit (Mode W): kernel (a) builds every window's MinMax-scaled training block into the caller's workspace,
@@ -784,8 +816,9 @@ extern "C" size_t hfrep_fit_windows_workspace(int n_windows, int T_win, int E) {
 extern "C" int hfrep_fit_windows(const hfrep_fit_cfg* c, const float* R, int T_all, int C, int col_lo,
                                  const int32_t* win_starts, int n_windows, int n_tasks, const int32_t* task_L,
                                  const int32_t* task_win, const float* W0, int w_stride, const int32_t* perm,
-                                 int64_t perm_task_stride, const float* sched, void* ws, size_t ws_bytes, float* W_out,
-                                 float* loss_hist, float* val_hist, int32_t* epochs_run, int32_t* status, void* stream) {
+                                 int64_t perm_task_stride, const uint32_t* task_seed, const float* sched, void* ws,
+                                 size_t ws_bytes, float* W_out, float* loss_hist, float* val_hist, int32_t* epochs_run,
+                                 int32_t* status, void* stream) {
     HFREP_REQUIRE(c && R && win_starts && task_win, "fit_windows: null argument");
     HFREP_REQUIRE(n_windows >= 1, "fit_windows: n_windows=%d", n_windows);
     const size_t need = hfrep_fit_windows_workspace(n_windows, c->T, c->E);
@@ -797,8 +830,8 @@ extern "C" int hfrep_fit_windows(const hfrep_fit_cfg* c, const float* R, int T_a
     if (rc != HFREP_OK) return rc;
     hfrep_fit_cfg cc = *c;
     cc.n_x = n_windows > 1 ? n_windows : 2;          // every task trains on its own block: one team per CTA
-    return fit_batched_impl(&cc, blocks, n_tasks, task_L, task_win, W0, w_stride, perm, perm_task_stride, sched, W_out,
-                            loss_hist, val_hist, epochs_run, status, nullptr, stream);
+    return fit_batched_impl(&cc, blocks, n_tasks, task_L, task_win, W0, w_stride, perm, perm_task_stride, task_seed, sched,
+                            W_out, loss_hist, val_hist, epochs_run, status, nullptr, stream);
 }
 
 // ------------------------------------------------------------------------------------------------------------
@@ -838,9 +871,9 @@ static int static_scratch_address(float** out) {
 extern "C" int hfrep_fit_windows_static(const hfrep_fit_cfg* c, const float* R, int T_all, int C, int col_lo,
                                         const int32_t* win_starts, int n_windows, int n_tasks,
                                         const int32_t* task_L, const int32_t* task_win, const float* W0, int w_stride,
-                                        const int32_t* perm, int64_t perm_task_stride, const float* sched,
-                                        float* W_out, float* loss_hist, float* val_hist, int32_t* epochs_run,
-                                        int32_t* status, void* stream) {
+                                        const int32_t* perm, int64_t perm_task_stride, const uint32_t* task_seed,
+                                        const float* sched, float* W_out, float* loss_hist, float* val_hist,
+                                        int32_t* epochs_run, int32_t* status, void* stream) {
     HFREP_REQUIRE(c != nullptr, "fit_windows_static: null argument");
     const size_t need = hfrep_fit_windows_workspace(n_windows, c->T, c->E);
     HFREP_REQUIRE(n_windows >= 1 && need > 0, "fit_windows_static: n_windows=%d T=%d E=%d", n_windows, c->T, c->E);
@@ -852,6 +885,6 @@ extern "C" int hfrep_fit_windows_static(const hfrep_fit_cfg* c, const float* R, 
     const int rc = static_scratch_address(&scratch);
     if (rc != HFREP_OK) return rc;
     return hfrep_fit_windows(c, R, T_all, C, col_lo, win_starts, n_windows, n_tasks, task_L, task_win, W0, w_stride, perm,
-                             perm_task_stride, sched, scratch, (size_t)HFREP_STATIC_SCRATCH_BYTES, W_out, loss_hist,
+                             perm_task_stride, task_seed, sched, scratch, (size_t)HFREP_STATIC_SCRATCH_BYTES, W_out, loss_hist,
                              val_hist, epochs_run, status, stream);
 }

@@ -52,6 +52,21 @@ def initial_weights(seed: int, E: int, L: int):
     return out[0], out[1]
 
 
+def device_permutations(stream_seed: int, epochs: int, n_fit: int) -> np.ndarray:
+    """Host replica of the kernel's device-side epoch shuffles (hfrep.h, task_seed): stable argsort of murmur3-finalised
+    keys of (seed, epoch, row).  For inspection and tests; the kernel never needs the table."""
+    M = np.uint64(0xFFFFFFFF)
+    i = np.arange(1, n_fit + 1, dtype=np.uint64)
+    out = np.empty((epochs, n_fit), np.int32)
+    for e in range(epochs):
+        h = (np.uint64(stream_seed) * np.uint64(0x9E3779B1) & M) ^ (np.uint64(e + 1) * np.uint64(0x85EBCA77) & M) ^ (i * np.uint64(0xC2B2AE3D) & M)
+        h ^= h >> np.uint64(16); h = h * np.uint64(0x85EBCA6B) & M
+        h ^= h >> np.uint64(13); h = h * np.uint64(0xC2B2AE35) & M
+        h ^= h >> np.uint64(16)
+        out[e] = np.argsort(h, kind="stable")
+    return out
+
+
 def epoch_permutations(seed: int, epochs: int, n_fit: int) -> np.ndarray:
     """Per-epoch row orders standing in for Keras' shuffle=True (int32 [epochs][n_fit])."""
     rng = np.random.Generator(np.random.Philox(key=int(seed)))
@@ -148,6 +163,7 @@ def _side_streams(device, n):
 def fit_batched(X: torch.Tensor, task_L, W0: torch.Tensor, *, E: int, T: int, n_fit: int | None = None,
                 perm: torch.Tensor | None = None, task_x: torch.Tensor | None = None, dump_step: int | None = None,
                 warps_per_task: int = 0, bucket: bool = True, W_out: torch.Tensor | None = None, after_bucket=None,
+                shuffle_seeds=None,
                 **cfg_kw) -> FitResult:
     """Kernel (b) for a batch of tasks.  X f32 [n_x][T][E] (device, scaled); task_L sequence of ints;
     W0 f32 [n][w_stride] (device).  Tasks are grouped by padded latent width (multiples of 4) and each
@@ -183,6 +199,9 @@ def fit_batched(X: torch.Tensor, task_L, W0: torch.Tensor, *, E: int, T: int, n_
         tx = task_x.index_select(0, order_t).contiguous() if task_x is not None else None
         perms = perm.index_select(0, order_t).contiguous() if per_task_perm else perm
     perm_stride = perms.shape[1] * perms.shape[2] if per_task_perm else 0
+    tseed = None
+    if shuffle_seeds is not None:                      # device-side epoch shuffles (Keras shuffle=True), one stream per task
+        tseed = _device_ints(np.asarray(shuffle_seeds, np.uint32)[order].view(np.int32), device)
 
     if W_out is None:
         W_out = torch.zeros_like(W0s)      # rows are packed with each task's own L; the tail stays zero
@@ -209,7 +228,7 @@ def fit_batched(X: torch.Tensor, task_L, W0: torch.Tensor, *, E: int, T: int, n_
             off = lambda t, a=a: None if t is None else C.c_void_p(t.data_ptr() + a * t.stride(0) * t.element_size())
             check(lib.hfrep_fit_batched(
                 C.byref(cfg), ptr(X), b - a, off(tL), off(tx), off(W0s), w_stride,
-                off(perms) if per_task_perm else ptr(perms), perm_stride, ptr(sched), off(W_out), off(loss),
+                off(perms) if per_task_perm else ptr(perms), perm_stride, off(tseed), ptr(sched), off(W_out), off(loss),
                 off(val), off(epochs_run), off(status), off(grads), C.c_void_p(s.cuda_stream)))
             if after_bucket is not None:
                 after_bucket(a, b, s.cuda_stream)      # e.g. this bucket's evaluation, right behind its fit
@@ -335,14 +354,15 @@ def fit_and_score(data: "ReplicationData", task_L, W0d: torch.Tensor, *, perm=No
                                 window=data.window, want_oos=want_oos, want_weights=want_weights,
                                 alpha=fit_kw.get("alpha", .2), launch=False)
     fit = fit_batched(data.Xtr32, task_L, W0d, E=data.E, T=data.n_train, perm=perm, warps_per_task=warps_per_task,
-                      W_out=W_out, after_bucket=score, **fit_kw)
+                      W_out=W_out, after_bucket=score, **fit_kw)      # fit_kw may carry shuffle_seeds
     return fit, ev
 
 
-def run_mode_r(data: ReplicationData, latent_dims, seeds=(123,), *, W0=None, perm=None, want_oos=True,
+def run_mode_r(data: ReplicationData, latent_dims, seeds=(123,), *, W0=None, perm=None, shuffle=False, want_oos=True,
                want_weights=False, warps_per_task=0, **fit_kw):
     """The notebook's sweep (autoencoder_v4.ipynb:158-165, :896-901) as one batched GPU pass:
-    for every (L, seed): fit, IS/OOS quality, ante, turnover, post, metrics.
+    for every (L, seed): fit, IS/OOS quality, ante, turnover, post, metrics.  shuffle=False is the deterministic row
+    order used for parity; shuffle=True reshuffles the fit rows every epoch on the device (Keras' default).
     Returns (tasks, FitResult, EvalResult); tasks[i] = (L, seed)."""
     # widest (slowest) tasks first: that is the launch order of the width buckets, and it spares a gather
     tasks = sorted(((int(L), int(s)) for s in seeds for L in latent_dims), key=lambda t: -((t[0] + 3) // 4))
@@ -355,6 +375,8 @@ def run_mode_r(data: ReplicationData, latent_dims, seeds=(123,), *, W0=None, per
         W0d = to_device(np.asarray(W0, np.float32), data.device)
         permd = None if perm is None else to_device(np.asarray(perm, np.int32), data.device)
         task_L = [L for L, _ in tasks]
+        if shuffle and perm is None:        # Keras' default shuffle=True: one device-side stream per (L, seed)
+            fit_kw["shuffle_seeds"] = [(s * 1000003 + L) & 0xFFFFFFFF for L, s in tasks]
         fit, ev = fit_and_score(data, task_L, W0d, perm=permd, want_oos=want_oos, want_weights=want_weights,
                                 warps_per_task=warps_per_task, **fit_kw)
     return tasks, fit, ev
@@ -362,7 +384,7 @@ def run_mode_r(data: ReplicationData, latent_dims, seeds=(123,), *, W0=None, per
 
 # ------------------------------------------------------------------------------------ Mode W front-end
 def fit_windows(R32: torch.Tensor, win_starts, T_win: int, task_L, task_win, W0: torch.Tensor, *, E: int, col_lo: int = 0,
-                perm: torch.Tensor | None = None, warps_per_task: int = 0, **cfg_kw):
+                perm: torch.Tensor | None = None, warps_per_task: int = 0, shuffle_seeds=None, **cfg_kw):
     """hfrep_fit_windows: kernel (a) gathers + MinMax-scales every training window into a scratch buffer, kernel (b)
     fits task i on window task_win[i].  Returns (FitResult, scratch blocks f32 [n_windows][T_win][E])."""
     device = R32.device
@@ -384,9 +406,10 @@ def fit_windows(R32: torch.Tensor, win_starts, T_win: int, task_L, task_win, W0:
     epochs_run = torch.zeros(n, dtype=torch.int32, device=device)
     status = torch.zeros(n, dtype=torch.int32, device=device)
     per_task_perm = perm is not None and perm.dim() == 3
+    tseed = None if shuffle_seeds is None else _device_ints(np.asarray(shuffle_seeds, np.uint32).view(np.int32), device)
     check(lib.hfrep_fit_windows(C.byref(cfg), ptr(R32), T_all, Cc, col_lo, ptr(starts), n_win, n, ptr(tL), ptr(tw),
                                 ptr(W0), W0.shape[1], ptr(perm), perm.shape[1] * perm.shape[2] if per_task_perm else 0,
-                                ptr(sched), ptr(ws), ws_bytes, ptr(W_out), ptr(loss), ptr(val), ptr(epochs_run),
+                                ptr(tseed), ptr(sched), ptr(ws), ws_bytes, ptr(W_out), ptr(loss), ptr(val), ptr(epochs_run),
                                 ptr(status), stream_ptr()))
     return FitResult(W_out, loss, val, epochs_run, status, None, W0.shape[1]), ws.view(n_win, T_win, E)
 

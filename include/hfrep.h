@@ -98,6 +98,9 @@ int hfrep_nadam_schedule(const hfrep_fit_cfg* cfg, int n_steps, float* sched_hos
  *   W0       f32 [n_tasks][w_stride] initial kernels: We (E x L) then Wd (L x E), packed with the task's own L
  *   perm     int32 [.. ][epochs][n_fit] per-epoch row order; NULL = no shuffling; perm_task_stride
  *            (in int32 elements) = 0 shares one table between all tasks
+ *   task_seed uint32 [n_tasks] | NULL  device-side epoch shuffles (Keras fit's shuffle=True without a host table): when
+ *            perm is NULL and task_seed is not, every epoch's row order is the stable argsort of the hash keys
+ *            fmix32(seed*0x9E3779B1 ^ (epoch+1)*0x85EBCA77 ^ (row+1)*0xC2B2AE3D) of the task's seed (murmur3 finaliser)
  *   sched    f32 [>= max_epochs*ceil(n_fit/batch)][4]  from hfrep_nadam_schedule, on the device
  *   W_out    f32 [n_tasks][w_stride]       final kernels, same packing
  *   loss_hist/val_hist f32 [n_tasks][max_epochs]   history.history['loss'|'val_loss']
@@ -106,8 +109,9 @@ int hfrep_nadam_schedule(const hfrep_fit_cfg* cfg, int n_steps, float* sched_hos
  */
 int hfrep_fit_batched(const hfrep_fit_cfg* cfg, const float* X, int n_tasks, const int32_t* task_L,
                       const int32_t* task_x, const float* W0, int w_stride, const int32_t* perm,
-                      int64_t perm_task_stride, const float* sched, float* W_out, float* loss_hist,
-                      float* val_hist, int32_t* epochs_run, int32_t* status, float* grad_out, void* stream);
+                      int64_t perm_task_stride, const uint32_t* task_seed, const float* sched, float* W_out,
+                      float* loss_hist, float* val_hist, int32_t* epochs_run, int32_t* status, float* grad_out,
+                      void* stream);
 
 /* Rolling refit (the north_star's per-window task; SURVEY §8d "Mode W", not in the reference): task i trains on the
  * window R[win_starts[task_win[i]] .. +cfg->T)[col_lo .. col_lo+cfg->E), MinMax-scaled per window exactly as
@@ -118,8 +122,9 @@ size_t hfrep_fit_windows_workspace(int n_windows, int T_win, int E);
 int hfrep_fit_windows(const hfrep_fit_cfg* cfg, const float* R, int T_all, int C, int col_lo,
                       const int32_t* win_starts, int n_windows, int n_tasks, const int32_t* task_L,
                       const int32_t* task_win, const float* W0, int w_stride, const int32_t* perm,
-                      int64_t perm_task_stride, const float* sched, void* ws, size_t ws_bytes, float* W_out,
-                      float* loss_hist, float* val_hist, int32_t* epochs_run, int32_t* status, void* stream);
+                      int64_t perm_task_stride, const uint32_t* task_seed, const float* sched, void* ws,
+                      size_t ws_bytes, float* W_out, float* loss_hist, float* val_hist, int32_t* epochs_run,
+                      int32_t* status, void* stream);
 
 /* hfrep_fit_windows for callers that cannot allocate device memory.  (No counterpart in the reference: the reference
  * never touches a GPU.)  Same arguments as hfrep_fit_windows minus the workspace: the scaled window blocks go into a
@@ -133,8 +138,8 @@ int hfrep_fit_windows(const hfrep_fit_cfg* cfg, const float* R, int T_all, int C
 int hfrep_fit_windows_static(const hfrep_fit_cfg* cfg, const float* R, int T_all, int C, int col_lo,
                              const int32_t* win_starts, int n_windows, int n_tasks, const int32_t* task_L,
                              const int32_t* task_win, const float* W0, int w_stride, const int32_t* perm,
-                             int64_t perm_task_stride, const float* sched, float* W_out, float* loss_hist,
-                             float* val_hist, int32_t* epochs_run, int32_t* status, void* stream);
+                             int64_t perm_task_stride, const uint32_t* task_seed, const float* sched, float* W_out,
+                             float* loss_hist, float* val_hist, int32_t* epochs_run, int32_t* status, void* stream);
 
 /* ---------------------------------------------------------------------------------------
  * Kernel (c): fused out-of-sample predict + rolling OLS + replica + ex-post + metrics, one

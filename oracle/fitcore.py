@@ -212,3 +212,21 @@ def make_perm(seed: int, epochs: int, n_fit: int) -> np.ndarray:
     """Explicit per-epoch row orders standing in for Keras' shuffle=True (App. A.3)."""
     rng = np.random.Generator(np.random.Philox(key=int(seed)))
     return np.stack([rng.permutation(n_fit) for _ in range(epochs)]).astype(np.int32)
+
+
+def device_perm(stream_seed: int, epochs: int, n_fit: int) -> np.ndarray:
+    """The CUDA path's device-side epoch shuffle restated (include/hfrep.h, `task_seed`): per epoch the stable argsort of
+    fmix32(seed*0x9E3779B1 ^ (epoch+1)*0x85EBCA77 ^ (row+1)*0xC2B2AE3D).  A stand-in for Keras' shuffle=True whose RNG
+    cannot be reproduced; both sides of a parity check use this table."""
+    M = 0xFFFFFFFF
+    out = np.empty((epochs, n_fit), np.int32)
+    for e in range(epochs):
+        keys = []
+        for i in range(n_fit):
+            h = ((stream_seed * 0x9E3779B1) & M) ^ (((e + 1) * 0x85EBCA77) & M) ^ (((i + 1) * 0xC2B2AE3D) & M)
+            h ^= h >> 16; h = (h * 0x85EBCA6B) & M
+            h ^= h >> 13; h = (h * 0xC2B2AE35) & M
+            h ^= h >> 16
+            keys.append(h)
+        out[e] = np.argsort(np.array(keys, np.uint64), kind="stable")
+    return out

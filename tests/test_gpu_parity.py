@@ -370,3 +370,27 @@ def test_long_training_block_stacked_rows(hf):
         assert np.max(np.abs(res.val_loss[0, :6].cpu().numpy() - o["val_loss"]) / o["val_loss"]) < TOL
         We, Wd = hf.engine.unpack_weights(res.W[0].cpu().numpy(), E, L)
         assert rel_err(We, o["We"]) < TOL and rel_err(Wd, o["Wd"]) < TOL
+
+
+def test_device_side_shuffle(hf, data):
+    """Device-side epoch shuffles (task_seed): the kernel's counter-based permutations equal the oracle's table, and a fit
+    driven by them equals the oracle fit driven by that table (early stopping included)."""
+    from oracle import fitcore
+    g = load_golden("ref_modeR_L8")
+    x = data.Xtr32[0].cpu().numpy()
+    seeds = [5, 77777]
+    tabs = [fitcore.device_perm(s, 40, 126) for s in seeds]
+    assert np.array_equal(tabs[0], hf.engine.device_permutations(5, 40, 126))
+    assert sorted(tabs[0][3].tolist()) == list(range(126)) and not np.array_equal(tabs[0][3], tabs[1][3])
+    E, L = data.E, 8
+    W0 = hf.engine.to_device(hf.engine.pack_weights([(g["We0"], g["Wd0"])] * 2, E, 2 * E * L), data.device)
+    for wpt in (1, 3, 6):
+        res = hf.fit_batched(data.Xtr32, [L, L], W0, E=E, T=168, max_epochs=40, patience=3, shuffle_seeds=seeds,
+                             warps_per_task=wpt)
+        for i, tab in enumerate(tabs):
+            o = fitcore.fit(x, g["We0"], g["Wd0"], fitcore.FitConfig(epochs=40, patience=3), perm=tab)
+            n = int(res.epochs_run[i])
+            assert n == o["epochs_run"]
+            assert np.max(np.abs(res.loss[i, :n].cpu().numpy() - o["loss"]) / o["loss"]) < TOL
+            We, _ = hf.engine.unpack_weights(res.W[i].cpu().numpy(), E, L)
+            assert rel_err(We, o["We"]) < TOL

@@ -99,7 +99,7 @@ def test_argument_validation_without_gpu():
     """Bad shapes are rejected before any CUDA call."""
     cfg = _lib.fit_cfg(E=30)
     one = ctypes.c_void_p(16)
-    rc = _lib.lib.hfrep_fit_batched(ctypes.byref(cfg), one, 1, one, None, one, 2000, None, 0, one, one, one, one, one, one,
+    rc = _lib.lib.hfrep_fit_batched(ctypes.byref(cfg), one, 1, one, None, one, 2000, None, 0, None, one, one, one, one, one, one,
                                     None, None)
     assert rc == -1 and b"E=30" in _lib.lib.hfrep_last_error()
     ecfg = _lib.eval_cfg(window=100)

@@ -29,13 +29,13 @@ def _call(hf, static, R, starts, T_win, E, task_L, task_win, W0, epochs):
     stream = hf._lib.stream_ptr()
     if static:
         rc = lib.hfrep_fit_windows_static(C.byref(cfg), ptr(R), R.shape[0], R.shape[1], 0, ptr(st), n_win, n, ptr(tL), ptr(tw),
-                                          ptr(W0), W0.shape[1], None, 0, ptr(sched), ptr(out["W"]), ptr(out["loss"]),
+                                          ptr(W0), W0.shape[1], None, 0, None, ptr(sched), ptr(out["W"]), ptr(out["loss"]),
                                           ptr(out["val"]), ptr(out["epochs"]), ptr(out["status"]), stream)
     else:
         ws_bytes = lib.hfrep_fit_windows_workspace(n_win, T_win, E)
         ws = torch.empty(ws_bytes // 4, dtype=torch.float32, device=dev)
         rc = lib.hfrep_fit_windows(C.byref(cfg), ptr(R), R.shape[0], R.shape[1], 0, ptr(st), n_win, n, ptr(tL), ptr(tw),
-                                   ptr(W0), W0.shape[1], None, 0, ptr(sched), ptr(ws), ws_bytes, ptr(out["W"]),
+                                   ptr(W0), W0.shape[1], None, 0, None, ptr(sched), ptr(ws), ws_bytes, ptr(out["W"]),
                                    ptr(out["loss"]), ptr(out["val"]), ptr(out["epochs"]), ptr(out["status"]), stream)
     torch.cuda.synchronize()
     return rc, out
@@ -71,7 +71,7 @@ def test_fit_windows_static_rejects_oversize():
     cfg = hf._lib.fit_cfg(E=E, T=T_win, n_fit=126, L_max=4)
     one = torch.zeros(16, device=dev)
     p = hf._lib.ptr(one)
-    rc = hf._lib.lib.hfrep_fit_windows_static(C.byref(cfg), p, 400, E, 0, p, n_win, 1, p, p, p, 2 * E * 4, None, 0, p,
+    rc = hf._lib.lib.hfrep_fit_windows_static(C.byref(cfg), p, 400, E, 0, p, n_win, 1, p, p, p, 2 * E * 4, None, 0, None, p,
                                               p, p, p, p, p, None)
     assert rc == -1
     msg = hf._lib.lib.hfrep_last_error().decode()
