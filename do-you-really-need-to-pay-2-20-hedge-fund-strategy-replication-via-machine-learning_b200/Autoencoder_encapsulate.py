@@ -27,6 +27,7 @@ class config:
     epochs = 1000           # Autoencoder_encapsulate.py:86
     batch_size = 48         # :88
     validation_split = .25  # :89
+    beta_index = "first"    # 'first' = the reference (window 0's OLS for every month, :167); 'rolling' = window k for month k
 
 
 class MinMaxScaler:
@@ -193,7 +194,7 @@ class AE:
             plt.show()
 
     # -- kernel (c) ---------------------------------------------------------------------------
-    def _evaluate(self, rf_test=None, window=24, want_oos=True, want_weights=False):
+    def _evaluate(self, rf_test=None, window=24, want_oos=True, want_weights=False, beta_rolling=False):
         dev = self._device()
         x_test = np.asarray(self._x_test, np.float64)
         y_test = np.asarray(self._y_test, np.float64)
@@ -205,7 +206,7 @@ class AE:
             ev = engine.predict_metrics(
                 engine.to_device(self._x_train, dev), engine.to_device(x_test, dev), engine.to_device(y_test, dev),
                 engine.to_device(np.asarray(rf_test, np.float64), dev), None, [self._latent_dim], self._packed(dev),
-                window=window, want_oos=want_oos, want_weights=want_weights)
+                window=window, want_oos=want_oos, want_weights=want_weights, beta_rolling=beta_rolling)
             torch.cuda.current_stream().synchronize()
         return ev
 
@@ -241,7 +242,8 @@ class AE:
         rf_tail = np.asarray(rf.iloc[-n_oos:], np.float64).reshape(-1)               # :185
         rf_test = np.zeros(n_test)
         rf_test[n_test - n_oos:] = rf_tail
-        ev = self._evaluate(rf_test, window=window, want_oos=False, want_weights=True)
+        ev = self._evaluate(rf_test, window=window, want_oos=False, want_weights=True,
+                            beta_rolling=(config.beta_index == "rolling"))
         ante = ev.ante[0].cpu().numpy()
         w = ev.weights[0].cpu().numpy()                                             # (n_oos, E, F)
         self._turnover = ev.turnover[0].cpu().numpy()

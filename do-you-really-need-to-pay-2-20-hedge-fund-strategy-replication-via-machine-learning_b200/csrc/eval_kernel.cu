@@ -30,6 +30,7 @@ struct EvalParams {
     double* ante; double* post; double* turnover; double* metrics; double* quality;
     unsigned char* mask; double* weights; double* beta; double* norm; int* status;
     int n_tasks, w_stride, E, F, T_train, T_test, window, want_oos, n_oos, n_pre, acols;
+    int rolling, nq, wsz; // beta_rolling: OLS of every window (nq warps, one workspace of wsz doubles each)
     int qsplit;           // CTAs per task: CTA (task, part) scores prefixes part, part+qsplit, ...; part 0 also builds the replica
     int off_float;        // byte offset of the float32 region inside dynamic shared memory (16-byte aligned)
     float alpha;
@@ -205,15 +206,15 @@ __global__ void __launch_bounds__(NTH_EVAL) eval_kernel(const EvalParams p) {
     const double* rfv = p.rf + row0;
 
     // ---- shared memory carve-up (doubles first)
-    double* A = reinterpret_cast<double*>(smem_raw);              // [window][acols]  QR workspace [M_w | Y_w]
-    double* betaS = A + (size_t)window * p.acols;                 // [HFREP_MAX_L][F]
-    double* G = betaS + HFREP_MAX_L * F;                          // [F][E]
-    double* normS = G + F * E;                                    // [F]
-    double* anteS = normS + F;                                    // [n_oos][F]
+    // OLS workspaces: nq blocks of wsz doubles = [A (window x acols) | beta (MAX_L x F) | G (F x E) | norm (F) | vhh (window)]
+    double* wsp = reinterpret_cast<double*>(smem_raw);
+    double* betaS = wsp + (size_t)window * p.acols;               // workspace 0: beta_0, G_0, norm_0 (the reference's choice)
+    double* G = betaS + HFREP_MAX_L * F;
+    double* normS = G + F * E;
+    double* anteS = wsp + (size_t)p.nq * p.wsz;                   // [n_oos][F]
     double* postS = anteS + (size_t)n_oos * F;                    // [n_oos][F]
     double* turnS = postS + (size_t)n_oos * F;                    // [n_oos][F]
     double* cstat = turnS + (size_t)n_oos * F;                    // [NW][3][HFREP_MAX_E]
-    double* vhh = cstat + NW * 3 * HFREP_MAX_E;                   // [window] Householder vector
     float* We = reinterpret_cast<float*>(smem_raw + p.off_float); // [E][WS]
     float* Wd = We + HFREP_MAX_E * WS;                            // [L][WS]
     float* M = Wd + HFREP_MAX_L * WS;                             // [T_test][WS] latent factors
@@ -299,23 +300,32 @@ __global__ void __launch_bounds__(NTH_EVAL) eval_kernel(const EvalParams p) {
         maskS[idx] = acc < 0.f ? 1 : 0;
     }
 
-    // ---- OLS on window 0 (:148-156): Householder QR of [M_0 | Y_0] in float64, warp 0, lane = column
+    // ---- OLS (:148-156): Householder QR of [M_w | Y_w] in float64 by one warp (lane = column), then
+    //      helper.normalization (helper.py:10-17) and G_w = beta_w^T Wd (:167).  The reference only ever uses window 0
+    //      (App. B.1); beta_rolling solves every window and writes that month's weights straight to `weights`.
     const int ncol = L + F;
-    if (warp == 0) {
+    auto ols_window = [&](int w0, double* ws) {
+        double* A = ws;
+        double* beta = A + (size_t)window * p.acols;
+        double* Gw = beta + HFREP_MAX_L * F;
+        double* normW = Gw + F * E;
+        double* vhh = normW + F;
+        const float* Mw = M + (size_t)w0 * WS;
+        const double* Yw = Yte + (size_t)w0 * F;
         for (int idx = lane; idx < window * ncol; idx += 32) {
             const int r = idx / ncol, c = idx - r * ncol;
-            A[r * p.acols + c] = c < L ? (double)M[r * WS + c] : Yte[(size_t)r * F + (c - L)];
+            A[r * p.acols + c] = c < L ? (double)Mw[r * WS + c] : Yw[(size_t)r * F + (c - L)];
         }
         __syncwarp();
         double dmax = 0., dmin = INFINITY;
         for (int k = 0; k < L; ++k) {
             // column k below the diagonal -> Householder vector v (all lanes compute the same scalars)
-            double s = 0.;
-            for (int r = k; r < window; ++r) { const double a = A[r * p.acols + k]; s += a * a; }
+            double sq = 0.;
+            for (int r = k; r < window; ++r) { const double a = A[r * p.acols + k]; sq += a * a; }
             const double akk = A[k * p.acols + k];
-            const double nrm = sqrt(s);
+            const double nrm = sqrt(sq);
             const double alph = akk > 0. ? -nrm : nrm;
-            const double vtv = s - 2. * akk * alph + alph * alph;      // |x - alph e1|^2
+            const double vtv = sq - 2. * akk * alph + alph * alph;      // |x - alph e1|^2
             dmax = fmax(dmax, fabs(alph)); dmin = fmin(dmin, fabs(alph));
             __syncwarp();
             for (int r = k + lane; r < window; r += 32) vhh[r] = A[r * p.acols + k] - (r == k ? alph : 0.);
@@ -341,36 +351,53 @@ __global__ void __launch_bounds__(NTH_EVAL) eval_kernel(const EvalParams p) {
         for (int f = lane; f < F; f += 32) {
             for (int l = L - 1; l >= 0; --l) {
                 double acc = A[l * p.acols + L + f];
-                for (int j = l + 1; j < L; ++j) acc -= A[l * p.acols + j] * betaS[j * F + f];
-                betaS[l * F + f] = acc / A[l * p.acols + l];
+                for (int j = l + 1; j < L; ++j) acc -= A[l * p.acols + j] * beta[j * F + f];
+                beta[l * F + f] = acc / A[l * p.acols + l];
             }
-            // helper.normalization (helper.py:10-17): sd(Y)/sd(M beta), ddof = 1
+            // helper.normalization: sd(Y)/sd(M beta), ddof = 1
             double my = 0., mr = 0.;
             for (int r = 0; r < window; ++r) {
                 double rh = 0.;
-                for (int l = 0; l < L; ++l) rh += (double)M[r * WS + l] * betaS[l * F + f];
-                mr += rh; my += Yte[(size_t)r * F + f];
+                for (int l = 0; l < L; ++l) rh += (double)Mw[r * WS + l] * beta[l * F + f];
+                mr += rh; my += Yw[(size_t)r * F + f];
             }
             mr /= window; my /= window;
             double vr = 0., vy = 0.;
             for (int r = 0; r < window; ++r) {
                 double rh = 0.;
-                for (int l = 0; l < L; ++l) rh += (double)M[r * WS + l] * betaS[l * F + f];
-                const double dy = Yte[(size_t)r * F + f] - my;
+                for (int l = 0; l < L; ++l) rh += (double)Mw[r * WS + l] * beta[l * F + f];
+                const double dy = Yw[(size_t)r * F + f] - my;
                 vr += (rh - mr) * (rh - mr) / (window - 1);
                 vy += dy * dy / (window - 1);
             }
-            normS[f] = sqrt(vy) / sqrt(vr);
+            normW[f] = sqrt(vy) / sqrt(vr);
         }
-    }
-    __syncthreads();
-
-    // ---- G = beta_0^T Wd  (F x E), float64 (:167)
-    for (int idx = tid; idx < F * E; idx += NTH_EVAL) {
-        const int f = idx / E, e = idx - f * E;
-        double acc = 0.;
-        for (int l = 0; l < L; ++l) acc += betaS[l * F + f] * (double)Wd[l * WS + e];
-        G[idx] = acc;
+        __syncwarp();
+        for (int idx = lane; idx < F * E; idx += 32) {            // G_w = beta_w^T Wd
+            const int f = idx / E, e = idx - f * E;
+            double acc = 0.;
+            for (int l = 0; l < L; ++l) acc += beta[l * F + f] * (double)Wd[l * WS + e];
+            Gw[idx] = acc;
+        }
+        __syncwarp();
+    };
+    double* wg = p.weights ? p.weights + (size_t)task * n_oos * E * F : nullptr;
+    __syncthreads();                                              // masks are complete
+    if (!p.rolling) {
+        if (warp == 0) ols_window(0, wsp);
+    } else if (warp < p.nq) {
+        double* ws = wsp + (size_t)warp * p.wsz;
+        for (int w = warp; w < n_oos; w += p.nq) {
+            ols_window(w, ws);
+            const double* Gw = ws + (size_t)window * p.acols + HFREP_MAX_L * F;
+            const double* normW = Gw + F * E;
+            for (int idx = lane; idx < E * F; idx += 32) {        // that month's weights, layout [e][f]
+                const int e = idx / F, f = idx - e * F;
+                wg[((size_t)w * E + e) * F + f] = Gw[f * E + e] * (maskS[w * E + e] ? .2 : 1.) * normW[f];
+            }
+            __syncwarp();
+        }
+        if (warp == 0) ols_window(0, wsp);                        // the reported beta / norm stay window 0's
     }
     __syncthreads();
 
@@ -383,22 +410,22 @@ __global__ void __launch_bounds__(NTH_EVAL) eval_kernel(const EvalParams p) {
         double sumw = 0., dot = 0., pen = 0., dabs = 0.;
         for (int e = 0; e < E; ++e) {
             const double g = G[f * E + e];
-            const double wk = g * (maskS[k * E + e] ? .2 : 1.) * nf;
+            auto wt = [&](int kk) -> double {                     // weight of ETF e for fund f in month kk
+                return p.rolling ? wg[((size_t)kk * E + e) * F + f] : g * (maskS[kk * E + e] ? .2 : 1.) * nf;
+            };
+            const double wk = wt(k);
             sumw += wk;
             dot += Xte[(size_t)row * E + e] * wk;
-            if (p.weights) p.weights[(((size_t)task * n_oos + k) * E + e) * F + f] = wk;
+            if (wg && !p.rolling) wg[((size_t)k * E + e) * F + f] = wk;
             if (k >= 1 && p.sigma) {                              // transaction_cost + price_impact, helper.py:65-92
-                const double old = g * (maskS[(k - 1) * E + e] ? .2 : 1.) * nf;
+                const double old = wt(k - 1);
                 const double sg = p.sigma[(size_t)(k - 1) * E + e] * scale_c;
                 const double d = old - wk;
                 const double tc = .5 * d * d * sg;
                 const double pi = phi * wk * sg * d - old * sg * d - .5 * d * d * sg;
                 pen += tc + pi;
             }
-            if (k + 1 < n_oos) {
-                const double nxt = g * (maskS[(k + 1) * E + e] ? .2 : 1.) * nf;
-                dabs += fabs(wk - nxt);
-            }
+            if (k + 1 < n_oos) dabs += fabs(wk - wt(k + 1));
         }
         const double a = (1. - sumw) * rfv[row] + dot;
         anteS[idx] = a;
@@ -494,7 +521,7 @@ extern "C" int hfrep_predict_metrics(const hfrep_eval_cfg* c, const double* Xtr,
     HFREP_REQUIRE(c->window >= 2 && c->window <= 64, "predict_metrics: window=%d outside 2..64", c->window);
     HFREP_REQUIRE(c->T_test >= c->window + 2, "predict_metrics: T_test=%d needs at least window+2 rows", c->T_test);
     HFREP_REQUIRE(w_stride >= 2 * c->E, "predict_metrics: w_stride=%d", w_stride);
-    HFREP_REQUIRE(c->beta_rolling == 0, "predict_metrics: beta_rolling=1 is not available in this build");
+    HFREP_REQUIRE(!c->beta_rolling || weights, "predict_metrics: beta_rolling=1 keeps the per-month weights in the `weights` output; pass it");
     HFREP_REQUIRE(!quality || Xtr, "predict_metrics: quality needs Xtr");
     HFREP_REQUIRE(!(post) || sigma, "predict_metrics: post needs sigma");
 
@@ -507,8 +534,10 @@ extern "C" int hfrep_predict_metrics(const hfrep_eval_cfg* c, const double* Xtr,
     p.acols = HFREP_MAX_L + c->F + 1;       // odd-ish stride keeps the column walks off a single bank
     p.alpha = c->alpha; p.cost_param = c->cost_param; p.phi = c->phi;
 
-    size_t dbl = (size_t)c->window * p.acols + HFREP_MAX_L * c->F + (size_t)c->F * c->E + c->F +
-                 3 * (size_t)p.n_oos * c->F + (NTH_EVAL / 32) * 3 * HFREP_MAX_E + c->window;
+    p.rolling = c->beta_rolling ? 1 : 0;
+    p.nq = p.rolling ? 4 : 1;
+    p.wsz = (int)((size_t)c->window * p.acols + HFREP_MAX_L * c->F + (size_t)c->F * c->E + c->F + c->window);
+    size_t dbl = (size_t)p.nq * p.wsz + 3 * (size_t)p.n_oos * c->F + (NTH_EVAL / 32) * 3 * HFREP_MAX_E;
     dbl = (dbl + 1) & ~(size_t)1;           // float region starts 16-byte aligned
     p.off_float = (int)(dbl * 8);
     const size_t flt = (size_t)HFREP_MAX_E * WS + (size_t)HFREP_MAX_L * WS + (size_t)c->T_test * WS;

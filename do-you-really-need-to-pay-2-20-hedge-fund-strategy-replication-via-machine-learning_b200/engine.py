@@ -267,7 +267,7 @@ def rolling_sigma(R64: torch.Tensor, starts: torch.Tensor, window: int) -> torch
 
 def predict_metrics(Xtr64, Xte64, Yte64, rf64, sigma, task_L, W, *, window=24, want_oos=True,
                     want_weights=False, alpha=.2, cost_param=.05, phi=.5, task_row0=None, T_test=None,
-                    want_quality=True, launch=True):
+                    want_quality=True, launch=True, beta_rolling=False):
     """Kernel (c) for a batch of trained tasks (all tensors on the device, float64 unless noted).
     launch=False only allocates the result and returns (result, launcher): launcher(a, b, stream) scores tasks
     [a, b) on `stream` — used to start a width bucket's evaluation right behind its fit, concurrently with the
@@ -278,7 +278,8 @@ def predict_metrics(Xtr64, Xte64, Yte64, rf64, sigma, task_L, W, *, window=24, w
     T_test = Xte64.shape[0] if T_test is None else T_test      # rolling refit: rows per task, not the history
     F = Yte64.shape[1]
     cfg = _lib.eval_cfg(E=E, F=F, T_train=(Xtr64.shape[0] if Xtr64 is not None else 0), T_test=T_test, window=window,
-                        want_oos=int(want_oos), alpha=alpha, cost_param=cost_param, phi=phi)
+                        want_oos=int(want_oos), alpha=alpha, cost_param=cost_param, phi=phi, beta_rolling=int(beta_rolling))
+    want_weights = want_weights or beta_rolling       # rolling betas keep the per-month weights in that buffer
     n_oos, n_pre = T_test - window - 1, T_test - 2
     tL = task_L if isinstance(task_L, torch.Tensor) else _device_ints(np.asarray(task_L, np.int32), device)
     f64 = dict(dtype=torch.float64, device=device)

@@ -154,7 +154,8 @@ typedef struct hfrep_eval_cfg {
     int32_t T_train;      /* rows of Xtr (168) */
     int32_t T_test;       /* rows of the test block (169) */
     int32_t window;       /* OLS / ex-post window (24), <= 64 */
-    int32_t beta_rolling; /* 0 = reference behaviour (window 0's beta/norm for every month, :167); 1 = window i */
+    int32_t beta_rolling; /* 0 = reference behaviour (window 0's beta/norm for every month, :167); 1 = month k uses
+                             window k's (the evident intent) — needs the `weights` output as storage */
     int32_t want_oos;     /* 1 = also the expanding-prefix quality loops (:115-131) */
     float alpha;          /* LeakyReLU slope */
     double cost_param;    /* .05  (helper.py:65,83) */

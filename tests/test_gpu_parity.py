@@ -394,3 +394,25 @@ def test_device_side_shuffle(hf, data):
             assert np.max(np.abs(res.loss[i, :n].cpu().numpy() - o["loss"]) / o["loss"]) < TOL
             We, _ = hf.engine.unpack_weights(res.W[i].cpu().numpy(), E, L)
             assert rel_err(We, o["We"]) < TOL
+
+
+@pytest.mark.parametrize("L", [2, 8, 21])
+def test_rolling_beta_option(hf, data, ref_inputs, L):
+    """beta_rolling=1 (month k uses window k's OLS — the evident intent behind Autoencoder_encapsulate.py:167, which
+    hard-codes window 0): against the oracle's beta_index='rolling' on the reference run's trained kernels."""
+    from oracle import ae_oracle
+    g = load_golden(f"ref_modeR_L{L}")
+    etf, hfd, rf = ref_inputs["etf"], ref_inputs["hfd"], ref_inputs["rf"]
+    ae = ae_oracle.AEOracle(etf[:168], hfd[:168], etf[168:], hfd[168:], L)
+    ae.We, ae.Wd = g["We"], g["Wd"]
+    ante = ae.ante(rf, beta_index="rolling")
+    post = ae.post(etf)
+    turn = ae.turnover()
+    E = data.E
+    W = hf.engine.to_device(hf.engine.pack_weights([(g["We"], g["Wd"])], E, 2 * E * L), data.device)
+    ev = hf.predict_metrics(data.Xtr64, data.Xte64, data.Yte64, data.rf64, data.sigma, [L], W, window=24,
+                            want_oos=False, beta_rolling=True)
+    assert rel_err(ev.weights[0].cpu().numpy(), ae.weights) < TOL
+    assert rel_err(ev.ante[0].cpu().numpy(), ante) < TOL and rel_err(ev.post[0].cpu().numpy(), post) < TOL
+    assert rel_err(ev.turnover[0].cpu().numpy(), turn) < TOL
+    assert rel_err(ev.beta[0, :L].cpu().numpy(), ae.betas[0]) < TOL          # reported beta / norm stay window 0's
