@@ -791,7 +791,8 @@ static int fit_batched_impl(const hfrep_fit_cfg* c, const float* X, int n_tasks,
     int wpt = c->warps_per_task;
     if (wpt == 0) {                                  // pick the mapping from the amount of parallel work
         const int sms = sm_count();
-        wpt = n_tasks <= sms ? 6 : (n_tasks < 24 * sms ? 3 : 1);
+        // one warp per task only pays off for wide tasks in large numbers (measured: L=20 x 1024 -> 1 warp wins, L=8 x 20000 -> 3 warps win)
+        wpt = n_tasks <= sms ? 6 : ((n_tasks >= 4 * sms && c->L_max >= 16) ? 1 : 3);
     }
     HFREP_REQUIRE(wpt == 1 || wpt == 3 || wpt == 6, "fit_batched: warps_per_task=%d (0, 1, 3 or 6)", wpt);
     return fit_dispatch(p, c->L_max, wpt, (cudaStream_t)stream);
