@@ -41,7 +41,7 @@ class EvalCfg(C.Structure):
 
 
 EXPORTS = ("hfrep_last_error", "hfrep_version", "hfrep_window_index", "hfrep_window_gather",
-           "hfrep_rolling_sigma", "hfrep_fit_cfg_default", "hfrep_nadam_schedule", "hfrep_fit_batched", "hfrep_fit_windows_workspace", "hfrep_fit_windows", "hfrep_fit_windows_static",
+           "hfrep_rolling_sigma", "hfrep_fit_cfg_default", "hfrep_nadam_schedule", "hfrep_fit_batched", "hfrep_fit_windows_workspace", "hfrep_fit_windows", "hfrep_fit_windows_static", "hfrep_fit_wide_workspace", "hfrep_fit_wide", "hfrep_predict_wide",
            "hfrep_eval_cfg_default", "hfrep_predict_metrics", "hfrep_series_metrics", "hfrep_ex_post_return", "hfrep_forward",
            "hfrep_ffma_peak")
 
@@ -70,6 +70,11 @@ def _load():
                                       C.c_int, vp, i64, vp, vp, vp, C.c_size_t, vp, vp, vp, vp, vp, vp]
     lib.hfrep_fit_windows_static.argtypes = [C.POINTER(FitCfg), vp, C.c_int, C.c_int, C.c_int, vp, C.c_int, C.c_int, vp, vp, vp,
                                              C.c_int, vp, i64, vp, vp, vp, vp, vp, vp, vp, vp]
+    lib.hfrep_fit_wide_workspace.argtypes = [C.c_int, C.c_int, C.c_int]
+    lib.hfrep_fit_wide.argtypes = [C.POINTER(FitCfg), vp, C.c_int, C.c_int, vp, vp, vp, i64, vp, vp, C.c_size_t, vp, vp, vp,
+                                   vp, vp, vp]
+    lib.hfrep_predict_wide.argtypes = [vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, C.c_int, vp, vp,
+                                       vp, vp, vp]
     lib.hfrep_eval_cfg_default.argtypes = [C.POINTER(EvalCfg)]
     lib.hfrep_eval_cfg_default.restype = None
     lib.hfrep_predict_metrics.argtypes = [C.POINTER(EvalCfg), vp, vp, vp, vp, vp, C.c_int, vp, vp, vp, C.c_int] + [vp] * 11
@@ -79,9 +84,11 @@ def _load():
     lib.hfrep_ffma_peak.argtypes = [C.c_int, vp, C.POINTER(C.c_double), vp]
     for name in EXPORTS:
         fn = getattr(lib, name)
-        if name not in ("hfrep_last_error", "hfrep_fit_cfg_default", "hfrep_eval_cfg_default", "hfrep_fit_windows_workspace"):
+        if name not in ("hfrep_last_error", "hfrep_fit_cfg_default", "hfrep_eval_cfg_default", "hfrep_fit_windows_workspace",
+                        "hfrep_fit_wide_workspace"):
             fn.restype = C.c_int
     lib.hfrep_fit_windows_workspace.restype = C.c_size_t
+    lib.hfrep_fit_wide_workspace.restype = C.c_size_t
     return lib
 
 

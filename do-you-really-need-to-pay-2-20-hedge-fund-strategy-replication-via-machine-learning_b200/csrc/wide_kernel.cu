@@ -1,0 +1,355 @@
+// Wide variant of kernels (b) and (c) for the synthetic scale-up (BASELINE configs[3]: 500 ETFs, 10 000 funds,
+// 252-day training windows, rolling refit).  Same arithmetic as fit_kernel / eval_kernel — bias-free E -> L -> E
+// LeakyReLU autoencoder, MSE, Nadam, validation tail, early stopping (Autoencoder_encapsulate.py:19-35, :72-96), then
+// OLS of the funds on the latent factors and the replica return of the next row (:133-201 with the reference's own
+// alignment) — for shapes whose state does not fit shared memory: weights and Nadam state live in a caller-provided
+// global workspace (L2-resident: 6*E*L floats per task), activations of the current mini-batch in shared memory.
+//
+// ROUND-1 STATUS: correct first.  Plain FP32 FFMA with L1/L2-served operands, one CTA per task; the tcgen05 / TMA
+// version (seeds batched along N so the encoder GEMM becomes [rows x 500].[500 x (L*S)], 3xTF32) is the next step and
+// is NOT what this file is yet.
+#include "common.cuh"
+
+#include <cmath>
+
+namespace hfrep {
+
+constexpr int WIDE_THREADS = 256;
+constexpr int WIDE_MAX_L = 32;
+
+struct WideFitParams {
+    const float* X;            // [n_x][T][E] scaled training blocks
+    const int* task_x;         // block of each task (NULL: block 0)
+    const float* W0;           // [n_tasks][2*E*L]
+    const int* perm;           // optional [..][epochs][n_fit]
+    long long perm_task_stride;
+    const float4* sched;
+    float* ws;                 // [n_tasks][6*E*L]: We, Wd, mWe, vWe, mWd, vWd
+    float* W_out;              // [n_tasks][2*E*L]
+    float* loss_hist; float* val_hist; int* epochs_run; int* status;
+    int n_tasks, E, L, T, n_fit, n_val, batch, max_epochs, patience, early_stop;
+    float alpha, lr, b1, b2, eps;
+};
+
+__device__ __forceinline__ float block_sum(float v, float* red) {
+    v = warp_sum(v);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    __syncthreads();
+    if (lane == 0) red[warp] = v;
+    __syncthreads();
+    float s = 0.f;
+    for (int w = 0; w < WIDE_THREADS / 32; ++w) s += red[w];
+    return s;
+}
+
+__global__ void __launch_bounds__(WIDE_THREADS) fit_wide_kernel(const WideFitParams p) {
+    extern __shared__ __align__(16) float sm[];
+    const int task = blockIdx.x, tid = threadIdx.x;
+    const int E = p.E, L = p.L, B = p.batch;
+    float* H = sm;                         // [B][L]   h = lrelu(x We)
+    float* dZh = H + B * L;                // [B][L]
+    float* dZy = dZh + B * L;              // [B][E]
+    int* rows = reinterpret_cast<int*>(dZy + (size_t)B * E);   // [B] training-block rows of the mini-batch
+    float* red = reinterpret_cast<float*>(rows + B);           // [8]
+
+    const size_t EL = (size_t)E * L;
+    float* We = p.ws + (size_t)task * 6 * EL;   // [E][L]
+    float* Wd = We + EL;                         // [L][E]
+    float* mWe = Wd + EL; float* vWe = mWe + EL; float* mWd = vWe + EL; float* vWd = mWd + EL;
+    const float* X = p.X + (size_t)(p.task_x ? p.task_x[task] : 0) * p.T * E;
+    const float* w0 = p.W0 + (size_t)task * 2 * EL;
+    for (size_t i = tid; i < EL; i += WIDE_THREADS) {
+        We[i] = w0[i]; Wd[i] = w0[EL + i];
+        mWe[i] = vWe[i] = mWd[i] = vWd[i] = 0.f;
+    }
+    __syncthreads();
+
+    const int* perm_t = p.perm ? p.perm + (size_t)task * p.perm_task_stride : nullptr;
+    const float alpha = p.alpha, omb1 = 1.f - p.b1, omb2 = 1.f - p.b2;
+    const int n_fit = p.n_fit, n_val = p.n_val;
+    int step = 0, wait = 0, epochs_run = 0, st = 0;
+    float best = INFINITY;
+
+    // forward of the mini-batch in `rows` (nb rows); train: also dZy, dZh, weight gradients and the Nadam update
+    auto run_batch = [&](int nb, bool train) -> float {
+        // H = lrelu(X_b We): one output per thread, l fastest (We row coalesced, x broadcast)
+        for (int o = tid; o < nb * L; o += WIDE_THREADS) {
+            const int r = o / L, l = o - r * L;
+            const float* xr = X + (size_t)rows[r] * E;
+            float acc = 0.f;
+            for (int e = 0; e < E; ++e) acc = fmaf(__ldg(xr + e), We[(size_t)e * L + l], acc);
+            H[o] = lrelu(acc, alpha);
+        }
+        __syncthreads();
+        // Zy = H Wd, squared error, dZy: e fastest (Wd row coalesced, h broadcast from shared memory)
+        const float coef = 2.f / (float)(nb * E);
+        float sse = 0.f;
+        for (int o = tid; o < nb * E; o += WIDE_THREADS) {
+            const int r = o / E, e = o - r * E;
+            float acc = 0.f;
+            for (int l = 0; l < L; ++l) acc = fmaf(H[r * L + l], Wd[(size_t)l * E + e], acc);
+            const float d = lrelu(acc, alpha) - __ldg(X + (size_t)rows[r] * E + e);
+            sse = fmaf(d, d, sse);
+            if (train) dZy[o] = lrelu_grad(acc, coef * d, alpha);
+        }
+        if (!train) return sse;
+        __syncthreads();
+        // dZh = (dZy Wd^T) o lrelu'(zh): a warp per output, lanes over e (both operands coalesced), fixed-order reduce
+        {
+            const int lane = tid & 31, warp = tid >> 5;
+            for (int o = warp; o < nb * L; o += WIDE_THREADS / 32) {
+                const int r = o / L, l = o - r * L;
+                float acc = 0.f;
+                for (int e = lane; e < E; e += 32) acc = fmaf(dZy[(size_t)r * E + e], Wd[(size_t)l * E + e], acc);
+                acc = warp_sum(acc);
+                if (lane == 0) dZh[o] = lrelu_grad(H[o], acc, alpha);     // sign(h) == sign(zh) for alpha > 0
+            }
+        }
+        __syncthreads();
+        // gradients + Nadam, element-wise over the 2*E*L weights
+        const float4 sc = __ldg(p.sched + step);
+        for (size_t i = tid; i < 2 * EL; i += WIDE_THREADS) {
+            float g = 0.f;
+            float *w, *m, *v;
+            if (i < EL) {                                  // dWd[l][e] = sum_r H[r][l] dZy[r][e]
+                const int l = (int)(i / E), e = (int)(i - (size_t)l * E);
+                for (int r = 0; r < nb; ++r) g = fmaf(H[r * L + l], dZy[(size_t)r * E + e], g);
+                w = Wd + i; m = mWd + i; v = vWd + i;
+            } else {                                       // dWe[e][l] = sum_r X_b[r][e] dZh[r][l]
+                const size_t j = i - EL;
+                const int e = (int)(j / L), l = (int)(j - (size_t)e * L);
+                for (int r = 0; r < nb; ++r) g = fmaf(__ldg(X + (size_t)rows[r] * E + e), dZh[r * L + l], g);
+                w = We + j; m = mWe + j; v = vWe + j;
+            }
+            const float mm = p.b1 * *m + omb1 * g;
+            const float vv = p.b2 * *v + omb2 * (g * g);
+            *m = mm; *v = vv;
+            *w -= p.lr * (sc.x * g + sc.y * mm) / (sqrtf(vv * sc.z) + p.eps);
+        }
+        ++step;
+        __syncthreads();
+        return sse;
+    };
+
+    for (int epoch = 0; epoch < p.max_epochs; ++epoch) {
+        float lsum = 0.f, vsum = 0.f;
+        for (int lo = 0; lo < n_fit; lo += B) {
+            const int nb = min(B, n_fit - lo);
+            for (int q = tid; q < nb; q += WIDE_THREADS)
+                rows[q] = perm_t ? __ldg(perm_t + (size_t)epoch * n_fit + lo + q) : lo + q;
+            __syncthreads();
+            lsum += run_batch(nb, true);
+        }
+        for (int lo = 0; lo < n_val; lo += B) {
+            const int nb = min(B, n_val - lo);
+            __syncthreads();
+            for (int q = tid; q < nb; q += WIDE_THREADS) rows[q] = n_fit + lo + q;
+            __syncthreads();
+            vsum += run_batch(nb, false);
+        }
+        const float loss = block_sum(lsum, red) / ((float)E * n_fit);
+        const float val = n_val > 0 ? block_sum(vsum, red) / ((float)E * n_val) : NAN;
+        if (tid == 0) {
+            p.loss_hist[(size_t)task * p.max_epochs + epoch] = loss;
+            p.val_hist[(size_t)task * p.max_epochs + epoch] = val;
+        }
+        epochs_run = epoch + 1;
+        if (!isfinite(loss)) st = 1;
+        if (p.early_stop) {
+            ++wait;
+            if (val < best) { best = val; wait = 0; }
+            if (wait >= p.patience && epoch > 0) break;
+        }
+        __syncthreads();
+    }
+    float* wo = p.W_out + (size_t)task * 2 * EL;
+    for (size_t i = tid; i < EL; i += WIDE_THREADS) { wo[i] = We[i]; wo[EL + i] = Wd[i]; }
+    if (tid == 0) { p.epochs_run[task] = epochs_run; p.status[task] = st; }
+}
+
+// ------------------------------------------------------------------------------------------------ wide evaluation
+struct WideEvalParams {
+    const double* etf; const double* hfd; const double* rf;   // full histories [T][E], [T][F], [T]
+    const int* task_row0;      // first row of each task's (window+2)-row test block
+    const float* W;            // [n_tasks][2*E*L] trained kernels
+    double* replica;           // [n_tasks][F]   replica return of row row0+window+1
+    int* status;
+    int n_tasks, E, F, L, window;
+    float alpha;
+};
+
+// One CTA per task.  Latent rows, mask, c_l = sum_e etf[t+1][e] mask_e Wd[l][e], s_l = sum_e mask_e Wd[l][e] once;
+// then per fund (threads over funds): Householder-QR least squares (the pinv-OLS of :151 for full-rank windows),
+// helper.normalization, and replica = (1 - norm*beta.s) rf + norm*beta.c  (:167-168, :188-190 with the sums over
+// ETFs regrouped through the latent factors, so a fund costs O(L*window) instead of O(E)).
+__global__ void __launch_bounds__(WIDE_THREADS) eval_wide_kernel(const WideEvalParams p) {
+    extern __shared__ __align__(16) unsigned char smraw[];
+    const int task = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int E = p.E, F = p.F, L = p.L, window = p.window, R = window + 2;
+    double* Q = reinterpret_cast<double*>(smraw);      // [window][L] : R factor in the upper triangle after QR
+    double* V = Q + window * L;                         // [L][window] Householder vectors
+    double* bh = V + L * window;                        // [L] 2/|v|^2
+    double* cl = bh + L;                                // [L]
+    double* sl = cl + L;                                // [L]
+    float* M = reinterpret_cast<float*>(sl + L);        // [R][L] latent factors of the test block
+    unsigned char* mask = reinterpret_cast<unsigned char*>(M + R * L);   // [E]
+    __shared__ int s_status;
+    const size_t EL = (size_t)E * L;
+    const float* We = p.W + (size_t)task * 2 * EL;
+    const float* Wd = We + EL;
+    const int row0 = p.task_row0[task];
+    const double* X = p.etf + (size_t)row0 * E;
+    const double* Y = p.hfd + (size_t)row0 * F;
+    if (tid == 0) s_status = 0;
+
+    // latent rows, float32 sequential (encoder.predict on raw rows, :140)
+    for (int o = tid; o < R * L; o += WIDE_THREADS) {
+        const int r = o / L, l = o - r * L;
+        float acc = 0.f;
+        for (int e = 0; e < E; ++e) acc = fmaf((float)X[(size_t)r * E + e], We[(size_t)e * L + l], acc);
+        M[o] = lrelu(acc, p.alpha);
+    }
+    __syncthreads();
+    // mask from the row after the OLS window (:163-166), float32
+    for (int e = tid; e < E; e += WIDE_THREADS) {
+        float acc = 0.f;
+        for (int l = 0; l < L; ++l) acc = fmaf(M[window * L + l], Wd[(size_t)l * E + e], acc);
+        mask[e] = acc < 0.f ? 1 : 0;
+    }
+    for (int o = tid; o < window * L; o += WIDE_THREADS) Q[o] = (double)M[o];
+    __syncthreads();
+    // c_l, s_l: a warp per latent factor
+    for (int l = warp; l < L; l += WIDE_THREADS / 32) {
+        double c = 0., s = 0.;
+        for (int e = lane; e < E; e += 32) {
+            const double w = (double)Wd[(size_t)l * E + e] * (mask[e] ? .2 : 1.);
+            c += X[(size_t)(window + 1) * E + e] * w;
+            s += w;
+        }
+        c = warp_sum(c); s = warp_sum(s);
+        if (lane == 0) { cl[l] = c; sl[l] = s; }
+    }
+    // Householder QR of the latent block (window x L), warp 0, lane = column
+    if (warp == 0) {
+        double dmax = 0., dmin = INFINITY;
+        for (int k = 0; k < L; ++k) {
+            double sq = 0.;
+            for (int r = k; r < window; ++r) sq += Q[r * L + k] * Q[r * L + k];
+            const double akk = Q[k * L + k];
+            const double nrm = sqrt(sq);
+            const double alph = akk > 0. ? -nrm : nrm;
+            const double vtv = sq - 2. * akk * alph + alph * alph;
+            dmax = fmax(dmax, fabs(alph)); dmin = fmin(dmin, fabs(alph));
+            __syncwarp();
+            for (int r = lane; r < window; r += 32) V[k * window + r] = r < k ? 0. : Q[r * L + k] - (r == k ? alph : 0.);
+            if (lane == 0) bh[k] = vtv > 0. ? 2. / vtv : 0.;
+            __syncwarp();
+            for (int c = k + 1 + lane; c < L; c += 32) {
+                double wj = 0.;
+                for (int r = k; r < window; ++r) wj += V[k * window + r] * Q[r * L + c];
+                wj *= bh[k];
+                for (int r = k; r < window; ++r) Q[r * L + c] -= V[k * window + r] * wj;
+            }
+            __syncwarp();
+            if (lane == 0) Q[k * L + k] = alph;
+            __syncwarp();
+        }
+        if (!(dmin > 1e-13 * dmax) && lane == 0) s_status = 2;
+    }
+    __syncthreads();
+    // funds
+    constexpr int MAXW = 64;
+    const double rf_next = p.rf[row0 + window + 1];
+    for (int f = tid; f < F; f += WIDE_THREADS) {
+        double y[MAXW], beta[WIDE_MAX_L];
+        double my = 0.;
+        for (int r = 0; r < window; ++r) { y[r] = Y[(size_t)r * F + f]; my += y[r]; }
+        my /= window;
+        double vy = 0.;
+        for (int r = 0; r < window; ++r) vy += (y[r] - my) * (y[r] - my) / (window - 1);
+        for (int k = 0; k < L; ++k) {                       // Q^T y
+            double wj = 0.;
+            for (int r = k; r < window; ++r) wj += V[k * window + r] * y[r];
+            wj *= bh[k];
+            for (int r = k; r < window; ++r) y[r] -= V[k * window + r] * wj;
+        }
+        for (int l = L - 1; l >= 0; --l) {                  // back substitution
+            double acc = y[l];
+            for (int j = l + 1; j < L; ++j) acc -= Q[l * L + j] * beta[j];
+            beta[l] = acc / Q[l * L + l];
+        }
+        double mr = 0.;                                     // helper.normalization (helper.py:10-17)
+        for (int r = 0; r < window; ++r) {
+            double rh = 0.;
+            for (int l = 0; l < L; ++l) rh += (double)M[r * L + l] * beta[l];
+            y[r] = rh; mr += rh;
+        }
+        mr /= window;
+        double vr = 0.;
+        for (int r = 0; r < window; ++r) vr += (y[r] - mr) * (y[r] - mr) / (window - 1);
+        const double norm = sqrt(vy) / sqrt(vr);
+        double bs = 0., bc = 0.;
+        for (int l = 0; l < L; ++l) { bs += beta[l] * sl[l]; bc += beta[l] * cl[l]; }
+        p.replica[(size_t)task * F + f] = (1. - norm * bs) * rf_next + norm * bc;
+    }
+    if (tid == 0 && p.status) p.status[task] = s_status;
+}
+
+}  // namespace hfrep
+
+using namespace hfrep;
+
+extern "C" size_t hfrep_fit_wide_workspace(int n_tasks, int E, int L) {
+    if (n_tasks <= 0 || E <= 0 || L <= 0) return 0;
+    return sizeof(float) * 6 * (size_t)n_tasks * E * L;
+}
+
+extern "C" int hfrep_fit_wide(const hfrep_fit_cfg* c, const float* X, int n_tasks, int L, const int32_t* task_x,
+                              const float* W0, const int32_t* perm, int64_t perm_task_stride, const float* sched,
+                              void* ws, size_t ws_bytes, float* W_out, float* loss_hist, float* val_hist,
+                              int32_t* epochs_run, int32_t* status, void* stream) {
+    HFREP_REQUIRE(c && X && W0 && sched && ws && W_out && loss_hist && val_hist && epochs_run && status,
+                  "fit_wide: null argument");
+    HFREP_REQUIRE(n_tasks >= 0, "fit_wide: n_tasks=%d", n_tasks);
+    if (n_tasks == 0) return HFREP_OK;
+    HFREP_REQUIRE(c->E >= 1 && c->E <= 4096, "fit_wide: E=%d outside 1..4096", c->E);
+    HFREP_REQUIRE(L >= 1 && L <= WIDE_MAX_L, "fit_wide: L=%d outside 1..%d", L, WIDE_MAX_L);
+    HFREP_REQUIRE(c->T >= 2 && c->n_fit >= 1 && c->n_fit <= c->T && c->batch >= 1, "fit_wide: T=%d n_fit=%d batch=%d", c->T,
+                  c->n_fit, c->batch);
+    HFREP_REQUIRE(ws_bytes >= hfrep_fit_wide_workspace(n_tasks, c->E, L), "fit_wide: workspace of %zu bytes needed, %zu given",
+                  hfrep_fit_wide_workspace(n_tasks, c->E, L), ws_bytes);
+    HFREP_REQUIRE(c->n_x == 1 || task_x, "fit_wide: n_x=%d needs task_x", c->n_x);
+    WideFitParams p;
+    p.X = X; p.task_x = task_x; p.W0 = W0; p.perm = perm; p.perm_task_stride = perm_task_stride;
+    p.sched = reinterpret_cast<const float4*>(sched); p.ws = static_cast<float*>(ws); p.W_out = W_out;
+    p.loss_hist = loss_hist; p.val_hist = val_hist; p.epochs_run = epochs_run; p.status = status;
+    p.n_tasks = n_tasks; p.E = c->E; p.L = L; p.T = c->T; p.n_fit = c->n_fit; p.n_val = c->T - c->n_fit; p.batch = c->batch;
+    p.max_epochs = c->max_epochs; p.patience = c->patience; p.early_stop = c->early_stop;
+    p.alpha = c->alpha; p.lr = c->lr; p.b1 = c->beta_1; p.b2 = c->beta_2; p.eps = c->epsilon;
+    const size_t smem = sizeof(float) * (2 * (size_t)c->batch * L + (size_t)c->batch * c->E + c->batch + 16);
+    HFREP_REQUIRE(smem <= 227 * 1024, "fit_wide: %zu bytes of shared memory needed (batch x E too large)", smem);
+    HFREP_CUDA_OK(cudaFuncSetAttribute(fit_wide_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    fit_wide_kernel<<<n_tasks, WIDE_THREADS, smem, (cudaStream_t)stream>>>(p);
+    HFREP_CUDA_OK(cudaGetLastError());
+    return HFREP_OK;
+}
+
+extern "C" int hfrep_predict_wide(const double* etf, const double* hfd, const double* rf, int T, int E, int F, int L,
+                                  int window, float alpha, int n_tasks, const int32_t* task_row0, const float* W,
+                                  double* replica, int32_t* status, void* stream) {
+    HFREP_REQUIRE(etf && hfd && rf && task_row0 && W && replica, "predict_wide: null argument");
+    HFREP_REQUIRE(n_tasks >= 0, "predict_wide: n_tasks=%d", n_tasks);
+    if (n_tasks == 0) return HFREP_OK;
+    HFREP_REQUIRE(L >= 1 && L <= WIDE_MAX_L, "predict_wide: L=%d outside 1..%d", L, WIDE_MAX_L);
+    HFREP_REQUIRE(window >= L && window <= 64, "predict_wide: window=%d must satisfy L <= window <= 64 (the least-squares "
+                  "solve is QR; the minimum-norm case L > window is not built)", window);
+    HFREP_REQUIRE(E >= 1 && F >= 1 && T >= window + 2, "predict_wide: E=%d F=%d T=%d", E, F, T);
+    WideEvalParams p;
+    p.etf = etf; p.hfd = hfd; p.rf = rf; p.task_row0 = task_row0; p.W = W; p.replica = replica; p.status = status;
+    p.n_tasks = n_tasks; p.E = E; p.F = F; p.L = L; p.window = window; p.alpha = alpha;
+    const size_t smem = sizeof(double) * (2 * (size_t)window * L + 3 * L) + sizeof(float) * (size_t)(window + 2) * L + E + 16;
+    HFREP_CUDA_OK(cudaFuncSetAttribute(eval_wide_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    eval_wide_kernel<<<n_tasks, WIDE_THREADS, smem, (cudaStream_t)stream>>>(p);
+    HFREP_CUDA_OK(cudaGetLastError());
+    return HFREP_OK;
+}

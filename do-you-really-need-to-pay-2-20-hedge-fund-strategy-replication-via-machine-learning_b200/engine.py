@@ -415,6 +415,55 @@ def fit_windows(R32: torch.Tensor, win_starts, T_win: int, task_L, task_win, W0:
     return FitResult(W_out, loss, val, epochs_run, status, None, W0.shape[1]), ws.view(n_win, T_win, E)
 
 
+def run_mode_w_wide(etf, hfd, rf, *, train_window: int, latent_dim: int, seeds=(123,), ols_window: int = 24, device=None,
+                    W0=None, windows=None, **fit_kw):
+    """Rolling refit for wide shapes (hundreds of ETFs, thousands of funds: BASELINE configs[3]).  Same task definition
+    and alignment as run_mode_w; kernel (a) builds the MinMax-scaled training windows, hfrep_fit_wide trains on them with
+    weights in a global workspace, hfrep_predict_wide regresses every fund on the latent factors and returns the replica
+    return of row t+1.  `windows`: optional subset of window indices (a bounded sample of the 4 747 windows of configs[3])."""
+    dev = _dev(device)
+    etf = np.asarray(etf, np.float64)
+    hfd = np.asarray(hfd, np.float64)
+    rf = np.asarray(rf, np.float64).reshape(-1)
+    T, E = etf.shape
+    F = hfd.shape[1]
+    L = latent_dim
+    ts = np.arange(train_window, T - 1)
+    if windows is not None:
+        ts = ts[np.asarray(windows)]
+    n_win = len(ts)
+    tasks = [(wi, int(s)) for s in seeds for wi in range(n_win)]
+    n = len(tasks)
+    with torch.cuda.device(dev):
+        R32 = to_device(etf.astype(np.float32), dev)
+        blocks = window_gather(R32, (ts - train_window).astype(np.int32), train_window, 0, E, minmax=True)
+        if W0 is None:
+            W0 = pack_weights([initial_weights(s * 100003 + wi, E, L) for wi, s in tasks], E, 2 * E * L)
+        W0d = to_device(np.asarray(W0, np.float32), dev)
+        n_fit = int(np.floor(train_window * .75))
+        cfg = _lib.fit_cfg(E=E, T=train_window, n_fit=n_fit, L_max=min(L, _lib.MAX_L), n_x=n_win, **fit_kw)
+        steps = cfg.max_epochs * ((n_fit + cfg.batch - 1) // cfg.batch)
+        sched = nadam_schedule(cfg, steps, dev)
+        ws_bytes = lib.hfrep_fit_wide_workspace(n, E, L)
+        ws = torch.empty(ws_bytes // 4, dtype=torch.float32, device=dev)
+        W_out = torch.empty_like(W0d)
+        loss = torch.full((n, cfg.max_epochs), float("nan"), dtype=torch.float32, device=dev)
+        val = torch.full((n, cfg.max_epochs), float("nan"), dtype=torch.float32, device=dev)
+        epochs_run = torch.zeros(n, dtype=torch.int32, device=dev)
+        status = torch.zeros(n, dtype=torch.int32, device=dev)
+        tw = _device_ints(np.asarray([wi for wi, _ in tasks], np.int32), dev)
+        check(lib.hfrep_fit_wide(C.byref(cfg), ptr(blocks), n, L, ptr(tw), ptr(W0d), None, 0, ptr(sched), ptr(ws), ws_bytes,
+                                 ptr(W_out), ptr(loss), ptr(val), ptr(epochs_run), ptr(status), stream_ptr()))
+        fit = FitResult(W_out, loss, val, epochs_run, status, None, 2 * E * L)
+        row0 = _device_ints((ts - ols_window)[[wi for wi, _ in tasks]].astype(np.int32), dev)
+        etf_d, hfd_d, rf_d = to_device(etf, dev), to_device(hfd, dev), to_device(rf, dev)
+        replica = torch.empty((n, F), dtype=torch.float64, device=dev)
+        est = torch.zeros(n, dtype=torch.int32, device=dev)
+        check(lib.hfrep_predict_wide(ptr(etf_d), ptr(hfd_d), ptr(rf_d), T, E, F, L, ols_window, fit_kw.get("alpha", .2), n,
+                                     ptr(row0), ptr(W_out), ptr(replica), ptr(est), stream_ptr()))
+    return dict(t=ts, replica=replica.view(len(seeds), n_win, F), fit=fit, eval_status=est, blocks=blocks, tasks=tasks)
+
+
 def run_mode_w(etf, hfd, rf, *, train_window: int, latent_dim: int, seeds=(123,), ols_window: int = 24, device=None,
                W0=None, **fit_kw):
     """Rolling refit (north_star's per-(window, seed) task; SURVEY §8d Mode W — an extension, the reference fits once):

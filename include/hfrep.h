@@ -194,6 +194,25 @@ int hfrep_predict_metrics(const hfrep_eval_cfg* cfg, const double* Xtr, const do
 int hfrep_forward(const float* W, int E, int L, const float* x, int n, int encode_only, float alpha, float* out,
                   void* stream);
 
+/* ---------------------------------------------------------------------------------------
+ * Wide variant (BASELINE configs[3]: 500 ETFs x 10 000 funds, rolling refit) of kernels (b) and (c): same arithmetic for
+ * shapes whose per-task state does not fit shared memory.  Round 1: correct first (plain FP32 FFMA, L1/L2-served operands),
+ * one CTA per task; weights and Nadam state live in the caller's workspace.
+ *   hfrep_fit_wide: X f32 [n_x][T][E] scaled blocks (e.g. the workspace of hfrep_window_gather with minmax=1), every task
+ *   the same latent width L <= 32; W0 / W_out f32 [n_tasks][2*E*L] (We then Wd); ws f32, 6*E*L floats per task;
+ *   cfg supplies E (<= 4096), T, n_fit, batch, epochs, patience, Nadam constants, n_x.
+ *   hfrep_predict_wide: task i evaluates rows [task_row0[i], +window+2) of the full histories etf f64 [T][E], hfd f64 [T][F],
+ *   rf f64 [T]: latent factors of those rows (float32), OLS of every fund on the first `window` rows (float64 QR, needs
+ *   L <= window <= 64), normalisation, LeakyReLU mask from row `window`, and replica[i][f] = the replica return of row
+ *   window+1 (Autoencoder_encapsulate.py:133-193 with its own alignment; sums over ETFs regrouped through the L factors). */
+size_t hfrep_fit_wide_workspace(int n_tasks, int E, int L);
+int hfrep_fit_wide(const hfrep_fit_cfg* cfg, const float* X, int n_tasks, int L, const int32_t* task_x, const float* W0,
+                   const int32_t* perm, int64_t perm_task_stride, const float* sched, void* ws, size_t ws_bytes,
+                   float* W_out, float* loss_hist, float* val_hist, int32_t* epochs_run, int32_t* status, void* stream);
+int hfrep_predict_wide(const double* etf, const double* hfd, const double* rf, int T, int E, int F, int L, int window,
+                       float alpha, int n_tasks, const int32_t* task_row0, const float* W, double* replica,
+                       int32_t* status, void* stream);
+
 /* Stand-alone statistics of any (n, F) return block against `fund` (n, F) and rf (n): out f64 [HFREP_N_STATS][F], rows
  *   0 annualised Sharpe (autoencoder_v4.ipynb:715-721)      1 tracking error, 2 correlation (not in the reference; App. A.9)
  *   3 Omega(0 %), 4 Omega(10 %) (ipynb:695-705)              5 historical cVaR(5 %) (ipynb:729-757)

@@ -416,3 +416,34 @@ def test_rolling_beta_option(hf, data, ref_inputs, L):
     assert rel_err(ev.ante[0].cpu().numpy(), ante) < TOL and rel_err(ev.post[0].cpu().numpy(), post) < TOL
     assert rel_err(ev.turnover[0].cpu().numpy(), turn) < TOL
     assert rel_err(ev.beta[0, :L].cpu().numpy(), ae.betas[0]) < TOL          # reported beta / norm stay window 0's
+
+
+@pytest.mark.parametrize("E,F,L", [(500, 300, 8), (96, 40, 16)])
+def test_wide_variant_rolling_refit(hf, E, F, L):
+    """configs[3] shape at test scale (500 ETFs, hundreds of funds, 252-row windows, rolling refit) through the wide
+    kernels, against the Mode-W oracle (the reference's AE restatement called per window)."""
+    from oracle import ae_oracle, fitcore
+    rng = np.random.default_rng(E + L)
+    T, W, ols = 270, 252, 24
+    fac = rng.normal(size=(T, 10)) * .01
+    etf = fac @ rng.normal(size=(10, E)) + rng.normal(size=(T, E)) * .005
+    beta = rng.normal(size=(E, F)) * (rng.uniform(size=(E, F)) < 5. / E)
+    hfd = etf @ beta + rng.normal(size=(T, F)) * .003
+    rf = np.full(T, 1e-4)
+    out = hf.run_mode_w_wide(etf, hfd, rf, train_window=W, latent_dim=L, seeds=(3,), ols_window=ols, device="cuda:0",
+                             windows=[0, 5, 16], max_epochs=12, early_stop=0)
+    ts = out["t"]
+    assert int(out["fit"].status.abs().sum()) == 0 and int(out["eval_status"].abs().sum()) == 0
+    etf32 = etf.astype(np.float32).astype(np.float64)
+    cfg = fitcore.FitConfig(epochs=12, early_stop=False)
+    rep = out["replica"].cpu().numpy()
+    for wi, t in enumerate(ts):
+        We0, Wd0 = hf.engine.initial_weights(3 * 100003 + wi, E, L)
+        ae = ae_oracle.AEOracle(etf32[t - W:t], hfd[t - W:t], etf[t - ols:t + 2], hfd[t - ols:t + 2], L)
+        o = ae.train(We0, Wd0, cfg=cfg)
+        got_loss = out["fit"].loss[wi, :12].cpu().numpy()
+        assert np.max(np.abs(got_loss - o["loss"]) / o["loss"]) < TOL
+        We, Wd = hf.engine.unpack_weights(out["fit"].W[wi].cpu().numpy(), E, L)
+        assert rel_err(We, o["We"]) < TOL and rel_err(Wd, o["Wd"]) < TOL
+        want = ae.ante(rf[t - ols:t + 2], window=ols)[0]
+        assert rel_err(rep[0, wi], want) < TOL, (wi, np.max(np.abs(rep[0, wi] - want)))
