@@ -15,7 +15,7 @@
 namespace hfrep {
 
 constexpr int WIDE_THREADS = 256;
-constexpr int WIDE_MAX_L = 32;
+constexpr int WIDE_MAX_L = 64;
 
 struct WideFitParams {
     const float* X;            // [n_x][T][E] scaled training blocks
@@ -216,7 +216,14 @@ __global__ void __launch_bounds__(WIDE_THREADS) eval_wide_kernel(const WideEvalP
         for (int l = 0; l < L; ++l) acc = fmaf(M[window * L + l], Wd[(size_t)l * E + e], acc);
         mask[e] = acc < 0.f ? 1 : 0;
     }
-    for (int o = tid; o < window * L; o += WIDE_THREADS) Q[o] = (double)M[o];
+    // least squares on the latent block: QR of M (window x L) when L <= window; when L > window the system is
+    // underdetermined and pinv (:151) returns the minimum-norm solution, obtained from the QR of M^T (L x window)
+    const bool minnorm = L > window;
+    const int nr = minnorm ? L : window, nc = minnorm ? window : L;
+    for (int o = tid; o < window * L; o += WIDE_THREADS) {
+        const int r = o / L, l = o - r * L;               // M[r][l]
+        if (minnorm) Q[l * nc + r] = (double)M[o]; else Q[o] = (double)M[o];
+    }
     __syncthreads();
     // c_l, s_l: a warp per latent factor
     for (int l = warp; l < L; l += WIDE_THREADS / 32) {
@@ -229,29 +236,29 @@ __global__ void __launch_bounds__(WIDE_THREADS) eval_wide_kernel(const WideEvalP
         c = warp_sum(c); s = warp_sum(s);
         if (lane == 0) { cl[l] = c; sl[l] = s; }
     }
-    // Householder QR of the latent block (window x L), warp 0, lane = column
+    // Householder QR (nr x nc), warp 0, lane = column
     if (warp == 0) {
         double dmax = 0., dmin = INFINITY;
-        for (int k = 0; k < L; ++k) {
+        for (int k = 0; k < nc; ++k) {
             double sq = 0.;
-            for (int r = k; r < window; ++r) sq += Q[r * L + k] * Q[r * L + k];
-            const double akk = Q[k * L + k];
+            for (int r = k; r < nr; ++r) sq += Q[r * nc + k] * Q[r * nc + k];
+            const double akk = Q[k * nc + k];
             const double nrm = sqrt(sq);
             const double alph = akk > 0. ? -nrm : nrm;
             const double vtv = sq - 2. * akk * alph + alph * alph;
             dmax = fmax(dmax, fabs(alph)); dmin = fmin(dmin, fabs(alph));
             __syncwarp();
-            for (int r = lane; r < window; r += 32) V[k * window + r] = r < k ? 0. : Q[r * L + k] - (r == k ? alph : 0.);
+            for (int r = lane; r < nr; r += 32) V[k * nr + r] = r < k ? 0. : Q[r * nc + k] - (r == k ? alph : 0.);
             if (lane == 0) bh[k] = vtv > 0. ? 2. / vtv : 0.;
             __syncwarp();
-            for (int c = k + 1 + lane; c < L; c += 32) {
+            for (int c = k + 1 + lane; c < nc; c += 32) {
                 double wj = 0.;
-                for (int r = k; r < window; ++r) wj += V[k * window + r] * Q[r * L + c];
+                for (int r = k; r < nr; ++r) wj += V[k * nr + r] * Q[r * nc + c];
                 wj *= bh[k];
-                for (int r = k; r < window; ++r) Q[r * L + c] -= V[k * window + r] * wj;
+                for (int r = k; r < nr; ++r) Q[r * nc + c] -= V[k * nr + r] * wj;
             }
             __syncwarp();
-            if (lane == 0) Q[k * L + k] = alph;
+            if (lane == 0) Q[k * nc + k] = alph;
             __syncwarp();
         }
         if (!(dmin > 1e-13 * dmax) && lane == 0) s_status = 2;
@@ -261,22 +268,38 @@ __global__ void __launch_bounds__(WIDE_THREADS) eval_wide_kernel(const WideEvalP
     constexpr int MAXW = 64;
     const double rf_next = p.rf[row0 + window + 1];
     for (int f = tid; f < F; f += WIDE_THREADS) {
-        double y[MAXW], beta[WIDE_MAX_L];
+        double y[MAXW], beta[MAXW];
         double my = 0.;
         for (int r = 0; r < window; ++r) { y[r] = Y[(size_t)r * F + f]; my += y[r]; }
         my /= window;
         double vy = 0.;
         for (int r = 0; r < window; ++r) vy += (y[r] - my) * (y[r] - my) / (window - 1);
-        for (int k = 0; k < L; ++k) {                       // Q^T y
-            double wj = 0.;
-            for (int r = k; r < window; ++r) wj += V[k * window + r] * y[r];
-            wj *= bh[k];
-            for (int r = k; r < window; ++r) y[r] -= V[k * window + r] * wj;
-        }
-        for (int l = L - 1; l >= 0; --l) {                  // back substitution
-            double acc = y[l];
-            for (int j = l + 1; j < L; ++j) acc -= Q[l * L + j] * beta[j];
-            beta[l] = acc / Q[l * L + l];
+        if (!minnorm) {
+            for (int k = 0; k < L; ++k) {                   // Q^T y
+                double wj = 0.;
+                for (int r = k; r < window; ++r) wj += V[k * nr + r] * y[r];
+                wj *= bh[k];
+                for (int r = k; r < window; ++r) y[r] -= V[k * nr + r] * wj;
+            }
+            for (int l = L - 1; l >= 0; --l) {              // back substitution
+                double acc = y[l];
+                for (int j = l + 1; j < L; ++j) acc -= Q[l * nc + j] * beta[j];
+                beta[l] = acc / Q[l * nc + l];
+            }
+        } else {
+            // M^T = H_0..H_{w-1} [R; 0]  =>  beta = H_0..H_{w-1} [R^-T y; 0]
+            for (int i = 0; i < window; ++i) {              // forward substitution with R^T
+                double acc = y[i];
+                for (int j = 0; j < i; ++j) acc -= Q[j * nc + i] * beta[j];
+                beta[i] = acc / Q[i * nc + i];
+            }
+            for (int l = window; l < L; ++l) beta[l] = 0.;
+            for (int k = window - 1; k >= 0; --k) {
+                double wj = 0.;
+                for (int r = k; r < L; ++r) wj += V[k * nr + r] * beta[r];
+                wj *= bh[k];
+                for (int r = k; r < L; ++r) beta[r] -= V[k * nr + r] * wj;
+            }
         }
         double mr = 0.;                                     // helper.normalization (helper.py:10-17)
         for (int r = 0; r < window; ++r) {
@@ -341,8 +364,7 @@ extern "C" int hfrep_predict_wide(const double* etf, const double* hfd, const do
     HFREP_REQUIRE(n_tasks >= 0, "predict_wide: n_tasks=%d", n_tasks);
     if (n_tasks == 0) return HFREP_OK;
     HFREP_REQUIRE(L >= 1 && L <= WIDE_MAX_L, "predict_wide: L=%d outside 1..%d", L, WIDE_MAX_L);
-    HFREP_REQUIRE(window >= L && window <= 64, "predict_wide: window=%d must satisfy L <= window <= 64 (the least-squares "
-                  "solve is QR; the minimum-norm case L > window is not built)", window);
+    HFREP_REQUIRE(window >= 2 && window <= 64, "predict_wide: window=%d outside 2..64", window);
     HFREP_REQUIRE(E >= 1 && F >= 1 && T >= window + 2, "predict_wide: E=%d F=%d T=%d", E, F, T);
     WideEvalParams p;
     p.etf = etf; p.hfd = hfd; p.rf = rf; p.task_row0 = task_row0; p.W = W; p.replica = replica; p.status = status;

@@ -199,11 +199,11 @@ int hfrep_forward(const float* W, int E, int L, const float* x, int n, int encod
  * shapes whose per-task state does not fit shared memory.  Round 1: correct first (plain FP32 FFMA, L1/L2-served operands),
  * one CTA per task; weights and Nadam state live in the caller's workspace.
  *   hfrep_fit_wide: X f32 [n_x][T][E] scaled blocks (e.g. the workspace of hfrep_window_gather with minmax=1), every task
- *   the same latent width L <= 32; W0 / W_out f32 [n_tasks][2*E*L] (We then Wd); ws f32, 6*E*L floats per task;
+ *   the same latent width L <= 64; W0 / W_out f32 [n_tasks][2*E*L] (We then Wd); ws f32, 6*E*L floats per task;
  *   cfg supplies E (<= 4096), T, n_fit, batch, epochs, patience, Nadam constants, n_x.
  *   hfrep_predict_wide: task i evaluates rows [task_row0[i], +window+2) of the full histories etf f64 [T][E], hfd f64 [T][F],
- *   rf f64 [T]: latent factors of those rows (float32), OLS of every fund on the first `window` rows (float64 QR, needs
- *   L <= window <= 64), normalisation, LeakyReLU mask from row `window`, and replica[i][f] = the replica return of row
+ *   rf f64 [T]: latent factors of those rows (float32), OLS of every fund on the first `window` rows (float64 QR; for
+ *   L > window the minimum-norm solution pinv gives, via the QR of the transposed block; window <= 64), normalisation, LeakyReLU mask from row `window`, and replica[i][f] = the replica return of row
  *   window+1 (Autoencoder_encapsulate.py:133-193 with its own alignment; sums over ETFs regrouped through the L factors). */
 size_t hfrep_fit_wide_workspace(int n_tasks, int E, int L);
 int hfrep_fit_wide(const hfrep_fit_cfg* cfg, const float* X, int n_tasks, int L, const int32_t* task_x, const float* W0,

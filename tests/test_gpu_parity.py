@@ -418,7 +418,7 @@ def test_rolling_beta_option(hf, data, ref_inputs, L):
     assert rel_err(ev.beta[0, :L].cpu().numpy(), ae.betas[0]) < TOL          # reported beta / norm stay window 0's
 
 
-@pytest.mark.parametrize("E,F,L", [(500, 300, 8), (96, 40, 16)])
+@pytest.mark.parametrize("E,F,L", [(500, 300, 8), (96, 40, 16), (120, 50, 32)])   # L=32 > 24 OLS rows: minimum-norm solve
 def test_wide_variant_rolling_refit(hf, E, F, L):
     """configs[3] shape at test scale (500 ETFs, hundreds of funds, 252-row windows, rolling refit) through the wide
     kernels, against the Mode-W oracle (the reference's AE restatement called per window)."""
