@@ -31,6 +31,7 @@ struct EvalParams {
     unsigned char* mask; double* weights; double* beta; double* norm; int* status;
     int n_tasks, w_stride, E, F, T_train, T_test, window, want_oos, n_oos, n_pre, acols;
     int rolling, nq, wsz; // beta_rolling: OLS of every window (nq warps, one workspace of wsz doubles each)
+    int series_dbl;       // doubles reserved for ante/post/turnover [3][n_oos][F] (>= the quality phase's prediction buffers)
     int qsplit;           // CTAs per task: CTA (task, part) scores prefixes part, part+qsplit, ...; part 0 also builds the replica
     int off_float;        // byte offset of the float32 region inside dynamic shared memory (16-byte aligned)
     float alpha;
@@ -79,44 +80,46 @@ __device__ __forceinline__ void forward_row(const float (&x)[HFREP_MAX_E], float
     for (int e = 0; e < HFREP_MAX_E; ++e) y[e] = lrelu(y[e], alpha);
 }
 
-// r2_score (uniform average, sklearn's zero-denominator rule) and per-column-RMSE mean of one block of
-// `n` rows, rows strided over the lanes of one warp.  scaled row = x*scale + shift (MinMaxScaler), all f64.
+// r2_score (uniform average, sklearn's zero-denominator rule) and per-column-RMSE mean of one block of `n` rows by one
+// warp.  Pass of 32 rows: lane = row does the float32 forward pass in registers and parks the prediction in the warp's
+// shared buffer ybuf [32][WS]; then lane = column accumulates that column's squared residuals and squared deviations in
+// float64 (scaled value recomputed as x*scale + shift, MinMaxScaler, without FMA contraction).  No per-lane arrays of
+// partial sums, so the kernel stays under 128 registers.
 // cstat: per-warp shared scratch [3][HFREP_MAX_E] doubles = scale, shift, mean of the scaled column.
 __device__ void block_quality(const double* x, int n, int E, int L, const double* cstat, const float* We,
-                              const float* Wd, float alpha, int lane, double& r2, double& rmse) {
-    double ssr[HFREP_MAX_E], sst[HFREP_MAX_E];
+                              const float* Wd, float alpha, int lane, float* ybuf, double& r2, double& rmse) {
+    double ssr = 0., sst = 0.;                       // lane = column e
+    const double sc = lane < E ? cstat[lane] : 0., sh = lane < E ? cstat[HFREP_MAX_E + lane] : 0.;
+    const double mu = lane < E ? cstat[2 * HFREP_MAX_E + lane] : 0.;
+    for (int r0 = 0; r0 < n; r0 += 32) {
+        const int r = r0 + lane;
+        if (r < n) {
+            float xf[HFREP_MAX_E], yf[HFREP_MAX_E];
 #pragma unroll
-    for (int e = 0; e < HFREP_MAX_E; ++e) ssr[e] = sst[e] = 0.;
-    for (int r = lane; r < n; r += 32) {
-        float xf[HFREP_MAX_E], yf[HFREP_MAX_E];
-        double xs[HFREP_MAX_E];
+            for (int e = 0; e < HFREP_MAX_E; ++e)
+                xf[e] = e < E ? (float)__dadd_rn(__dmul_rn(x[(size_t)r * E + e], cstat[e]), cstat[HFREP_MAX_E + e]) : 0.f;
+            forward_row(xf, yf, We, Wd, E, L, alpha);
 #pragma unroll
-        for (int e = 0; e < HFREP_MAX_E; ++e) {
-            xs[e] = e < E ? __dadd_rn(__dmul_rn(x[(size_t)r * E + e], cstat[e]), cstat[HFREP_MAX_E + e]) : 0.;   // X *= scale; X += min_
-            xf[e] = (float)xs[e];
+            for (int e4 = 0; e4 < HFREP_MAX_E / 4; ++e4)
+                *reinterpret_cast<float4*>(ybuf + lane * WS + 4 * e4) = make_float4(yf[4 * e4], yf[4 * e4 + 1], yf[4 * e4 + 2], yf[4 * e4 + 3]);
         }
-        forward_row(xf, yf, We, Wd, E, L, alpha);
-#pragma unroll
-        for (int e = 0; e < HFREP_MAX_E; ++e) {
-            if (e < E) {
-                const double d = xs[e] - (double)yf[e];
-                const double c = xs[e] - cstat[2 * HFREP_MAX_E + e];
-                ssr[e] += d * d;
-                sst[e] += c * c;
+        __syncwarp();
+        if (lane < E) {
+            const int m = min(32, n - r0);
+            for (int q = 0; q < m; ++q) {
+                const double xs = __dadd_rn(__dmul_rn(x[(size_t)(r0 + q) * E + lane], sc), sh);   // X *= scale; X += min_
+                const double d = xs - (double)ybuf[q * WS + lane];
+                const double c = xs - mu;
+                ssr += d * d;
+                sst += c * c;
             }
         }
+        __syncwarp();
     }
-    double r2s = 0., rms = 0.;
-#pragma unroll
-    for (int e = 0; e < HFREP_MAX_E; ++e) {
-        if (e < E) {
-            const double num = warp_sum(ssr[e]), den = warp_sum(sst[e]);
-            r2s += den != 0. ? 1. - num / den : (num != 0. ? 0. : 1.);
-            rms += sqrt(num / n);
-        }
-    }
-    r2 = r2s / E;
-    rmse = rms / E;
+    const double r2e = lane < E ? (sst != 0. ? 1. - ssr / sst : (ssr != 0. ? 0. : 1.)) : 0.;
+    const double rme = lane < E ? sqrt(ssr / n) : 0.;
+    r2 = warp_sum(r2e) / E;
+    rmse = warp_sum(rme) / E;
 }
 
 // The 11 per-series statistics of one return series of n values (stride ss) against a fund series y (stride ys),
@@ -192,7 +195,7 @@ __device__ void series_stats(const double* s, int ss, const double* y, int ys, c
     }
 }
 
-__global__ void __launch_bounds__(NTH_EVAL) eval_kernel(const EvalParams p) {
+__global__ void __launch_bounds__(NTH_EVAL, 2) eval_kernel(const EvalParams p) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int task = blockIdx.x / p.qsplit, qpart = blockIdx.x - task * p.qsplit;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -214,7 +217,9 @@ __global__ void __launch_bounds__(NTH_EVAL) eval_kernel(const EvalParams p) {
     double* anteS = wsp + (size_t)p.nq * p.wsz;                   // [n_oos][F]
     double* postS = anteS + (size_t)n_oos * F;                    // [n_oos][F]
     double* turnS = postS + (size_t)n_oos * F;                    // [n_oos][F]
-    double* cstat = turnS + (size_t)n_oos * F;                    // [NW][3][HFREP_MAX_E]
+    double* cstat = anteS + p.series_dbl;                         // [NW][3][HFREP_MAX_E]
+    // the quality phase runs before the replica stages: its prediction buffers [NW][32][WS] floats share their storage
+    float* ybuf = reinterpret_cast<float*>(anteS) + warp * 32 * WS;
     float* We = reinterpret_cast<float*>(smem_raw + p.off_float); // [E][WS]
     float* Wd = We + HFREP_MAX_E * WS;                            // [L][WS]
     float* M = Wd + HFREP_MAX_L * WS;                             // [T_test][WS] latent factors
@@ -245,7 +250,7 @@ __global__ void __launch_bounds__(NTH_EVAL) eval_kernel(const EvalParams p) {
             }
             __syncwarp();
             double r2, rmse;
-            block_quality(p.Xtr, p.T_train, E, L, cs, We, Wd, alpha, lane, r2, rmse);
+            block_quality(p.Xtr, p.T_train, E, L, cs, We, Wd, alpha, lane, ybuf, r2, rmse);
             if (lane == 0) { q[0] = r2; q[1] = rmse; }
             __syncwarp();
         }
@@ -273,7 +278,7 @@ __global__ void __launch_bounds__(NTH_EVAL) eval_kernel(const EvalParams p) {
                 }
                 __syncwarp();
                 double r2, rmse;
-                block_quality(Xte, n, E, L, cs, We, Wd, alpha, lane, r2, rmse);
+                block_quality(Xte, n, E, L, cs, We, Wd, alpha, lane, ybuf, r2, rmse);
                 if (lane == 0) { q[2 + j] = r2; q[2 + p.n_pre + j] = rmse; }
                 __syncwarp();
             }
@@ -537,7 +542,11 @@ extern "C" int hfrep_predict_metrics(const hfrep_eval_cfg* c, const double* Xtr,
     p.rolling = c->beta_rolling ? 1 : 0;
     p.nq = p.rolling ? 4 : 1;
     p.wsz = (int)((size_t)c->window * p.acols + HFREP_MAX_L * c->F + (size_t)c->F * c->E + c->F + c->window);
-    size_t dbl = (size_t)p.nq * p.wsz + 3 * (size_t)p.n_oos * c->F + (NTH_EVAL / 32) * 3 * HFREP_MAX_E;
+    p.wsz = (p.wsz + 1) & ~1;                // keeps what follows 16-byte aligned (float4 prediction buffers)
+    p.series_dbl = (int)(3 * (size_t)p.n_oos * c->F);
+    if (p.series_dbl < (NTH_EVAL / 32) * 32 * WS / 2) p.series_dbl = (NTH_EVAL / 32) * 32 * WS / 2;
+    p.series_dbl = (p.series_dbl + 1) & ~1;
+    size_t dbl = (size_t)p.nq * p.wsz + (size_t)p.series_dbl + (NTH_EVAL / 32) * 3 * HFREP_MAX_E;
     dbl = (dbl + 1) & ~(size_t)1;           // float region starts 16-byte aligned
     p.off_float = (int)(dbl * 8);
     const size_t flt = (size_t)HFREP_MAX_E * WS + (size_t)HFREP_MAX_L * WS + (size_t)c->T_test * WS;

@@ -76,6 +76,12 @@ def test_host_prep_matches_oracle(ref_inputs):
         assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1])
         assert np.abs(a[0]).max() <= np.sqrt(6 / (22 + L))
     assert np.array_equal(engine.epoch_permutations(7, 5, 126), fitcore.make_perm(7, 5, 126))
+    # device-side shuffle streams: host replica == oracle restatement, and every row is a permutation
+    for seed in (0, 5, 123456789, 0xFFFFFFFF):
+        tab = engine.device_permutations(seed, 4, 126)
+        assert np.array_equal(tab, fitcore.device_perm(seed, 4, 126))
+        assert all(sorted(r.tolist()) == list(range(126)) for r in tab)
+    assert not np.array_equal(engine.device_permutations(5, 2, 126)[0], engine.device_permutations(5, 2, 126)[1])
     We, Wd = engine.initial_weights(1, 22, 5)
     row = engine.pack_weights([(We, Wd)], 22, 2 * 22 * 8)[0]
     We2, Wd2 = engine.unpack_weights(row, 22, 5)
