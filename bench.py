@@ -117,6 +117,28 @@ def cpu_baseline_single_core(budget_s=20.):
             "sample": f"L in {sorted(sample)} of the cfg2 sweep, full pipeline, {spent:.1f} s on one core"}
 
 
+def cpu_best_effort():
+    """the fit alone as compiled C (oracle/c/fit_oracle.c, gcc -O2 -march=native, OpenMP over the 21
+    tasks of the sweep) on all host cores — shown so the speed-up is not only "Python overhead removed".  The
+    evaluation stages are NOT included, so this over-states the CPU's task-fits/sec."""
+    try:
+        from oracle import c_oracle, fitcore, ae_oracle
+        etf, _, _ = synthetic_returns()
+        x = ae_oracle.minmax_fit_transform(etf[:168]).astype(np.float32)
+        W = np.zeros((len(LATENTS), 2 * E * max(LATENTS)), np.float32)
+        for i, L in enumerate(LATENTS):
+            a, b = fitcore.initial_weights(123, E, L)
+            W[i, :E * L], W[i, E * L:2 * E * L] = a.ravel(), b.ravel()
+        c_oracle.fit_many(x, LATENTS, W.copy(), epochs=50)                      # warm-up
+        t = time.perf_counter()
+        _, _, ep = c_oracle.fit_many(x, LATENTS, W, epochs=EPOCHS)
+        dt = time.perf_counter() - t
+        return {"value": len(LATENTS) / dt, "unit": UNIT, "cores": len(os.sched_getaffinity(0)), "kind": "port-c, fit only",
+                "sample": f"21 fits of the sweep, {float(ep.mean()):.0f} epochs on average, no evaluation stages, {dt:.2f} s"}
+    except Exception as exc:                                # no gcc on the box: report why, do not fail the bench
+        return {"unavailable": str(exc)[:200]}
+
+
 # --------------------------------------------------------------------------------------- clocks
 class ClockSampler:
     FIELDS = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
@@ -326,6 +348,7 @@ def gpu_arm(args):
         "gpu_launches": args.steps * (n_buckets + 1),
         "roofline": roofline,
         "cpu_baseline": cpu,
+        "cpu_best_effort": cpu_best_effort() if cpu is not None else None,
         "ensemble": ens,
         "wall_s_timed_region": wall,
     }

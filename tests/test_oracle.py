@@ -107,3 +107,18 @@ def test_reference_import_is_unmodified_source():
         assert np.allclose(helper.normalization(g["norm_Y"], g["norm_X"], g["norm_beta"], 24), g["norm_out"])
     finally:
         refbridge.unload()
+
+
+def test_c_restatement_agrees_with_numpy_restatement():
+    """Two independent restatements of the fit (numpy float32, plain C float32) must agree within the parity tolerance,
+    on the reference run's inputs: deterministic order for 1000 epochs, and shuffled order with the same early stop."""
+    from oracle import c_oracle
+    g = load_golden("ref_modeR_L21")
+    o = c_oracle.fit(g["x_train_scaled"], g["We0"], g["Wd0"], epochs=1000)
+    assert o["epochs_run"] == 1000
+    assert np.max(np.abs(o["loss"] - g["loss"]) / g["loss"]) < 1e-5
+    assert rel_err(o["We"], g["We"]) < 1e-5 and rel_err(o["Wd"], g["Wd"]) < 1e-5
+    gs = load_golden("ref_modeR_L8_shuffled")
+    o = c_oracle.fit(gs["x_train_scaled"], gs["We0"], gs["Wd0"], epochs=1000, perm=fitcore.make_perm(int(gs["perm_seed"]), 1000, 126))
+    assert o["epochs_run"] == int(gs["epochs_run"])
+    assert np.max(np.abs(o["val_loss"] - gs["val_loss"]) / gs["val_loss"]) < 1e-5
