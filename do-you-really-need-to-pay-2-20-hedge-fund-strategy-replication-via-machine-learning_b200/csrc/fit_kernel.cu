@@ -5,10 +5,11 @@
 // i.e. the Keras fit loop; semantics restated in SURVEY.md App. A.1-A.6.
 //
 // Per mini-batch step, three phases separated by team barriers:
-//   rows    one lane per batch row (CS=2: a lane pair per row, each half of the columns): the row's
-//           zh -> h -> zy -> y, squared error, dzy -> dzh accumulate in REGISTERS; weights are read as
-//           warp-broadcast 128-bit shared loads (1 LDS.128 per 4 FFMA) in rolled k4-loops (small code,
-//           few live registers).  h, dzy, dzh rows are parked in shared memory for the weight gradients.
+//   rows    every warp of the team walks all batch rows, three rows per lane (lane pair g: rows g, g+16, g+32 of a
+//           48-row pass), and owns float2 column pieces of the latent and the ETF block (2*NW lane classes).  The
+//           rows' zh -> h -> zy -> y, squared error, dzy -> dzh accumulate in REGISTERS; one weight LDS.64 feeds
+//           three rows (3 FFMA2).  h, dzy, dzh rows are parked in shared memory for the other classes and for the
+//           weight gradients.
 //   grads   dWd = H^T dZy and dWe = X_b^T dZh as 4x4 register tiles (outer products, 2 LDS.128 per 16
 //           FFMA); the batch rows are split over the team's warps (split-K), partial tiles go to
 //           shared memory in tile-major order.
@@ -106,11 +107,12 @@ __device__ __forceinline__ float fast_sqrt(float x) {      // MUFU.SQRT, 1 ulp; 
     return r;
 }
 
-// LP: padded latent width; NW: warps per team; CS: lanes per batch row (1, or 2 = a lane pair splits the columns);
-// TPC: most teams per CTA (the launch picks blockDim.x / (32*NW) <= TPC teams from the shared-memory budget); FULL: fully unroll the k-loops of the rows phase (latency mapping: one warp per scheduler,
-// registers are free, the compiler software-pipelines the shared loads) instead of rolling them (throughput mapping)
+// LP: padded latent width; NW: warps per team (1, 2, 3 or 6: 2*NW lane classes must divide the 12 ETF float2 pieces);
+// TPC: most teams per CTA (the launch picks blockDim.x / (32*NW) <= TPC teams from the shared-memory budget);
+// FULL: fully unroll the k-loops of the rows phase (latency mapping: a handful of tasks, registers are free, the
+// compiler software-pipelines the shared loads) instead of rolling them (throughput mapping);
 // XT: batch-tile mode (see Lay::team_floats) — any block length T, any block per task, several teams per CTA
-template <int LP, int NW, int CS, int TPC, bool FULL, bool XT>
+template <int LP, int NW, int TPC, bool FULL, bool XT>
 __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
     extern __shared__ __align__(16) float smem[];
     constexpr int NTH = 32 * NW;
@@ -118,17 +120,6 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
     constexpr int CT = Lay<LP>::CT;
     constexpr int NT5 = Lay<LP>::NT5;
     constexpr int NEL = Lay<LP>::NEL;
-    // Column split of the rows phase (CS == 2): the pair shares a row; lane `part` owns the float4 column groups
-    // g = 2i+part of the latent block (plus half of the last group when their number is odd) and the ETF columns
-    // [part*12, part*12+12).  CS == 1: a lane owns everything.
-    // CS == 4 (latency mapping, LP % 8 == 0): a lane quad shares a row; lane `part` owns the float2 pieces at
-    // columns 8j + 2*part of both the latent and the ETF block (see rows_phase_quad).
-    constexpr int NG4 = (CS == 4) ? 0 : CT / CS;   // whole float4 latent groups per lane
-    constexpr int TAIL = (CS == 2) ? (CT % 2) : 0; // 1: one extra float2 piece per lane
-    constexpr int LPC = (CS == 4) ? LP / 4 : 4 * NG4 + 2 * TAIL;   // latent columns per lane
-    constexpr int EPC = EP / CS;                   // ETF columns per lane
-    constexpr int ROWS = NTH / CS;                 // batch rows per pass
-    constexpr int UK = FULL ? EP / 4 : 2;          // unroll of the k4-loops
     const int team = threadIdx.x / NTH;
     const int tl = threadIdx.x - team * NTH;       // lane within the team
     const int warp = tl >> 5, lane = tl & 31;
@@ -179,9 +170,9 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
             if (t < 6 * CT) {                            // dWd tile (lt, et): Wd[lt*4+i][et*4+jj]
                 const int lt = t / 6, et = t - lt * 6;
                 o = EP * LP + (lt * 4 + i) * WDS + et * 4 + jj;
-            } else {                                     // dWe tile (et, lt): We[et*4+i][lt*4+jj]
+            } else {                                     // dWe tile (lt, et): We[et*4+i][lt*4+jj]
                 const int u = t - 6 * CT;
-                const int et = u / CT, lt = u - et * CT;
+                const int lt = u / 6, et = u - lt * 6;
                 o = (et * 4 + i) * LP + lt * 4 + jj;
             }
             woff[idx] = o;
@@ -208,226 +199,146 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
     const int* perm_t = p.perm ? p.perm + (size_t)task * p.perm_task_stride : nullptr;
     const float alpha = p.alpha;
     const float omb1 = 1.f - p.b1, omb2 = 1.f - p.b2;
-    const int part_id = (CS == 1) ? 0 : (tl & (CS - 1));      // which column part this lane handles
-    const int row_in_pass = tl / CS;
 
     // ---------------------------------------------------------------- rows phase
-    // Forward (and backward to dZh) of the batch rows, one row per lane (pair).  Returns the lane's share of the
-    // squared error.  Lanes without a row work on the all-zero row T and park their (all-zero) results in
-    // scratch row BP, so the phase needs no predication and pairs stay converged.
-    // All multiply-adds are packed FFMA2 (fma.rn.f32x2, sm_100): two IEEE-rounded FP32 FMAs per issue slot,
-    // bit-identical to scalar fmaf.
+    // Forward (and backward to dZh) of the batch rows.  Returns the lane's share of the squared error.  Lanes
+    // without a row work on the all-zero row and park their (all-zero) results in scratch row BP, so the phase
+    // needs no predication.  All multiply-adds are packed FFMA2 (fma.rn.f32x2, sm_100): two IEEE-rounded FP32
+    // FMAs per issue slot, bit-identical to scalar fmaf.
+    // Shared-memory loads, not FMAs, bound a one-row-per-lane layout: a broadcast LDS.128 costs 2 cycles of the SM's
+    // shared-memory pipe and would feed only 2 FFMA2 (profiles/microbench/lds_wavefronts.cu: LDS.64 / LDS.128 run at
+    // 1 / 2 cycles only when lane pairs share an address or the warp alternates between two).  So a lane holds
+    // THREE rows (g, g+16, g+32 of the pass; g = lane/2) and float2 column pieces p = class + j*NC of the latent and
+    // the ETF block (class = 2*warp + lane&1, NC = 2*NW): one LDS.64 (two-address pattern, 1 cycle) feeds 3 FFMA2,
+    // row loads are pair-shared LDS.128 (2 cycles).  Every warp walks all rows, so h and dzy rows cross warps:
+    // two team barriers per pass (a __syncwarp for one-warp teams).
+    // Pieces past the block (LP/2 not a multiple of NC) are computed on whatever follows in shared memory and dropped.
     auto rows_phase = [&](const int* xoff, int nb, bool train, float coef) -> float {
+        constexpr int NC = 2 * NW;
+        constexpr int NPL = (LP / 2 + NC - 1) / NC;   // latent pieces per lane
+        constexpr int NPE = (EP / 2) / NC;            // ETF pieces per lane (12 splits evenly over 2, 4, 6, 12 classes)
+        static_assert((EP / 2) % NC == 0, "column-split mapping: 2*NW must divide 12");
+        const int cls = 2 * warp + (lane & 1);
+        const int g = lane >> 1;
+        const float* Wl = We + 2 * cls;               // piece i of a We row at Wl + 2*NC*i
+        const float* Wy = Wd + 2 * cls;               // piece i of a Wd row at Wy + 2*NC*i
         float2 sse2 = make_float2(0.f, 0.f);
 #pragma unroll 1
-        for (int r0 = 0; r0 < nb; r0 += ROWS) {
-            const int r = r0 + row_in_pass;
-            const bool valid = r < nb;
-            const float* xr = Xs + (valid ? (XT ? r * XS : xoff[r]) : zero_row);
-            const int rs = valid ? r : BP;
-            float* hrow = H + rs * HS;
-            float* yrow = dZy + rs * XS;
-            // own latent columns: float4 groups at 4*(CS*i+part_id), tail float2 at 4*(CT-1)+2*part_id
-            const int lcol0 = 4 * part_id;
-            const int ltail = 4 * (CT - 1) + 2 * part_id;
-            // ---- zh (own columns) = x . We[:, cols]
-            float2 zh[LPC / 2];
+        for (int r0 = 0; r0 < nb; r0 += 48) {
+            const float* xr[3];
+            int rs[3];
 #pragma unroll
-            for (int l = 0; l < LPC / 2; ++l) zh[l] = make_float2(0.f, 0.f);
-#pragma unroll (UK)
+            for (int j = 0; j < 3; ++j) {
+                const int r = r0 + g + 16 * j;
+                const bool valid = r < nb;
+                xr[j] = Xs + (valid ? (XT ? r * XS : xoff[r]) : zero_row);
+                rs[j] = valid ? r : BP;
+            }
+            // ---- zh pieces = x . We[:, own pieces]
+            float2 zh[3][NPL];
+#pragma unroll
+            for (int j = 0; j < 3; ++j)
+#pragma unroll
+                for (int i = 0; i < NPL; ++i) zh[j][i] = make_float2(0.f, 0.f);
+#pragma unroll (FULL ? EP / 4 : 1)
             for (int e4 = 0; e4 < EP / 4; ++e4) {
-                const float4 xv = ld4(xr + 4 * e4);
-                const float xe[4] = {xv.x, xv.y, xv.z, xv.w};
+                float xe[3][4];
 #pragma unroll
-                for (int k = 0; k < 4; ++k) {
-                    const float* wrow = We + (4 * e4 + k) * LP;
-                    const float2 xx = make_float2(xe[k], xe[k]);
-#pragma unroll
-                    for (int i = 0; i < NG4; ++i) {
-                        const float4 w = ld4(wrow + lcol0 + 4 * CS * i);
-                        zh[2 * i + 0] = __ffma2_rn(xx, make_float2(w.x, w.y), zh[2 * i + 0]);
-                        zh[2 * i + 1] = __ffma2_rn(xx, make_float2(w.z, w.w), zh[2 * i + 1]);
-                    }
-                    if constexpr (TAIL) zh[2 * NG4] = __ffma2_rn(xx, ld2(wrow + ltail), zh[2 * NG4]);
+                for (int j = 0; j < 3; ++j) {
+                    const float4 v = ld4(xr[j] + 4 * e4);
+                    xe[j][0] = v.x; xe[j][1] = v.y; xe[j][2] = v.z; xe[j][3] = v.w;
                 }
+#pragma unroll
+                for (int k = 0; k < 4; ++k)
+#pragma unroll
+                    for (int i = 0; i < NPL; ++i) {
+                        const float2 w = ld2(Wl + (4 * e4 + k) * LP + 2 * NC * i);
+#pragma unroll
+                        for (int j = 0; j < 3; ++j) zh[j][i] = __ffma2_rn(make_float2(xe[j][k], xe[j][k]), w, zh[j][i]);
+                    }
             }
 #pragma unroll
-            for (int i = 0; i < NG4; ++i)
-                st4(hrow + lcol0 + 4 * CS * i, make_float4(lrelu(zh[2 * i].x, alpha), lrelu(zh[2 * i].y, alpha),
-                                                           lrelu(zh[2 * i + 1].x, alpha), lrelu(zh[2 * i + 1].y, alpha)));
-            if constexpr (TAIL) st2(hrow + ltail, make_float2(lrelu(zh[2 * NG4].x, alpha), lrelu(zh[2 * NG4].y, alpha)));
-            if constexpr (CS > 1) __syncwarp();
-            // ---- zy (own EPC columns) = h . Wd[:, cols]; h re-read from the row (written by the pair)
-            float2 zy[EPC / 2];
+            for (int i = 0; i < NPL; ++i)
+                if (cls + NC * i < LP / 2) {
 #pragma unroll
-            for (int e = 0; e < EPC / 2; ++e) zy[e] = make_float2(0.f, 0.f);
-            const float* wdp = Wd + part_id * EPC;
-#pragma unroll (UK)
+                    for (int j = 0; j < 3; ++j)
+                        st2(H + rs[j] * HS + 2 * (cls + NC * i), make_float2(lrelu(zh[j][i].x, alpha), lrelu(zh[j][i].y, alpha)));
+                }
+            team_sync<NW>(team);
+            // ---- zy pieces = h . Wd[:, own pieces]
+            float2 zy[3][NPE];
+#pragma unroll
+            for (int j = 0; j < 3; ++j)
+#pragma unroll
+                for (int i = 0; i < NPE; ++i) zy[j][i] = make_float2(0.f, 0.f);
+#pragma unroll (FULL ? CT : 1)
             for (int l4 = 0; l4 < CT; ++l4) {
-                const float4 hv = ld4(hrow + 4 * l4);
-                const float hl[4] = {hv.x, hv.y, hv.z, hv.w};
+                float hl[3][4];
 #pragma unroll
-                for (int k = 0; k < 4; ++k) {
-                    const float2 hh = make_float2(hl[k], hl[k]);
+                for (int j = 0; j < 3; ++j) {
+                    const float4 v = ld4(H + rs[j] * HS + 4 * l4);
+                    hl[j][0] = v.x; hl[j][1] = v.y; hl[j][2] = v.z; hl[j][3] = v.w;
+                }
 #pragma unroll
-                    for (int e4 = 0; e4 < EPC / 4; ++e4) {
-                        const float4 w = ld4(wdp + (4 * l4 + k) * WDS + 4 * e4);
-                        zy[2 * e4 + 0] = __ffma2_rn(hh, make_float2(w.x, w.y), zy[2 * e4 + 0]);
-                        zy[2 * e4 + 1] = __ffma2_rn(hh, make_float2(w.z, w.w), zy[2 * e4 + 1]);
+                for (int k = 0; k < 4; ++k)
+#pragma unroll
+                    for (int i = 0; i < NPE; ++i) {
+                        const float2 w = ld2(Wy + (4 * l4 + k) * WDS + 2 * NC * i);
+#pragma unroll
+                        for (int j = 0; j < 3; ++j) zy[j][i] = __ffma2_rn(make_float2(hl[j][k], hl[j][k]), w, zy[j][i]);
                     }
-                }
             }
-            // ---- squared error and dLoss/dzy on the lane's columns
+            // ---- squared error and dLoss/dzy on the lane's pieces
 #pragma unroll
-            for (int e4 = 0; e4 < EPC / 4; ++e4) {
-                const float4 xv = ld4(xr + part_id * EPC + 4 * e4);
-                const float xe[4] = {xv.x, xv.y, xv.z, xv.w};
-                float z[4] = {zy[2 * e4].x, zy[2 * e4].y, zy[2 * e4 + 1].x, zy[2 * e4 + 1].y};
+            for (int j = 0; j < 3; ++j)
 #pragma unroll
-                for (int k = 0; k < 4; ++k) {
-                    const float d = lrelu(z[k], alpha) - xe[k];
-                    if (k & 1) sse2.y = fmaf(d, d, sse2.y); else sse2.x = fmaf(d, d, sse2.x);
-                    z[k] = lrelu_grad(z[k], coef * d, alpha);      // now dzy
+                for (int i = 0; i < NPE; ++i) {
+                    const float2 xv = ld2(xr[j] + 2 * (cls + NC * i));
+                    const float dx = lrelu(zy[j][i].x, alpha) - xv.x, dy = lrelu(zy[j][i].y, alpha) - xv.y;
+                    sse2.x = fmaf(dx, dx, sse2.x);
+                    sse2.y = fmaf(dy, dy, sse2.y);
+                    zy[j][i] = make_float2(lrelu_grad(zy[j][i].x, coef * dx, alpha), lrelu_grad(zy[j][i].y, coef * dy, alpha));
                 }
-                zy[2 * e4] = make_float2(z[0], z[1]);
-                zy[2 * e4 + 1] = make_float2(z[2], z[3]);
-            }
             if (train) {
 #pragma unroll
-                for (int e4 = 0; e4 < EPC / 4; ++e4)
-                    st4(yrow + part_id * EPC + 4 * e4, make_float4(zy[2 * e4].x, zy[2 * e4].y, zy[2 * e4 + 1].x, zy[2 * e4 + 1].y));
-                float2 dzy[EP / 2];
-                if constexpr (CS > 1) {
-                    __syncwarp();
+                for (int j = 0; j < 3; ++j)
 #pragma unroll
-                    for (int e4 = 0; e4 < EP / 4; ++e4) {
-                        const float4 v = ld4(yrow + 4 * e4);
-                        dzy[2 * e4] = make_float2(v.x, v.y); dzy[2 * e4 + 1] = make_float2(v.z, v.w);
-                    }
-                } else {
+                    for (int i = 0; i < NPE; ++i) st2(dZy + rs[j] * XS + 2 * (cls + NC * i), zy[j][i]);
+                team_sync<NW>(team);
+                // ---- dzh pieces = (dzy . Wd[l, :]) * lrelu'(zh) for the own latent columns; the ETF index is the outer
+                // loop (a float4 of each dzy row and of each own Wd row per step), two packed partial sums per (row, column)
+                float2 acc[3][2 * NPL];
 #pragma unroll
-                    for (int e = 0; e < EP / 2; ++e) dzy[e] = zy[e];
-                }
-                // ---- dzh (own columns) = (dzy . Wd[l, :]) * lrelu'(zh); two packed partial sums per column
-                float* grow = dZh + rs * HS;
-                auto dzh_col = [&](int l, float hsign) -> float {
-                    const float* wr = Wd + l * WDS;
-                    float2 a01 = make_float2(0.f, 0.f), a23 = make_float2(0.f, 0.f);
+                for (int j = 0; j < 3; ++j)
 #pragma unroll
-                    for (int e4 = 0; e4 < EP / 4; ++e4) {
-                        const float4 w = ld4(wr + 4 * e4);
-                        a01 = __ffma2_rn(dzy[2 * e4 + 0], make_float2(w.x, w.y), a01);
-                        a23 = __ffma2_rn(dzy[2 * e4 + 1], make_float2(w.z, w.w), a23);
-                    }
-                    return lrelu_grad(hsign, (a01.x + a01.y) + (a23.x + a23.y), alpha);   // sign(h) == sign(zh) for alpha > 0
-                };
-#pragma unroll 1
-                for (int i = 0; i < NG4; ++i) {
-                    const int l0 = lcol0 + 4 * CS * i;
-                    const float4 hv = ld4(hrow + l0);
-                    st4(grow + l0, make_float4(dzh_col(l0, hv.x), dzh_col(l0 + 1, hv.y), dzh_col(l0 + 2, hv.z),
-                                               dzh_col(l0 + 3, hv.w)));
-                }
-                if constexpr (TAIL) {
-                    const float2 hv = ld2(hrow + ltail);
-                    st2(grow + ltail, make_float2(dzh_col(ltail, hv.x), dzh_col(ltail + 1, hv.y)));
-                }
-            }
-        }
-        return sse2.x + sse2.y;
-    };
-
-    // ---------------------------------------------------------------- rows phase, quad variant (CS == 4)
-    // Same arithmetic as rows_phase with a row spread over four lanes: every lane owns the float2 pieces at
-    // columns 8j + 2*part (j < LP/8 latent pieces, 3 ETF pieces).  A quarter of the FMAs per lane, twice the
-    // warps: the latency mapping for a handful of tasks.  Rows are exchanged through the shared rows + __syncwarp.
-    auto rows_phase_quad = [&](const int* xoff, int nb, bool train, float coef) -> float {
-        constexpr int NPL = LP >= 8 ? LP / 8 : 1;  // latent float2 pieces per lane (only instantiated for LP % 8 == 0)
-        constexpr int NPE = EP / 8;                // ETF float2 pieces per lane (3)
-        float2 sse2 = make_float2(0.f, 0.f);
-#pragma unroll 1
-        for (int r0 = 0; r0 < nb; r0 += ROWS) {
-            const int r = r0 + row_in_pass;
-            const bool valid = r < nb;
-            const float* xr = Xs + (valid ? (XT ? r * XS : xoff[r]) : zero_row);
-            const int rs = valid ? r : BP;
-            float* hrow = H + rs * HS;
-            float* yrow = dZy + rs * XS;
-            float* grow = dZh + rs * HS;
-            const int c0 = 2 * part_id;            // own pieces start at column 8j + c0
-            // ---- zh pieces = x . We[:, own columns]
-            float2 zh[NPL];
-#pragma unroll
-            for (int l = 0; l < NPL; ++l) zh[l] = make_float2(0.f, 0.f);
-#pragma unroll
-            for (int e4 = 0; e4 < EP / 4; ++e4) {
-                const float4 xv = ld4(xr + 4 * e4);
-                const float xe[4] = {xv.x, xv.y, xv.z, xv.w};
-#pragma unroll
-                for (int k = 0; k < 4; ++k) {
-                    const float* wrow = We + (4 * e4 + k) * LP + c0;
-                    const float2 xx = make_float2(xe[k], xe[k]);
-#pragma unroll
-                    for (int j = 0; j < NPL; ++j) zh[j] = __ffma2_rn(xx, ld2(wrow + 8 * j), zh[j]);
-                }
-            }
-#pragma unroll
-            for (int j = 0; j < NPL; ++j)
-                st2(hrow + 8 * j + c0, make_float2(lrelu(zh[j].x, alpha), lrelu(zh[j].y, alpha)));
-            __syncwarp();
-            // ---- zy pieces = h . Wd[:, own columns]
-            float2 zy[NPE];
-#pragma unroll
-            for (int e = 0; e < NPE; ++e) zy[e] = make_float2(0.f, 0.f);
-#pragma unroll
-            for (int l4 = 0; l4 < CT; ++l4) {
-                const float4 hv = ld4(hrow + 4 * l4);
-                const float hl[4] = {hv.x, hv.y, hv.z, hv.w};
-#pragma unroll
-                for (int k = 0; k < 4; ++k) {
-                    const float* wrow = Wd + (4 * l4 + k) * WDS + c0;
-                    const float2 hh = make_float2(hl[k], hl[k]);
-#pragma unroll
-                    for (int j = 0; j < NPE; ++j) zy[j] = __ffma2_rn(hh, ld2(wrow + 8 * j), zy[j]);
-                }
-            }
-            // ---- squared error and dLoss/dzy on the lane's columns
-#pragma unroll
-            for (int j = 0; j < NPE; ++j) {
-                const float2 xv = ld2(xr + 8 * j + c0);
-                const float dx = lrelu(zy[j].x, alpha) - xv.x, dy = lrelu(zy[j].y, alpha) - xv.y;
-                sse2.x = fmaf(dx, dx, sse2.x);
-                sse2.y = fmaf(dy, dy, sse2.y);
-                zy[j] = make_float2(lrelu_grad(zy[j].x, coef * dx, alpha), lrelu_grad(zy[j].y, coef * dy, alpha));
-            }
-            if (train) {
-#pragma unroll
-                for (int j = 0; j < NPE; ++j) st2(yrow + 8 * j + c0, zy[j]);
-                __syncwarp();
-                float2 dzy[EP / 2];
-#pragma unroll
+                    for (int c = 0; c < 2 * NPL; ++c) acc[j][c] = make_float2(0.f, 0.f);
+#pragma unroll (FULL ? EP / 4 : 1)
                 for (int e4 = 0; e4 < EP / 4; ++e4) {
-                    const float4 v = ld4(yrow + 4 * e4);
-                    dzy[2 * e4] = make_float2(v.x, v.y); dzy[2 * e4 + 1] = make_float2(v.z, v.w);
-                }
-                // ---- dzh pieces = (dzy . Wd[l, :]) * lrelu'(zh) for the own latent columns
+                    float2 d01[3], d23[3];
 #pragma unroll
-                for (int j = 0; j < NPL; ++j) {
-                    float out[2];
-#pragma unroll
-                    for (int k = 0; k < 2; ++k) {
-                        const float* wr = Wd + (8 * j + c0 + k) * WDS;
-                        float2 a01 = make_float2(0.f, 0.f), a23 = make_float2(0.f, 0.f);
-#pragma unroll
-                        for (int e4 = 0; e4 < EP / 4; ++e4) {
-                            const float4 w = ld4(wr + 4 * e4);
-                            a01 = __ffma2_rn(dzy[2 * e4 + 0], make_float2(w.x, w.y), a01);
-                            a23 = __ffma2_rn(dzy[2 * e4 + 1], make_float2(w.z, w.w), a23);
-                        }
-                        out[k] = lrelu_grad(k ? zh[j].y : zh[j].x, (a01.x + a01.y) + (a23.x + a23.y), alpha);
+                    for (int j = 0; j < 3; ++j) {
+                        const float4 v = ld4(dZy + rs[j] * XS + 4 * e4);
+                        d01[j] = make_float2(v.x, v.y); d23[j] = make_float2(v.z, v.w);
                     }
-                    st2(grow + 8 * j + c0, make_float2(out[0], out[1]));
+#pragma unroll
+                    for (int c = 0; c < 2 * NPL; ++c) {
+                        const float4 w = ld4(Wd + (2 * (cls + NC * (c >> 1)) + (c & 1)) * WDS + 4 * e4);
+#pragma unroll
+                        for (int j = 0; j < 3; ++j) {
+                            acc[j][c] = __ffma2_rn(d01[j], make_float2(w.x, w.y), acc[j][c]);
+                            acc[j][c] = __ffma2_rn(d23[j], make_float2(w.z, w.w), acc[j][c]);
+                        }
+                    }
                 }
+#pragma unroll
+                for (int i = 0; i < NPL; ++i)
+                    if (cls + NC * i < LP / 2) {
+#pragma unroll
+                        for (int j = 0; j < 3; ++j)
+                            st2(dZh + rs[j] * HS + 2 * (cls + NC * i),
+                                make_float2(lrelu_grad(zh[j][i].x, acc[j][2 * i].x + acc[j][2 * i].y, alpha),
+                                            lrelu_grad(zh[j][i].y, acc[j][2 * i + 1].x + acc[j][2 * i + 1].y, alpha)));
+                    }
             }
         }
         return sse2.x + sse2.y;
@@ -445,7 +356,7 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
                 a0 = (int)(H - Xs) + lt * 4; b0 = (int)(dZy - Xs) + et * 4; bstr = XS;
             } else {                                     // dWe tile: A = X_b[:, et*4..], B = dZh[:, lt*4..]
                 const int u = t - 6 * CT;
-                const int et = u / CT, lt = u - et * CT;
+                const int lt = u / 6, et = u - lt * 6;     // lt-major like dWd: six consecutive lanes share a chunk
                 a0 = et * 4; b0 = (int)(dZh - Xs) + lt * 4; bstr = HS;
             }
             float2 acc[4][2];
@@ -596,8 +507,7 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
             if constexpr (!XT) prefetch_next();
             float sse = 0.f;
             if (!(p.debug_skip & 1)) {
-                if constexpr (CS == 4) sse = rows_phase_quad(xoff, nb, train, 2.f / (float)(nb * E));
-                else sse = rows_phase(xoff, nb, train, 2.f / (float)(nb * E));
+                sse = rows_phase(xoff, nb, train, 2.f / (float)(nb * E));
             }
             if (train) {
                 lsum += sse;
@@ -671,7 +581,7 @@ static size_t fit_smem_bytes(const FitParams& p, int tpc, bool xt) {
 // Resident mode: teams of one CTA share the staged training block, so several teams per CTA need n_x == 1 and the block
 // must fit.  Batch-tile mode (own block per task, or a block too long for shared memory) has neither limit.  The launch
 // takes the largest team count (<= TPC) whose shared memory fits.
-template <int LP, int NW, int CS, int TPC, bool FULL, bool XT>
+template <int LP, int NW, int TPC, bool FULL, bool XT>
 static int launch_fit_mode(const FitParams& p, cudaStream_t stream) {
     int tpc = TPC;
     while (tpc > 1 && fit_smem_bytes<LP, NW>(p, tpc, XT) > kMaxSmem) --tpc;
@@ -680,7 +590,7 @@ static int launch_fit_mode(const FitParams& p, cudaStream_t stream) {
     const size_t smem = fit_smem_bytes<LP, NW>(p, tpc, XT);
     HFREP_REQUIRE(smem <= kMaxSmem, "fit: %zu bytes of shared memory needed (batch=%d too large for the narrow kernel)", smem,
                   p.batch);
-    auto kern = fit_kernel<LP, NW, CS, TPC, FULL, XT>;
+    auto kern = fit_kernel<LP, NW, TPC, FULL, XT>;
     HFREP_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const int grid = (p.n_tasks + tpc - 1) / tpc;
     kern<<<grid, 32 * NW * tpc, smem, stream>>>(p);
@@ -688,30 +598,28 @@ static int launch_fit_mode(const FitParams& p, cudaStream_t stream) {
     return HFREP_OK;
 }
 
-template <int LP, int NW, int CS, int TPC, bool FULL>
+template <int LP, int NW, int TPC, bool FULL>
 static int launch_fit(const FitParams& p, cudaStream_t stream) {
     const bool resident = p.shared_x && fit_smem_bytes<LP, NW>(p, 1, false) <= kMaxSmem && !p.force_tile;
-    return resident ? launch_fit_mode<LP, NW, CS, TPC, FULL, false>(p, stream)
-                    : launch_fit_mode<LP, NW, CS, TPC, FULL, true>(p, stream);
+    return resident ? launch_fit_mode<LP, NW, TPC, FULL, false>(p, stream)
+                    : launch_fit_mode<LP, NW, TPC, FULL, true>(p, stream);
 }
 
-// warps per task:
-//   1  one warp per task, lane pairs share a row (16 rows per pass): most work per issued instruction, for grids
-//      with thousands of tasks;
-//   3  three warps per task, lane pairs share a row (48 rows per pass = one batch): the default;
-//   6  six warps per task, lane quads share a row, k-loops fully unrolled: the latency mapping for a handful of
-//      tasks (LP padded to a multiple of 8).
+// warps per task (every mapping runs the same phases; they differ in how many warps share a task's columns):
+//   6  up to ~5 tasks per SM (one team per CTA, k-loops fully unrolled): the latency mapping;
+//   2  the throughput mapping beyond that;
+//   1, 3  kept for experiments: 1 has the least shared-memory traffic per task but needs more resident tasks than
+//      shared memory admits to hide its latency; 3 sits between 2 and 6 and wins nowhere on the measured sweep.
 template <int LP>
 static int dispatch_mapping(const FitParams& p, int wpt, cudaStream_t stream) {
-    if (wpt == 1) return launch_fit<LP, 1, 2, 8, false>(p, stream);
-    if (wpt == 3) return launch_fit<LP, 3, 2, (LP <= 8 ? 8 : 6), false>(p, stream);
-    if constexpr (LP % 8 == 0) return launch_fit<LP, 6, 4, 1, true>(p, stream);
-    else return set_err(HFREP_ERR_ARG, "fit: internal: the quad mapping needs LP %% 8 == 0");
+    if (wpt == 1) return launch_fit<LP, 1, 8, false>(p, stream);
+    if (wpt == 2) return launch_fit<LP, 2, 6, false>(p, stream);
+    if (wpt == 3) return launch_fit<LP, 3, (LP <= 8 ? 8 : 6), false>(p, stream);
+    return launch_fit<LP, 6, 1, true>(p, stream);
 }
 
 int fit_dispatch(const FitParams& p, int L_max, int wpt, cudaStream_t stream) {
-    // the latency mapping (6 warps, a lane quad per row) splits the columns in float2 pieces of 8-column groups
-    const int LP = (wpt == 6) ? ((L_max + 7) & ~7) : ((L_max + 3) & ~3);
+    const int LP = (L_max + 3) & ~3;
     switch (LP) {
         case 4: return dispatch_mapping<4>(p, wpt, stream);
         case 8: return dispatch_mapping<8>(p, wpt, stream);
@@ -789,12 +697,12 @@ static int fit_batched_impl(const hfrep_fit_cfg* c, const float* X, int n_tasks,
     p.alpha = c->alpha; p.lr = c->lr; p.b1 = c->beta_1; p.b2 = c->beta_2; p.eps = c->epsilon;
 
     int wpt = c->warps_per_task;
-    if (wpt == 0) {                                  // pick the mapping from the amount of parallel work
-        const int sms = sm_count();
-        // one warp per task only pays off for wide tasks in large numbers (measured: L=20 x 1024 -> 1 warp wins, L=8 x 20000 -> 3 warps win)
-        wpt = n_tasks <= sms ? 6 : ((n_tasks >= 4 * sms && c->L_max >= 16) ? 1 : 3);
+    if (wpt == 0) {                                  // pick the mapping from the amount of parallel work in THIS call
+        const int sms = sm_count();                  // (callers that split a job over several calls pass it explicitly)
+        // measured on the L = 1..21 sweep x seeds (profiles/README.md): 6 warps win up to ~5 tasks per SM, 2 warps beyond
+        wpt = n_tasks <= 5 * sms ? 6 : 2;
     }
-    HFREP_REQUIRE(wpt == 1 || wpt == 3 || wpt == 6, "fit_batched: warps_per_task=%d (0, 1, 3 or 6)", wpt);
+    HFREP_REQUIRE(wpt == 1 || wpt == 2 || wpt == 3 || wpt == 6, "fit_batched: warps_per_task=%d (0, 1, 2, 3 or 6)", wpt);
     return fit_dispatch(p, c->L_max, wpt, (cudaStream_t)stream);
 }
 

@@ -160,6 +160,13 @@ def _side_streams(device, n):
     return pool[:n]
 
 
+def warps_per_task_for(n_tasks: int, device) -> int:
+    """Kernel (b) mapping for a job of n_tasks fits running at the same time (all width groups together): the same
+    rule hfrep_fit_batched applies to a single call (csrc/fit_kernel.cu, dispatch_mapping)."""
+    sms = torch.cuda.get_device_properties(device).multi_processor_count
+    return 6 if n_tasks <= 5 * sms else 2
+
+
 def fit_batched(X: torch.Tensor, task_L, W0: torch.Tensor, *, E: int, T: int, n_fit: int | None = None,
                 perm: torch.Tensor | None = None, task_x: torch.Tensor | None = None, dump_step: int | None = None,
                 warps_per_task: int = 0, bucket: bool = True, W_out: torch.Tensor | None = None, after_bucket=None,
@@ -216,6 +223,8 @@ def fit_batched(X: torch.Tensor, task_L, W0: torch.Tensor, *, E: int, T: int, n_
     LP = (L_sorted + 3) // 4 * 4
     bounds = [0] + [i for i in range(1, n) if LP[i] != LP[i - 1]] + [n] if bucket else [0, n]
     groups = [(bounds[i], bounds[i + 1]) for i in range(len(bounds) - 1)]
+    if warps_per_task == 0 and len(groups) > 1:
+        cfg.warps_per_task = warps_per_task_for(n, device)   # the groups run concurrently: map by the whole job's size
     main = torch.cuda.current_stream(device)
     streams = _side_streams(device, len(groups)) if len(groups) > 1 else [main]
     ready = torch.cuda.Event()

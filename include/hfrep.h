@@ -82,7 +82,8 @@ typedef struct hfrep_fit_cfg {
     float alpha;          /* LeakyReLU slope .2 */
     float lr, beta_1, beta_2, epsilon, schedule_decay, decay_base;  /* Nadam(): 1e-3,.9,.999,1e-7,.004,.96 */
     int32_t n_x;          /* number of training blocks in X; 1 = all tasks share block 0 */
-    int32_t warps_per_task; /* 0 = choose from n_tasks; 1 or 3 = throughput mappings; 6 = latency mapping */
+    int32_t warps_per_task; /* 0 = choose from this call's n_tasks; 1, 2, 3 = throughput mappings (1 needs many tasks
+                               per SM); 6 = latency mapping for a handful of tasks */
     int32_t dump_step;    /* global step (0-based) whose gradients go to grad_out, if grad_out != NULL */
 } hfrep_fit_cfg;
 
