@@ -16,13 +16,14 @@
 //   update  element-wise over the 48*LP weight slots: sum the NW partials in fixed order, Nadam (m, v in
 //           shared memory next to the weights), write the weight back.
 // Shared memory (floats, rows 16-byte aligned).  Per CTA: Xs [(T+1)][28] (shared by the CTA's teams when all
-// tasks train on the same block; cols >= E zero, row T zero), woff [48*LP] (tile-major slot -> weight offset).
+// tasks train on the same block; cols >= E zero, row T zero), woff [12*LP] (tile-major slot quad -> weight offset).
 // Per team: We [24][LP], Wd [LP][28], H [BP+1][HS], dZh [BP+1][HS], dZy [BP+1][28] (row BP = scratch row for
-// idle lanes), part [NW][48*LP], mv [48*LP] float2, xoff [2][BP] (row offsets of the current / next batch: the fused
+// idle lanes), part [NW][48*LP], mv [12*LP][2] float4 (one-warp teams; else registers), xoff [2][BP] (row offsets of the current / next batch: the fused
 // window gather — shuffled orders cost nothing extra).
 // LP = L rounded up to 4; zero padding is exactly neutral (zero activations, zero gradients, Nadam(0)=0).
 #include "common.cuh"
 
+#include <algorithm>
 #include <cmath>
 #include <cstdlib>
 
@@ -60,15 +61,15 @@ struct Lay {
     static constexpr int CT = LP / 4;
     static constexpr int NT5 = 12 * CT;        // weight tiles: dWd (CT x 6) then dWe (6 x CT)
     static constexpr int NEL = NT5 * 16;       // = 48*LP weight slots, tile-major
-    // Nadam's m, v: registers when the team has >= 3 warps (LP/2 or LP/4 slots per lane), else shared memory
-    __host__ __device__ static constexpr bool mv_in_regs(int NW) { return NW >= 3; }
+    // Nadam's m, v: registers when the team has >= 2 warps (at most 5 slot quads per lane), else shared memory
+    __host__ __device__ static constexpr bool mv_in_regs(int NW) { return NW >= 2; }
     // XT (batch-tile mode): the training block stays in global memory / L2 and only the current mini-batch's rows
     // sit in a per-team tile [BP+1][XS], refilled with cp.async; else the whole block is resident once per CTA.
     __host__ __device__ static size_t team_floats(int BP, int NW, bool XT, int PS) {
         return (size_t)EP * LP + (size_t)LP * WDS + (size_t)(BP + 1) * HS * 2 + (size_t)(BP + 1) * XS +
                (size_t)NW * NEL + (mv_in_regs(NW) ? 0 : 2 * (size_t)NEL) + 2 * BP + 64 + (XT ? (size_t)(BP + 1) * XS : 0) + PS;
     }
-    __host__ __device__ static size_t cta_floats(int T, bool XT) { return (XT ? 0 : (size_t)(T + 1) * XS) + NEL; }
+    __host__ __device__ static size_t cta_floats(int T, bool XT) { return (XT ? 0 : (size_t)(T + 1) * XS) + NEL / 4; }
 };
 
 template <int NW>
@@ -139,9 +140,9 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
     float* dZy = dZh + (BP + 1) * HS;
     float* part = dZy + (BP + 1) * XS;
     constexpr bool MVREG = Lay<LP>::mv_in_regs(NW);
-    constexpr int EPL = MVREG ? NEL / NTH : 1;     // weight slots per lane when m, v live in registers
-    static_assert(!MVREG || NEL % NTH == 0, "register-resident Nadam state needs a whole number of slots per lane");
-    float2* mv = reinterpret_cast<float2*>(part + NW * NEL);
+    constexpr int NQ = NEL / 4;                    // slot quads: four consecutive columns of one weight row
+    constexpr int QPL = MVREG ? (NQ + NTH - 1) / NTH : 1;   // quads per lane when m, v live in registers
+    float4* mv = reinterpret_cast<float4*>(part + NW * NEL);   // [NQ][2]: m, v of a quad (shared-memory variant)
     int* xoff_tab = reinterpret_cast<int*>(part + NW * NEL + (MVREG ? 0 : 2 * NEL));   // [2][BP], double-buffered per segment
     float* red = reinterpret_cast<float*>(xoff_tab + 2 * BP);          // [2][32], double-buffered per epoch
     // Xs: what the phases address rows in — the resident block (row r at xoff[r]) or the team's batch tile (row r at r*XS)
@@ -163,19 +164,19 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
                 Xs[idx] = (r < T && c < E) ? __ldg(xg + (size_t)r * E + c) : 0.f;
             }
         }
-        // tile-major weight slot -> offset from We
-        for (int idx = threadIdx.x; idx < NEL; idx += blockDim.x) {
-            const int i = idx / (NT5 * 4), t = (idx - i * (NT5 * 4)) >> 2, jj = idx & 3;   // slot layout [i][tile][jj]
+        // tile-major slot quad [i][tile] -> offset of its four consecutive weights from We
+        for (int qd = threadIdx.x; qd < NQ; qd += blockDim.x) {
+            const int i = qd / NT5, t = qd - i * NT5;
             int o;
-            if (t < 6 * CT) {                            // dWd tile (lt, et): Wd[lt*4+i][et*4+jj]
+            if (t < 6 * CT) {                            // dWd tile (lt, et): Wd[lt*4+i][et*4 ..]
                 const int lt = t / 6, et = t - lt * 6;
-                o = EP * LP + (lt * 4 + i) * WDS + et * 4 + jj;
-            } else {                                     // dWe tile (lt, et): We[et*4+i][lt*4+jj]
+                o = EP * LP + (lt * 4 + i) * WDS + et * 4;
+            } else {                                     // dWe tile (lt, et): We[et*4+i][lt*4 ..]
                 const int u = t - 6 * CT;
                 const int lt = u / 6, et = u - lt * 6;
-                o = (et * 4 + i) * LP + lt * 4 + jj;
+                o = (et * 4 + i) * LP + lt * 4;
             }
-            woff[idx] = o;
+            woff[qd] = o;
         }
     }
     if (active) {
@@ -190,7 +191,7 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
             Wd[idx] = (l < L0 && e < E) ? w0[E * L0 + l * E + e] : 0.f;
         }
         if constexpr (!MVREG)
-            for (int idx = tl; idx < NEL; idx += NTH) mv[idx] = make_float2(0.f, 0.f);
+            for (int idx = tl; idx < 2 * NQ; idx += NTH) mv[idx] = make_float4(0.f, 0.f, 0.f, 0.f);
     }
     __syncthreads();
     if (!active) return;
@@ -383,41 +384,67 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
     };
 
     // ---------------------------------------------------------------- update phase (Nadam, element-wise)
-    float2 mvr[EPL];
+    // A lane handles slot quads (four consecutive columns of one weight row): the NW partial sums, the weights and
+    // (one-warp teams) m, v move as 128-bit shared accesses; the partials are summed in warp order.
+    float4 m4r[QPL], v4r[QPL];
 #pragma unroll
-    for (int j = 0; j < EPL; ++j) mvr[j] = make_float2(0.f, 0.f);
-    auto update_slot = [&](int idx, float2& s2, const float4& sc, bool dump) {
-        float g = part[idx];
+    for (int j = 0; j < QPL; ++j) m4r[j] = v4r[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+    auto quad_gradient = [&](int qd) -> float4 {
+        float4 g = ld4(part + 4 * qd);
 #pragma unroll
-        for (int w = 1; w < NW; ++w) g += part[w * NEL + idx];
-        s2.x = p.b1 * s2.x + omb1 * g;
-        s2.y = p.b2 * s2.y + omb2 * (g * g);
-        const float m_bar = sc.x * g + sc.y * s2.x;
-        const int o = woff[idx];
-        We[o] -= __fdividef(p.lr * m_bar, fast_sqrt(s2.y * sc.z) + p.eps);
-        if (dump) {
-            float* go = p.grad_out + (size_t)task * p.w_stride;
-            if (o >= EP * LP) {
-                const int r = (o - EP * LP) / WDS, c = (o - EP * LP) - r * WDS;
-                if (r < L && c < E) go[E * L + r * E + c] = g;
-            } else {
-                const int r = o / LP, c = o - r * LP;
-                if (r < E && c < L) go[r * L + c] = g;
+        for (int w = 1; w < NW; ++w) {
+            const float4 t = ld4(part + w * NEL + 4 * qd);
+            g.x += t.x; g.y += t.y; g.z += t.z; g.w += t.w;
+        }
+        return g;
+    };
+    auto update_quad = [&](int qd, float4& m4, float4& v4, const float4& sc) {
+        const float4 g = quad_gradient(qd);
+        auto delta = [&](float gk, float& m, float& v) -> float {
+            m = p.b1 * m + omb1 * gk;
+            v = p.b2 * v + omb2 * (gk * gk);
+            const float m_bar = sc.x * gk + sc.y * m;
+            return __fdividef(p.lr * m_bar, fast_sqrt(v * sc.z) + p.eps);
+        };
+        const int o = woff[qd];
+        float4 wv = ld4(We + o);
+        wv.x -= delta(g.x, m4.x, v4.x);
+        wv.y -= delta(g.y, m4.y, v4.y);
+        wv.z -= delta(g.z, m4.z, v4.z);
+        wv.w -= delta(g.w, m4.w, v4.w);
+        st4(We + o, wv);
+    };
+    // test hook (cfg.dump_step): the summed gradient of one step, unpadded, to global memory.  Kept out of the update
+    // loop: a branch per quad there would stop the compiler from interleaving the quads' dependency chains.
+    auto dump_gradient = [&]() {
+        float* go = p.grad_out + (size_t)task * p.w_stride;
+        for (int qd = tl; qd < NQ; qd += NTH) {
+            const float4 g = quad_gradient(qd);
+            const float gv[4] = {g.x, g.y, g.z, g.w};
+            const int o = woff[qd];
+            for (int k = 0; k < 4; ++k) {
+                if (o >= EP * LP) {
+                    const int r = (o - EP * LP) / WDS, c = (o - EP * LP) - r * WDS + k;
+                    if (r < L && c < E) go[E * L + r * E + c] = gv[k];
+                } else {
+                    const int r = o / LP, c = o - r * LP + k;
+                    if (r < E && c < L) go[r * L + c] = gv[k];
+                }
             }
         }
     };
-    auto update_phase = [&](int step) {
-        const float4 sc = __ldg(p.sched + step);
-        const bool dump = p.grad_out != nullptr && step == p.dump_step;
+    auto update_phase = [&](int step, const float4& sc) {
+        if (p.grad_out != nullptr && step == p.dump_step) dump_gradient();
         if constexpr (MVREG) {
 #pragma unroll
-            for (int j = 0; j < EPL; ++j) update_slot(tl + j * NTH, mvr[j], sc, dump);
+            for (int j = 0; j < QPL; ++j)
+                if (NQ % NTH == 0 || tl + j * NTH < NQ) update_quad(tl + j * NTH, m4r[j], v4r[j], sc);
         } else {
 #pragma unroll 2
-            for (int idx = tl; idx < NEL; idx += NTH) {
-                float2 s2 = mv[idx];
-                update_slot(idx, s2, sc, dump);
-                mv[idx] = s2;
+            for (int qd = tl; qd < NQ; qd += NTH) {
+                float4 m4 = mv[2 * qd], v4 = mv[2 * qd + 1];
+                update_quad(qd, m4, v4, sc);
+                mv[2 * qd] = m4; mv[2 * qd + 1] = v4;
             }
         }
     };
@@ -505,6 +532,12 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
                 }
             };
             if constexpr (!XT) prefetch_next();
+            // this step's Nadam scalars: the global load is issued here and first used after two phases, so its latency
+            // (the only global access of a step) is off the critical path of a one-team CTA
+            float4 sc = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (train)
+                asm volatile("ld.global.nc.v4.f32 {%0,%1,%2,%3}, [%4];"
+                             : "=f"(sc.x), "=f"(sc.y), "=f"(sc.z), "=f"(sc.w) : "l"(p.sched + step));
             float sse = 0.f;
             if (!(p.debug_skip & 1)) {
                 sse = rows_phase(xoff, nb, train, 2.f / (float)(nb * E));
@@ -515,7 +548,7 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
                 if (!(p.debug_skip & 2)) grads_phase(xoff, nb);
                 team_sync<NW>(team);
                 if constexpr (XT) prefetch_next();          // the copy overlaps the update phase
-                if (!(p.debug_skip & 4)) update_phase(step);
+                if (!(p.debug_skip & 4)) update_phase(step, sc);
                 ++step;
             } else {
                 vsum += sse;
@@ -584,6 +617,7 @@ static size_t fit_smem_bytes(const FitParams& p, int tpc, bool xt) {
 template <int LP, int NW, int TPC, bool FULL, bool XT>
 static int launch_fit_mode(const FitParams& p, cudaStream_t stream) {
     int tpc = TPC;
+    if (const char* cap = getenv("HFREP_TPC")) tpc = std::max(1, std::min(TPC, atoi(cap)));   // tuning only
     while (tpc > 1 && fit_smem_bytes<LP, NW>(p, tpc, XT) > kMaxSmem) --tpc;
     // two half-size CTAs per SM beat one big one when both fit (finer scheduling granularity)
     if (tpc > 1 && tpc % 2 == 0 && 2 * fit_smem_bytes<LP, NW>(p, tpc / 2, XT) <= kMaxSmem) tpc /= 2;
