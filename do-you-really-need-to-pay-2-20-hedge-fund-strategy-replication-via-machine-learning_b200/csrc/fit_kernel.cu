@@ -18,7 +18,7 @@
 // Shared memory (floats, rows 16-byte aligned).  Per CTA: Xs [(T+1)][28] (shared by the CTA's teams when all
 // tasks train on the same block; cols >= E zero, row T zero), woff [12*LP] (tile-major slot quad -> weight offset).
 // Per team: We [24][LP], Wd [LP][28], H [BP+1][HS], dZh [BP+1][HS], dZy [BP+1][28] (row BP = scratch row for
-// idle lanes), part [NW][48*LP], mv [12*LP][2] float4 (one-warp teams; else registers), xoff [2][BP] (row offsets of the current / next batch: the fused
+// idle lanes), part [KS][48*LP] (KS <= NW partial sums per slot, Lay::ks), mv [12*LP][2] float4 (one-warp teams; else registers), xoff [2][BP] (row offsets of the current / next batch: the fused
 // window gather — shuffled orders cost nothing extra).
 // LP = L rounded up to 4; zero padding is exactly neutral (zero activations, zero gradients, Nadam(0)=0).
 #include "common.cuh"
@@ -61,13 +61,19 @@ struct Lay {
     static constexpr int CT = LP / 4;
     static constexpr int NT5 = 12 * CT;        // weight tiles: dWd (CT x 6) then dWe (6 x CT)
     static constexpr int NEL = NT5 * 16;       // = 48*LP weight slots, tile-major
+    // grads phase: the tiles form TG groups of <= 32 (one lane per tile).  When the team's warps divide evenly over the
+    // groups, a warp keeps ONE group and takes every KS-th batch row (KS = NW/TG partial sums per slot); otherwise every
+    // warp walks all groups and takes every NW-th row (KS = NW).
+    static constexpr int TG = (NT5 + 31) / 32;
+    __host__ __device__ static constexpr bool grouped(int NW) { return TG > 1 && NW % TG == 0; }
+    __host__ __device__ static constexpr int ks(int NW) { return grouped(NW) ? NW / TG : NW; }
     // Nadam's m, v: registers when the team has >= 2 warps (at most 5 slot quads per lane), else shared memory
     __host__ __device__ static constexpr bool mv_in_regs(int NW) { return NW >= 2; }
     // XT (batch-tile mode): the training block stays in global memory / L2 and only the current mini-batch's rows
     // sit in a per-team tile [BP+1][XS], refilled with cp.async; else the whole block is resident once per CTA.
     __host__ __device__ static size_t team_floats(int BP, int NW, bool XT, int PS) {
         return (size_t)EP * LP + (size_t)LP * WDS + (size_t)(BP + 1) * HS * 2 + (size_t)(BP + 1) * XS +
-               (size_t)NW * NEL + (mv_in_regs(NW) ? 0 : 2 * (size_t)NEL) + 2 * BP + 64 + (XT ? (size_t)(BP + 1) * XS : 0) + PS;
+               (size_t)ks(NW) * NEL + (mv_in_regs(NW) ? 0 : 2 * (size_t)NEL) + 2 * BP + 64 + (XT ? (size_t)(BP + 1) * XS : 0) + PS;
     }
     __host__ __device__ static size_t cta_floats(int T, bool XT) { return (XT ? 0 : (size_t)(T + 1) * XS) + NEL / 4; }
 };
@@ -142,8 +148,9 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
     constexpr bool MVREG = Lay<LP>::mv_in_regs(NW);
     constexpr int NQ = NEL / 4;                    // slot quads: four consecutive columns of one weight row
     constexpr int QPL = MVREG ? (NQ + NTH - 1) / NTH : 1;   // quads per lane when m, v live in registers
-    float4* mv = reinterpret_cast<float4*>(part + NW * NEL);   // [NQ][2]: m, v of a quad (shared-memory variant)
-    int* xoff_tab = reinterpret_cast<int*>(part + NW * NEL + (MVREG ? 0 : 2 * NEL));   // [2][BP], double-buffered per segment
+    constexpr int KS = Lay<LP>::ks(NW);            // partial sums per weight slot (see Lay::TG)
+    float4* mv = reinterpret_cast<float4*>(part + KS * NEL);   // [NQ][2]: m, v of a quad (shared-memory variant)
+    int* xoff_tab = reinterpret_cast<int*>(part + KS * NEL + (MVREG ? 0 : 2 * NEL));   // [2][BP], double-buffered per segment
     float* red = reinterpret_cast<float*>(xoff_tab + 2 * BP);          // [2][32], double-buffered per epoch
     // Xs: what the phases address rows in — the resident block (row r at xoff[r]) or the team's batch tile (row r at r*XS)
     float* Xs = XT ? red + 64 : smem;
@@ -347,9 +354,14 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
 
     // ---------------------------------------------------------------- weight-gradient phase (split-K over warps)
     auto grads_phase = [&](const int* xoff, int nb) {
-        float* mypart = part + warp * NEL;
+        constexpr bool GRP = Lay<LP>::grouped(NW);
+        constexpr int TPG = NT5 / Lay<LP>::TG;          // tiles per group (12*CT/TG: a multiple of 6)
+        const int grp = GRP ? warp % Lay<LP>::TG : 0;
+        const int kq = GRP ? warp / Lay<LP>::TG : warp;  // first batch row of this warp
+        const int tend = GRP ? (grp + 1) * TPG : NT5;
+        float* mypart = part + kq * NEL;
 #pragma unroll 1
-        for (int t = lane; t < NT5; t += 32) {
+        for (int t = grp * TPG + lane; t < tend; t += 32) {
             const bool dec = t < 6 * CT;
             int a0, b0, bstr;
             if (dec) {                                   // dWd tile: A = H[:, lt*4..], B = dZy[:, et*4..]
@@ -364,7 +376,7 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
 #pragma unroll
             for (int i = 0; i < 4; ++i) acc[i][0] = acc[i][1] = make_float2(0.f, 0.f);
 #pragma unroll 4
-            for (int q = warp; q < nb; q += NW) {
+            for (int q = kq; q < nb; q += KS) {
                 const int ao = dec ? q * HS : (XT ? q * XS : xoff[q]);
                 const float4 a = ld4(Xs + a0 + ao);
                 const float4 b = ld4(Xs + b0 + q * bstr);
@@ -392,7 +404,7 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
     auto quad_gradient = [&](int qd) -> float4 {
         float4 g = ld4(part + 4 * qd);
 #pragma unroll
-        for (int w = 1; w < NW; ++w) {
+        for (int w = 1; w < KS; ++w) {
             const float4 t = ld4(part + w * NEL + 4 * qd);
             g.x += t.x; g.y += t.y; g.z += t.z; g.w += t.w;
         }
