@@ -10,15 +10,16 @@
 //           rows' zh -> h -> zy -> y, squared error, dzy -> dzh accumulate in REGISTERS; one weight LDS.64 feeds
 //           three rows (3 FFMA2).  h, dzy, dzh rows are parked in shared memory for the other classes and for the
 //           weight gradients.
-//   grads   dWd = H^T dZy and dWe = X_b^T dZh as 4x4 register tiles (outer products, 2 LDS.128 per 16
-//           FFMA); the batch rows are split over the team's warps (split-K), partial tiles go to
-//           shared memory in tile-major order.
-//   update  element-wise over the 48*LP weight slots: sum the NW partials in fixed order, Nadam (m, v in
-//           shared memory next to the weights), write the weight back.
+//   grads   dWd = H^T dZy and dWe = X_b^T dZh as 4x4 register tiles (outer products, 2 LDS.128 per 8 FFMA2), one
+//           lane per tile; the tiles form groups of <= 32 and the batch rows are split over the warps of a group
+//           (split-K); partial tiles go to shared memory in tile-major order.
+//   update  over the 12*LP slot quads (four consecutive columns of a weight row): sum the KS partials in fixed
+//           order, Nadam (m, v in registers; shared memory for one-warp teams), write the weights back.
 // Shared memory (floats, rows 16-byte aligned).  Per CTA: Xs [(T+1)][28] (shared by the CTA's teams when all
 // tasks train on the same block; cols >= E zero, row T zero), woff [12*LP] (tile-major slot quad -> weight offset).
 // Per team: We [24][LP], Wd [LP][28], H [BP+1][HS], dZh [BP+1][HS], dZy [BP+1][28] (row BP = scratch row for
-// idle lanes), part [KS][48*LP] (KS <= NW partial sums per slot, Lay::ks), mv [12*LP][2] float4 (one-warp teams; else registers), xoff [2][BP] (row offsets of the current / next batch: the fused
+// idle lanes), part [KS][48*LP] (KS <= NW partial sums per slot, Lay::ks), mv [12*LP][2] float4 (one-warp teams),
+// xoff [2][T] (position in the epoch's order -> row offset in Xs, this epoch's and the next one's: the fused
 // window gather — shuffled orders cost nothing extra).
 // LP = L rounded up to 4; zero padding is exactly neutral (zero activations, zero gradients, Nadam(0)=0).
 #include "common.cuh"
@@ -71,9 +72,10 @@ struct Lay {
     __host__ __device__ static constexpr bool mv_in_regs(int NW) { return NW >= 2; }
     // XT (batch-tile mode): the training block stays in global memory / L2 and only the current mini-batch's rows
     // sit in a per-team tile [BP+1][XS], refilled with cp.async; else the whole block is resident once per CTA.
-    __host__ __device__ static size_t team_floats(int BP, int NW, bool XT, int PS) {
+    __host__ __device__ static size_t team_floats(int BP, int NW, bool XT, int PS, int T) {
         return (size_t)EP * LP + (size_t)LP * WDS + (size_t)(BP + 1) * HS * 2 + (size_t)(BP + 1) * XS +
-               (size_t)ks(NW) * NEL + (mv_in_regs(NW) ? 0 : 2 * (size_t)NEL) + 2 * BP + 64 + (XT ? (size_t)(BP + 1) * XS : 0) + PS;
+               (size_t)ks(NW) * NEL + (mv_in_regs(NW) ? 0 : 2 * (size_t)NEL) + (XT ? 0 : 2 * (size_t)((T + 3) & ~3)) + 64 +
+               (XT ? (size_t)(BP + 1) * XS : 0) + PS;
     }
     __host__ __device__ static size_t cta_floats(int T, bool XT) { return (XT ? 0 : (size_t)(T + 1) * XS) + NEL / 4; }
 };
@@ -135,7 +137,7 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
     const int T = p.T, E = p.E, BP = p.BP;
 
     const size_t cf = Lay<LP>::cta_floats(T, XT);
-    const size_t tf = Lay<LP>::team_floats(BP, NW, XT, p.PS);
+    const size_t tf = Lay<LP>::team_floats(BP, NW, XT, p.PS, T);
     // [Xs (resident mode only) | woff | team 0 | team 1 ...]
     int* woff = reinterpret_cast<int*>(smem + (XT ? 0 : (size_t)(T + 1) * XS));
     float* base = smem + cf + (size_t)team * tf;
@@ -150,8 +152,11 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
     constexpr int QPL = MVREG ? (NQ + NTH - 1) / NTH : 1;   // quads per lane when m, v live in registers
     constexpr int KS = Lay<LP>::ks(NW);            // partial sums per weight slot (see Lay::TG)
     float4* mv = reinterpret_cast<float4*>(part + KS * NEL);   // [NQ][2]: m, v of a quad (shared-memory variant)
-    int* xoff_tab = reinterpret_cast<int*>(part + KS * NEL + (MVREG ? 0 : 2 * NEL));   // [2][BP], double-buffered per segment
-    float* red = reinterpret_cast<float*>(xoff_tab + 2 * BP);          // [2][32], double-buffered per epoch
+    // resident mode: row-offset tables of a whole epoch (position in the epoch's order -> offset of the row in Xs: the
+    // fused window gather, so shuffled orders cost nothing), [2][TP], one being read while the next epoch's is written
+    const int TP = XT ? 0 : (T + 3) & ~3;
+    int* xoff_tab = reinterpret_cast<int*>(part + KS * NEL + (MVREG ? 0 : 2 * NEL));
+    float* red = reinterpret_cast<float*>(xoff_tab + 2 * TP);          // [2][32], double-buffered per epoch
     // Xs: what the phases address rows in — the resident block (row r at xoff[r]) or the team's batch tile (row r at r*XS)
     float* Xs = XT ? red + 64 : smem;
     unsigned* keyS = reinterpret_cast<unsigned*>(red + 64 + (XT ? (BP + 1) * XS : 0));   // [n_fit] shuffle keys
@@ -492,36 +497,43 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
         }
         team_sync<NW>(team);
     };
-    auto set_rows = [&](int* xoff, int epoch, int seg) {
+    // batch-tile mode: refill the tile with the rows of a segment
+    auto set_rows = [&](int epoch, int seg) {
         const bool val = seg >= n_tb;
         const int lo = (val ? seg - n_tb : seg) * batch;
         const int nb = min(batch, (val ? n_val : n_fit) - lo);
-        if constexpr (XT) {
-            // refill the batch tile: cp.async of the rows' E floats (16-, 8- or 4-byte pieces by alignment)
-            const int pw = ((E & 3) == 0 && (((size_t)xb * T * E) & 3) == 0) ? 4 : (((E & 1) == 0 && (((size_t)xb * T * E) & 1) == 0) ? 2 : 1);
-            const int ppr = E / pw;                       // pieces per row
-            for (int idx = tl; idx < nb * ppr; idx += NTH) {
-                const int q = idx / ppr, c = (idx - q * ppr) * pw;
-                const int row = val ? n_fit + lo + q : (perm_t ? __ldg(perm_t + (size_t)epoch * n_fit + lo + q) : (dev_shuffle ? permS[lo + q] : lo + q));
-                const float* src = xg + (size_t)row * E + c;
-                const unsigned dst = (unsigned)__cvta_generic_to_shared(Xs + q * XS + c);
-                if (pw == 4) asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
-                else if (pw == 2) asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(dst), "l"(src) : "memory");
-                else asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(src) : "memory");
-            }
-            asm volatile("cp.async.commit_group;" ::: "memory");
-        } else {
-            for (int q = tl; q < nb; q += NTH) {
-                const int row = val ? n_fit + lo + q : (perm_t ? __ldg(perm_t + (size_t)epoch * n_fit + lo + q) : (dev_shuffle ? permS[lo + q] : lo + q));
-                xoff[q] = row * XS;
-            }
+        // cp.async of the rows' E floats (16-, 8- or 4-byte pieces by alignment)
+        const int pw = ((E & 3) == 0 && (((size_t)xb * T * E) & 3) == 0) ? 4 : (((E & 1) == 0 && (((size_t)xb * T * E) & 1) == 0) ? 2 : 1);
+        const int ppr = E / pw;                       // pieces per row
+        for (int idx = tl; idx < nb * ppr; idx += NTH) {
+            const int q = idx / ppr, c = (idx - q * ppr) * pw;
+            const int row = val ? n_fit + lo + q : (perm_t ? __ldg(perm_t + (size_t)epoch * n_fit + lo + q) : (dev_shuffle ? permS[lo + q] : lo + q));
+            const float* src = xg + (size_t)row * E + c;
+            const unsigned dst = (unsigned)__cvta_generic_to_shared(Xs + q * XS + c);
+            if (pw == 4) asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
+            else if (pw == 2) asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(dst), "l"(src) : "memory");
+            else asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(src) : "memory");
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+    // resident mode: the training part of an epoch's offset table (the validation tail never changes)
+    const bool ident = perm_t == nullptr && !dev_shuffle;   // the same order every epoch: one table, written once
+    auto fill_order = [&](int* tab, int epoch) {
+        for (int i = tl; i < n_fit; i += NTH) {
+            const int row = perm_t ? __ldg(perm_t + (size_t)epoch * n_fit + i) : (dev_shuffle ? permS[i] : i);
+            tab[i] = row * XS;
         }
     };
     auto rows_ready = [&]() {                          // the tile refill issued by this thread has landed
         if constexpr (XT) asm volatile("cp.async.wait_group 0;" ::: "memory");
     };
     if (dev_shuffle) make_perm(0);
-    set_rows(xoff_tab, 0, 0);
+    if constexpr (XT) {
+        set_rows(0, 0);
+    } else {
+        for (int i = n_fit + tl; i < T; i += NTH) xoff_tab[i] = xoff_tab[TP + i] = i * XS;
+        fill_order(xoff_tab, 0);
+    }
     rows_ready();
     team_sync<NW>(team);
     for (int epoch = 0; epoch < p.max_epochs; ++epoch) {
@@ -531,16 +543,21 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
             const bool train = seg < n_tb;
             const int lo = (train ? seg : seg - n_tb) * batch;
             const int nb = min(batch, (train ? n_fit : n_val) - lo);
-            const int* xoff = xoff_tab + cur * BP;
-            int* xnext = xoff_tab + (cur ^ 1) * BP;
-            // rows of the next segment (next epoch's first batch after the last one): resident mode writes the other
-            // offset table right away; tile mode refills the single tile once its last reader is done
+            const int* xoff = xoff_tab + cur * TP + (train ? lo : n_fit + lo);   // (unused in batch-tile mode)
+            const bool last = seg + 1 == n_seg;
+            const int ne = epoch + 1 < p.max_epochs ? epoch + 1 : epoch;
+            // what the next segment needs.  Resident mode: nothing within an epoch; in its last segment the next epoch's
+            // order goes to the other table.  Tile mode refills the single tile once its last reader is done.
             auto prefetch_next = [&]() {
-                if (seg + 1 < n_seg) set_rows(xnext, epoch, seg + 1);
-                else {
-                    const int ne = epoch + 1 < p.max_epochs ? epoch + 1 : epoch;
-                    if (dev_shuffle) make_perm(ne);       // this epoch's order is no longer needed: its last table is out
-                    set_rows(xnext, ne, 0);
+                if constexpr (XT) {
+                    if (!last) set_rows(epoch, seg + 1);
+                    else {
+                        if (dev_shuffle) make_perm(ne);   // this epoch's order is no longer needed: its last tile is out
+                        set_rows(ne, 0);
+                    }
+                } else if (last && !ident) {
+                    if (dev_shuffle) make_perm(ne);
+                    fill_order(xoff_tab + (cur ^ 1) * TP, ne);
                 }
             };
             if constexpr (!XT) prefetch_next();
@@ -567,7 +584,7 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
                 if constexpr (XT) { team_sync<NW>(team); prefetch_next(); }
             }
             rows_ready();
-            cur ^= 1;
+            if (!XT && last && !ident) cur ^= 1;
             team_sync<NW>(team);
         }
         // epoch losses: one barrier; the scratch alternates between epochs so no second barrier is needed
@@ -620,7 +637,7 @@ constexpr size_t kMaxSmem = 227 * 1024;
 
 template <int LP, int NW>
 static size_t fit_smem_bytes(const FitParams& p, int tpc, bool xt) {
-    return sizeof(float) * (Lay<LP>::cta_floats(p.T, xt) + tpc * Lay<LP>::team_floats(p.BP, NW, xt, p.PS));
+    return sizeof(float) * (Lay<LP>::cta_floats(p.T, xt) + tpc * Lay<LP>::team_floats(p.BP, NW, xt, p.PS, p.T));
 }
 
 // Resident mode: teams of one CTA share the staged training block, so several teams per CTA need n_x == 1 and the block
