@@ -345,7 +345,7 @@ def gpu_arm(args):
         "clocks": clocks,
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                 "ms_per_step": e2e_ms / args.steps},
-        "gpu_launches": args.steps * (n_buckets + 1),
+        "gpu_launches": args.steps * 2 * n_buckets,      # fit_kernel + eval_kernel per width bucket
         "roofline": roofline,
         "cpu_baseline": cpu,
         "cpu_best_effort": cpu_best_effort() if cpu is not None else None,

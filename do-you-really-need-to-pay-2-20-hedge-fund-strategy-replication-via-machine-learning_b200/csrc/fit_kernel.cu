@@ -763,7 +763,8 @@ static int fit_batched_impl(const hfrep_fit_cfg* c, const float* X, int n_tasks,
     if (wpt == 0) {                                  // pick the mapping from the amount of parallel work in THIS call
         const int sms = sm_count();                  // (callers that split a job over several calls pass it explicitly)
         // measured on the L = 1..21 sweep x seeds (profiles/README.md): 6 warps win up to ~5 tasks per SM, 2 warps beyond
-        wpt = n_tasks <= 5 * sms ? 6 : 2;
+        // (narrow tasks in large numbers: one warp per task — L = 8 x 4096 tasks 6.6 vs 7.8 ms per 100 epochs; L = 20: 14.8 vs 12.1)
+        wpt = n_tasks <= 5 * sms ? 6 : ((c->L_max <= 8 && n_tasks >= 10 * sms) ? 1 : 2);
     }
     HFREP_REQUIRE(wpt == 1 || wpt == 2 || wpt == 3 || wpt == 6, "fit_batched: warps_per_task=%d (0, 1, 2, 3 or 6)", wpt);
     return fit_dispatch(p, c->L_max, wpt, (cudaStream_t)stream);
