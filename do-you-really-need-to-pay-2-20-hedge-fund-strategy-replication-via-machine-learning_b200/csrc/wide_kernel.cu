@@ -5,12 +5,14 @@
 // alignment) — for shapes whose state does not fit shared memory: weights and Nadam state live in a caller-provided
 // global workspace (L2-resident: 6*E*L floats per task), activations of the current mini-batch in shared memory.
 //
-// ROUND-1 STATUS: correct first.  Plain FP32 FFMA with L1/L2-served operands, one CTA per task; the tcgen05 / TMA
-// version (seeds batched along N so the encoder GEMM becomes [rows x 500].[500 x (L*S)], 3xTF32) is the next step and
-// is NOT what this file is yet.
+// Two fit kernels: fit_wide_kernel (v1: correct first, any E <= 4096 and L <= 64, weights in the global workspace) and
+// fit_wide2_kernel (E <= 512, L <= 16: ETF columns dealt to threads, weights in registers, packed FFMA2, shuffle
+// scatter-reductions over the ETFs; 4.3-4.6x faster than v1).  The tcgen05 / TMA version (seeds batched along N so the
+// encoder GEMM becomes [rows x 500].[500 x (L*S)], 3xTF32) is the next step and is NOT what this file is yet.
 #include "common.cuh"
 
 #include <cmath>
+#include <cstdlib>
 
 namespace hfrep {
 
@@ -164,6 +166,266 @@ __global__ void __launch_bounds__(WIDE_THREADS) fit_wide_kernel(const WideFitPar
     }
     float* wo = p.W_out + (size_t)task * 2 * EL;
     for (size_t i = tid; i < EL; i += WIDE_THREADS) { wo[i] = We[i]; wo[EL + i] = Wd[i]; }
+    if (tid == 0) { p.epochs_run[task] = epochs_run; p.status[task] = st; }
+}
+
+// ------------------------------------------------------------------------------------------------ wide fit, v2
+// The same training run with the ETF columns dealt to threads: thread t owns columns [t*EPT, t*EPT+EPT) and keeps ITS rows
+// of We and ITS columns of Wd in registers for the whole run, so no weight ever moves through shared memory.  Of the five
+// contractions of a step, three are then thread-local (zy = h Wd, dWd = h^T dzy, dWe = x^T dzh: the other operand is a
+// broadcast row of h / dzh from shared memory) and two reduce over the ETFs, i.e. over threads (zh = x We, dzh = dzy Wd^T):
+// a lane forms its 32 partial products (32/LP rows x LP latents), a 31-shuffle scatter-reduction leaves each lane with one
+// complete warp sum, the warps' sums meet in shared memory.  x rows are read from global memory (L1/L2) three times per step,
+// coalesced; dzy is never stored.  Nadam's m, v live in the caller's workspace, laid out [slot][thread] (coalesced).
+// E <= 512, L <= 16 (else the v1 kernel above).
+template <int NV, int MASK>
+__device__ __forceinline__ float warp_scatter_sum(float (&v)[32], int lane, int& j0) {
+    if constexpr (NV == 1) {
+        float s = v[0];
+#pragma unroll
+        for (int m = MASK; m >= 1; m >>= 1) s += __shfl_xor_sync(0xffffffffu, s, m);
+        return s;
+    } else {
+        constexpr int HALF = NV / 2;
+        const bool up = (lane & MASK) != 0;
+#pragma unroll
+        for (int i = 0; i < HALF; ++i) {
+            const float send = up ? v[i] : v[i + HALF];
+            const float keep = up ? v[i + HALF] : v[i];
+            v[i] = keep + __shfl_xor_sync(0xffffffffu, send, MASK);
+        }
+        if (up) j0 += HALF;
+        return warp_scatter_sum<HALF, MASK / 2>(v, lane, j0);
+    }
+}
+
+template <int LP, int EPT>
+__global__ void __launch_bounds__(512 / EPT) fit_wide2_kernel(const WideFitParams p) {
+    extern __shared__ __align__(16) float sm[];
+    constexpr int RG = 32 / LP;                 // batch rows per reduction group (32 values per lane)
+    constexpr int LH = LP / 2;                  // latent columns are held in pairs: every FMA is a packed FFMA2
+    const int task = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int NT = blockDim.x, NWARP = NT >> 5;
+    const int E = p.E, L = p.L, B = p.batch;
+    const int BP = (B + 3) & ~3;                // rows of the shared tiles (a multiple of RG)
+    float* H = sm;                              // [BP][LP]  h = lrelu(zh)
+    float* dZh = H + BP * LP;                   // [BP][LP]
+    float* part = dZh + BP * LP;                // [NWARP][BP][LP] per-warp sums over the warp's ETF columns
+    int* rows = reinterpret_cast<int*>(part + (size_t)NWARP * BP * LP);   // [BP]
+    float* red = reinterpret_cast<float*>(rows + BP);                     // [32]
+
+    const size_t EL = (size_t)E * L;
+    const float* X = p.X + (size_t)(p.task_x ? p.task_x[task] : 0) * p.T * E;
+    const float* w0 = p.W0 + (size_t)task * 2 * EL;
+    const int e0 = tid * EPT;
+    float2 We[EPT][LH], Wd[LH][EPT];            // We[k][j] = We[e0+k][2j, 2j+1];  Wd[j][k] = Wd[2j, 2j+1][e0+k]
+    auto w_at = [&](size_t base, int idx, bool in) { return in ? w0[base + idx] : 0.f; };
+#pragma unroll
+    for (int k = 0; k < EPT; ++k)
+#pragma unroll
+        for (int j = 0; j < LH; ++j) {
+            const bool ine = e0 + k < E;
+            We[k][j] = make_float2(w_at(0, (e0 + k) * L + 2 * j, ine && 2 * j < L), w_at(0, (e0 + k) * L + 2 * j + 1, ine && 2 * j + 1 < L));
+            Wd[j][k] = make_float2(w_at(EL, 2 * j * E + e0 + k, ine && 2 * j < L), w_at(EL, (2 * j + 1) * E + e0 + k, ine && 2 * j + 1 < L));
+        }
+    // Nadam state: slot s of thread t at mv[s*NT + t] (m) and mv[(NS + s)*NT + t] (v); slots = We then Wd
+    constexpr int NS = 2 * EPT * LP;
+    float* mv = p.ws + (size_t)task * (2 * NS) * NT;
+    for (int s = 0; s < 2 * NS; ++s) mv[(size_t)s * NT + tid] = 0.f;
+
+    const int* perm_t = p.perm ? p.perm + (size_t)task * p.perm_task_stride : nullptr;
+    const float alpha = p.alpha, omb1 = 1.f - p.b1, omb2 = 1.f - p.b2;
+    const int n_fit = p.n_fit, n_val = p.n_val;
+    int step = 0, wait = 0, epochs_run = 0, st = 0;
+    float best = INFINITY;
+
+    auto load_x = [&](int r, int nb, float (&x)[EPT]) {          // the thread's columns of batch row r (zeros past the batch / E)
+        const float* xr = X + (size_t)rows[r < nb ? r : 0] * E + e0;
+#pragma unroll
+        for (int k = 0; k < EPT; ++k) x[k] = (r < nb && e0 + k < E) ? __ldg(xr + k) : 0.f;
+    };
+    auto cross_warp = [&](int o) -> float {                      // sum of the warps' sums for output o
+        float sacc = 0.f;
+        for (int w = 0; w < NWARP; ++w) sacc += part[(size_t)w * BP * LP + o];
+        return sacc;
+    };
+    const float4* sched = p.sched;
+    auto upd = [&](float& w, float g, int slot, const float4& sc) {
+        float* mp = mv + (size_t)slot * NT + tid;
+        float* vp = mv + (size_t)(NS + slot) * NT + tid;
+        const float mm = p.b1 * *mp + omb1 * g;
+        const float vv = p.b2 * *vp + omb2 * (g * g);
+        *mp = mm; *vp = vv;
+        w -= p.lr * (sc.x * g + sc.y * mm) / (sqrtf(vv * sc.z) + p.eps);
+    };
+
+    auto run_batch = [&](int nb, bool train) -> float {
+        // ---- pass 1: zh = x We (reduce over ETFs)
+        for (int r0 = 0; r0 < nb; r0 += RG) {
+            float v[32];
+#pragma unroll
+            for (int g = 0; g < RG; ++g) {
+                float x[EPT];
+                load_x(r0 + g, nb, x);
+#pragma unroll
+                for (int j = 0; j < LH; ++j) {
+                    float2 a = make_float2(0.f, 0.f);
+#pragma unroll
+                    for (int k = 0; k < EPT; ++k) a = __ffma2_rn(make_float2(x[k], x[k]), We[k][j], a);
+                    v[g * LP + 2 * j] = a.x; v[g * LP + 2 * j + 1] = a.y;
+                }
+            }
+            int j0 = 0;
+            const float sum = warp_scatter_sum<32, 16>(v, lane, j0);
+            part[(size_t)warp * BP * LP + r0 * LP + j0] = sum;
+        }
+        __syncthreads();
+        for (int o = tid; o < nb * LP; o += NT) H[o] = lrelu(cross_warp(o), alpha);
+        __syncthreads();
+        // ---- pass 2: zy = h Wd, error, dzy; dWd += h^T dzy; dzh partials = dzy Wd^T (reduce over ETFs)
+        const float coef = 2.f / (float)(nb * E);
+        float sse = 0.f;
+        float2 gWd[LH][EPT];
+#pragma unroll
+        for (int j = 0; j < LH; ++j)
+#pragma unroll
+            for (int k = 0; k < EPT; ++k) gWd[j][k] = make_float2(0.f, 0.f);
+        for (int r0 = 0; r0 < nb; r0 += RG) {
+            float v[32];
+#pragma unroll
+            for (int g = 0; g < RG; ++g) {
+                const int r = r0 + g;
+                float x[EPT], dzy[EPT];
+                float2 h[LH];
+                load_x(r, nb, x);
+#pragma unroll
+                for (int l4 = 0; l4 < LP / 4; ++l4) {
+                    const float4 hv = *reinterpret_cast<const float4*>(H + (r < nb ? r : 0) * LP + 4 * l4);
+                    h[2 * l4] = make_float2(hv.x, hv.y); h[2 * l4 + 1] = make_float2(hv.z, hv.w);
+                }
+#pragma unroll
+                for (int k = 0; k < EPT; ++k) {
+                    float2 a = make_float2(0.f, 0.f);
+#pragma unroll
+                    for (int j = 0; j < LH; ++j) a = __ffma2_rn(h[j], Wd[j][k], a);
+                    const float zy = a.x + a.y;
+                    const float d = r < nb ? lrelu(zy, alpha) - x[k] : 0.f;       // columns past E: zy = x = 0
+                    sse = fmaf(d, d, sse);
+                    dzy[k] = lrelu_grad(zy, coef * d, alpha);
+                }
+                if (train) {
+#pragma unroll
+                    for (int j = 0; j < LH; ++j) {
+                        float2 a = make_float2(0.f, 0.f);
+#pragma unroll
+                        for (int k = 0; k < EPT; ++k) {
+                            const float2 dd = make_float2(dzy[k], dzy[k]);
+                            gWd[j][k] = __ffma2_rn(h[j], dd, gWd[j][k]);
+                            a = __ffma2_rn(dd, Wd[j][k], a);
+                        }
+                        v[g * LP + 2 * j] = a.x; v[g * LP + 2 * j + 1] = a.y;
+                    }
+                }
+            }
+            if (train) {
+                int j0 = 0;
+                const float sum = warp_scatter_sum<32, 16>(v, lane, j0);
+                part[(size_t)warp * BP * LP + r0 * LP + j0] = sum;
+            }
+        }
+        if (!train) return sse;
+        // ---- Nadam on the thread's own weights (Wd now: its gradient is complete and pass 3 does not read Wd)
+        const float4 sc = __ldg(sched + step);
+#pragma unroll
+        for (int j = 0; j < LH; ++j)
+#pragma unroll
+            for (int k = 0; k < EPT; ++k) {
+                upd(Wd[j][k].x, gWd[j][k].x, EPT * LP + (2 * j) * EPT + k, sc);
+                upd(Wd[j][k].y, gWd[j][k].y, EPT * LP + (2 * j + 1) * EPT + k, sc);
+                if (k == EPT - 1) asm volatile("" ::: "memory");    // keep the m, v loads of later slots from piling up in registers
+            }
+        __syncthreads();
+        for (int o = tid; o < nb * LP; o += NT) dZh[o] = lrelu_grad(H[o], cross_warp(o), alpha);   // sign(h) == sign(zh)
+        __syncthreads();
+        // ---- pass 3: dWe = x^T dzh
+        float2 gWe[EPT][LH];
+#pragma unroll
+        for (int k = 0; k < EPT; ++k)
+#pragma unroll
+            for (int j = 0; j < LH; ++j) gWe[k][j] = make_float2(0.f, 0.f);
+#pragma unroll 2
+        for (int r = 0; r < nb; ++r) {
+            float x[EPT];
+            load_x(r, nb, x);
+#pragma unroll
+            for (int l4 = 0; l4 < LP / 4; ++l4) {
+                const float4 gv = *reinterpret_cast<const float4*>(dZh + r * LP + 4 * l4);
+#pragma unroll
+                for (int k = 0; k < EPT; ++k) {
+                    const float2 xx = make_float2(x[k], x[k]);
+                    gWe[k][2 * l4] = __ffma2_rn(xx, make_float2(gv.x, gv.y), gWe[k][2 * l4]);
+                    gWe[k][2 * l4 + 1] = __ffma2_rn(xx, make_float2(gv.z, gv.w), gWe[k][2 * l4 + 1]);
+                }
+            }
+        }
+#pragma unroll
+        for (int k = 0; k < EPT; ++k)
+#pragma unroll
+            for (int j = 0; j < LH; ++j) {
+                upd(We[k][j].x, gWe[k][j].x, k * LP + 2 * j, sc);
+                upd(We[k][j].y, gWe[k][j].y, k * LP + 2 * j + 1, sc);
+                if (j == LH - 1) asm volatile("" ::: "memory");
+            }
+        ++step;
+        return sse;
+    };
+
+    for (int epoch = 0; epoch < p.max_epochs; ++epoch) {
+        float lsum = 0.f, vsum = 0.f;
+        for (int lo = 0; lo < n_fit; lo += B) {
+            const int nb = min(B, n_fit - lo);
+            __syncthreads();
+            for (int q = tid; q < nb; q += NT) rows[q] = perm_t ? __ldg(perm_t + (size_t)epoch * n_fit + lo + q) : lo + q;
+            __syncthreads();
+            lsum += run_batch(nb, true);
+        }
+        for (int lo = 0; lo < n_val; lo += B) {
+            const int nb = min(B, n_val - lo);
+            __syncthreads();
+            for (int q = tid; q < nb; q += NT) rows[q] = n_fit + lo + q;
+            __syncthreads();
+            vsum += run_batch(nb, false);
+        }
+        // epoch losses: fixed-order block sums
+        const float l1 = warp_sum(lsum), v1 = warp_sum(vsum);
+        __syncthreads();
+        if (lane == 0) { red[warp] = l1; red[16 + warp] = v1; }
+        __syncthreads();
+        float loss = 0.f, val = 0.f;
+        for (int w = 0; w < NWARP; ++w) { loss += red[w]; val += red[16 + w]; }
+        loss = loss / ((float)E * n_fit);
+        val = n_val > 0 ? val / ((float)E * n_val) : NAN;
+        if (tid == 0) {
+            p.loss_hist[(size_t)task * p.max_epochs + epoch] = loss;
+            p.val_hist[(size_t)task * p.max_epochs + epoch] = val;
+        }
+        epochs_run = epoch + 1;
+        if (!isfinite(loss)) st = 1;
+        if (p.early_stop) {
+            ++wait;
+            if (val < best) { best = val; wait = 0; }
+            if (wait >= p.patience && epoch > 0) break;
+        }
+    }
+    float* wo = p.W_out + (size_t)task * 2 * EL;
+#pragma unroll
+    for (int k = 0; k < EPT; ++k)
+#pragma unroll
+        for (int j = 0; j < LH; ++j)
+            if (e0 + k < E) {
+                if (2 * j < L) { wo[(size_t)(e0 + k) * L + 2 * j] = We[k][j].x; wo[EL + (size_t)(2 * j) * E + e0 + k] = Wd[j][k].x; }
+                if (2 * j + 1 < L) { wo[(size_t)(e0 + k) * L + 2 * j + 1] = We[k][j].y; wo[EL + (size_t)(2 * j + 1) * E + e0 + k] = Wd[j][k].y; }
+            }
     if (tid == 0) { p.epochs_run[task] = epochs_run; p.status[task] = st; }
 }
 
@@ -322,9 +584,38 @@ __global__ void __launch_bounds__(WIDE_THREADS) eval_wide_kernel(const WideEvalP
 
 using namespace hfrep;
 
+// v2 geometry: padded latent width, ETF columns per thread, threads per CTA (0: shape outside v2, use the v1 kernel)
+struct Wide2Geom { int LP, EPT, NT; };
+static Wide2Geom wide2_geom(int E, int L, int n_tasks) {
+    Wide2Geom g{0, 0, 0};
+    if (E > 512 || L > 32) return g;
+    g.LP = L <= 8 ? 8 : (L <= 16 ? 16 : 32);
+    // registers hold 2*EPT*LP weights per thread: 64 at most; few tasks -> more, narrower threads
+    if (g.LP == 32) { g.LP = 0; return g; }      // 3*LP live weight/gradient registers per thread do not fit yet: v1
+    g.EPT = 16 / g.LP;                           // 16 weights of We and of Wd per thread: 256 or 512 threads for 500 ETFs
+                                                 // (measured: 32 per thread halves the reduction work per FMA but leaves too
+                                                 // few warps to hide the reduction's shuffle chain: 45.7 vs 29.4 ms at L = 8)
+    g.NT = 32 * (((E + g.EPT - 1) / g.EPT + 31) / 32);
+    return g;
+}
+
 extern "C" size_t hfrep_fit_wide_workspace(int n_tasks, int E, int L) {
     if (n_tasks <= 0 || E <= 0 || L <= 0) return 0;
-    return sizeof(float) * 6 * (size_t)n_tasks * E * L;
+    const Wide2Geom g = wide2_geom(E, L, n_tasks);
+    const size_t v1 = 6 * (size_t)E * L, v2 = g.NT ? 4 * (size_t)g.EPT * g.LP * g.NT : 0;
+    return sizeof(float) * (size_t)n_tasks * (v1 > v2 ? v1 : v2);
+}
+
+template <int LP, int EPT>
+static int launch_fit_wide2(const WideFitParams& p, int NT, cudaStream_t stream) {
+    const int BP = (p.batch + 3) & ~3, NWARP = NT / 32;
+    const size_t smem = sizeof(float) * ((size_t)(2 + NWARP) * BP * LP + BP + 32);
+    HFREP_REQUIRE(smem <= 227 * 1024, "fit_wide: %zu bytes of shared memory needed (batch too large)", smem);
+    auto kern = fit_wide2_kernel<LP, EPT>;
+    HFREP_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    kern<<<p.n_tasks, NT, smem, stream>>>(p);
+    HFREP_CUDA_OK(cudaGetLastError());
+    return HFREP_OK;
 }
 
 extern "C" int hfrep_fit_wide(const hfrep_fit_cfg* c, const float* X, int n_tasks, int L, const int32_t* task_x,
@@ -349,6 +640,12 @@ extern "C" int hfrep_fit_wide(const hfrep_fit_cfg* c, const float* X, int n_task
     p.n_tasks = n_tasks; p.E = c->E; p.L = L; p.T = c->T; p.n_fit = c->n_fit; p.n_val = c->T - c->n_fit; p.batch = c->batch;
     p.max_epochs = c->max_epochs; p.patience = c->patience; p.early_stop = c->early_stop;
     p.alpha = c->alpha; p.lr = c->lr; p.b1 = c->beta_1; p.b2 = c->beta_2; p.eps = c->epsilon;
+    const Wide2Geom g = getenv("HFREP_WIDE_V1") ? Wide2Geom{0, 0, 0} : wide2_geom(c->E, L, n_tasks);
+    if (g.NT) {
+        cudaStream_t st = (cudaStream_t)stream;
+        if (g.LP == 8) return launch_fit_wide2<8, 2>(p, g.NT, st);
+        return launch_fit_wide2<16, 1>(p, g.NT, st);
+    }
     const size_t smem = sizeof(float) * (2 * (size_t)c->batch * L + (size_t)c->batch * c->E + c->batch + 16);
     HFREP_REQUIRE(smem <= 227 * 1024, "fit_wide: %zu bytes of shared memory needed (batch x E too large)", smem);
     HFREP_CUDA_OK(cudaFuncSetAttribute(fit_wide_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

@@ -423,7 +423,9 @@ def test_rolling_beta_option(hf, data, ref_inputs, L):
     assert rel_err(ev.beta[0, :L].cpu().numpy(), ae.betas[0]) < TOL          # reported beta / norm stay window 0's
 
 
-@pytest.mark.parametrize("E,F,L", [(500, 300, 8), (96, 40, 16), (120, 50, 32)])   # L=32 > 24 OLS rows: minimum-norm solve
+# (500, ., 8) and (96, ., 16): the register-resident kernel (two / one ETF column per thread); (37, ., 5) and (130, ., 11): its
+# padding (odd E, L not a multiple of 8); (120, ., 32): the general kernel, and L=32 > 24 OLS rows: minimum-norm solve
+@pytest.mark.parametrize("E,F,L", [(500, 300, 8), (96, 40, 16), (37, 20, 5), (130, 30, 11), (120, 50, 32)])
 def test_wide_variant_rolling_refit(hf, E, F, L):
     """configs[3] shape at test scale (500 ETFs, hundreds of funds, 252-row windows, rolling refit) through the wide
     kernels, against the Mode-W oracle (the reference's AE restatement called per window)."""
