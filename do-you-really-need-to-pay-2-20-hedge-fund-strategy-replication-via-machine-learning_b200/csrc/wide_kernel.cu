@@ -6,7 +6,7 @@
 // global workspace (L2-resident: 6*E*L floats per task), activations of the current mini-batch in shared memory.
 //
 // Two fit kernels: fit_wide_kernel (v1: correct first, any E <= 4096 and L <= 64, weights in the global workspace) and
-// fit_wide2_kernel (E <= 512, L <= 16: ETF columns dealt to threads, weights in registers, packed FFMA2, shuffle
+// fit_wide2_kernel (E <= 512, L <= 32: ETF columns dealt to threads, weights in registers, packed FFMA2, shuffle
 // scatter-reductions over the ETFs; 4.3-4.6x faster than v1).  The tcgen05 / TMA version (seeds batched along N so the
 // encoder GEMM becomes [rows x 500].[500 x (L*S)], 3xTF32) is the next step and is NOT what this file is yet.
 #include "common.cuh"
@@ -177,7 +177,7 @@ __global__ void __launch_bounds__(WIDE_THREADS) fit_wide_kernel(const WideFitPar
 // a lane forms its 32 partial products (32/LP rows x LP latents), a 31-shuffle scatter-reduction leaves each lane with one
 // complete warp sum, the warps' sums meet in shared memory.  x rows are read from global memory (L1/L2) three times per step,
 // coalesced; dzy is never stored.  Nadam's m, v live in the caller's workspace, laid out [slot][thread] (coalesced).
-// E <= 512, L <= 16 (else the v1 kernel above).
+// E <= 512, L <= 32 (else the v1 kernel above).
 template <int NV, int MASK>
 __device__ __forceinline__ float warp_scatter_sum(float (&v)[32], int lane, int& j0) {
     if constexpr (NV == 1) {
@@ -213,6 +213,10 @@ __global__ void __launch_bounds__(512 / EPT) fit_wide2_kernel(const WideFitParam
     float* part = dZh + BP * LP;                // [NWARP][BP][LP] per-warp sums over the warp's ETF columns
     int* rows = reinterpret_cast<int*>(part + (size_t)NWARP * BP * LP);   // [BP]
     float* red = reinterpret_cast<float*>(rows + BP);                     // [32]
+    // LP = 32: the 32 gradient accumulators of dWd and the 32 values of the dzh reduction do not fit the 128 registers of
+    // a 512-thread CTA together, so dzy is parked in shared memory (a private column per thread) and dWd gets its own pass
+    constexpr bool SPLIT = LP * EPT > 16;
+    float* dzyS = red + 32;                                               // [BP][NT*EPT] (SPLIT only)
 
     const size_t EL = (size_t)E * L;
     const float* X = p.X + (size_t)(p.task_x ? p.task_x[task] : 0) * p.T * E;
@@ -314,13 +318,17 @@ __global__ void __launch_bounds__(512 / EPT) fit_wide2_kernel(const WideFitParam
                     dzy[k] = lrelu_grad(zy, coef * d, alpha);
                 }
                 if (train) {
+                    if constexpr (SPLIT) {
+#pragma unroll
+                        for (int k = 0; k < EPT; ++k) dzyS[(size_t)(r < nb ? r : BP - 1) * NT * EPT + tid * EPT + k] = dzy[k];
+                    }
 #pragma unroll
                     for (int j = 0; j < LH; ++j) {
                         float2 a = make_float2(0.f, 0.f);
 #pragma unroll
                         for (int k = 0; k < EPT; ++k) {
                             const float2 dd = make_float2(dzy[k], dzy[k]);
-                            gWd[j][k] = __ffma2_rn(h[j], dd, gWd[j][k]);
+                            if constexpr (!SPLIT) gWd[j][k] = __ffma2_rn(h[j], dd, gWd[j][k]);
                             a = __ffma2_rn(dd, Wd[j][k], a);
                         }
                         v[g * LP + 2 * j] = a.x; v[g * LP + 2 * j + 1] = a.y;
@@ -334,6 +342,22 @@ __global__ void __launch_bounds__(512 / EPT) fit_wide2_kernel(const WideFitParam
             }
         }
         if (!train) return sse;
+        if constexpr (SPLIT) {                  // dWd += h^T dzy from the parked dzy column (the thread's own: no barrier)
+            for (int r = 0; r < nb; ++r) {
+                float2 dd[EPT];
+#pragma unroll
+                for (int k = 0; k < EPT; ++k) { const float d = dzyS[(size_t)r * NT * EPT + tid * EPT + k]; dd[k] = make_float2(d, d); }
+#pragma unroll
+                for (int l4 = 0; l4 < LP / 4; ++l4) {
+                    const float4 hv = *reinterpret_cast<const float4*>(H + r * LP + 4 * l4);
+#pragma unroll
+                    for (int k = 0; k < EPT; ++k) {
+                        gWd[2 * l4][k] = __ffma2_rn(make_float2(hv.x, hv.y), dd[k], gWd[2 * l4][k]);
+                        gWd[2 * l4 + 1][k] = __ffma2_rn(make_float2(hv.z, hv.w), dd[k], gWd[2 * l4 + 1][k]);
+                    }
+                }
+            }
+        }
         // ---- Nadam on the thread's own weights (Wd now: its gradient is complete and pass 3 does not read Wd)
         const float4 sc = __ldg(sched + step);
 #pragma unroll
@@ -591,8 +615,7 @@ static Wide2Geom wide2_geom(int E, int L, int n_tasks) {
     if (E > 512 || L > 32) return g;
     g.LP = L <= 8 ? 8 : (L <= 16 ? 16 : 32);
     // registers hold 2*EPT*LP weights per thread: 64 at most; few tasks -> more, narrower threads
-    if (g.LP == 32) { g.LP = 0; return g; }      // 3*LP live weight/gradient registers per thread do not fit yet: v1
-    g.EPT = 16 / g.LP;                           // 16 weights of We and of Wd per thread: 256 or 512 threads for 500 ETFs
+    g.EPT = g.LP == 8 ? 2 : 1;                   // 16 weights of We and of Wd per thread (32 at L > 16): 256 or 512 threads
                                                  // (measured: 32 per thread halves the reduction work per FMA but leaves too
                                                  // few warps to hide the reduction's shuffle chain: 45.7 vs 29.4 ms at L = 8)
     g.NT = 32 * (((E + g.EPT - 1) / g.EPT + 31) / 32);
@@ -609,7 +632,7 @@ extern "C" size_t hfrep_fit_wide_workspace(int n_tasks, int E, int L) {
 template <int LP, int EPT>
 static int launch_fit_wide2(const WideFitParams& p, int NT, cudaStream_t stream) {
     const int BP = (p.batch + 3) & ~3, NWARP = NT / 32;
-    const size_t smem = sizeof(float) * ((size_t)(2 + NWARP) * BP * LP + BP + 32);
+    const size_t smem = sizeof(float) * ((size_t)(2 + NWARP) * BP * LP + BP + 32 + (LP * EPT > 16 ? (size_t)BP * NT * EPT : 0));
     HFREP_REQUIRE(smem <= 227 * 1024, "fit_wide: %zu bytes of shared memory needed (batch too large)", smem);
     auto kern = fit_wide2_kernel<LP, EPT>;
     HFREP_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -644,7 +667,8 @@ extern "C" int hfrep_fit_wide(const hfrep_fit_cfg* c, const float* X, int n_task
     if (g.NT) {
         cudaStream_t st = (cudaStream_t)stream;
         if (g.LP == 8) return launch_fit_wide2<8, 2>(p, g.NT, st);
-        return launch_fit_wide2<16, 1>(p, g.NT, st);
+        if (g.LP == 16) return launch_fit_wide2<16, 1>(p, g.NT, st);
+        return launch_fit_wide2<32, 1>(p, g.NT, st);
     }
     const size_t smem = sizeof(float) * (2 * (size_t)c->batch * L + (size_t)c->batch * c->E + c->batch + 16);
     HFREP_REQUIRE(smem <= 227 * 1024, "fit_wide: %zu bytes of shared memory needed (batch x E too large)", smem);
