@@ -425,7 +425,7 @@ def fit_windows(R32: torch.Tensor, win_starts, T_win: int, task_L, task_win, W0:
 
 
 def run_mode_w_wide(etf, hfd, rf, *, train_window: int, latent_dim: int, seeds=(123,), ols_window: int = 24, device=None,
-                    W0=None, windows=None, **fit_kw):
+                    W0=None, windows=None, timings: dict | None = None, **fit_kw):
     """Rolling refit for wide shapes (hundreds of ETFs, thousands of funds: BASELINE configs[3]).  Same task definition
     and alignment as run_mode_w; kernel (a) builds the MinMax-scaled training windows, hfrep_fit_wide trains on them with
     weights in a global workspace, hfrep_predict_wide regresses every fund on the latent factors and returns the replica
@@ -461,8 +461,13 @@ def run_mode_w_wide(etf, hfd, rf, *, train_window: int, latent_dim: int, seeds=(
         epochs_run = torch.zeros(n, dtype=torch.int32, device=dev)
         status = torch.zeros(n, dtype=torch.int32, device=dev)
         tw = _device_ints(np.asarray([wi for wi, _ in tasks], np.int32), dev)
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)] if timings is not None else None
+        if ev:
+            ev[0].record()
         check(lib.hfrep_fit_wide(C.byref(cfg), ptr(blocks), n, L, ptr(tw), ptr(W0d), None, 0, ptr(sched), ptr(ws), ws_bytes,
                                  ptr(W_out), ptr(loss), ptr(val), ptr(epochs_run), ptr(status), stream_ptr()))
+        if ev:
+            ev[1].record()
         fit = FitResult(W_out, loss, val, epochs_run, status, None, 2 * E * L)
         row0 = _device_ints((ts - ols_window)[[wi for wi, _ in tasks]].astype(np.int32), dev)
         etf_d, hfd_d, rf_d = to_device(etf, dev), to_device(hfd, dev), to_device(rf, dev)
@@ -470,6 +475,11 @@ def run_mode_w_wide(etf, hfd, rf, *, train_window: int, latent_dim: int, seeds=(
         est = torch.zeros(n, dtype=torch.int32, device=dev)
         check(lib.hfrep_predict_wide(ptr(etf_d), ptr(hfd_d), ptr(rf_d), T, E, F, L, ols_window, fit_kw.get("alpha", .2), n,
                                      ptr(row0), ptr(W_out), ptr(replica), ptr(est), stream_ptr()))
+        if ev:                                   # kernel times of the fit and of its input copies + evaluation (CUDA events)
+            ev[2].record()
+            ev[2].synchronize()
+            timings["fit_ms"] = ev[0].elapsed_time(ev[1])
+            timings["eval_ms"] = ev[1].elapsed_time(ev[2])
     return dict(t=ts, replica=replica.view(len(seeds), n_win, F), fit=fit, eval_status=est, blocks=blocks, tasks=tasks)
 
 
