@@ -27,6 +27,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdlib>
+#include <type_traits>
 
 namespace hfrep {
 
@@ -226,7 +227,8 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
     // row loads are pair-shared LDS.128 (2 cycles).  Every warp walks all rows, so h and dzy rows cross warps:
     // two team barriers per pass (a __syncwarp for one-warp teams).
     // Pieces past the block (LP/2 not a multiple of NC) are computed on whatever follows in shared memory and dropped.
-    auto rows_phase = [&](const int* xoff, int nb, bool train, float coef) -> float {
+    auto rows_pass = [&](auto RC, const int* xoff, int r0, int nb, bool train, float coef, float2& sse2) {
+        constexpr int R = decltype(RC)::value;      // rows per lane in this pass: 3, or 2 when rows g+32 are all past the batch
         constexpr int NC = 2 * NW;
         constexpr int NPL = (LP / 2 + NC - 1) / NC;   // latent pieces per lane
         constexpr int NPE = (EP / 2) / NC;            // ETF pieces per lane (12 splits evenly over 2, 4, 6, 12 classes)
@@ -235,29 +237,27 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
         const int g = lane >> 1;
         const float* Wl = We + 2 * cls;               // piece i of a We row at Wl + 2*NC*i
         const float* Wy = Wd + 2 * cls;               // piece i of a Wd row at Wy + 2*NC*i
-        float2 sse2 = make_float2(0.f, 0.f);
-#pragma unroll 1
-        for (int r0 = 0; r0 < nb; r0 += 48) {
-            const float* xr[3];
-            int rs[3];
+        {
+            const float* xr[R];
+            int rs[R];
 #pragma unroll
-            for (int j = 0; j < 3; ++j) {
+            for (int j = 0; j < R; ++j) {
                 const int r = r0 + g + 16 * j;
                 const bool valid = r < nb;
                 xr[j] = Xs + (valid ? (XT ? r * XS : xoff[r]) : zero_row);
                 rs[j] = valid ? r : BP;
             }
             // ---- zh pieces = x . We[:, own pieces]
-            float2 zh[3][NPL];
+            float2 zh[R][NPL];
 #pragma unroll
-            for (int j = 0; j < 3; ++j)
+            for (int j = 0; j < R; ++j)
 #pragma unroll
                 for (int i = 0; i < NPL; ++i) zh[j][i] = make_float2(0.f, 0.f);
 #pragma unroll (FULL ? EP / 4 : 1)
             for (int e4 = 0; e4 < EP / 4; ++e4) {
-                float xe[3][4];
+                float xe[R][4];
 #pragma unroll
-                for (int j = 0; j < 3; ++j) {
+                for (int j = 0; j < R; ++j) {
                     const float4 v = ld4(xr[j] + 4 * e4);
                     xe[j][0] = v.x; xe[j][1] = v.y; xe[j][2] = v.z; xe[j][3] = v.w;
                 }
@@ -267,28 +267,28 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
                     for (int i = 0; i < NPL; ++i) {
                         const float2 w = ld2(Wl + (4 * e4 + k) * LP + 2 * NC * i);
 #pragma unroll
-                        for (int j = 0; j < 3; ++j) zh[j][i] = __ffma2_rn(make_float2(xe[j][k], xe[j][k]), w, zh[j][i]);
+                        for (int j = 0; j < R; ++j) zh[j][i] = __ffma2_rn(make_float2(xe[j][k], xe[j][k]), w, zh[j][i]);
                     }
             }
 #pragma unroll
             for (int i = 0; i < NPL; ++i)
                 if (cls + NC * i < LP / 2) {
 #pragma unroll
-                    for (int j = 0; j < 3; ++j)
+                    for (int j = 0; j < R; ++j)
                         st2(H + rs[j] * HS + 2 * (cls + NC * i), make_float2(lrelu(zh[j][i].x, alpha), lrelu(zh[j][i].y, alpha)));
                 }
             team_sync<NW>(team);
             // ---- zy pieces = h . Wd[:, own pieces]
-            float2 zy[3][NPE];
+            float2 zy[R][NPE];
 #pragma unroll
-            for (int j = 0; j < 3; ++j)
+            for (int j = 0; j < R; ++j)
 #pragma unroll
                 for (int i = 0; i < NPE; ++i) zy[j][i] = make_float2(0.f, 0.f);
 #pragma unroll (FULL ? CT : 1)
             for (int l4 = 0; l4 < CT; ++l4) {
-                float hl[3][4];
+                float hl[R][4];
 #pragma unroll
-                for (int j = 0; j < 3; ++j) {
+                for (int j = 0; j < R; ++j) {
                     const float4 v = ld4(H + rs[j] * HS + 4 * l4);
                     hl[j][0] = v.x; hl[j][1] = v.y; hl[j][2] = v.z; hl[j][3] = v.w;
                 }
@@ -298,12 +298,12 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
                     for (int i = 0; i < NPE; ++i) {
                         const float2 w = ld2(Wy + (4 * l4 + k) * WDS + 2 * NC * i);
 #pragma unroll
-                        for (int j = 0; j < 3; ++j) zy[j][i] = __ffma2_rn(make_float2(hl[j][k], hl[j][k]), w, zy[j][i]);
+                        for (int j = 0; j < R; ++j) zy[j][i] = __ffma2_rn(make_float2(hl[j][k], hl[j][k]), w, zy[j][i]);
                     }
             }
             // ---- squared error and dLoss/dzy on the lane's pieces
 #pragma unroll
-            for (int j = 0; j < 3; ++j)
+            for (int j = 0; j < R; ++j)
 #pragma unroll
                 for (int i = 0; i < NPE; ++i) {
                     const float2 xv = ld2(xr[j] + 2 * (cls + NC * i));
@@ -314,22 +314,22 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
                 }
             if (train) {
 #pragma unroll
-                for (int j = 0; j < 3; ++j)
+                for (int j = 0; j < R; ++j)
 #pragma unroll
                     for (int i = 0; i < NPE; ++i) st2(dZy + rs[j] * XS + 2 * (cls + NC * i), zy[j][i]);
                 team_sync<NW>(team);
                 // ---- dzh pieces = (dzy . Wd[l, :]) * lrelu'(zh) for the own latent columns; the ETF index is the outer
                 // loop (a float4 of each dzy row and of each own Wd row per step), two packed partial sums per (row, column)
-                float2 acc[3][2 * NPL];
+                float2 acc[R][2 * NPL];
 #pragma unroll
-                for (int j = 0; j < 3; ++j)
+                for (int j = 0; j < R; ++j)
 #pragma unroll
                     for (int c = 0; c < 2 * NPL; ++c) acc[j][c] = make_float2(0.f, 0.f);
 #pragma unroll (FULL ? EP / 4 : 1)
                 for (int e4 = 0; e4 < EP / 4; ++e4) {
-                    float2 d01[3], d23[3];
+                    float2 d01[R], d23[R];
 #pragma unroll
-                    for (int j = 0; j < 3; ++j) {
+                    for (int j = 0; j < R; ++j) {
                         const float4 v = ld4(dZy + rs[j] * XS + 4 * e4);
                         d01[j] = make_float2(v.x, v.y); d23[j] = make_float2(v.z, v.w);
                     }
@@ -337,7 +337,7 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
                     for (int c = 0; c < 2 * NPL; ++c) {
                         const float4 w = ld4(Wd + (2 * (cls + NC * (c >> 1)) + (c & 1)) * WDS + 4 * e4);
 #pragma unroll
-                        for (int j = 0; j < 3; ++j) {
+                        for (int j = 0; j < R; ++j) {
                             acc[j][c] = __ffma2_rn(d01[j], make_float2(w.x, w.y), acc[j][c]);
                             acc[j][c] = __ffma2_rn(d23[j], make_float2(w.z, w.w), acc[j][c]);
                         }
@@ -347,12 +347,20 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
                 for (int i = 0; i < NPL; ++i)
                     if (cls + NC * i < LP / 2) {
 #pragma unroll
-                        for (int j = 0; j < 3; ++j)
+                        for (int j = 0; j < R; ++j)
                             st2(dZh + rs[j] * HS + 2 * (cls + NC * i),
                                 make_float2(lrelu_grad(zh[j][i].x, acc[j][2 * i].x + acc[j][2 * i].y, alpha),
                                             lrelu_grad(zh[j][i].y, acc[j][2 * i + 1].x + acc[j][2 * i + 1].y, alpha)));
                     }
             }
+        }
+    };
+    auto rows_phase = [&](const int* xoff, int nb, bool train, float coef) -> float {
+        float2 sse2 = make_float2(0.f, 0.f);
+#pragma unroll 1
+        for (int r0 = 0; r0 < nb; r0 += 48) {
+            if (nb - r0 <= 32) rows_pass(std::integral_constant<int, 2>(), xoff, r0, nb, train, coef, sse2);
+            else rows_pass(std::integral_constant<int, 3>(), xoff, r0, nb, train, coef, sse2);
         }
         return sse2.x + sse2.y;
     };
