@@ -206,18 +206,125 @@ def replica_metrics(series, fund, rf):
     return st["sharpe"], st["tracking_error"], st["correlation"]
 
 
-def data_analysis(df, name, rf=None, start=None, end=None, span=None, real_data=False):
-    """The notebook's report table (autoencoder_v4.ipynb:774-849), real_data=False columns, computed on the GPU.
-    real_data=True adds Fama-French alphas and the GRS/HK tests, which the notebook runs through statsmodels and R
-    (rpy2): out of scope here and refused rather than silently dropped."""
-    if real_data:
-        raise NotImplementedError("FF3/FF5 alphas and GRS/HK tests need statsmodels and R; only real_data=False is built")
+# Fama-French factor frames, as the notebook keeps them in globals (autoencoder_v4.ipynb cells "three_factor = ...",
+# "five_factor = ..."): assign them (e.g. from load_ff_factors) before data_analysis(real_data=True), or pass them in.
+three_factor = None
+five_factor = None
+
+
+def load_ff_factors(path, start='1994-04-30', end='2022-04-30'):
+    """The notebook's factor cells: daily Mkt-RF / SMB / HML in per cent -> calendar-month sums -> log(x/100 + 1) ->
+    rows start..end.  Used for both files: the notebook reads the same three columns from the 5-factor file."""
+    f = pd.read_csv(path, usecols=['Date', 'Mkt-RF', 'SMB', 'HML'])
+    f['Date'] = pd.to_datetime(f['Date'], format='%Y%m%d')
+    f = f.set_index('Date')
+    try:
+        f = f.resample('ME').sum()
+    except ValueError:                       # pandas < 2.2 spells month-end 'M'
+        f = f.resample('M').sum()
+    return np.log(f / 100 + 1).loc[start:end, :]
+
+
+def OLS_alpha(ret, X):
+    """Intercept of ret ~ const + X (the notebook's sm.OLS(ret, sm.add_constant(X)).fit().params[0]); values only,
+    like statsmodels (no index alignment)."""
+    y = np.asarray(ret, np.float64).reshape(-1)
+    Z = np.asarray(X, np.float64)
+    Z = Z.reshape(len(y), -1)
+    return float(np.linalg.lstsq(np.column_stack([np.ones(len(y)), Z]), y, rcond=None)[0][0])
+
+
+def grstest(ret_mat, factor_mat):
+    """Gibbons-Ross-Shanken test, restated from the R function of the notebook (cell "grstest<-function").
+    Returns [[F], [p]] like the R matrix (F: N x N for N test assets; the notebook passes one)."""
+    from scipy import stats as _st
+    R = np.asarray(ret_mat, np.float64)
+    R = R.reshape(len(R), -1)
+    Fm = np.asarray(factor_mat, np.float64)
+    Fm = Fm.reshape(len(R), -1)
+    T, N = R.shape
+    K = Fm.shape[1]
+    dat = np.column_stack([np.ones(T), Fm])
+    b = np.linalg.solve(dat.T @ dat, dat.T @ R)              # (K+1, N)
+    e = R - dat @ b
+    sigma = e.T @ e / (T - K - 1)
+    alpha = b[0].reshape(N, 1)
+    mean = Fm.mean(axis=0, keepdims=True)
+    omega = (Fm - mean).T @ (Fm - mean) / (T - 1)
+    tem1 = alpha.T @ np.linalg.solve(sigma, alpha)
+    tem2 = 1 + mean @ np.linalg.solve(omega, mean.T)
+    F = (T / N) * ((T - N - K) / (T - K - 1)) * (tem1 / tem2)
+    return np.vstack([F, _st.f.sf(F, N, T - N - K)])
+
+
+def hktest(rt, rb):
+    """Huberman-Kandel spanning test, restated from the R function of the notebook (cell "hktest <- function",
+    pracma::mldivide / inv / eig, corpcor::pseudoinverse).  Returns [[F], [p]]."""
+    from scipy import stats as _st
+    Rt = np.asarray(rt, np.float64)
+    Rt = Rt.reshape(len(Rt), -1)
+    Rb = np.asarray(rb, np.float64)
+    Rb = Rb.reshape(len(Rt), -1)
+    Tn, N = Rt.shape
+    K = Rb.shape[1]
+    A = np.vstack([np.concatenate([[1.], np.zeros(K)]), np.concatenate([[0.], -np.ones(K)])])
+    Cm = np.vstack([np.zeros((1, N)), -np.ones((1, N))])
+    X = np.column_stack([np.ones(Tn), Rb])
+    B = np.linalg.lstsq(X, Rt, rcond=None)[0]
+    Theta = A @ B - Cm
+    e = Rt - X @ B
+    Sigma = np.atleast_2d(np.cov(e, rowvar=False))
+    H = Theta @ np.linalg.inv(Sigma) @ Theta.T
+    mu1 = Rb.mean(axis=0, keepdims=True)
+    V11i = np.linalg.pinv(np.atleast_2d(np.cov(Rb, rowvar=False)))
+    a1 = (mu1 @ V11i @ mu1.T).item()
+    b1 = float(np.sum(V11i @ mu1.T))
+    c1 = float(np.sum(V11i))
+    G = np.array([[1 + a1, b1], [b1, c1]])
+    lam = np.linalg.eigvals(H @ np.linalg.inv(G))
+    Ui = float(np.real(np.prod(1 + lam)))
+    if N == 1:
+        Ftest = (Tn - K - 1) * (Ui - 1) / 2
+        pval = _st.f.sf(Ftest, 2, Tn - K - 1)
+    else:
+        Ftest = (Tn - K - N) * (np.sqrt(Ui) - 1) / N
+        pval = _st.f.sf(Ftest, 2 * N, 2 * (Tn - N - K))
+    return np.array([[Ftest], [pval]])
+
+
+def data_analysis(df, name, rf=None, start=None, end=None, span=None, real_data=True, three_factor=None, five_factor=None):
+    """The notebook's report table (autoencoder_v4.ipynb:774-849).  The per-series statistics run on the GPU
+    (hfrep_series_metrics); real_data=True adds, as in the notebook, the Fama-French 3- and "5"-factor alphas (the
+    notebook reads the same three columns from both files) and the GRS / HK tests against `span` (or the other columns),
+    restated on the host from the notebook's statsmodels call and R functions.  The factor frames come from the module
+    globals `three_factor` / `five_factor` (the notebook's globals) unless passed in."""
     vals = np.asarray(df, np.float64)
     rfv = np.zeros(len(vals)) if rf is None else np.asarray(rf, np.float64).reshape(-1)
     st = series_statistics(vals, vals, rfv)
-    stats = pd.DataFrame({'Skewness': st["skewness"], 'Kurtosis': st["kurtosis"], 'Omega_ratio(0%)': st["omega0"],
-                          'Omega_ratio(10%)': st["omega10"], 'cVaR(95%)': st["cvar5"], 'CEQ Gamma=2': st["ceq2"],
-                          'CEQ Gamma=5': st["ceq5"], 'CEQ Gamma=10': st["ceq10"], 'Annualized_Sharpe': st["sharpe"]})
+    cols = {'Skewness': st["skewness"], 'Kurtosis': st["kurtosis"], 'Omega_ratio(0%)': st["omega0"],
+            'Omega_ratio(10%)': st["omega10"], 'cVaR(95%)': st["cvar5"], 'CEQ Gamma=2': st["ceq2"],
+            'CEQ Gamma=5': st["ceq5"], 'CEQ Gamma=10': st["ceq10"], 'Annualized_Sharpe': st["sharpe"]}
+    if real_data:
+        g = globals()
+        f3 = three_factor if three_factor is not None else g.get("three_factor")
+        f5 = five_factor if five_factor is not None else g.get("five_factor")
+        if f3 is None or f5 is None:
+            raise ValueError("data_analysis(real_data=True) needs the Fama-French factor frames: set helper.three_factor / "
+                             "helper.five_factor (see load_ff_factors) or pass three_factor= / five_factor=")
+        cut = lambda x: x.loc[start:end, ] if (start and end and hasattr(x, "loc")) else x
+        f3v, f5v = np.asarray(cut(f3), np.float64), np.asarray(cut(f5), np.float64)
+        spanv = None if span is None else np.asarray(cut(span), np.float64)
+        a3, a5, grsf, grsp, hkf, hkp = [], [], [], [], [], []
+        for j in range(vals.shape[1]):
+            a3.append(OLS_alpha(vals[:, j], f3v))
+            a5.append(OLS_alpha(vals[:, j], f5v))
+            bench = spanv if spanv is not None else np.delete(vals, j, axis=1)
+            hk, grs = hktest(vals[:, j], bench), grstest(vals[:, j], bench)
+            hkf.append(hk[0][0]); hkp.append(round(float(hk[1][0]), 6))
+            grsf.append(grs[0][0]); grsp.append(round(float(grs[1][0]), 6))
+        cols.update({'FF3F_alpha': a3, 'FF5F_alpha': a5, 'GRS_testF': grsf, 'HK_testF': hkf, 'GRS_test_pval': grsp,
+                     'HK_test_pval': hkp})
+    stats = pd.DataFrame(cols)
     stats.index = name
     return stats
 

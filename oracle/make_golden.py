@@ -93,6 +93,44 @@ def helper_vectors(helper):
     return out
 
 
+# autoencoder_v4.ipynb, output of cell "hfd_res" (data_analysis(hfd[-144:], ..., span=factor_etf_data, real_data=True,
+# start='2010-05-31', end='2022-04-30')): the columns the notebook computes through statsmodels and R, as printed there
+# (6 decimals), rows in hfd column order.  The reference's own run; typed in because neither statsmodels nor R is here.
+HFD_RES_REAL = {
+    "FF3F_alpha": [0.000785, 0.001608, -0.000468, -0.000521, -0.000613, 0.001002, -0.001443, 0.001154, 0.002767, 0.003339,
+                   -0.000749, 0.000360, 0.002785],
+    "FF5F_alpha": [0.000820, 0.001615, -0.000447, -0.000518, -0.000564, 0.001045, -0.001386, 0.001171, 0.002788, 0.003381,
+                   -0.000700, 0.000386, 0.002814],
+    "GRS_testF": [7.392153, 8.236073, 2.162217, 1.759139, 1.452288, 9.067233, 0.130346, 7.380064, 25.902891, 8.431606,
+                  2.458737, 0.121840, 20.653348],
+    "HK_testF": [9.357224, 7.793611, 1.406071, 9.439554, 2.616191, 11.474257, 0.638452, 6.257770, 24.243047, 9.357745,
+                 2.226949, 0.117562, 19.318581],
+    "GRS_test_pval": [0.007514, 0.004848, 0.144036, 0.187230, 0.230513, 0.003169, 0.718703, 0.007562, 0.000001, 0.004384,
+                      0.119484, 0.727654, 0.000013],
+    "HK_test_pval": [0.000167, 0.000655, 0.249080, 0.000155, 0.077212, 0.000027, 0.529879, 0.002593, 0.000000, 0.000166,
+                     0.112260, 0.889187, 0.000000],
+}
+
+
+def ff_factor_fixture():
+    """The notebook's three_factor / five_factor cells run on the reference's own data files (pandas only), cut to the
+    144 out-of-sample months, plus the printed table above."""
+    out = {}
+    for key, fname in (("three_factor", "F-F_Research_Data_Factors_daily.CSV"),
+                       ("five_factor", "F-F_Research_Data_5_Factors_2x3_daily.CSV")):
+        f = pd.read_csv(os.path.join(refbridge.REFERENCE_ROOT, "data", fname), usecols=['Date', 'Mkt-RF', 'SMB', 'HML'])
+        f['Date'] = pd.to_datetime(f['Date'], format='%Y%m%d')
+        f.set_index('Date', inplace=True)
+        f = f.resample('ME').sum()
+        f = np.log(f / 100 + 1)
+        f = f.loc['1994-04-30':'2022-04-30', :]
+        cut = f.loc['2010-05-31':'2022-04-30', ]
+        out[key] = cut.values
+        out[key + "_dates"] = np.array([str(d.date()) for d in cut.index])
+    out.update({"want_" + k: np.array(v) for k, v in HFD_RES_REAL.items()})
+    return out
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
     ae_mod, helper, keras = refbridge.load()
@@ -118,6 +156,7 @@ def main():
     np.savez_compressed(os.path.join(OUT, "ref_modeR_L8_shuffled.npz"), **res)
     print(f"L=8 shuffled: epochs_run={res['epochs_run']} is_r2={res['is_r2']:.4f}")
     np.savez_compressed(os.path.join(OUT, "ref_helpers.npz"), **helper_vectors(helper))
+    np.savez_compressed(os.path.join(OUT, "ref_ff_factors.npz"), **ff_factor_fixture())
     refbridge.unload()
 
 

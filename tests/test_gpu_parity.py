@@ -152,14 +152,26 @@ def test_known_answer_table(hf, ref_inputs):
     assert np.allclose(sh, expect, atol=5e-7)
     assert np.allclose(co, 1.) and np.allclose(te, 0.)
     import pandas as pd
-    table = hf.helper.data_analysis(pd.DataFrame(hfd, columns=ref_inputs["hfd_columns"]), ref_inputs["hfd_fullname"], rf=rf)
+    table = hf.helper.data_analysis(pd.DataFrame(hfd, columns=ref_inputs["hfd_columns"]), ref_inputs["hfd_fullname"], rf=rf,
+                                    real_data=False)
     hedg = table.iloc[0]
     want = {"Annualized_Sharpe": 0.725028, "Omega_ratio(0%)": 1.908581, "Omega_ratio(10%)": 0.593268, "cVaR(95%)": -0.031864,
             "CEQ Gamma=2": 0.033211, "Skewness": -1.321605, "Kurtosis": 6.283068}
     for k, v in want.items():
         assert abs(hedg[k] - v) < 5e-7, (k, hedg[k], v)
-    with pytest.raises(NotImplementedError):
-        hf.helper.data_analysis(pd.DataFrame(hfd), list(range(13)), rf=rf, real_data=True)
+    with pytest.raises(ValueError):                       # real_data=True (the reference's default) needs the factor frames
+        hf.helper.data_analysis(pd.DataFrame(hfd), list(range(13)), rf=rf)
+    # the notebook's own call: dated frames, start / end, span = the 22 ETFs; all 15 columns of the printed table
+    ff = load_golden("ref_ff_factors")
+    idx = pd.to_datetime(ref_inputs["dates"])
+    frame = lambda a, cols=None: pd.DataFrame(a, index=idx[-len(a):], columns=cols)
+    full = hf.helper.data_analysis(frame(hfd, ref_inputs["hfd_columns"]), ref_inputs["hfd_fullname"], rf=rf,
+                                   span=frame(ref_inputs["etf"]), real_data=True, start='2010-05-31', end='2022-04-30',
+                                   three_factor=frame(ff["three_factor"]), five_factor=frame(ff["five_factor"]))
+    assert list(full.columns[-6:]) == ['FF3F_alpha', 'FF5F_alpha', 'GRS_testF', 'HK_testF', 'GRS_test_pval', 'HK_test_pval']
+    for col in full.columns[-6:]:
+        assert np.max(np.abs(full[col].values - ff["want_" + col])) < 1e-6, col
+    assert abs(full["Annualized_Sharpe"].iloc[12] - 1.204837) < 5e-7
 
 
 @pytest.mark.parametrize("E,L,T,batch", [(22, 5, 168, 48), (10, 3, 64, 16), (24, 24, 100, 32), (22, 1, 57, 48),

@@ -159,3 +159,24 @@ def test_dropin_modules_resolve_to_the_package():
     assert out.returncode == 0, out.stderr
     assert "(self, rf, hfd, window=24)" in out.stdout and "(self, patience=5, verbose=2, plot=True)" in out.stdout
     assert "(old_x, new_x, covMatrix, param=0.05, phi=0.5)" in out.stdout
+
+
+
+def test_ff_alpha_grs_hk_match_the_notebooks_printed_table(ref_inputs):
+    """FF3/FF5 alphas, GRS and HK tests (restated from the notebook's statsmodels call and R functions) against the
+    values the reference printed for the 13 real indices (autoencoder_v4.ipynb, cell `hfd_res`): host code, no GPU."""
+    import hfrep
+    ff = load_golden("ref_ff_factors")
+    hfd, etf = ref_inputs["hfd"][-144:], ref_inputs["etf"][-144:]
+    h = hfrep.helper
+    got = {"FF3F_alpha": [h.OLS_alpha(hfd[:, j], ff["three_factor"]) for j in range(13)],
+           "FF5F_alpha": [h.OLS_alpha(hfd[:, j], ff["five_factor"]) for j in range(13)],
+           "GRS_testF": [h.grstest(hfd[:, j], etf)[0][0] for j in range(13)],
+           "GRS_test_pval": [h.grstest(hfd[:, j], etf)[1][0] for j in range(13)],
+           "HK_testF": [h.hktest(hfd[:, j], etf)[0][0] for j in range(13)],
+           "HK_test_pval": [h.hktest(hfd[:, j], etf)[1][0] for j in range(13)]}
+    for k, v in got.items():
+        assert np.max(np.abs(np.asarray(v, float).reshape(-1) - ff["want_" + k])) < 1e-6, k
+    # several test assets at once (the R functions' general case): finite, p in [0, 1]
+    hk, grs = h.hktest(hfd[:, :3], etf), h.grstest(hfd[:, :3], etf)
+    assert hk.shape == (2, 1) and 0 <= hk[1][0] <= 1 and np.isfinite(grs).all()
