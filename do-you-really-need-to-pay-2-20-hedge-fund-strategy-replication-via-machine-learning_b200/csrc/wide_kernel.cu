@@ -248,9 +248,11 @@ __global__ void __launch_bounds__(512 / EPT) fit_wide2_kernel(const WideFitParam
 #pragma unroll
         for (int k = 0; k < EPT; ++k) x[k] = (r < nb && e0 + k < E) ? __ldg(xr + k) : 0.f;
     };
-    auto cross_warp = [&](int o) -> float {                      // sum of the warps' sums for output o
+    auto cross_warp = [&](int o) -> float {                      // sum of the warps' sums for output o, in warp order
         float sacc = 0.f;
-        for (int w = 0; w < NWARP; ++w) sacc += part[(size_t)w * BP * LP + o];
+#pragma unroll
+        for (int w = 0; w < 16 / EPT; ++w)                        // (independent loads: unrolled over the most warps a CTA has)
+            if (w < NWARP) sacc += part[(size_t)w * BP * LP + o];
         return sacc;
     };
     const float4* sched = p.sched;
@@ -366,7 +368,6 @@ __global__ void __launch_bounds__(512 / EPT) fit_wide2_kernel(const WideFitParam
             for (int k = 0; k < EPT; ++k) {
                 upd(Wd[j][k].x, gWd[j][k].x, EPT * LP + (2 * j) * EPT + k, sc);
                 upd(Wd[j][k].y, gWd[j][k].y, EPT * LP + (2 * j + 1) * EPT + k, sc);
-                if (k == EPT - 1) asm volatile("" ::: "memory");    // keep the m, v loads of later slots from piling up in registers
             }
         __syncthreads();
         for (int o = tid; o < nb * LP; o += NT) dZh[o] = lrelu_grad(H[o], cross_warp(o), alpha);   // sign(h) == sign(zh)
@@ -398,7 +399,6 @@ __global__ void __launch_bounds__(512 / EPT) fit_wide2_kernel(const WideFitParam
             for (int j = 0; j < LH; ++j) {
                 upd(We[k][j].x, gWe[k][j].x, k * LP + 2 * j, sc);
                 upd(We[k][j].y, gWe[k][j].y, k * LP + 2 * j + 1, sc);
-                if (j == LH - 1) asm volatile("" ::: "memory");
             }
         ++step;
         return sse;
