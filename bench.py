@@ -36,7 +36,7 @@ LATENTS = list(range(1, 22))
 EPOCHS = 1000
 # dram__bytes_read.sum + dram__bytes_write.sum per fit_kernel launch of the cfg2 sweep, from the committed
 # `ncu --set full` capture (profiles/r1_ncu_full_cfg2_summary.txt): the kernel is shared-memory resident.
-NCU_DRAM_BYTES_PER_FIT_LAUNCH = 68e3
+NCU_DRAM_BYTES_PER_FIT_LAUNCH = 80e3
 
 
 def synthetic_returns(seed=20240611):
