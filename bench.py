@@ -158,17 +158,24 @@ class ClockSampler:
 
     def _read(self):
         for line in self.proc.stdout:
-            self.rows.append([c.strip() for c in line.split(",")])
+            self.rows.append((time.perf_counter(), [c.strip() for c in line.split(",")]))
 
-    def stop(self):
+    def stop(self, t_from=None):
+        """Samples taken since t_from (the start of the timed region).  nvidia-smi needs a few hundred ms to start, so
+        the sampler is started before the warm-up steps; if a short timed region caught no sample, the samples of the
+        warm-up (the same steps, the same load) are reported and `window` says so."""
         if self.proc:
             self.proc.terminate()
-        sm = [float(r[0]) for r in self.rows if len(r) >= 6 and r[0].replace(".", "").isdigit()]
-        mx = [float(r[1]) for r in self.rows if len(r) >= 6 and r[1].replace(".", "").isdigit()]
+        rows = [r for t, r in self.rows if t_from is None or t >= t_from]
+        window = "timed region"
+        if not rows:
+            rows, window = [r for _, r in self.rows], "warm-up + timed region (the timed region was shorter than one sampling period)"
+        sm = [float(r[0]) for r in rows if len(r) >= 6 and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in rows if len(r) >= 6 and r[1].replace(".", "").isdigit()]
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        reasons = sorted({n for r in self.rows if len(r) >= 6 for n, v in zip(names, r[2:6]) if v.lower() == "active"})
+        reasons = sorted({n for r in rows if len(r) >= 6 for n, v in zip(names, r[2:6]) if v.lower() == "active"})
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": reasons, "samples": len(sm)}
+                "reasons": reasons, "samples": len(sm), "window": window}
 
 
 # --------------------------------------------------------------------------------------- GPU arm
@@ -221,19 +228,24 @@ def gpu_arm(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    # ---- warm-up
+    # ---- warm-up (the clock sampler starts here: see ClockSampler.stop)
+    sampler = ClockSampler(local)
+    sampler.start()
     for _ in range(max(args.warmup, 3)):
         resident_step()
         flush.fill_(1)
+    t_wait = time.perf_counter()
+    while len(sampler.rows) < 2 and sampler.proc is not None and time.perf_counter() - t_wait < 5.:
+        resident_step()                      # more (untimed) warm-up until the sampler has seen the GPU under this load
+        flush.fill_(1)
+        torch.cuda.synchronize()
     e2e_step()
     barrier()
 
     # ---- timed: K steps, device time per step from CUDA events (L2 flushed between steps, flush not timed)
-    sampler = ClockSampler(local)
-    sampler.start()
     evs = [[torch.cuda.Event(enable_timing=True) for _ in range(3)] for _ in range(args.steps)]
     barrier()
-    t_wall = time.perf_counter()
+    t_wall = t_timed = time.perf_counter()
     last = None
     for k in range(args.steps):
         last = resident_step(evs[k])
@@ -265,7 +277,7 @@ def gpu_arm(args):
         h2d, d2h = e2e_step()
     barrier()
     e2e_s = time.perf_counter() - t0
-    clocks = sampler.stop()
+    clocks = sampler.stop(t_timed)
 
     # ---- max over ranks
     tt = torch.tensor([total_ms, e2e_s * 1e3, float(np.mean(fit_ms))], dtype=torch.float64, device=dev)
