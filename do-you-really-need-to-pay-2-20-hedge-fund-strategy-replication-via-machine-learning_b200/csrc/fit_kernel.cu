@@ -226,7 +226,7 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
     // the ETF block (class = 2*warp + lane&1, NC = 2*NW): one LDS.64 (two-address pattern, 1 cycle) feeds 3 FFMA2,
     // row loads are pair-shared LDS.128 (2 cycles).  Every warp walks all rows, so h and dzy rows cross warps:
     // two team barriers per pass (a __syncwarp for one-warp teams).
-    // Pieces past the block (LP/2 not a multiple of NC) are skipped: the warps that own them idle there.
+    // Pieces past the block (LP/2 not a multiple of NC) are computed on whatever follows in shared memory and dropped.
     auto rows_pass = [&](auto RC, const int* xoff, int r0, int nb, bool train, float coef, float2& sse2) {
         constexpr int R = decltype(RC)::value;      // rows per lane in this pass: 3, or 2 when rows g+32 are all past the batch
         constexpr int NC = 2 * NW;
@@ -265,9 +265,6 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
                 for (int k = 0; k < 4; ++k)
 #pragma unroll
                     for (int i = 0; i < NPL; ++i) {
-                        // a piece past the latent block: the same for both lanes of a pair and all pairs of the warp
-                        // (LP/2 and NC are even), so the skip is a warp-uniform branch
-                        if ((LP / 2) % NC != 0 && i == NPL - 1 && cls + NC * i >= LP / 2) continue;
                         const float2 w = ld2(Wl + (4 * e4 + k) * LP + 2 * NC * i);
 #pragma unroll
                         for (int j = 0; j < R; ++j) zh[j][i] = __ffma2_rn(make_float2(xe[j][k], xe[j][k]), w, zh[j][i]);
@@ -338,7 +335,6 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
                     }
 #pragma unroll
                     for (int c = 0; c < 2 * NPL; ++c) {
-                        if ((LP / 2) % NC != 0 && (c >> 1) == NPL - 1 && cls + NC * (c >> 1) >= LP / 2) continue;
                         const float4 w = ld4(Wd + (2 * (cls + NC * (c >> 1)) + (c & 1)) * WDS + 4 * e4);
 #pragma unroll
                         for (int j = 0; j < R; ++j) {
@@ -392,7 +388,7 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
             float2 acc[4][2];
 #pragma unroll
             for (int i = 0; i < 4; ++i) acc[i][0] = acc[i][1] = make_float2(0.f, 0.f);
-#pragma unroll 4
+#pragma unroll 8
             for (int q = kq; q < nb; q += KS) {
                 const int ao = dec ? q * HS : (XT ? q * XS : xoff[q]);
                 const float4 a = ld4(Xs + a0 + ao);
