@@ -253,7 +253,7 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
             for (int j = 0; j < R; ++j)
 #pragma unroll
                 for (int i = 0; i < NPL; ++i) zh[j][i] = make_float2(0.f, 0.f);
-#pragma unroll (FULL ? EP / 4 : 1)
+#pragma unroll (FULL ? EP / 4 : 2)
             for (int e4 = 0; e4 < EP / 4; ++e4) {
                 float xe[R][4];
 #pragma unroll
@@ -284,7 +284,7 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
             for (int j = 0; j < R; ++j)
 #pragma unroll
                 for (int i = 0; i < NPE; ++i) zy[j][i] = make_float2(0.f, 0.f);
-#pragma unroll (FULL ? CT : 1)
+#pragma unroll (FULL ? CT : 2)
             for (int l4 = 0; l4 < CT; ++l4) {
                 float hl[R][4];
 #pragma unroll
@@ -325,7 +325,7 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
                 for (int j = 0; j < R; ++j)
 #pragma unroll
                     for (int c = 0; c < 2 * NPL; ++c) acc[j][c] = make_float2(0.f, 0.f);
-#pragma unroll (FULL ? EP / 4 : 1)
+#pragma unroll (FULL ? EP / 4 : 2)
                 for (int e4 = 0; e4 < EP / 4; ++e4) {
                     float2 d01[R], d23[R];
 #pragma unroll
