@@ -197,10 +197,12 @@ int hfrep_forward(const float* W, int E, int L, const float* x, int n, int encod
 
 /* ---------------------------------------------------------------------------------------
  * Wide variant (BASELINE configs[3]: 500 ETFs x 10 000 funds, rolling refit) of kernels (b) and (c): same arithmetic for
- * shapes whose per-task state does not fit shared memory.  Round 1: correct first (plain FP32 FFMA, L1/L2-served operands),
- * one CTA per task; weights and Nadam state live in the caller's workspace.
+ * shapes whose per-task state does not fit shared memory, one CTA per task.  E <= 512 and L <= 32 run a register-resident
+ * kernel (ETF columns dealt to threads, weights in registers, Nadam state in the workspace); other shapes a general kernel
+ * with weights and Nadam state in the workspace.
  *   hfrep_fit_wide: X f32 [n_x][T][E] scaled blocks (e.g. the workspace of hfrep_window_gather with minmax=1), every task
- *   the same latent width L <= 64; W0 / W_out f32 [n_tasks][2*E*L] (We then Wd); ws f32, 6*E*L floats per task;
+ *   the same latent width L <= 64; W0 / W_out f32 [n_tasks][2*E*L] (We then Wd); ws f32, hfrep_fit_wide_workspace bytes
+ *   (at least 6*E*L floats per task);
  *   cfg supplies E (<= 4096), T, n_fit, batch, epochs, patience, Nadam constants, n_x.
  *   hfrep_predict_wide: task i evaluates rows [task_row0[i], +window+2) of the full histories etf f64 [T][E], hfd f64 [T][F],
  *   rf f64 [T]: latent factors of those rows (float32), OLS of every fund on the first `window` rows (float64 QR; for
