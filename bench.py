@@ -194,7 +194,10 @@ def gpu_arm(args):
         dist.init_process_group("nccl", device_id=dev)
 
     etf, hfd, rf = synthetic_returns()
-    seeds = [123 + rank * args.seeds + s for s in range(args.seeds)]
+    # Weak scaling needs the same work on every GPU.  Early stopping makes a sweep's length depend on its seeds (measured:
+    # 7.1 to 8.8 ms per 21-fit sweep over four seeds), so every rank runs the sweep of the SAME seeds; the ranks' results are
+    # still separate task executions (the job's aggregate counts n_gpus x fits_per_step_per_gpu fits per step).
+    seeds = [123 + s for s in range(args.seeds)]
     data = hfrep.ReplicationData(etf, hfd, rf, window=WINDOW, device=dev)
     tasks = sorted(((L, s) for s in seeds for L in LATENTS), key=lambda t: -((t[0] + 3) // 4))   # widest first
     n_tasks = len(tasks)
@@ -281,7 +284,13 @@ def gpu_arm(args):
 
     # ---- max over ranks
     tt = torch.tensor([total_ms, e2e_s * 1e3, float(np.mean(fit_ms))], dtype=torch.float64, device=dev)
+    per_rank = None
     if world > 1:
+        # per-rank step time and SM clock (diagnostic: which rank the max comes from, and whether its clock differs)
+        mine = torch.tensor([total_ms / args.steps, clocks["sm_mhz"] or -1.], dtype=torch.float64, device=dev)
+        allr = [torch.zeros_like(mine) for _ in range(world)]
+        dist.all_gather(allr, mine)
+        per_rank = {"ms_per_step": [round(float(t[0]), 4) for t in allr], "sm_mhz": [float(t[1]) for t in allr]}
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
     total_ms, e2e_ms, fit_ms_mean = (float(v) for v in tt.cpu())
     value = world * n_tasks * args.steps / (total_ms * 1e-3)
@@ -384,8 +393,10 @@ def gpu_arm(args):
         "config": {"workload": f"cfg2: 13 indices x 145 windows x L=1..21 x {args.seeds} seed(s) per GPU (Mode R), synthetic 337x(22+13+1)",
                    "fits_per_step_per_gpu": n_tasks, "triples_per_step_per_gpu": n_tasks * F * 145,
                    "epochs": EPOCHS, "epochs_run_mean": float(epochs_run.mean()), "shuffle": False,
+                   "seeds_per_rank": "the same on every rank (fixed work per GPU; run lengths under early stopping depend on the seed)",
                    "l2": "flushed between steps (256 MiB write, not timed); inputs are KB-sized and smem-resident"},
         "clocks": clocks,
+        "per_rank": per_rank,
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                 "ms_per_step": e2e_ms / args.steps},
         "gpu_launches": args.steps * 2 * n_buckets,      # fit_kernel + eval_kernel per width bucket
