@@ -15,6 +15,7 @@ LIB_PATH = os.path.join(_HERE, "libhfrep.so")
 MAX_E, MAX_L, MAX_F = 24, 24, 32
 STATIC_SCRATCH_BYTES = 4 << 20     # HFREP_STATIC_SCRATCH_BYTES
 N_STATS = 11                       # HFREP_N_STATS
+SCHED_STRIDE = 8                   # HFREP_SCHED_STRIDE
 STAT_NAMES = ("sharpe", "tracking_error", "correlation", "omega0", "omega10", "cvar5", "ceq2", "ceq5", "ceq10",
               "skewness", "kurtosis")
 
@@ -40,7 +41,7 @@ class EvalCfg(C.Structure):
                 ("alpha", C.c_float), ("cost_param", C.c_double), ("phi", C.c_double)]
 
 
-EXPORTS = ("hfrep_last_error", "hfrep_version", "hfrep_window_index", "hfrep_window_gather",
+EXPORTS = ("hfrep_last_error", "hfrep_version", "hfrep_window_index", "hfrep_window_gather", "hfrep_window_gather_f64",
            "hfrep_rolling_sigma", "hfrep_fit_cfg_default", "hfrep_nadam_schedule", "hfrep_fit_batched", "hfrep_fit_windows_workspace", "hfrep_fit_windows", "hfrep_fit_windows_static", "hfrep_fit_wide_workspace", "hfrep_fit_wide", "hfrep_predict_wide",
            "hfrep_eval_cfg_default", "hfrep_predict_metrics", "hfrep_series_metrics", "hfrep_ex_post_return", "hfrep_forward",
            "hfrep_ffma_peak")
@@ -59,6 +60,7 @@ def _load():
     lib.hfrep_version.restype = C.c_int
     lib.hfrep_window_index.argtypes = [C.c_int, C.c_int, C.c_int, vp, vp, C.c_int]
     lib.hfrep_window_gather.argtypes = [vp, C.c_int, C.c_int, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, vp, vp]
+    lib.hfrep_window_gather_f64.argtypes = lib.hfrep_window_gather.argtypes
     lib.hfrep_rolling_sigma.argtypes = [vp, C.c_int, C.c_int, vp, C.c_int, C.c_int, vp, vp]
     lib.hfrep_fit_cfg_default.argtypes = [C.POINTER(FitCfg)]
     lib.hfrep_fit_cfg_default.restype = None

@@ -1,10 +1,17 @@
 #!/bin/sh
 # Build libhfrep.so in-tree for sm_100a (B200).  Usage: sh build.sh [extra nvcc flags]
+# fit_kernel.cu is compiled with -fmad=false: its sums follow the canonical order, the only fused
+# operations are the explicit fma intrinsics.  (Same recipe as __graft_entry__.build().)
 set -e
 here="$(cd "$(dirname "$0")" && pwd)"
 out="$here/../libhfrep.so"
-nvcc -std=c++17 -O3 -gencode arch=compute_100a,code=sm_100a -lineinfo \
-     -Xcompiler -fPIC -shared "$@" \
-     "$here/common.cu" "$here/fit_kernel.cu" "$here/eval_kernel.cu" "$here/gather_kernel.cu" "$here/wide_kernel.cu" \
-     -o "$out"
+mkdir -p "$here/build"
+flags="-std=c++17 -O3 -gencode arch=compute_100a,code=sm_100a -lineinfo -Xcompiler -fPIC"
+for f in common fit_kernel eval_kernel gather_kernel wide_kernel; do
+    extra=""
+    [ "$f" = fit_kernel ] && extra="-fmad=false"
+    nvcc $flags $extra "$@" -c "$here/$f.cu" -o "$here/build/$f.o" &
+done
+wait
+nvcc -shared -gencode arch=compute_100a,code=sm_100a "$here"/build/*.o -o "$out"
 echo "built $out"

@@ -1,6 +1,8 @@
 // Error plumbing, device queries and the window index tables of libhfrep.
 #include "common.cuh"
 
+#include <atomic>
+
 namespace hfrep {
 
 char* err_buf() {
@@ -17,21 +19,21 @@ int set_err(int code, const char* fmt, ...) {
 }
 
 int sm_count() {
-    static int cached[64] = {0};
+    static std::atomic<int> cached[64];
     int dev = 0;
     if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
-    if (cached[dev] == 0) {
-        int n = 0;
+    int n = cached[dev].load(std::memory_order_relaxed);
+    if (n == 0) {
         if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
-        cached[dev] = n;
+        cached[dev].store(n, std::memory_order_relaxed);
     }
-    return cached[dev];
+    return n;
 }
 
 }  // namespace hfrep
 
 extern "C" const char* hfrep_last_error(void) { return hfrep::err_buf(); }
-extern "C" int hfrep_version(void) { return 100; }
+extern "C" int hfrep_version(void) { return 200; }
 
 // Window bookkeeping of the reference, bit-exact.
 extern "C" int hfrep_window_index(int kind, int T, int window, int32_t* starts, int32_t* lens, int cap) {

@@ -209,7 +209,8 @@ __global__ void __launch_bounds__(NTH_EVAL, 2) eval_kernel(const EvalParams p) {
     const double* rfv = p.rf + row0;
 
     // ---- shared memory carve-up (doubles first)
-    // OLS workspaces: nq blocks of wsz doubles = [A (window x acols) | beta (MAX_L x F) | G (F x E) | norm (F) | vhh (window)]
+    // OLS workspaces: nq blocks of wsz doubles = [A (window x acols) | beta (MAX_L x F) | G (F x E) | norm (F) | vhh (window) |
+    //                                             scratch of the rank-deficient path (MAX_L x MAX_L + 3 MAX_L)]
     double* wsp = reinterpret_cast<double*>(smem_raw);
     double* betaS = wsp + (size_t)window * p.acols;               // workspace 0: beta_0, G_0, norm_0 (the reference's choice)
     double* G = betaS + HFREP_MAX_L * F;
@@ -351,14 +352,119 @@ __global__ void __launch_bounds__(NTH_EVAL, 2) eval_kernel(const EvalParams p) {
             }
             __syncwarp();
         }
-        if (!(dmin > 1e-13 * dmax)) { if (lane == 0) s_status = 2; }
-        // back substitution, lane = fund
-        for (int f = lane; f < F; f += 32) {
-            for (int l = L - 1; l >= 0; --l) {
-                double acc = A[l * p.acols + L + f];
-                for (int j = l + 1; j < L; ++j) acc -= A[l * p.acols + j] * beta[j * F + f];
-                beta[l * F + f] = acc / A[l * p.acols + l];
+        const bool deficient = !(dmin > 1e-13 * dmax);
+        if (!deficient) {
+            // back substitution, lane = fund
+            for (int f = lane; f < F; f += 32)
+                for (int l = L - 1; l >= 0; --l) {
+                    double acc = A[l * p.acols + L + f];
+                    for (int j = l + 1; j < L; ++j) acc -= A[l * p.acols + j] * beta[j * F + f];
+                    beta[l * F + f] = acc / A[l * p.acols + l];
+                }
+        } else {
+            // Rank-deficient latent block (a dead or duplicated latent unit): OLS(Y, X).fit() (:151) is pinv(X) Y, the
+            // MINIMUM-NORM least-squares solution.  Complete orthogonal decomposition, as LAPACK's xGELSY does it:
+            // column-pivoted Householder QR  M P = Q [T; 0]  with T = [R11 R12] of rank r rows, then the QR of T^T
+            // (L x r) = Z [S; 0], so that  beta = P Z [S^-T (Q^T y)_1..r ; 0].  status = 2 reports that this path ran.
+            if (lane == 0) s_status = 2;
+            double* S2 = normW + F + window;              // [L][MAX_L]: T^T, then Householder vectors below S's diagonal
+            double* d2 = S2 + HFREP_MAX_L * HFREP_MAX_L;  // [L] diagonal of S
+            double* t2 = d2 + HFREP_MAX_L;                // [L] 2 / v^T v
+            int* perm = reinterpret_cast<int*>(t2 + HFREP_MAX_L);   // [L] column order
+            __syncwarp();
+            for (int idx = lane; idx < window * ncol; idx += 32) {
+                const int r = idx / ncol, c = idx - r * ncol;
+                A[r * p.acols + c] = c < L ? (double)Mw[r * WS + c] : Yw[(size_t)r * F + (c - L)];
             }
+            if (lane < L) perm[lane] = lane;
+            __syncwarp();
+            int rank = 0;
+            double n0 = 0.;
+            for (int k = 0; k < L; ++k) {
+                // pivot: the remaining column with the largest norm below row k (every lane computes the same choice)
+                int best = k;
+                double bsq = -1.;
+                for (int c = k; c < L; ++c) {
+                    double sq = 0.;
+                    for (int r = k; r < window; ++r) { const double a = A[r * p.acols + c]; sq += a * a; }
+                    if (sq > bsq) { bsq = sq; best = c; }
+                }
+                const double nrm = sqrt(bsq);
+                if (k == 0) n0 = nrm;
+                if (!(nrm > 1e-13 * n0)) break;           // what is left is numerically zero: rank = k
+                __syncwarp();
+                if (best != k) {
+                    for (int r = lane; r < window; r += 32) {
+                        const double t = A[r * p.acols + k]; A[r * p.acols + k] = A[r * p.acols + best]; A[r * p.acols + best] = t;
+                    }
+                    if (lane == 0) { const int t = perm[k]; perm[k] = perm[best]; perm[best] = t; }
+                }
+                __syncwarp();
+                const double akk = A[k * p.acols + k];
+                const double alph = akk > 0. ? -nrm : nrm;
+                const double vtv = bsq - 2. * akk * alph + alph * alph;
+                __syncwarp();
+                for (int r = k + lane; r < window; r += 32) vhh[r] = A[r * p.acols + k] - (r == k ? alph : 0.);
+                __syncwarp();
+                const double bh = 2. / vtv;
+                for (int c = k + 1 + lane; c < ncol; c += 32) {
+                    double wj = 0.;
+                    for (int r = k; r < window; ++r) wj += vhh[r] * A[r * p.acols + c];
+                    wj *= bh;
+                    for (int r = k; r < window; ++r) A[r * p.acols + c] -= vhh[r] * wj;
+                }
+                __syncwarp();
+                if (lane == 0) {
+                    A[k * p.acols + k] = alph;
+                    for (int r = k + 1; r < window; ++r) A[r * p.acols + k] = 0.;
+                }
+                __syncwarp();
+                rank = k + 1;
+            }
+            // T^T (L x rank) and its Householder QR
+            for (int idx = lane; idx < L * rank; idx += 32) {
+                const int i = idx / rank, j = idx - i * rank;               // S2[i][j] = T[j][i] (zero below T's diagonal)
+                S2[i * HFREP_MAX_L + j] = i >= j ? A[j * p.acols + i] : 0.;
+            }
+            __syncwarp();
+            for (int k = 0; k < rank; ++k) {
+                double sq = 0.;
+                for (int i = k; i < L; ++i) { const double a = S2[i * HFREP_MAX_L + k]; sq += a * a; }
+                const double akk = S2[k * HFREP_MAX_L + k];
+                const double nrm = sqrt(sq);
+                const double alph = akk > 0. ? -nrm : nrm;
+                const double vtv = sq - 2. * akk * alph + alph * alph;
+                const double bh = vtv > 0. ? 2. / vtv : 0.;
+                __syncwarp();
+                if (lane == 0) { S2[k * HFREP_MAX_L + k] = akk - alph; d2[k] = alph; t2[k] = bh; }   // v = x - alph e1, in place
+                __syncwarp();
+                for (int c = k + 1 + lane; c < rank; c += 32) {
+                    double wj = 0.;
+                    for (int i = k; i < L; ++i) wj += S2[i * HFREP_MAX_L + k] * S2[i * HFREP_MAX_L + c];
+                    wj *= bh;
+                    for (int i = k; i < L; ++i) S2[i * HFREP_MAX_L + c] -= S2[i * HFREP_MAX_L + k] * wj;
+                }
+                __syncwarp();
+            }
+            for (int f = lane; f < F; f += 32) {
+                double z[HFREP_MAX_L];
+                for (int i = 0; i < rank; ++i) {                            // S^T u = (Q^T y)_1..r : forward substitution
+                    double acc = A[i * p.acols + L + f];
+                    for (int j = 0; j < i; ++j) acc -= S2[j * HFREP_MAX_L + i] * z[j];
+                    z[i] = acc / d2[i];
+                }
+                for (int i = rank; i < L; ++i) z[i] = 0.;
+                for (int k = rank - 1; k >= 0; --k) {                       // beta' = H_0 .. H_{r-1} [u; 0]
+                    double wj = 0.;
+                    for (int i = k; i < L; ++i) wj += S2[i * HFREP_MAX_L + k] * z[i];
+                    wj *= t2[k];
+                    for (int i = k; i < L; ++i) z[i] -= S2[i * HFREP_MAX_L + k] * wj;
+                }
+                for (int i = 0; i < L; ++i) beta[perm[i] * F + f] = z[i];   // undo the column order
+            }
+        }
+        __syncwarp();
+        for (int f = lane; f < F; f += 32) {
             // helper.normalization: sd(Y)/sd(M beta), ddof = 1
             double my = 0., mr = 0.;
             for (int r = 0; r < window; ++r) {
@@ -541,7 +647,9 @@ extern "C" int hfrep_predict_metrics(const hfrep_eval_cfg* c, const double* Xtr,
 
     p.rolling = c->beta_rolling ? 1 : 0;
     p.nq = p.rolling ? 4 : 1;
-    p.wsz = (int)((size_t)c->window * p.acols + HFREP_MAX_L * c->F + (size_t)c->F * c->E + c->F + c->window);
+    // ... + the scratch of the rank-deficient path (T^T, its Householder scalars, the column order)
+    p.wsz = (int)((size_t)c->window * p.acols + HFREP_MAX_L * c->F + (size_t)c->F * c->E + c->F + c->window +
+                  HFREP_MAX_L * HFREP_MAX_L + 3 * HFREP_MAX_L);
     p.wsz = (p.wsz + 1) & ~1;                // keeps what follows 16-byte aligned (float4 prediction buffers)
     p.series_dbl = (int)(3 * (size_t)p.n_oos * c->F);
     if (p.series_dbl < (NTH_EVAL / 32) * 32 * WS / 2) p.series_dbl = (NTH_EVAL / 32) * 32 * WS / 2;
@@ -553,7 +661,7 @@ extern "C" int hfrep_predict_metrics(const hfrep_eval_cfg* c, const double* Xtr,
     const size_t smem = dbl * 8 + flt * 4 + (size_t)p.n_oos * c->E + 16;
     HFREP_REQUIRE(smem <= 227 * 1024, "predict_metrics: %zu bytes of shared memory needed (T_test=%d too long)", smem,
                   c->T_test);
-    HFREP_CUDA_OK(cudaFuncSetAttribute(eval_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    HFREP_CUDA_OK(cudaFuncSetAttribute(eval_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024)));
     // few tasks: spread each task's 167 expanding-prefix evaluations over several CTAs so the whole GPU works
     p.qsplit = 1;
     if (quality && c->want_oos) {

@@ -13,8 +13,18 @@
 //   grads   dWd = H^T dZy and dWe = X_b^T dZh as 4x4 register tiles (outer products, 2 LDS.128 per 8 FFMA2), one
 //           lane per tile; the tiles form groups of <= 32 and the batch rows are split over the warps of a group
 //           (split-K); partial tiles go to shared memory in tile-major order.
-//   update  over the 12*LP slot quads (four consecutive columns of a weight row): sum the KS partials in fixed
+//   update  over the 12*LP slot quads (four consecutive columns of a weight row): sum the partials in the canonical
 //           order, Nadam (m, v in registers; shared memory for one-warp teams), write the weights back.
+// CANONICAL SUMMATION ORDER (oracle/fitcore.py and oracle/c/fit_oracle.c follow the same one): every sum
+// that feeds the weights has one fixed order in every mapping, so a run's weight trajectory is bit-identical across the
+// mappings and to the CPU oracle — a LeakyReLU pre-activation within rounding of zero would otherwise send two correct
+// float32 implementations down different branches (3e-5 jumps in the loss history).
+//   zh[r][l]  fused chain over e = 0..E-1;  zy[r][e]  fused chain over l = 0..L-1   (padding adds exact zeros)
+//   dzy = lrelu'(zy) * (coef * (y - x)), coef = 2 / (rows * E) rounded once
+//   dh[r][l] = S_even + S_odd, fused chains over the even / the odd ETFs, ascending
+//   dWd, dWe = (p0 + p2 + p4) + (p1 + p3 + p5), p_c = fused chain over the batch positions q = c, c+6, c+12, ...
+//   Nadam in Keras' operation order, IEEE division and square root, every operation rounded on its own.
+// This file is compiled with -fmad=false: the only fused operations are the explicit fma intrinsics.
 // Shared memory (floats, rows 16-byte aligned).  Per CTA: Xs [(T+1)][28] (shared by the CTA's teams when all
 // tasks train on the same block; cols >= E zero, row T zero), woff [12*LP] (tile-major slot quad -> weight offset).
 // Per team: We [24][LP], Wd [LP][28], H [BP+1][HS], dZh [BP+1][HS], dZy [BP+1][28] (row BP = scratch row for
@@ -25,6 +35,7 @@
 #include "common.cuh"
 
 #include <algorithm>
+#include <atomic>
 #include <cmath>
 #include <cstdlib>
 #include <type_traits>
@@ -69,13 +80,18 @@ struct Lay {
     static constexpr int TG = (NT5 + 31) / 32;
     __host__ __device__ static constexpr bool grouped(int NW) { return TG > 1 && NW % TG == 0; }
     __host__ __device__ static constexpr int ks(int NW) { return grouped(NW) ? NW / TG : NW; }
+    // The batch positions form six classes (q mod 6, one fused chain each: the canonical order); a warp takes the
+    // classes kq, kq+KS, ...  KS is 1, 2, 3 or 6 for the team sizes 1, 2, 3, 6.  Partial sums kept per weight slot in
+    // shared memory: the canonical combination (p0+p2+p4)+(p1+p3+p5) is formed by the warp itself when it owns a whole
+    // parity (KS = 1: the total; KS = 2: one parity each), else all six class sums are stored.
+    __host__ __device__ static constexpr int npart(int NW) { return ks(NW) >= 3 ? 6 : ks(NW); }
     // Nadam's m, v: registers when the team has >= 2 warps (at most 5 slot quads per lane), else shared memory
     __host__ __device__ static constexpr bool mv_in_regs(int NW) { return NW >= 2; }
     // XT (batch-tile mode): the training block stays in global memory / L2 and only the current mini-batch's rows
     // sit in a per-team tile [BP+1][XS], refilled with cp.async; else the whole block is resident once per CTA.
     __host__ __device__ static size_t team_floats(int BP, int NW, bool XT, int PS, int T) {
         return (size_t)EP * LP + (size_t)LP * WDS + (size_t)(BP + 1) * HS * 2 + (size_t)(BP + 1) * XS +
-               (size_t)ks(NW) * NEL + (mv_in_regs(NW) ? 0 : 2 * (size_t)NEL) + (XT ? 0 : 2 * (size_t)((T + 3) & ~3)) + 64 +
+               (size_t)npart(NW) * NEL + (mv_in_regs(NW) ? 0 : 2 * (size_t)NEL) + (XT ? 0 : 2 * (size_t)((T + 3) & ~3)) + 64 +
                (XT ? (size_t)(BP + 1) * XS : 0) + PS;
     }
     __host__ __device__ static size_t cta_floats(int T, bool XT) { return (XT ? 0 : (size_t)(T + 1) * XS) + NEL / 4; }
@@ -111,11 +127,6 @@ __device__ __forceinline__ void st4(float* p, float4 v) { *reinterpret_cast<floa
 
 __device__ __forceinline__ float2 ld2(const float* p) { return *reinterpret_cast<const float2*>(p); }
 __device__ __forceinline__ void st2(float* p, float2 v) { *reinterpret_cast<float2*>(p) = v; }
-__device__ __forceinline__ float fast_sqrt(float x) {      // MUFU.SQRT, 1 ulp; exact 0 for 0
-    float r;
-    asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
-    return r;
-}
 
 // LP: padded latent width; NW: warps per team (1, 2, 3 or 6: 2*NW lane classes must divide the 12 ETF float2 pieces);
 // TPC: most teams per CTA (the launch picks blockDim.x / (32*NW) <= TPC teams from the shared-memory budget);
@@ -151,12 +162,14 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
     constexpr bool MVREG = Lay<LP>::mv_in_regs(NW);
     constexpr int NQ = NEL / 4;                    // slot quads: four consecutive columns of one weight row
     constexpr int QPL = MVREG ? (NQ + NTH - 1) / NTH : 1;   // quads per lane when m, v live in registers
-    constexpr int KS = Lay<LP>::ks(NW);            // partial sums per weight slot (see Lay::TG)
-    float4* mv = reinterpret_cast<float4*>(part + KS * NEL);   // [NQ][2]: m, v of a quad (shared-memory variant)
+    constexpr int KS = Lay<LP>::ks(NW);            // row-class stride of a warp in the grads phase (see Lay::npart)
+    constexpr int NPART = Lay<LP>::npart(NW);      // partial sums per weight slot in shared memory
+    static_assert(6 % KS == 0, "canonical order: the warps of a tile group must divide the six row classes");
+    float4* mv = reinterpret_cast<float4*>(part + NPART * NEL);   // [NQ][2]: m, v of a quad (shared-memory variant)
     // resident mode: row-offset tables of a whole epoch (position in the epoch's order -> offset of the row in Xs: the
     // fused window gather, so shuffled orders cost nothing), [2][TP], one being read while the next epoch's is written
     const int TP = XT ? 0 : (T + 3) & ~3;
-    int* xoff_tab = reinterpret_cast<int*>(part + KS * NEL + (MVREG ? 0 : 2 * NEL));
+    int* xoff_tab = reinterpret_cast<int*>(part + NPART * NEL + (MVREG ? 0 : 2 * NEL));
     float* red = reinterpret_cast<float*>(xoff_tab + 2 * TP);          // [2][32], double-buffered per epoch
     // Xs: what the phases address rows in — the resident block (row r at xoff[r]) or the team's batch tile (row r at r*XS)
     float* Xs = XT ? red + 64 : smem;
@@ -365,14 +378,13 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
         return sse2.x + sse2.y;
     };
 
-    // ---------------------------------------------------------------- weight-gradient phase (split-K over warps)
+    // ---------------------------------------------------------------- weight-gradient phase (row classes over warps)
     auto grads_phase = [&](const int* xoff, int nb) {
         constexpr bool GRP = Lay<LP>::grouped(NW);
         constexpr int TPG = NT5 / Lay<LP>::TG;          // tiles per group (12*CT/TG: a multiple of 6)
         const int grp = GRP ? warp % Lay<LP>::TG : 0;
-        const int kq = GRP ? warp / Lay<LP>::TG : warp;  // first batch row of this warp
+        const int kq = GRP ? warp / Lay<LP>::TG : warp;  // first row class of this warp
         const int tend = GRP ? (grp + 1) * TPG : NT5;
-        float* mypart = part + kq * NEL;
 #pragma unroll 1
         for (int t = grp * TPG + lane; t < tend; t += 32) {
             const bool dec = t < 6 * CT;
@@ -385,26 +397,59 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
                 const int lt = u / 6, et = u - lt * 6;     // lt-major like dWd: six consecutive lanes share a chunk
                 a0 = et * 4; b0 = (int)(dZh - Xs) + lt * 4; bstr = HS;
             }
-            float2 acc[4][2];
+            // the fused chain of one row class: positions c, c+6, c+12, ...
+            auto class_chain = [&](int c, float2 (&acc)[4][2]) {
 #pragma unroll
-            for (int i = 0; i < 4; ++i) acc[i][0] = acc[i][1] = make_float2(0.f, 0.f);
+                for (int i = 0; i < 4; ++i) acc[i][0] = acc[i][1] = make_float2(0.f, 0.f);
 #pragma unroll 8
-            for (int q = kq; q < nb; q += KS) {
-                const int ao = dec ? q * HS : (XT ? q * XS : xoff[q]);
-                const float4 a = ld4(Xs + a0 + ao);
-                const float4 b = ld4(Xs + b0 + q * bstr);
-                const float av[4] = {a.x, a.y, a.z, a.w};
-                const float2 b01 = make_float2(b.x, b.y), b23 = make_float2(b.z, b.w);
+                for (int q = c; q < nb; q += 6) {
+                    const int ao = dec ? q * HS : (XT ? q * XS : xoff[q]);
+                    const float4 a = ld4(Xs + a0 + ao);
+                    const float4 b = ld4(Xs + b0 + q * bstr);
+                    const float av[4] = {a.x, a.y, a.z, a.w};
+                    const float2 b01 = make_float2(b.x, b.y), b23 = make_float2(b.z, b.w);
 #pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                    const float2 aa = make_float2(av[i], av[i]);
-                    acc[i][0] = __ffma2_rn(aa, b01, acc[i][0]);
-                    acc[i][1] = __ffma2_rn(aa, b23, acc[i][1]);
+                    for (int i = 0; i < 4; ++i) {
+                        const float2 aa = make_float2(av[i], av[i]);
+                        acc[i][0] = __ffma2_rn(aa, b01, acc[i][0]);
+                        acc[i][1] = __ffma2_rn(aa, b23, acc[i][1]);
+                    }
                 }
-            }
+            };
+            auto add_to = [&](float2 (&tot)[4][2], const float2 (&acc)[4][2]) {
 #pragma unroll
-            for (int i = 0; i < 4; ++i)
-                st4(mypart + i * (NT5 * 4) + t * 4, make_float4(acc[i][0].x, acc[i][0].y, acc[i][1].x, acc[i][1].y));   // lanes -> consecutive 16 B
+                for (int i = 0; i < 4; ++i)
+#pragma unroll
+                    for (int h = 0; h < 2; ++h)
+                        tot[i][h] = make_float2(__fadd_rn(tot[i][h].x, acc[i][h].x), __fadd_rn(tot[i][h].y, acc[i][h].y));
+            };
+            auto store = [&](int slot, const float2 (&v)[4][2]) {
+                float* dst = part + slot * NEL;
+#pragma unroll
+                for (int i = 0; i < 4; ++i)
+                    st4(dst + i * (NT5 * 4) + t * 4, make_float4(v[i][0].x, v[i][0].y, v[i][1].x, v[i][1].y));   // lanes -> consecutive 16 B
+            };
+            float2 acc[4][2];
+            if constexpr (KS >= 3) {                     // every class sum goes to shared memory; the update phase combines
+#pragma unroll
+                for (int c = 0; c < 6 / KS; ++c) {
+                    class_chain(kq + c * KS, acc);
+                    store(kq + c * KS, acc);
+                }
+            } else {                                     // KS = 2: this warp's parity (p_kq + p_kq+2) + p_kq+4;  KS = 1: both
+                float2 par[4][2];
+                class_chain(kq, par);
+                class_chain(kq + 2, acc); add_to(par, acc);
+                class_chain(kq + 4, acc); add_to(par, acc);
+                if constexpr (KS == 1) {
+                    float2 odd[4][2];
+                    class_chain(1, odd);
+                    class_chain(3, acc); add_to(odd, acc);
+                    class_chain(5, acc); add_to(odd, acc);
+                    add_to(par, odd);
+                }
+                store(kq, par);
+            }
         }
     };
 
@@ -414,29 +459,40 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
     float4 m4r[QPL], v4r[QPL];
 #pragma unroll
     for (int j = 0; j < QPL; ++j) m4r[j] = v4r[j] = make_float4(0.f, 0.f, 0.f, 0.f);
-    auto quad_gradient = [&](int qd) -> float4 {
-        float4 g = ld4(part + 4 * qd);
-#pragma unroll
-        for (int w = 1; w < KS; ++w) {
-            const float4 t = ld4(part + w * NEL + 4 * qd);
-            g.x += t.x; g.y += t.y; g.z += t.z; g.w += t.w;
-        }
-        return g;
+    auto add4 = [](const float4& a, const float4& b) {
+        return make_float4(__fadd_rn(a.x, b.x), __fadd_rn(a.y, b.y), __fadd_rn(a.z, b.z), __fadd_rn(a.w, b.w));
     };
-    auto update_quad = [&](int qd, float4& m4, float4& v4, const float4& sc) {
+    auto quad_gradient = [&](int qd) -> float4 {        // canonical combination of the class sums (see Lay::npart)
+        const float* pq = part + 4 * qd;
+        if constexpr (NPART == 6) {
+            const float4 even = add4(add4(ld4(pq), ld4(pq + 2 * NEL)), ld4(pq + 4 * NEL));
+            const float4 odd = add4(add4(ld4(pq + NEL), ld4(pq + 3 * NEL)), ld4(pq + 5 * NEL));
+            return add4(even, odd);
+        } else if constexpr (NPART == 2) {
+            return add4(ld4(pq), ld4(pq + NEL));
+        } else {
+            return ld4(pq);
+        }
+    };
+    // Keras 2.7 Nadam._resource_apply_dense, operation by operation (oracle/fitcore.py Nadam.step):
+    // sa = {1 - m_schedule_new, 1 - m_schedule_next, 1 - beta_2^t, 1 - mu_t}, sb.x = mu_{t+1}
+    auto update_quad = [&](int qd, float4& m4, float4& v4, const float4& sa, const float4& sb) {
         const float4 g = quad_gradient(qd);
         auto delta = [&](float gk, float& m, float& v) -> float {
-            m = p.b1 * m + omb1 * gk;
-            v = p.b2 * v + omb2 * (gk * gk);
-            const float m_bar = sc.x * gk + sc.y * m;
-            return __fdividef(p.lr * m_bar, fast_sqrt(v * sc.z) + p.eps);
+            const float g_prime = __fdiv_rn(gk, sa.x);
+            m = __fadd_rn(__fmul_rn(p.b1, m), __fmul_rn(omb1, gk));
+            const float m_prime = __fdiv_rn(m, sa.y);
+            v = __fadd_rn(__fmul_rn(p.b2, v), __fmul_rn(omb2, __fmul_rn(gk, gk)));
+            const float v_prime = __fdiv_rn(v, sa.z);
+            const float m_bar = __fadd_rn(__fmul_rn(sa.w, g_prime), __fmul_rn(sb.x, m_prime));
+            return __fdiv_rn(__fmul_rn(p.lr, m_bar), __fadd_rn(__fsqrt_rn(v_prime), p.eps));
         };
         const int o = woff[qd];
         float4 wv = ld4(We + o);
-        wv.x -= delta(g.x, m4.x, v4.x);
-        wv.y -= delta(g.y, m4.y, v4.y);
-        wv.z -= delta(g.z, m4.z, v4.z);
-        wv.w -= delta(g.w, m4.w, v4.w);
+        wv.x = __fsub_rn(wv.x, delta(g.x, m4.x, v4.x));
+        wv.y = __fsub_rn(wv.y, delta(g.y, m4.y, v4.y));
+        wv.z = __fsub_rn(wv.z, delta(g.z, m4.z, v4.z));
+        wv.w = __fsub_rn(wv.w, delta(g.w, m4.w, v4.w));
         st4(We + o, wv);
     };
     // test hook (cfg.dump_step): the summed gradient of one step, unpadded, to global memory.  Kept out of the update
@@ -458,17 +514,17 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
             }
         }
     };
-    auto update_phase = [&](int step, const float4& sc) {
+    auto update_phase = [&](int step, const float4& sa, const float4& sb) {
         if (p.grad_out != nullptr && step == p.dump_step) dump_gradient();
         if constexpr (MVREG) {
 #pragma unroll
             for (int j = 0; j < QPL; ++j)
-                if (NQ % NTH == 0 || tl + j * NTH < NQ) update_quad(tl + j * NTH, m4r[j], v4r[j], sc);
+                if (NQ % NTH == 0 || tl + j * NTH < NQ) update_quad(tl + j * NTH, m4r[j], v4r[j], sa, sb);
         } else {
 #pragma unroll 2
             for (int qd = tl; qd < NQ; qd += NTH) {
                 float4 m4 = mv[2 * qd], v4 = mv[2 * qd + 1];
-                update_quad(qd, m4, v4, sc);
+                update_quad(qd, m4, v4, sa, sb);
                 mv[2 * qd] = m4; mv[2 * qd + 1] = v4;
             }
         }
@@ -571,10 +627,13 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
             if constexpr (!XT) prefetch_next();
             // this step's Nadam scalars: the global load is issued here and first used after two phases, so its latency
             // (the only global access of a step) is off the critical path of a one-team CTA
-            float4 sc = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (train)
+            float4 sa = make_float4(1.f, 1.f, 1.f, 0.f), sb = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (train) {
                 asm volatile("ld.global.nc.v4.f32 {%0,%1,%2,%3}, [%4];"
-                             : "=f"(sc.x), "=f"(sc.y), "=f"(sc.z), "=f"(sc.w) : "l"(p.sched + step));
+                             : "=f"(sa.x), "=f"(sa.y), "=f"(sa.z), "=f"(sa.w) : "l"(p.sched + 2 * step));
+                asm volatile("ld.global.nc.v4.f32 {%0,%1,%2,%3}, [%4];"
+                             : "=f"(sb.x), "=f"(sb.y), "=f"(sb.z), "=f"(sb.w) : "l"(p.sched + 2 * step + 1));
+            }
             float sse = 0.f;
             if (!(p.debug_skip & 1)) {
                 sse = rows_phase(xoff, nb, train, 2.f / (float)(nb * E));
@@ -585,7 +644,7 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
                 if (!(p.debug_skip & 2)) grads_phase(xoff, nb);
                 team_sync<NW>(team);
                 if constexpr (XT) prefetch_next();          // the copy overlaps the update phase
-                if (!(p.debug_skip & 4)) update_phase(step, sc);
+                if (!(p.debug_skip & 4)) update_phase(step, sa, sb);
                 ++step;
             } else {
                 vsum += sse;
@@ -618,8 +677,8 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
         }
         epochs_run = epoch + 1;
         if (!isfinite(loss)) st = 1;
-        if (p.early_stop) {                      // EarlyStopping.on_epoch_end (App. A.6)
-            ++wait;
+        if (p.early_stop && n_val > 0) {         // EarlyStopping.on_epoch_end (App. A.6); with no validation rows there is
+            ++wait;                              // no val_loss: Keras warns, leaves `wait` alone and trains every epoch
             if (val < best) { best = val; wait = 0; }
             if (wait >= p.patience && epoch > 0) break;
         }
@@ -662,7 +721,7 @@ static int launch_fit_mode(const FitParams& p, cudaStream_t stream) {
     HFREP_REQUIRE(smem <= kMaxSmem, "fit: %zu bytes of shared memory needed (batch=%d too large for the narrow kernel)", smem,
                   p.batch);
     auto kern = fit_kernel<LP, NW, TPC, FULL, XT>;
-    HFREP_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    HFREP_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024)));
     const int grid = (p.n_tasks + tpc - 1) / tpc;
     kern<<<grid, 32 * NW * tpc, smem, stream>>>(p);
     HFREP_CUDA_OK(cudaGetLastError());
@@ -727,10 +786,14 @@ extern "C" int hfrep_nadam_schedule(const hfrep_fit_cfg* c, int n_steps, float* 
         const float mu_t1 = c->beta_1 * (1.f - .5f * pw(c->decay_base, c->schedule_decay * nxt));
         const float ms_new = m_cache * mu_t;
         const float ms_next = ms_new * mu_t1;
-        out[4 * s + 0] = (1.f - mu_t) / (1.f - ms_new);
-        out[4 * s + 1] = mu_t1 / (1.f - ms_next);
-        out[4 * s + 2] = 1.f / (1.f - pw(c->beta_2, t));
-        out[4 * s + 3] = mu_t;
+        float* o = out + (size_t)HFREP_SCHED_STRIDE * s;
+        o[0] = 1.f - ms_new;                 // divides the gradient
+        o[1] = 1.f - ms_next;                // divides the first moment
+        o[2] = 1.f - pw(c->beta_2, t);       // divides the second moment
+        o[3] = 1.f - mu_t;
+        o[4] = mu_t1;
+        o[5] = mu_t;
+        o[6] = o[7] = 0.f;
         m_cache = ms_new;
     }
     return HFREP_OK;
@@ -753,6 +816,7 @@ static int fit_batched_impl(const hfrep_fit_cfg* c, const float* X, int n_tasks,
     HFREP_REQUIRE(w_stride >= 2 * c->E * c->L_max, "fit_batched: w_stride=%d < 2*E*L_max", w_stride);
     HFREP_REQUIRE(c->n_x >= 1 && (c->n_x == 1 || task_x), "fit_batched: n_x=%d needs task_x", c->n_x);
     HFREP_REQUIRE(((uintptr_t)sched & 15) == 0, "fit_batched: sched must be 16-byte aligned");
+    HFREP_REQUIRE(c->patience >= 0, "fit_batched: patience=%d", c->patience);
 
     FitParams p;
     p.X = X; p.task_L = task_L; p.task_x = task_x; p.W0 = W0; p.perm = perm; p.task_seed = task_seed;
@@ -828,24 +892,27 @@ extern "C" int hfrep_fit_windows(const hfrep_fit_cfg* c, const float* R, int T_a
 //
 // The array's name is only a handle on the host; its device address is looked up with cudaGetSymbolAddress the
 // first time the entry point runs on a device (with that device current) and remembered per device.  Make that
-// first call outside any stream capture.  All calls on one device share the one array: two calls whose kernels
+// first call outside any stream capture — and before the host's arena claims what is left of the GPU: with CUDA's
+// default lazy module loading the array (and each kernel variant's code) takes its device memory at that first use,
+// not when the library is loaded (CUDA_MODULE_LOADING=EAGER moves it to load time).
+// All calls on one device share the one array: two calls whose kernels
 // overlap on the GPU (different streams, no dependency) overwrite each other's blocks.  Nothing in the array
 // has to start at zero — kernel (a) rewrites every element the fit reads — so no clearing is done between calls.
 // No cudaMalloc / cudaFree / allocating library routine is called on this path.
 static __device__ __align__(256) float g_window_scratch[HFREP_STATIC_SCRATCH_BYTES / sizeof(float)];
 
 static int static_scratch_address(float** out) {
-    static float* cached[64] = {nullptr};
+    static std::atomic<float*> cached[64];       // per device; host threads may race to fill a slot with the same value
     int dev = -1;
     HFREP_CUDA_OK(cudaGetDevice(&dev));
     HFREP_REQUIRE(dev >= 0 && dev < 64, "fit_windows_static: device ordinal %d not supported", dev);
-    if (cached[dev] == nullptr) {
-        float* ptr = nullptr;
+    float* ptr = cached[dev].load(std::memory_order_acquire);
+    if (ptr == nullptr) {
         HFREP_CUDA_OK(cudaGetSymbolAddress((void**)&ptr, g_window_scratch));
         HFREP_REQUIRE(ptr != nullptr, "fit_windows_static: no device address for the scratch array");
-        cached[dev] = ptr;
+        cached[dev].store(ptr, std::memory_order_release);
     }
-    *out = cached[dev];
+    *out = ptr;
     return HFREP_OK;
 }
 

@@ -12,21 +12,25 @@ namespace hfrep {
 // One CTA per window per pass (grid-stride over windows).  Threads walk the (row, col) elements of the
 // window in output order, so stores are fully coalesced and loads are coalesced per source row.
 // Fast path: ncols % 4 == 0 and 16-byte aligned rows -> float4 loads/stores.
-__global__ void __launch_bounds__(256) window_gather_kernel(const float* __restrict__ R, int C,
+// TS = float or double: the returns matrix as the caller holds it.  With a float64 source (the reference's DataFrames are
+// float64) min, max and the scaling are taken on the float64 values and the result is rounded to float32 once — exactly
+// MinMaxScaler on float64 followed by Keras' cast (Autoencoder_encapsulate.py:62-65, :83).
+template <typename TS>
+__global__ void __launch_bounds__(256) window_gather_kernel(const TS* __restrict__ R, int C,
                                                             const int* __restrict__ starts, int n, int len,
                                                             int col_lo, int ncols, int minmax, int vec4,
                                                             float* __restrict__ out) {
     extern __shared__ double cst[];          // [2][ncols]: scale, shift (only when minmax)
     for (int w = blockIdx.x; w < n; w += gridDim.x) {
-        const float* src = R + (size_t)starts[w] * C + col_lo;
+        const TS* src = R + (size_t)starts[w] * C + col_lo;
         float* dst = out + (size_t)w * len * ncols;
         if (minmax) {
             __syncthreads();
             for (int c = threadIdx.x; c < ncols; c += blockDim.x) {
-                float lo = INFINITY, hi = -INFINITY;
+                TS lo = INFINITY, hi = -INFINITY;
                 for (int r = 0; r < len; ++r) {
-                    const float v = __ldg(src + (size_t)r * C + c);
-                    lo = fminf(lo, v); hi = fmaxf(hi, v);
+                    const TS v = __ldg(src + (size_t)r * C + c);
+                    lo = v < lo ? v : lo; hi = v > hi ? v : hi;
                 }
                 double rng = (double)hi - (double)lo;
                 if (rng == 0.) rng = 1.;
@@ -39,17 +43,17 @@ __global__ void __launch_bounds__(256) window_gather_kernel(const float* __restr
                 const int r = idx / ncols, c = idx - r * ncols;
                 dst[idx] = (float)__dadd_rn(__dmul_rn((double)__ldg(src + (size_t)r * C + c), cst[c]), cst[ncols + c]);   // X *= scale; X += min_ (no FMA contraction)
             }
-        } else if (vec4) {
+        } else if (sizeof(TS) == 4 && vec4) {    // (float source only)
             const int q = ncols >> 2;
             for (int idx = threadIdx.x; idx < len * q; idx += blockDim.x) {
                 const int r = idx / q, c4 = idx - r * q;
-                const float4 v = __ldg(reinterpret_cast<const float4*>(src + (size_t)r * C) + c4);
+                const float4 v = __ldg(reinterpret_cast<const float4*>(reinterpret_cast<const float*>(src) + (size_t)r * C) + c4);
                 reinterpret_cast<float4*>(dst)[idx] = v;
             }
         } else {
             for (int idx = threadIdx.x; idx < len * ncols; idx += blockDim.x) {
                 const int r = idx / ncols, c = idx - r * ncols;
-                dst[idx] = __ldg(src + (size_t)r * C + c);
+                dst[idx] = (float)__ldg(src + (size_t)r * C + c);
             }
         }
     }
@@ -115,25 +119,36 @@ __global__ void __launch_bounds__(256) ffma_peak_kernel(int iters, float* sink) 
 using namespace hfrep;
 
 namespace hfrep {
-int launch_window_gather(const float* R, int T, int C, const int32_t* starts, int n, int len, int col_lo, int ncols,
-                         int minmax, float* out, cudaStream_t stream) {
+template <typename TS>
+static int launch_window_gather_t(const TS* R, int T, int C, const int32_t* starts, int n, int len, int col_lo, int ncols,
+                                  int minmax, float* out, cudaStream_t stream) {
     HFREP_REQUIRE(n >= 0 && len >= 0, "window_gather: n=%d len=%d", n, len);
     if (n == 0 || len == 0) return HFREP_OK;             // empty batch: nothing to read or write
     HFREP_REQUIRE(R && starts && out, "window_gather: null argument");
     HFREP_REQUIRE(col_lo >= 0 && ncols >= 1 && col_lo + ncols <= C, "window_gather: columns [%d,%d) outside 0..%d", col_lo,
                   col_lo + ncols, C);
     HFREP_REQUIRE(len <= T, "window_gather: len=%d exceeds T=%d", len, T);
-    const int vec4 = !minmax && (ncols % 4 == 0) && (C % 4 == 0) && (col_lo % 4 == 0) &&
+    const int vec4 = sizeof(TS) == 4 && !minmax && (ncols % 4 == 0) && (C % 4 == 0) && (col_lo % 4 == 0) &&
                      (((uintptr_t)R | (uintptr_t)out) & 15) == 0;
     const size_t smem = minmax ? sizeof(double) * 2 * ncols : 0;
     HFREP_REQUIRE(smem <= 48 * 1024, "window_gather: ncols=%d too wide for the minmax path", ncols);
     const int sms = sm_count();
     const int grid = n < 8 * sms ? n : 8 * sms;      // whole multiples of the SM count once there is enough work
-    window_gather_kernel<<<grid, 256, smem, stream>>>(R, C, starts, n, len, col_lo, ncols, minmax, vec4, out);
+    window_gather_kernel<TS><<<grid, 256, smem, stream>>>(R, C, starts, n, len, col_lo, ncols, minmax, vec4, out);
     HFREP_CUDA_OK(cudaGetLastError());
     return HFREP_OK;
 }
+
+int launch_window_gather(const float* R, int T, int C, const int32_t* starts, int n, int len, int col_lo, int ncols,
+                         int minmax, float* out, cudaStream_t stream) {
+    return launch_window_gather_t<float>(R, T, C, starts, n, len, col_lo, ncols, minmax, out, stream);
+}
 }  // namespace hfrep
+
+extern "C" int hfrep_window_gather_f64(const double* R, int T, int C, const int32_t* starts, int n, int len, int col_lo,
+                                       int ncols, int minmax, float* out, void* stream) {
+    return launch_window_gather_t<double>(R, T, C, starts, n, len, col_lo, ncols, minmax, out, (cudaStream_t)stream);
+}
 
 extern "C" int hfrep_window_gather(const float* R, int T, int C, const int32_t* starts, int n, int len, int col_lo,
                                    int ncols, int minmax, float* out, void* stream) {

@@ -33,6 +33,19 @@ struct WideFitParams {
     float alpha, lr, b1, b2, eps;
 };
 
+// Keras 2.7 Nadam._resource_apply_dense, operation by operation, each rounded on its own (SURVEY App. A.4;
+// oracle/fitcore.py Nadam.step).  sa = {1 - m_schedule_new, 1 - m_schedule_next, 1 - beta_2^t, 1 - mu_t}, mu1 = mu_{t+1}.
+__device__ __forceinline__ float nadam_step(float w, float g, float& m, float& v, const float4& sa, float mu1, float b1,
+                                            float omb1, float b2, float omb2, float lr, float eps) {
+    const float g_prime = __fdiv_rn(g, sa.x);
+    m = __fadd_rn(__fmul_rn(b1, m), __fmul_rn(omb1, g));
+    const float m_prime = __fdiv_rn(m, sa.y);
+    v = __fadd_rn(__fmul_rn(b2, v), __fmul_rn(omb2, __fmul_rn(g, g)));
+    const float v_prime = __fdiv_rn(v, sa.z);
+    const float m_bar = __fadd_rn(__fmul_rn(sa.w, g_prime), __fmul_rn(mu1, m_prime));
+    return __fsub_rn(w, __fdiv_rn(__fmul_rn(lr, m_bar), __fadd_rn(__fsqrt_rn(v_prime), eps)));
+}
+
 __device__ __forceinline__ float block_sum(float v, float* red) {
     v = warp_sum(v);
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -109,7 +122,8 @@ __global__ void __launch_bounds__(WIDE_THREADS) fit_wide_kernel(const WideFitPar
         }
         __syncthreads();
         // gradients + Nadam, element-wise over the 2*E*L weights
-        const float4 sc = __ldg(p.sched + step);
+        const float4 sa = __ldg(p.sched + 2 * step);
+        const float mu1 = __ldg(p.sched + 2 * step + 1).x;
         for (size_t i = tid; i < 2 * EL; i += WIDE_THREADS) {
             float g = 0.f;
             float *w, *m, *v;
@@ -123,10 +137,9 @@ __global__ void __launch_bounds__(WIDE_THREADS) fit_wide_kernel(const WideFitPar
                 for (int r = 0; r < nb; ++r) g = fmaf(__ldg(X + (size_t)rows[r] * E + e), dZh[r * L + l], g);
                 w = We + j; m = mWe + j; v = vWe + j;
             }
-            const float mm = p.b1 * *m + omb1 * g;
-            const float vv = p.b2 * *v + omb2 * (g * g);
+            float mm = *m, vv = *v;
+            *w = nadam_step(*w, g, mm, vv, sa, mu1, p.b1, omb1, p.b2, omb2, p.lr, p.eps);
             *m = mm; *v = vv;
-            *w -= p.lr * (sc.x * g + sc.y * mm) / (sqrtf(vv * sc.z) + p.eps);
         }
         ++step;
         __syncthreads();
@@ -157,7 +170,7 @@ __global__ void __launch_bounds__(WIDE_THREADS) fit_wide_kernel(const WideFitPar
         }
         epochs_run = epoch + 1;
         if (!isfinite(loss)) st = 1;
-        if (p.early_stop) {
+        if (p.early_stop && n_val > 0) {         // no validation rows: no val_loss, Keras never stops (see fit_kernel.cu)
             ++wait;
             if (val < best) { best = val; wait = 0; }
             if (wait >= p.patience && epoch > 0) break;
@@ -256,13 +269,13 @@ __global__ void __launch_bounds__(512 / EPT) fit_wide2_kernel(const WideFitParam
         return sacc;
     };
     const float4* sched = p.sched;
-    auto upd = [&](float& w, float g, int slot, const float4& sc) {
+    float mu1 = 0.f;
+    auto upd = [&](float& w, float g, int slot, const float4& sa) {
         float* mp = mv + (size_t)slot * NT + tid;
         float* vp = mv + (size_t)(NS + slot) * NT + tid;
-        const float mm = p.b1 * *mp + omb1 * g;
-        const float vv = p.b2 * *vp + omb2 * (g * g);
+        float mm = *mp, vv = *vp;
+        w = nadam_step(w, g, mm, vv, sa, mu1, p.b1, omb1, p.b2, omb2, p.lr, p.eps);
         *mp = mm; *vp = vv;
-        w -= p.lr * (sc.x * g + sc.y * mm) / (sqrtf(vv * sc.z) + p.eps);
     };
 
     auto run_batch = [&](int nb, bool train) -> float {
@@ -361,7 +374,8 @@ __global__ void __launch_bounds__(512 / EPT) fit_wide2_kernel(const WideFitParam
             }
         }
         // ---- Nadam on the thread's own weights (Wd now: its gradient is complete and pass 3 does not read Wd)
-        const float4 sc = __ldg(sched + step);
+        const float4 sc = __ldg(sched + 2 * step);
+        mu1 = __ldg(sched + 2 * step + 1).x;
 #pragma unroll
         for (int j = 0; j < LH; ++j)
 #pragma unroll
@@ -435,7 +449,7 @@ __global__ void __launch_bounds__(512 / EPT) fit_wide2_kernel(const WideFitParam
         }
         epochs_run = epoch + 1;
         if (!isfinite(loss)) st = 1;
-        if (p.early_stop) {
+        if (p.early_stop && n_val > 0) {         // no validation rows: no val_loss, Keras never stops (see fit_kernel.cu)
             ++wait;
             if (val < best) { best = val; wait = 0; }
             if (wait >= p.patience && epoch > 0) break;
@@ -635,7 +649,7 @@ static int launch_fit_wide2(const WideFitParams& p, int NT, cudaStream_t stream)
     const size_t smem = sizeof(float) * ((size_t)(2 + NWARP) * BP * LP + BP + 32 + (LP * EPT > 16 ? (size_t)BP * NT * EPT : 0));
     HFREP_REQUIRE(smem <= 227 * 1024, "fit_wide: %zu bytes of shared memory needed (batch too large)", smem);
     auto kern = fit_wide2_kernel<LP, EPT>;
-    HFREP_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    HFREP_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024)));
     kern<<<p.n_tasks, NT, smem, stream>>>(p);
     HFREP_CUDA_OK(cudaGetLastError());
     return HFREP_OK;
@@ -656,6 +670,7 @@ extern "C" int hfrep_fit_wide(const hfrep_fit_cfg* c, const float* X, int n_task
     HFREP_REQUIRE(ws_bytes >= hfrep_fit_wide_workspace(n_tasks, c->E, L), "fit_wide: workspace of %zu bytes needed, %zu given",
                   hfrep_fit_wide_workspace(n_tasks, c->E, L), ws_bytes);
     HFREP_REQUIRE(c->n_x == 1 || task_x, "fit_wide: n_x=%d needs task_x", c->n_x);
+    HFREP_REQUIRE(((uintptr_t)sched & 15) == 0, "fit_wide: sched must be 16-byte aligned");
     WideFitParams p;
     p.X = X; p.task_x = task_x; p.W0 = W0; p.perm = perm; p.perm_task_stride = perm_task_stride;
     p.sched = reinterpret_cast<const float4*>(sched); p.ws = static_cast<float*>(ws); p.W_out = W_out;
@@ -672,7 +687,7 @@ extern "C" int hfrep_fit_wide(const hfrep_fit_cfg* c, const float* X, int n_task
     }
     const size_t smem = sizeof(float) * (2 * (size_t)c->batch * L + (size_t)c->batch * c->E + c->batch + 16);
     HFREP_REQUIRE(smem <= 227 * 1024, "fit_wide: %zu bytes of shared memory needed (batch x E too large)", smem);
-    HFREP_CUDA_OK(cudaFuncSetAttribute(fit_wide_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    HFREP_CUDA_OK(cudaFuncSetAttribute(fit_wide_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024)));
     fit_wide_kernel<<<n_tasks, WIDE_THREADS, smem, (cudaStream_t)stream>>>(p);
     HFREP_CUDA_OK(cudaGetLastError());
     return HFREP_OK;
@@ -691,7 +706,7 @@ extern "C" int hfrep_predict_wide(const double* etf, const double* hfd, const do
     p.etf = etf; p.hfd = hfd; p.rf = rf; p.task_row0 = task_row0; p.W = W; p.replica = replica; p.status = status;
     p.n_tasks = n_tasks; p.E = E; p.F = F; p.L = L; p.window = window; p.alpha = alpha;
     const size_t smem = sizeof(double) * (2 * (size_t)window * L + 3 * L) + sizeof(float) * (size_t)(window + 2) * L + E + 16;
-    HFREP_CUDA_OK(cudaFuncSetAttribute(eval_wide_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    HFREP_CUDA_OK(cudaFuncSetAttribute(eval_wide_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024)));
     eval_wide_kernel<<<n_tasks, WIDE_THREADS, smem, (cudaStream_t)stream>>>(p);
     HFREP_CUDA_OK(cudaGetLastError());
     return HFREP_OK;

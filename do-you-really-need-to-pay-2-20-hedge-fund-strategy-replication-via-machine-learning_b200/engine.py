@@ -119,7 +119,7 @@ def nadam_schedule(cfg: _lib.FitCfg, n_steps: int, device) -> torch.Tensor:
     key = (cfg.lr, cfg.beta_1, cfg.beta_2, cfg.epsilon, cfg.schedule_decay, cfg.decay_base, n_steps, str(device))
     t = _SCHED_CACHE.get(key)
     if t is None:
-        host = np.zeros((n_steps, 4), np.float32)
+        host = np.zeros((n_steps, _lib.SCHED_STRIDE), np.float32)
         check(lib.hfrep_nadam_schedule(C.byref(cfg), n_steps, ptr(host)))
         t = torch.from_numpy(host).to(device)
         _SCHED_CACHE[key] = t
@@ -320,15 +320,18 @@ def predict_metrics(Xtr64, Xte64, Yte64, rf64, sigma, task_L, W, *, window=24, w
 
 def window_gather(R: torch.Tensor, starts, length: int, col_lo: int = 0, ncols: int | None = None,
                   minmax: bool = False) -> torch.Tensor:
-    """Kernel (a): out[w] = R[starts[w]:starts[w]+length, col_lo:col_lo+ncols] (f32, device)."""
+    """Kernel (a): out[w] = R[starts[w]:starts[w]+length, col_lo:col_lo+ncols] (f32, device).  R float32 or float64
+    (device); a float64 source is scaled in float64 and rounded once, as MinMaxScaler + Keras' cast do."""
     T, Cc = R.shape
     ncols = Cc - col_lo if ncols is None else ncols
     st = starts if isinstance(starts, torch.Tensor) else torch.from_numpy(np.asarray(starts, np.int32)).to(R.device)
     if len(st) and (int(st.min()) < 0 or int(st.max()) + length > T):
         raise _lib.HfrepError("window_gather: a window reaches outside the returns matrix")
     out = torch.empty((len(st), length, ncols), dtype=torch.float32, device=R.device)
-    check(lib.hfrep_window_gather(ptr(R), T, Cc, ptr(st), len(st), length, col_lo, ncols, int(minmax), ptr(out),
-                                  stream_ptr()))
+    if R.dtype not in (torch.float32, torch.float64) or not R.is_contiguous():
+        raise _lib.HfrepError("window_gather: R must be a contiguous float32 or float64 matrix")
+    fn = lib.hfrep_window_gather if R.dtype == torch.float32 else lib.hfrep_window_gather_f64
+    check(fn(ptr(R), T, Cc, ptr(st), len(st), length, col_lo, ncols, int(minmax), ptr(out), stream_ptr()))
     return out
 
 
@@ -372,27 +375,64 @@ def fit_and_score(data: "ReplicationData", task_L, W0d: torch.Tensor, *, perm=No
     return fit, ev
 
 
+def mode_r_tasks(latent_dims, seeds):
+    """The (L, seed) grid of a Mode-R job in its canonical order: widest (slowest) tasks first — the launch order of the
+    width buckets, and the order the cyclic multi-GPU split deals from so that every rank gets the same mix of widths."""
+    return sorted(((int(L), int(s)) for s in seeds for L in latent_dims), key=lambda t: -((t[0] + 3) // 4))
+
+
 def run_mode_r(data: ReplicationData, latent_dims, seeds=(123,), *, W0=None, perm=None, shuffle=False, want_oos=True,
-               want_weights=False, warps_per_task=0, **fit_kw):
+               want_weights=False, warps_per_task=0, sharded=False, timings: dict | None = None, **fit_kw):
     """The notebook's sweep (autoencoder_v4.ipynb:158-165, :896-901) as one batched GPU pass:
     for every (L, seed): fit, IS/OOS quality, ante, turnover, post, metrics.  shuffle=False is the deterministic row
     order used for parity; shuffle=True reshuffles the fit rows every epoch on the device (Keras' default).
-    Returns (tasks, FitResult, EvalResult); tasks[i] = (L, seed)."""
-    # widest (slowest) tasks first: that is the launch order of the width buckets, and it spares a gather
-    tasks = sorted(((int(L), int(s)) for s in seeds for L in latent_dims), key=lambda t: -((t[0] + 3) // 4))
+    Returns (tasks, FitResult, EvalResult); tasks[i] = (L, seed).
+
+    sharded=True inside an initialised torch.distributed job (one process per GPU, `data` resident on this rank's GPU):
+    the task list is dealt cyclically over the ranks (distributed.shard), every rank fits and scores its own tasks — no
+    collective on the data path — and ONE all-gather of packed result records (distributed.gather_records, NCCL over
+    NVLink) leaves the complete results, in global task order, on every rank.  W0 / per-task perm, when given, cover
+    the whole grid in `mode_r_tasks` order.  `timings` receives compute_ms / gather_ms (CUDA events) when given."""
+    from . import distributed
+    tasks = mode_r_tasks(latent_dims, seeds)
+    rank, world = distributed.world() if sharded else (0, 1)
+    mine = distributed.shard(len(tasks), rank, world)
+    local = [tasks[i] for i in mine]
     E = data.E
     L_max = max(L for L, _ in tasks)
     w_stride = 2 * E * L_max
     with torch.cuda.device(data.device):
+        ev_t = [torch.cuda.Event(enable_timing=True) for _ in range(3)] if timings is not None else None
         if W0 is None:
-            W0 = pack_weights([initial_weights(s, E, L) for L, s in tasks], E, w_stride)
+            W0 = pack_weights([initial_weights(s, E, L) for L, s in local], E, w_stride)
+        elif world > 1:
+            W0 = np.asarray(W0, np.float32)[mine]
         W0d = to_device(np.asarray(W0, np.float32), data.device)
+        if perm is not None and world > 1 and np.asarray(perm).ndim == 3:
+            perm = np.asarray(perm)[mine]
         permd = None if perm is None else to_device(np.asarray(perm, np.int32), data.device)
-        task_L = [L for L, _ in tasks]
+        task_L = [L for L, _ in local]
         if shuffle and perm is None:        # Keras' default shuffle=True: one device-side stream per (L, seed)
-            fit_kw["shuffle_seeds"] = [(s * 1000003 + L) & 0xFFFFFFFF for L, s in tasks]
+            fit_kw["shuffle_seeds"] = [(s * 1000003 + L) & 0xFFFFFFFF for L, s in local]
+        if ev_t:
+            ev_t[0].record()
         fit, ev = fit_and_score(data, task_L, W0d, perm=permd, want_oos=want_oos, want_weights=want_weights,
                                 warps_per_task=warps_per_task, **fit_kw)
+        if ev_t:
+            ev_t[1].record()
+        if world > 1:
+            fields = [fit.W, fit.loss, fit.val_loss, fit.epochs_run, fit.status, fit.grads, ev.ante, ev.post, ev.turnover,
+                      ev.metrics, ev.quality, ev.mask, ev.beta, ev.norm, ev.status, ev.weights]
+            g = distributed.gather_records(fields, len(tasks), rank, world)
+            fit = FitResult(g[0], g[1], g[2], g[3], g[4], g[5], fit.w_stride)
+            ev = EvalResult(ante=g[6], post=g[7], turnover=g[8], metrics=g[9], quality=g[10], mask=g[11], beta=g[12],
+                            norm=g[13], status=g[14], weights=g[15])
+        if ev_t:
+            ev_t[2].record()
+            ev_t[2].synchronize()
+            timings["compute_ms"] = ev_t[0].elapsed_time(ev_t[1])
+            timings["gather_ms"] = ev_t[1].elapsed_time(ev_t[2])
+            timings["record_bytes_per_task"] = int(sum(t[0].numel() * t.element_size() for t in (fit.W, fit.loss, fit.val_loss, fit.epochs_run, fit.status, ev.ante, ev.post, ev.turnover, ev.metrics, ev.quality, ev.mask, ev.beta, ev.norm, ev.status) if t is not None))
     return tasks, fit, ev
 
 
@@ -435,7 +475,8 @@ def run_mode_w_wide(etf, hfd, rf, *, train_window: int, latent_dim: int, seeds=(
     weights in a global workspace, hfrep_predict_wide regresses every fund on the latent factors and returns the replica
     return of row t+1.  `windows`: optional subset of window indices (a bounded sample of the 4 747 windows of configs[3])."""
     dev = _dev(device)
-    etf = np.asarray(etf, np.float64)
+    src_f32 = np.asarray(etf).dtype == np.float32       # float32 history: windows are cut from it as it is; otherwise the
+    etf = np.asarray(etf, np.float64)                   # MinMax runs on the float64 values (as the reference's AE does)
     hfd = np.asarray(hfd, np.float64)
     rf = np.asarray(rf, np.float64).reshape(-1)
     T, E = etf.shape
@@ -448,8 +489,9 @@ def run_mode_w_wide(etf, hfd, rf, *, train_window: int, latent_dim: int, seeds=(
     tasks = [(wi, int(s)) for s in seeds for wi in range(n_win)]
     n = len(tasks)
     with torch.cuda.device(dev):
-        R32 = to_device(etf.astype(np.float32), dev)
-        blocks = window_gather(R32, (ts - train_window).astype(np.int32), train_window, 0, E, minmax=True)
+        etf_d = to_device(etf, dev)
+        Rsrc = etf_d.to(torch.float32) if src_f32 else etf_d
+        blocks = window_gather(Rsrc, (ts - train_window).astype(np.int32), train_window, 0, E, minmax=True)
         if W0 is None:
             W0 = pack_weights([initial_weights(s * 100003 + wi, E, L) for wi, s in tasks], E, 2 * E * L)
         W0d = to_device(np.asarray(W0, np.float32), dev)
@@ -474,7 +516,7 @@ def run_mode_w_wide(etf, hfd, rf, *, train_window: int, latent_dim: int, seeds=(
             ev[1].record()
         fit = FitResult(W_out, loss, val, epochs_run, status, None, 2 * E * L)
         row0 = _device_ints((ts - ols_window)[[wi for wi, _ in tasks]].astype(np.int32), dev)
-        etf_d, hfd_d, rf_d = to_device(etf, dev), to_device(hfd, dev), to_device(rf, dev)
+        hfd_d, rf_d = to_device(hfd, dev), to_device(rf, dev)
         replica = torch.empty((n, F), dtype=torch.float64, device=dev)
         est = torch.zeros(n, dtype=torch.int32, device=dev)
         check(lib.hfrep_predict_wide(ptr(etf_d), ptr(hfd_d), ptr(rf_d), T, E, F, L, ols_window, fit_kw.get("alpha", .2), n,
@@ -488,12 +530,17 @@ def run_mode_w_wide(etf, hfd, rf, *, train_window: int, latent_dim: int, seeds=(
 
 
 def run_mode_w(etf, hfd, rf, *, train_window: int, latent_dim: int, seeds=(123,), ols_window: int = 24, device=None,
-               W0=None, **fit_kw):
+               W0=None, sharded=False, **fit_kw):
     """Rolling refit (north_star's per-(window, seed) task; SURVEY §8d Mode W — an extension, the reference fits once):
     for t = train_window .. T-2 fit the autoencoder on rows [t-train_window, t) (MinMax on those rows, 75/25 split),
     then follow the reference's own alignment (Autoencoder_encapsulate.py:149-150,164,183): OLS on rows [t-ols_window, t),
-    mask from row t, replica for row t+1.  Returns dict(t, replica [seed][window][F], weights, fit)."""
+    mask from row t, replica for row t+1.  Returns dict(t, replica [seed][window][F], weights, fit).
+    sharded=True (inside a torch.distributed job, one process per GPU): the (window, seed) tasks are dealt cyclically
+    over the ranks, the returns matrices are replicated, and one all-gather of packed records returns the complete
+    replica / weights / kernels on every rank (see run_mode_r)."""
+    from . import distributed
     dev = _dev(device)
+    src_f32 = np.asarray(etf).dtype == np.float32       # see run_mode_w_wide
     etf = np.asarray(etf, np.float64)
     hfd = np.asarray(hfd, np.float64)
     rf = np.asarray(rf, np.float64).reshape(-1)
@@ -501,20 +548,37 @@ def run_mode_w(etf, hfd, rf, *, train_window: int, latent_dim: int, seeds=(123,)
     assert train_window >= ols_window and T >= train_window + 2
     ts = np.arange(train_window, T - 1)
     n_win = len(ts)
-    tasks = [(wi, int(s)) for s in seeds for wi in range(n_win)]
+    all_tasks = [(wi, int(s)) for s in seeds for wi in range(n_win)]
+    rank, world = distributed.world() if sharded else (0, 1)
+    mine = distributed.shard(len(all_tasks), rank, world)
+    tasks = [all_tasks[i] for i in mine]
     task_L = [latent_dim] * len(tasks)
     w_stride = 2 * E * latent_dim
     with torch.cuda.device(dev):
-        R32 = to_device(etf.astype(np.float32), dev)
+        etf_d = to_device(etf, dev)
         if W0 is None:
             W0 = pack_weights([initial_weights(s * 100003 + wi, E, latent_dim) for wi, s in tasks], E, w_stride)
+        elif world > 1:
+            W0 = np.asarray(W0, np.float32)[mine]
         W0d = to_device(np.asarray(W0, np.float32), dev)
-        fit, blocks = fit_windows(R32, ts - train_window, train_window, task_L, [wi for wi, _ in tasks], W0d, E=E, **fit_kw)
+        task_win = [wi for wi, _ in tasks]
+        if src_f32:        # one call: kernel (a) cuts + scales the float32 windows into a workspace, kernel (b) fits
+            fit, blocks = fit_windows(etf_d.to(torch.float32), ts - train_window, train_window, task_L, task_win, W0d, E=E,
+                                      **fit_kw)
+        else:              # float64 history: kernel (a)'s float64 path, then kernel (b) on the blocks
+            blocks = window_gather(etf_d, (ts - train_window).astype(np.int32), train_window, 0, E, minmax=True)
+            fit = fit_batched(blocks, task_L, W0d, E=E, T=train_window, task_x=_device_ints(np.asarray(task_win, np.int32), dev),
+                              **fit_kw)
         row0 = _device_ints((ts - ols_window)[[wi for wi, _ in tasks]].astype(np.int32), dev)
-        ev = predict_metrics(None, to_device(etf, dev), to_device(hfd, dev), to_device(rf, dev), None, task_L, fit.W,
+        ev = predict_metrics(None, etf_d, to_device(hfd, dev), to_device(rf, dev), None, task_L, fit.W,
                              window=ols_window, want_oos=False, want_quality=False, want_weights=True,
                              task_row0=row0, T_test=ols_window + 2, alpha=fit_kw.get("alpha", .2))
         F = hfd.shape[1]
+        if world > 1:
+            g = distributed.gather_records([ev.ante, ev.weights, ev.status, fit.W, fit.loss, fit.val_loss, fit.epochs_run,
+                                            fit.status], len(all_tasks), rank, world)
+            ev = dataclasses.replace(ev, ante=g[0], weights=g[1], status=g[2])
+            fit = FitResult(g[3], g[4], g[5], g[6], g[7], None, fit.w_stride)
         replica = ev.ante.view(len(seeds), n_win, F)
         weights = ev.weights.view(len(seeds), n_win, E, F)
-    return dict(t=ts, replica=replica, weights=weights, fit=fit, eval=ev, blocks=blocks, tasks=tasks)
+    return dict(t=ts, replica=replica, weights=weights, fit=fit, eval=ev, blocks=blocks, tasks=all_tasks)

@@ -10,8 +10,9 @@
  * Conventions
  *   - all pointers are DEVICE pointers unless the parameter name ends in _host;
  *   - matrices are row-major; "f32"/"f64" = IEEE float/double; indices are int32;
- *   - every call is asynchronous on `stream` and allocates nothing (every buffer, scratch
- *     included, is passed in by the caller);
+ *   - every call is asynchronous on `stream` and allocates nothing: buffers, scratch included,
+ *     are passed in by the caller (one exception: hfrep_fit_windows_static takes its scratch
+ *     from an array built into the library instead of from the caller);
  *   - return value 0 = ok, <0 = error; hfrep_last_error() returns a thread-local message;
  *   - no CPU fallback exists: without a CUDA device the calls return HFREP_ERR_CUDA.
  */
@@ -59,6 +60,11 @@ int hfrep_window_index(int kind, int T, int window, int32_t* starts_host, int32_
  */
 int hfrep_window_gather(const float* R, int T, int C, const int32_t* starts, int n, int len,
                         int col_lo, int ncols, int minmax, float* out, void* stream);
+/* The same from a float64 returns matrix (the reference's DataFrames are float64): min, max and the scaling are taken on
+ * the float64 values and the result is rounded to f32 once — MinMaxScaler on float64 (Autoencoder_encapsulate.py:62-65)
+ * followed by Keras' cast to float32 (:83), bit for bit.  Without minmax the values are rounded to f32. */
+int hfrep_window_gather_f64(const double* R, int T, int C, const int32_t* starts, int n, int len,
+                            int col_lo, int ncols, int minmax, float* out, void* stream);
 
 /* Rolling ex-post volatility (helper.py:121 + :75/:87): sigma[i][e] = sqrt(var(R[start_i..start_i+window), e], ddof=1)),
  * f64 in / f64 out.  R f64 [T][E], starts int32 [n], sigma f64 [n][E]. */
@@ -89,8 +95,11 @@ typedef struct hfrep_fit_cfg {
 
 void hfrep_fit_cfg_default(hfrep_fit_cfg* cfg);
 
-/* Nadam's scalar schedule is task-independent: fill sched f32 [n_steps][4] (host) with
- * {(1-mu_t)/(1-m_sched_t), mu_{t+1}/(1-m_sched_{t+1}), 1/(1-beta_2^t), mu_t}, t=1..n_steps. */
+/* Nadam's scalar schedule is task-independent: fill sched f32 [n_steps][HFREP_SCHED_STRIDE] (host) with
+ * {1-m_sched_t, 1-m_sched_{t+1}, 1-beta_2^t, 1-mu_t, mu_{t+1}, mu_t, 0, 0}, t=1..n_steps (Keras 2.7
+ * Nadam._prepare_local in float32, powers correctly rounded).  The first three DIVIDE the gradient and the two moments:
+ * the kernels apply Keras' operation order with IEEE division and square root, every operation rounded on its own. */
+#define HFREP_SCHED_STRIDE 8
 int hfrep_nadam_schedule(const hfrep_fit_cfg* cfg, int n_steps, float* sched_host);
 
 /*   X        f32 [n_x][T][E]        training blocks, already MinMax-scaled
@@ -102,11 +111,16 @@ int hfrep_nadam_schedule(const hfrep_fit_cfg* cfg, int n_steps, float* sched_hos
  *   task_seed uint32 [n_tasks] | NULL  device-side epoch shuffles (Keras fit's shuffle=True without a host table): when
  *            perm is NULL and task_seed is not, every epoch's row order is the stable argsort of the hash keys
  *            fmix32(seed*0x9E3779B1 ^ (epoch+1)*0x85EBCA77 ^ (row+1)*0xC2B2AE3D) of the task's seed (murmur3 finaliser)
- *   sched    f32 [>= max_epochs*ceil(n_fit/batch)][4]  from hfrep_nadam_schedule, on the device
+ *   sched    f32 [>= max_epochs*ceil(n_fit/batch)][HFREP_SCHED_STRIDE]  from hfrep_nadam_schedule, on the device, 16-byte aligned
  *   W_out    f32 [n_tasks][w_stride]       final kernels, same packing
  *   loss_hist/val_hist f32 [n_tasks][max_epochs]   history.history['loss'|'val_loss']
  *   epochs_run int32 [n_tasks];  status int32 [n_tasks] (0 ok, 1 non-finite loss)
  *   grad_out f32 [n_tasks][w_stride] | NULL   gradients (dWe, dWd) of step cfg->dump_step
+ * Every sum that feeds the weights follows one fixed order in every mapping (fused chains over the ETFs / latent
+ * units, six interleaved chains over the batch rows: DESIGN.md §5), so W_out does not depend on warps_per_task, on the
+ * task's place in the batch or on the staging mode, and equals the CPU oracle's canonical-order result bit for bit.
+ * With early_stop = 1 and no validation rows (n_fit == T) there is no val_loss to monitor: like Keras, the run
+ * trains all max_epochs.
  */
 int hfrep_fit_batched(const hfrep_fit_cfg* cfg, const float* X, int n_tasks, const int32_t* task_L,
                       const int32_t* task_x, const float* W0, int w_stride, const int32_t* perm,
@@ -133,7 +147,8 @@ int hfrep_fit_windows(const hfrep_fit_cfg* cfg, const float* R, int T_all, int C
  * hosts whose own arena already owns the GPU's memory, or that cannot take the device-wide stall of an allocation
  * while other streams are fitting.  Limits: n_windows * cfg->T * cfg->E * 4 bytes must fit the array, else the call
  * returns HFREP_ERR_ARG and names both sizes.  The first call on each device looks up the array's device address; make
- * that call outside stream capture.  All calls on a device share the array — calls that overlap on the GPU race on
+ * that call outside stream capture, and before the host's arena takes the rest of the GPU (CUDA loads the array and
+ * each kernel variant lazily, at first use, unless CUDA_MODULE_LOADING=EAGER).  All calls on a device share the array — calls that overlap on the GPU race on
  * it; calls ordered on one stream (or by events) are safe.  Nothing needs clearing between calls. */
 #define HFREP_STATIC_SCRATCH_BYTES (4u << 20)
 int hfrep_fit_windows_static(const hfrep_fit_cfg* cfg, const float* R, int T_all, int C, int col_lo,

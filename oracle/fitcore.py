@@ -13,6 +13,16 @@ reference call site that relies on it.
     predict()                                        Autoencoder_encapsulate.py:108,112,120,129,140
 
 All arithmetic is float32 (Keras casts inputs and keeps variables in float32).
+
+Summation order.  Float32 sums depend on their order, and this fit has a discrete element: a LeakyReLU
+pre-activation that passes within rounding of zero takes one branch or the other depending on the last bit of a
+22-term sum, which changes that row's gradient five-fold for one step (measured on the reference's data: L = 8,
+step 1993, row 87, unit 6, z = +4.1e-8 against -3.9e-8; the validation loss of that epoch then differs by 3.2e-5
+and the difference decays over the next epochs).  Two correct float32 implementations therefore agree to 1e-6 on
+most runs and to 3e-5 on some.  To make parity exact rather than lucky, `fit(order="canonical")` fixes the order
+of every sum that feeds the weights (the CANONICAL ORDER) — the CUDA fit kernel and the C restatement
+(oracle/c/fit_oracle.c) follow the same order, so the three produce bit-identical weight trajectories.
+`order="blas"` leaves the sums to numpy's BLAS (what Keras/Eigen effectively does; the timed CPU baseline).
 """
 from __future__ import annotations
 
@@ -68,20 +78,81 @@ def predict(x: np.ndarray, We: np.ndarray, Wd: np.ndarray, alpha: float = .2) ->
     return forward(np.asarray(x, F32), We, Wd, alpha)[3]
 
 
-def mse_and_grads(xb: np.ndarray, We: np.ndarray, Wd: np.ndarray, alpha: float):
+def fma32(a, b, c):
+    """RN_float32(a*b + c) with ONE rounding — the fused multiply-add of the CUDA kernel (`fma.rn.f32`) and of C's
+    fmaf(), emulated in float64: the product of two float32 is exact in float64; the float64 sum is rounded once more
+    when cast to float32, which differs from the single rounding only when the float64 sum lands exactly on the midpoint
+    of two float32 neighbours while the exact sum does not — detected with the exact rounding error of the addition
+    (TwoSum) and repaired by nudging the sum off the midpoint in the error's direction."""
+    p = np.asarray(a, np.float64) * np.asarray(b, np.float64)
+    c64 = np.asarray(c, np.float64)
+    s = p + c64
+    bb = s - p
+    err = (p - (s - bb)) + (c64 - bb)
+    tie = ((s.view(np.uint64) & np.uint64(0x1FFFFFFF)) == np.uint64(0x10000000)) & (err != 0)
+    if tie.any():
+        s = np.where(tie, np.nextafter(s, np.where(err > 0, np.inf, -np.inf)), s)
+    return s.astype(F32)
+
+
+def chain(a, b, axis_terms):
+    """Fused chain  acc = fma(a_k, b_k, acc), k in axis_terms order, from 0.  a: (n, K), b: (K, m) -> (n, m)."""
+    acc = np.zeros((a.shape[0], b.shape[1]), F32)
+    for k in axis_terms:
+        acc = fma32(a[:, k:k + 1], b[k:k + 1, :], acc)
+    return acc
+
+
+def class_sum(a, b):
+    """Canonical sum over batch positions (rows of a and b):  (p0 + p2 + p4) + (p1 + p3 + p5),  p_c = fused chain over the
+    positions q = c, c+6, c+12, ...  a: (nb, n), b: (nb, m) -> a^T b (n, m)."""
+    nb = a.shape[0]
+    p = [chain(a.T, b, range(c, nb, 6)) for c in range(6)]
+    return ((p[0] + p[2]) + p[4]) + ((p[1] + p[3]) + p[5])
+
+
+def forward_canonical(x, We, Wd, alpha):
+    zh = chain(x, We, range(x.shape[1]))
+    h = lrelu(zh, alpha)
+    zy = chain(h, Wd, range(h.shape[1]))
+    return zh, h, zy, lrelu(zy, alpha)
+
+
+def batch_loss(diff, order="blas"):
+    """mean over the last axis, then over the rows (App. A.2).  Canonical order: plain sequential float32 sums (row by
+    row over the ETFs, then over the rows), as the C restatement writes them."""
+    sq = (diff * diff).astype(F32)
+    if order == "canonical":
+        rows = np.cumsum(sq, axis=1, dtype=F32)[:, -1] / F32(sq.shape[1])
+        return F32(np.cumsum(rows, dtype=F32)[-1] / F32(sq.shape[0]))
+    return F32(np.mean(np.mean(sq, axis=-1, dtype=F32), dtype=F32))
+
+
+def mse_and_grads(xb: np.ndarray, We: np.ndarray, Wd: np.ndarray, alpha: float, order: str = "blas"):
     """One train-step forward/backward: loss = sum((y-x)^2)/(B*E) (App. A.2), dWe, dWd."""
     B, E = xb.shape
-    zh, h, zy, y = forward(xb, We, Wd, alpha)
+    canon = order == "canonical"
+    zh, h, zy, y = forward_canonical(xb, We, Wd, alpha) if canon else forward(xb, We, Wd, alpha)
     diff = y - xb
     # Keras: mean over the last axis, then SUM_OVER_BATCH_SIZE over the rows.
-    loss = F32(np.mean(np.mean(diff * diff, axis=-1, dtype=F32), dtype=F32))
+    loss = batch_loss(diff, order)
     a = F32(alpha)
-    dzy = (F32(2.0) * diff / F32(B * E)).astype(F32)
+    if canon:
+        dzy = (F32(F32(2.0) / F32(B * E)) * diff).astype(F32)     # the MSE gradient's scalar, rounded once
+    else:
+        dzy = (F32(2.0) * diff / F32(B * E)).astype(F32)
     dzy = np.where(zy > 0, dzy, a * dzy).astype(F32)      # LeakyReluGrad: features > 0 ? g : a*g
-    dWd = (h.T @ dzy).astype(F32)
-    dh = dzy @ Wd.T
-    dzh = np.where(zh > 0, dh, a * dh).astype(F32)
-    dWe = (xb.T @ dzh).astype(F32)
+    if canon:
+        dWd = class_sum(h, dzy)
+        WdT = np.ascontiguousarray(Wd.T)
+        dh = chain(dzy, WdT, range(0, E, 2)) + chain(dzy, WdT, range(1, E, 2))
+        dzh = np.where(zh > 0, dh, a * dh).astype(F32)
+        dWe = class_sum(xb, dzh)
+    else:
+        dWd = (h.T @ dzy).astype(F32)
+        dh = dzy @ Wd.T
+        dzh = np.where(zh > 0, dh, a * dh).astype(F32)
+        dWe = (xb.T @ dzh).astype(F32)
     return loss, dWe, dWd
 
 
@@ -138,8 +209,23 @@ def split_at(n_rows: int, validation_split: float) -> int:
     return int(np.floor(n_rows * (1. - validation_split)))
 
 
-def fit(x, We0, Wd0, cfg: FitConfig | None = None, perm=None, record_grads_at=()):
+def _c_backend():
+    """The C restatement (oracle/c/fit_oracle.c), or None where it cannot be built (no gcc)."""
+    try:
+        from oracle import c_oracle
+        c_oracle._lib()
+        return c_oracle
+    except Exception:
+        return None
+
+
+def fit(x, We0, Wd0, cfg: FitConfig | None = None, perm=None, record_grads_at=(), order="canonical", backend="auto"):
     """Model.fit(x, x, ...) as the reference calls it (Autoencoder_encapsulate.py:83-96).
+
+    order  : "canonical" (fixed summation order, see the module docstring) or "blas".
+    backend: "numpy", "c", or "auto" — the canonical order runs through the bit-identical C restatement when it is
+             available (it is 50x faster than the float64 emulation of fused multiply-adds below; tests/test_oracle.py
+             checks the two against each other) unless gradients of several steps are asked for.
 
     x      : (N, E) training rows (already MinMax-scaled by the caller), any float dtype
     We0/Wd0: initial kernels (E, L) / (L, E)
@@ -150,6 +236,19 @@ def fit(x, We0, Wd0, cfg: FitConfig | None = None, perm=None, record_grads_at=()
     """
     cfg = cfg or FitConfig()
     x = np.ascontiguousarray(x, dtype=F32)
+    record_grads_at = tuple(record_grads_at)
+    if order == "canonical" and backend in ("auto", "c") and len(record_grads_at) <= 1:
+        c = _c_backend()
+        if c is None and backend == "c":
+            raise RuntimeError("the C restatement could not be built")
+        if c is not None and cfg == dataclasses.replace(FitConfig(), epochs=cfg.epochs, batch_size=cfg.batch_size,
+                                                        validation_split=cfg.validation_split, patience=cfg.patience,
+                                                        early_stop=cfg.early_stop):
+            out = c.fit(x, We0, Wd0, epochs=cfg.epochs, perm=perm, canonical=True, batch=cfg.batch_size,
+                        patience=cfg.patience, early_stop=cfg.early_stop, validation_split=cfg.validation_split,
+                        grad_step=(record_grads_at[0] if record_grads_at else None))
+            out.setdefault("grads", {})
+            return out
     We = np.array(We0, dtype=F32, copy=True)
     Wd = np.array(Wd0, dtype=F32, copy=True)
     n_fit = split_at(len(x), cfg.validation_split)
@@ -160,11 +259,11 @@ def fit(x, We0, Wd0, cfg: FitConfig | None = None, perm=None, record_grads_at=()
     bs = cfg.batch_size
     epochs_run = 0
     for epoch in range(cfg.epochs):
-        order = np.arange(n_fit) if perm is None else np.asarray(perm[epoch])
+        row_order = np.arange(n_fit) if perm is None else np.asarray(perm[epoch])
         acc, cnt = F32(0.), 0
         for lo in range(0, n_fit, bs):
-            xb = x_fit[order[lo:lo + bs]]
-            loss, dWe, dWd = mse_and_grads(xb, We, Wd, cfg.alpha)
+            xb = x_fit[row_order[lo:lo + bs]]
+            loss, dWe, dWd = mse_and_grads(xb, We, Wd, cfg.alpha, order)
             if opt.t in record_grads_at:
                 grads[opt.t] = (dWe.copy(), dWd.copy())
             opt.step([We, Wd], [dWe, dWd])
@@ -174,16 +273,16 @@ def fit(x, We0, Wd0, cfg: FitConfig | None = None, perm=None, record_grads_at=()
         vacc, vcnt = F32(0.), 0
         for lo in range(0, len(x_val), bs):
             xb = x_val[lo:lo + bs]
-            y = forward(xb, We, Wd, cfg.alpha)[3]
-            d = y - xb
-            vl = F32(np.mean(np.mean(d * d, axis=-1, dtype=F32), dtype=F32))
+            y = (forward_canonical if order == "canonical" else forward)(xb, We, Wd, cfg.alpha)[3]
+            vl = batch_loss(y - xb, order)
             vacc = F32(vacc + vl * F32(len(xb)))
             vcnt += len(xb)
         val = F32(vacc / F32(vcnt)) if vcnt else F32(np.nan)
         val_hist.append(val)
         epochs_run = epoch + 1
-        if cfg.early_stop:
-            # EarlyStopping.on_epoch_end (App. A.6): strict '<', stop needs epoch > 0.
+        if cfg.early_stop and vcnt:
+            # EarlyStopping.on_epoch_end (App. A.6): strict '<', stop needs epoch > 0.  Without validation rows there is
+            # no 'val_loss': Keras warns, leaves `wait` alone and never stops.
             wait += 1
             if val < best:
                 best, wait = val, 0

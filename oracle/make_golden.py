@@ -57,6 +57,68 @@ def run_reference_AE(ae_mod, keras, data, L, seed, perm=None, patience=5, epochs
     return res
 
 
+def run_reference_deadunit(ae_mod, keras, data, g, dead=(3,), dup=None):
+    """Rank-deficient OLS windows through the reference's own `ante`/`post`/`turnover` (Autoencoder_encapsulate.py:133-224):
+    the trained L=8 kernels of fixture `g` with encoder column(s) `dead` zeroed (a latent unit that never fires) and,
+    optionally, column dup[1] made a copy of column dup[0] (two identical latent factors).  `OLS(Y, X).fit()` (:151) then
+    returns the MINIMUM-NORM solution (statsmodels' pinv)."""
+    etf, hfd, rf = data
+    from sklearn.model_selection import train_test_split
+    X_train, X_test, Y_train, Y_test = train_test_split(etf, hfd, shuffle=False, test_size=.5)
+    We, Wd = g["We"].copy(), g["Wd"].copy()
+    for c in dead:
+        We[:, c] = 0.
+    if dup is not None:
+        We[:, dup[1]] = We[:, dup[0]]
+    feed = iter([We, Wd])
+    keras.CONTROL.update(w0=lambda i, o: next(feed), perm=None, record_grads_at=(), fit_overrides={})
+    with refbridge.positional_series_getitem():
+        ae = ae_mod.AE(X_train, Y_train, X_test, Y_test, We.shape[1])
+        ae.autoencoder = ae_mod.Autoencoder(We.shape[1])          # what train() builds at :78, with the given kernels
+        ante = ae.ante(rf, hfd)
+        from cleaned_names import hfd_fullname
+        turn = ae.turnover(hfd_fullname)
+        post = ae.post(etf)
+        res = dict(We=We, Wd=Wd, ante=ante.values, post=post.values, turnover=turn["Turnover"].values,
+                   weights=np.array([w.values for w in ae.strat_weight_on_etf]))
+    keras.CONTROL.update(w0=None)
+    return res
+
+
+def run_reference_stacked(ae_mod, helper, keras, data, L, seed):
+    """The notebook's GAN-augmented run (autoencoder_v4.ipynb cells 47-51, raw lines :1368-1427) on the reference's own
+    generated paths GAN/generated_data2022-07-09.pkl: inverse MinMax with the scaler of the joined real data,
+    helper.factor_hf_split, vstack on top of the real training half, then AE(...).train() — 1 848 training rows."""
+    etf, hfd, rf = data
+    from sklearn.model_selection import train_test_split
+    from sklearn.preprocessing import MinMaxScaler
+    gen_data = helper.dic_read(os.path.join(refbridge.REFERENCE_ROOT, "GAN", "generated_data2022-07-09.pkl"))
+    data_scale = MinMaxScaler()
+    data_scale.fit(etf.join(hfd).join(rf))                                              # cell 47
+    ret_gen = np.array([data_scale.inverse_transform(gen_data[i]) for i in range(gen_data.shape[0])])
+    train_factor, train_temp = helper.factor_hf_split(ret_gen, 22)                      # cell 48
+    train_hf = train_temp[:, :13]
+    X_train, X_test, Y_train, Y_test = train_test_split(etf, hfd, shuffle=False, test_size=.5)
+    X_tr = np.vstack([train_factor, np.array(X_train)])                                 # cell 50
+    Y_tr = np.vstack([train_hf, np.array(Y_train)])
+    We0, Wd0 = fitcore.initial_weights(seed, etf.shape[1], L)
+    feed = iter([We0, Wd0])
+    keras.CONTROL.update(w0=lambda i, o: next(feed), perm=None, record_grads_at=(), fit_overrides={})
+    with refbridge.positional_series_getitem():
+        ae = ae_mod.AE(X_tr, Y_tr, X_test, Y_test, L)                                   # cell 51
+        ae.train(verbose=0, plot=False)
+        fit = keras.CONTROL["last_fit"]
+        res = dict(gen_data=np.asarray(gen_data), We0=We0, Wd0=Wd0, We=fit["We"], Wd=fit["Wd"], loss=fit["loss"],
+                   val_loss=fit["val_loss"], epochs_run=np.int32(fit["epochs_run"]), n_train_rows=np.int32(len(X_tr)),
+                   is_r2=ae.model_IS_r2(), is_rmse=ae.model_IS_RMSE(),
+                   oos_r2=np.array(ae.model_OOS_r2()), oos_rmse=np.array(ae.model_OOS_RMSE()))
+        ante = ae.ante(rf, hfd)
+        post = ae.post(etf)
+        res.update(ante=ante.values, post=post.values)
+    keras.CONTROL.update(w0=None)
+    return res
+
+
 def helper_vectors(helper):
     """Outputs of the reference's numeric helpers on seeded random inputs."""
     import random
@@ -155,6 +217,14 @@ def main():
     res["perm_seed"] = np.int32(123)
     np.savez_compressed(os.path.join(OUT, "ref_modeR_L8_shuffled.npz"), **res)
     print(f"L=8 shuffled: epochs_run={res['epochs_run']} is_r2={res['is_r2']:.4f}")
+    g8 = dict(np.load(os.path.join(OUT, "ref_modeR_L8.npz")))
+    np.savez_compressed(os.path.join(OUT, "ref_modeR_L8_deadunit.npz"),
+                        **run_reference_deadunit(ae_mod, keras, (etf, hfd, rf), g8, dead=(3,)))
+    np.savez_compressed(os.path.join(OUT, "ref_modeR_L8_rank6.npz"),
+                        **run_reference_deadunit(ae_mod, keras, (etf, hfd, rf), g8, dead=(3,), dup=(1, 6)))
+    res = run_reference_stacked(ae_mod, helper, keras, (etf, hfd, rf), 8, seed=123)
+    np.savez_compressed(os.path.join(OUT, "ref_stacked_L8.npz"), **res)
+    print(f"stacked rows L=8: {res['n_train_rows']} rows, epochs_run={res['epochs_run']} is_r2={res['is_r2']:.4f}")
     np.savez_compressed(os.path.join(OUT, "ref_helpers.npz"), **helper_vectors(helper))
     np.savez_compressed(os.path.join(OUT, "ref_ff_factors.npz"), **ff_factor_fixture())
     refbridge.unload()

@@ -1,8 +1,11 @@
 """Parity of the CUDA path (through the C ABI) against the committed golden fixtures — outputs of
 the REFERENCE'S OWN FILES run over shims (oracle/make_golden.py) — and against the portable CPU
-oracle on seeded synthetic inputs.  Tolerance (BASELINE.json north_star): window indices and
-LeakyReLU masks bit-exact; per-epoch losses, gradients, final kernels and replica returns within
-1e-5 relative in FP32.  All tests here need a GPU."""
+oracle on seeded synthetic inputs.  Bar (BASELINE.json north_star asks 1e-5 relative in FP32): window
+indices and LeakyReLU masks bit-exact; gradients and trained kernels of the narrow fit kernel
+BIT-IDENTICAL to the oracle (both follow the canonical summation order), for every
+thread mapping and staging mode, over whole 1000-epoch runs; per-epoch losses (summed in each
+implementation's own order — they feed nothing back), quality series, weights, replica returns
+within 1e-5.  All tests here need a GPU."""
 import numpy as np
 import pytest
 import torch
@@ -12,10 +15,6 @@ from conftest import load_golden, rel_err
 pytestmark = pytest.mark.gpu
 
 TOL = 1e-5
-# A 1000-epoch run takes 3000 dependent Nadam steps: last-bit differences of the summation order (every kernel mapping
-# and the numpy oracle sum in their own order) grow along the trajectory.  The first 100 epochs must hold TOL; the whole
-# run holds TOL_RUN (largest drift measured over the mappings: 3.2e-5 on the L=8 validation loss).
-TOL_RUN = 1e-4
 
 
 @pytest.fixture(scope="module")
@@ -49,10 +48,9 @@ def test_fit_matches_reference_run(hf, data, L, wpt):
     assert int(res.status[0]) == 0
     loss, val = res.loss[0, :n].cpu().numpy(), res.val_loss[0, :n].cpu().numpy()
     dl, dv = np.abs(loss - g["loss"]) / g["loss"], np.abs(val - g["val_loss"]) / g["val_loss"]
-    assert dl[:100].max() < TOL and dv[:100].max() < TOL
-    assert dl.max() < TOL_RUN and dv.max() < TOL_RUN
+    assert dl.max() < TOL and dv.max() < TOL                  # all 1000 epochs
     We, Wd = hf.engine.unpack_weights(res.W[0].cpu().numpy(), data.E, L)
-    assert rel_err(We, g["We"]) < TOL_RUN and rel_err(Wd, g["Wd"]) < TOL_RUN
+    assert np.array_equal(We, g["We"]) and np.array_equal(Wd, g["Wd"])     # 3000 Nadam steps later: the same bits
 
 
 @pytest.mark.parametrize("L", [2, 8, 21])
@@ -61,8 +59,7 @@ def test_gradients_match_reference_run(hf, data, L, step):
     g = load_golden(f"ref_modeR_L{L}")
     res, _ = _fit_golden(hf, data, g, dump_step=step, max_epochs=step // 3 + 1, early_stop=0)
     gWe, gWd = hf.engine.unpack_weights(res.grads[0].cpu().numpy(), data.E, L)
-    assert rel_err(gWe, g[f"grad_We_step{step}"]) < TOL
-    assert rel_err(gWd, g[f"grad_Wd_step{step}"]) < TOL
+    assert np.array_equal(gWe, g[f"grad_We_step{step}"]) and np.array_equal(gWd, g[f"grad_Wd_step{step}"])
 
 
 def test_shuffled_fit_with_early_stopping(hf, data):
@@ -77,7 +74,7 @@ def test_shuffled_fit_with_early_stopping(hf, data):
         assert np.max(np.abs(res.loss[0, :n].cpu().numpy() - g["loss"]) / g["loss"]) < TOL
         assert np.max(np.abs(res.val_loss[0, :n].cpu().numpy() - g["val_loss"]) / g["val_loss"]) < TOL
         We, Wd = hf.engine.unpack_weights(res.W[0].cpu().numpy(), data.E, L)
-        assert rel_err(We, g["We"]) < TOL and rel_err(Wd, g["Wd"]) < TOL
+        assert np.array_equal(We, g["We"]) and np.array_equal(Wd, g["Wd"])
         assert torch.isnan(res.loss[0, n:]).all()          # history holds one entry per epoch run
 
 
@@ -105,6 +102,64 @@ def test_eval_matches_reference_run(hf, data, name):
     lat = g["latent"].astype(np.float32)
     ref_mask = ((lat[24:24 + 144] @ g["Wd"]) < 0).astype(np.uint8)
     assert np.array_equal(ev.mask[0].cpu().numpy(), ref_mask)
+
+
+@pytest.mark.parametrize("name,rank", [("ref_modeR_L8_deadunit", 7), ("ref_modeR_L8_rank6", 6)])
+def test_rank_deficient_ols_matches_reference(hf, data, name, rank):
+    """A latent unit that never fires (zero encoder column) and two identical latent factors: the OLS windows are rank
+    deficient and `OLS(Y, X).fit()` (Autoencoder_encapsulate.py:151) returns pinv's MINIMUM-NORM solution.  Expected
+    values: the reference's own ante / post / turnover run on those kernels (oracle/make_golden.py)."""
+    g = load_golden(name)
+    E, L = data.E, g["We"].shape[1]
+    W = hf.engine.to_device(hf.engine.pack_weights([(g["We"], g["Wd"])], E, 2 * E * L), data.device)
+    for rolling in (False, True):
+        ev = hf.predict_metrics(data.Xtr64, data.Xte64, data.Yte64, data.rf64, data.sigma, [L], W,
+                                window=24, want_oos=False, want_weights=True, beta_rolling=rolling)
+        assert int(ev.status[0]) == 2                          # informational: the minimum-norm path ran
+        assert bool(torch.isfinite(ev.ante).all())
+        if rolling:
+            continue                                           # (every window solved the same way; values below are window 0's)
+        assert rel_err(ev.weights[0].cpu().numpy(), g["weights"]) < TOL
+        assert rel_err(ev.ante[0].cpu().numpy(), g["ante"]) < TOL
+        assert rel_err(ev.post[0].cpu().numpy(), g["post"]) < TOL
+        assert rel_err(ev.turnover[0].cpu().numpy(), g["turnover"]) < TOL
+        beta = ev.beta[0, :L].cpu().numpy()
+        dead = np.where(~g["We"].any(axis=0))[0]
+        assert np.all(beta[dead] == 0.)                        # the dead unit carries no weight, as pinv gives it
+
+
+def test_stacked_rows_flow_on_reference_generated_paths(hf, ref_inputs, monkeypatch):
+    """The notebook's GAN-augmented run (autoencoder_v4.ipynb:1368-1427) on the reference's own generated paths
+    (GAN/generated_data2022-07-09.pkl, carried in the fixture): inverse MinMax with the scaler of the joined real data,
+    factor_hf_split, vstack over the real training half, AE(...).train() on 1 848 rows (29 steps per epoch, batch-tile
+    mode), quality, ante, post — through the drop-in facade, against the reference's own run of those cells."""
+    import pandas as pd
+    from sklearn.preprocessing import MinMaxScaler
+    g = load_golden("ref_stacked_L8")
+    idx = pd.to_datetime(ref_inputs["dates"])
+    etf = pd.DataFrame(ref_inputs["etf"], index=idx, columns=ref_inputs["etf_columns"])
+    hfd = pd.DataFrame(ref_inputs["hfd"], index=idx, columns=ref_inputs["hfd_columns"])
+    rf = pd.DataFrame(ref_inputs["rf"], index=idx, columns=["RF"])
+    data_scale = MinMaxScaler()
+    data_scale.fit(etf.join(hfd).join(rf))                                                   # cell 47
+    ret_gen = np.array([data_scale.inverse_transform(p) for p in g["gen_data"]])
+    train_factor, train_temp = hf.helper.factor_hf_split(ret_gen, 22)                        # cell 48 (kernel (a))
+    X_tr = np.vstack([train_factor, np.array(etf.iloc[:168])])                               # cell 50
+    Y_tr = np.vstack([train_temp[:, :13], np.array(hfd.iloc[:168])])
+    assert len(X_tr) == int(g["n_train_rows"]) == 1848
+    monkeypatch.setattr(hf.engine, "initial_weights", lambda seed, E, L: (g["We0"].copy(), g["Wd0"].copy()))
+    monkeypatch.setattr(hf.config, "shuffle", False)
+    ae = hf.AE(X_tr, Y_tr, etf.iloc[168:], hfd.iloc[168:], 8)                                # cell 51
+    ae.train(verbose=0, plot=False)
+    n = int(g["epochs_run"])
+    assert len(ae.history.history["loss"]) == n
+    assert np.max(np.abs(np.array(ae.history.history["loss"], np.float32) - g["loss"]) / g["loss"]) < TOL
+    assert np.max(np.abs(np.array(ae.history.history["val_loss"], np.float32) - g["val_loss"]) / g["val_loss"]) < TOL
+    assert np.array_equal(ae.autoencoder.We, g["We"]) and np.array_equal(ae.autoencoder.Wd, g["Wd"])
+    assert abs(ae.model_IS_r2() - g["is_r2"]) < TOL and abs(ae.model_IS_RMSE() - g["is_rmse"]) < TOL
+    assert rel_err(ae.model_OOS_r2(), g["oos_r2"]) < TOL and rel_err(ae.model_OOS_RMSE(), g["oos_rmse"]) < TOL
+    assert rel_err(ae.ante(rf, hfd).values, g["ante"]) < TOL
+    assert rel_err(ae.post(etf).values, g["post"]) < TOL
 
 
 def test_mode_r_end_to_end(hf, data, ref_inputs):
@@ -192,7 +247,7 @@ def test_fit_vs_oracle_synthetic(hf, E, L, T, batch):
         assert np.max(np.abs(res.loss[0, :40].cpu().numpy() - o["loss"]) / o["loss"]) < TOL
         assert np.max(np.abs(res.val_loss[0, :40].cpu().numpy() - o["val_loss"]) / o["val_loss"]) < TOL
         We, Wd = hf.engine.unpack_weights(res.W[0].cpu().numpy(), E, L)
-        assert rel_err(We, o["We"]) < TOL and rel_err(Wd, o["Wd"]) < TOL
+        assert np.array_equal(We, o["We"]) and np.array_equal(Wd, o["Wd"])
 
 
 def test_per_task_blocks_and_perms(hf):
@@ -213,7 +268,7 @@ def test_per_task_blocks_and_perms(hf):
         o = fitcore.fit(xs[i], *pairs[i], fitcore.FitConfig(epochs=12, early_stop=False), perm=perms[i])
         assert np.max(np.abs(res.loss[i, :12].cpu().numpy() - o["loss"]) / o["loss"]) < TOL
         We, Wd = hf.engine.unpack_weights(res.W[i].cpu().numpy(), E, L)
-        assert rel_err(We, o["We"]) < TOL and rel_err(Wd, o["Wd"]) < TOL
+        assert np.array_equal(We, o["We"]) and np.array_equal(Wd, o["Wd"])
 
 
 def test_full_size_grid_properties(hf, data):
@@ -232,7 +287,9 @@ def test_full_size_grid_properties(hf, data):
     pick = [tasks.index(t3) for t3 in tasks3]
     for j, i in enumerate(pick):
         assert rel_err(fit3.loss[j, :60].cpu().numpy(), fit.loss[i, :60].cpu().numpy()) < TOL
-        assert rel_err(ev3.ante[j].cpu().numpy(), ev.ante[i].cpu().numpy()) < 1e-4
+        L3 = tasks3[j][0]
+        assert torch.equal(fit3.W[j, :2 * E * L3], fit.W[i, :2 * E * L3])     # canonical order: mapping-independent bits
+        assert torch.equal(ev3.ante[j], ev.ante[i])
 
 
 def test_window_gather(hf):
@@ -250,6 +307,14 @@ def test_window_gather(hf):
     out = hf.window_gather(Rd, starts[:9], 48, col_lo=0, ncols=22, minmax=True).cpu().numpy()
     ref = np.stack([ae_oracle.minmax_fit_transform(R[s:s + 48, :22]).astype(np.float32) for s in starts[:9]])
     assert np.array_equal(out, ref)
+    # float64 source: sklearn's float64 MinMax followed by the cast to float32, bit for bit (not the same numbers as
+    # scaling the float32-rounded matrix); plain gather = rounding
+    R64 = rng.normal(size=(337, 36)) * .03
+    R64d = hf.engine.to_device(R64, dev)
+    out = hf.window_gather(R64d, starts[:9], 48, col_lo=3, ncols=22, minmax=True).cpu().numpy()
+    ref = np.stack([ae_oracle.minmax_fit_transform(R64[s:s + 48, 3:25]).astype(np.float32) for s in starts[:9]])
+    assert np.array_equal(out, ref)
+    assert np.array_equal(hf.window_gather(R64d, starts[:4], 48).cpu().numpy(), np.stack([R64[s:s + 48] for s in starts[:4]]).astype(np.float32))
     with pytest.raises(hf._lib.HfrepError):
         hf.window_gather(Rd, np.array([300], np.int32), 48)
 
@@ -321,9 +386,12 @@ def test_errors_and_empty(hf, data):
     assert res.W.shape[0] == 0
 
 
-def test_mode_w_rolling_refit(hf):
+@pytest.mark.parametrize("src", ["float64", "float32"])
+def test_mode_w_rolling_refit(hf, src):
     """Rolling refit (window gather + MinMax into scratch -> fit per window -> one replica row per window) against the
-    Mode-W oracle, which calls the reference's AE restatement once per window."""
+    Mode-W oracle, which calls the reference's AE restatement once per window.  float64 history (the reference's
+    DataFrames): MinMax on the float64 values, rounded once, exactly the reference pipeline; float32 history: the
+    one-call hfrep_fit_windows path, windows cut from the float32 matrix."""
     from oracle import ae_oracle, fitcore
     rng = np.random.default_rng(5)
     T, E, F, W, L, ols = 70, 22, 5, 40, 3, 12
@@ -332,12 +400,15 @@ def test_mode_w_rolling_refit(hf):
     hfd = etf @ (rng.normal(size=(E, F)) * .1) + rng.normal(size=(T, F)) * .004
     rf = np.full(T, 1e-3)
     seeds = (7, 8)
+    if src == "float32":
+        etf = etf.astype(np.float32)
     out = hf.run_mode_w(etf, hfd, rf, train_window=W, latent_dim=L, seeds=seeds, ols_window=ols, device="cuda:0",
                         max_epochs=25, early_stop=0)
+    etf = etf.astype(np.float64)
     ts = out["t"]
     assert np.array_equal(ts, np.arange(W, T - 1)) and out["replica"].shape == (2, len(ts), F)
     assert int(out["fit"].status.abs().sum()) == 0 and int(out["eval"].status.abs().sum()) == 0
-    etf32 = etf.astype(np.float32).astype(np.float64)          # kernel (a) cuts the training windows from the f32 matrix
+    etf32 = etf                                                # the training windows' source, as float64 values
     # scratch blocks = MinMax of each window, bit-exact
     blocks = out["blocks"].cpu().numpy()
     for wi in (0, len(ts) - 1):
@@ -386,7 +457,7 @@ def test_long_training_block_stacked_rows(hf):
         assert np.max(np.abs(res.loss[0, :6].cpu().numpy() - o["loss"]) / o["loss"]) < TOL
         assert np.max(np.abs(res.val_loss[0, :6].cpu().numpy() - o["val_loss"]) / o["val_loss"]) < TOL
         We, Wd = hf.engine.unpack_weights(res.W[0].cpu().numpy(), E, L)
-        assert rel_err(We, o["We"]) < TOL and rel_err(Wd, o["Wd"]) < TOL
+        assert np.array_equal(We, o["We"]) and np.array_equal(Wd, o["Wd"])
 
 
 def test_device_side_shuffle(hf, data):
@@ -410,7 +481,7 @@ def test_device_side_shuffle(hf, data):
             assert n == o["epochs_run"]
             assert np.max(np.abs(res.loss[i, :n].cpu().numpy() - o["loss"]) / o["loss"]) < TOL
             We, _ = hf.engine.unpack_weights(res.W[i].cpu().numpy(), E, L)
-            assert rel_err(We, o["We"]) < TOL
+            assert np.array_equal(We, o["We"])
 
 
 @pytest.mark.parametrize("L", [2, 8, 21])
@@ -456,7 +527,7 @@ def test_wide_variant_rolling_refit(hf, E, F, L, K):
                              windows=[0, 5, 16], max_epochs=12, early_stop=0)
     ts = out["t"]
     assert int(out["fit"].status.abs().sum()) == 0 and int(out["eval_status"].abs().sum()) == 0
-    etf32 = etf.astype(np.float32).astype(np.float64)
+    etf32 = etf                                                # float64 history: MinMax on the float64 values
     cfg = fitcore.FitConfig(epochs=12, early_stop=False)
     rep = out["replica"].cpu().numpy()
     for wi, t in enumerate(ts):

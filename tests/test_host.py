@@ -90,13 +90,14 @@ def test_host_prep_matches_oracle(ref_inputs):
 
 def test_nadam_schedule_matches_oracle():
     cfg = _lib.fit_cfg()
-    sched = np.zeros((3000, 4), np.float32)
+    sched = np.zeros((3000, _lib.SCHED_STRIDE), np.float32)
     _lib.check(_lib.lib.hfrep_nadam_schedule(ctypes.byref(cfg), 3000, _lib.ptr(sched)))
     opt = fitcore.Nadam(fitcore.FitConfig(), [(1,)])
+    one = np.float32(1.)
     for t in range(3000):
         mu_t, mu_t1, ms_new, ms_next, vden = opt.coefficients()
-        want = [(1 - mu_t) / (1 - ms_new), mu_t1 / (1 - ms_next), 1 / vden, mu_t]
-        assert np.allclose(sched[t], want, rtol=5e-7), t
+        want = np.array([one - ms_new, one - ms_next, vden, one - mu_t, mu_t1, mu_t, 0, 0], np.float32)
+        assert np.array_equal(sched[t], want), t          # the very scalars the oracle divides and multiplies by: bit-equal
         opt.m_cache = ms_new
         opt.t += 1
 
@@ -139,6 +140,21 @@ local = torch.tensor([[float(i), float(i) * 2] for i in mine], dtype=torch.float
 full = D.gather_results(local, n)
 assert torch.equal(full[:, 0], torch.arange(n, dtype=torch.float64)), full
 assert torch.equal(full[:, 1], 2 * torch.arange(n, dtype=torch.float64))
+# the packed-record gather: several tensors of different dtypes and shapes (odd byte counts, a missing one) in ONE collective
+idx = torch.from_numpy(mine)
+fields = [idx.to(torch.float64)[:, None, None] * torch.ones(1, 3, 2, dtype=torch.float64), None,
+          idx.to(torch.int32), (idx % 7).to(torch.uint8)[:, None].repeat(1, 5), idx.to(torch.float32)[:, None] * torch.arange(3.)]
+calls = []
+orig = dist.all_gather_into_tensor
+dist.all_gather_into_tensor = lambda *a, **k: (calls.append(1), orig(*a, **k))[1]
+got = D.gather_records(fields, n)
+dist.all_gather_into_tensor = orig
+g = torch.arange(n)
+assert len(calls) == 1 and got[1] is None
+assert torch.equal(got[0], g.to(torch.float64)[:, None, None] * torch.ones(1, 3, 2, dtype=torch.float64))
+assert torch.equal(got[2], g.to(torch.int32)) and got[2].dtype == torch.int32
+assert torch.equal(got[3], (g % 7).to(torch.uint8)[:, None].repeat(1, 5))
+assert torch.equal(got[4], g.to(torch.float32)[:, None] * torch.arange(3.))
 dist.barrier(); dist.destroy_process_group()
 print("ok", rank)
 """)

@@ -27,6 +27,8 @@ def _call(hf, static, R, starts, T_win, E, task_L, task_win, W0, epochs):
     out = dict(W=torch.zeros_like(W0), loss=torch.zeros((n, epochs), device=dev), val=torch.zeros((n, epochs), device=dev),
                epochs=torch.zeros(n, dtype=torch.int32, device=dev), status=torch.zeros(n, dtype=torch.int32, device=dev))
     stream = hf._lib.stream_ptr()
+    torch.cuda.synchronize()
+    free_before = torch.cuda.mem_get_info(dev)[0]            # every torch allocation of this call is done by now
     if static:
         rc = lib.hfrep_fit_windows_static(C.byref(cfg), ptr(R), R.shape[0], R.shape[1], 0, ptr(st), n_win, n, ptr(tL), ptr(tw),
                                           ptr(W0), W0.shape[1], None, 0, None, ptr(sched), ptr(out["W"]), ptr(out["loss"]),
@@ -38,6 +40,7 @@ def _call(hf, static, R, starts, T_win, E, task_L, task_win, W0, epochs):
                                    ptr(W0), W0.shape[1], None, 0, None, ptr(sched), ptr(ws), ws_bytes, ptr(out["W"]),
                                    ptr(out["loss"]), ptr(out["val"]), ptr(out["epochs"]), ptr(out["status"]), stream)
     torch.cuda.synchronize()
+    out["free_delta"] = free_before - torch.cuda.mem_get_info(dev)[0] if static else None
     return rc, out
 
 
@@ -58,6 +61,8 @@ def test_fit_windows_static_matches_workspace_variant():
         rc_new, new = _call(hf, True, R, starts, T_win, E, task_L, task_win, W0, epochs)
         assert rc_ref == 0 and rc_new == 0, hf._lib.lib.hfrep_last_error()
         assert int(new["status"].abs().sum()) == 0 and int(new["epochs"].min()) == epochs
+        if call == 1:      # once the first call has loaded the array and the kernels, a call takes no device memory at all
+            assert new["free_delta"] == 0, new["free_delta"]
         for k in ("W", "loss", "val"):                      # same kernels on the same blocks: 1e-5 relative is the suite's bar
             a, b = new[k].cpu().numpy(), ref[k].cpu().numpy()
             assert np.max(np.abs(a - b)) <= 1e-5 * np.max(np.abs(b)), (call, k)
