@@ -1,18 +1,24 @@
 #!/usr/bin/env python
 """bench.py — replication task-fits/sec on B200 (BASELINE.json metric), one process per GPU.
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--seeds S] [--impl reference]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--cpu-procs P]
 
 A *step* is one pass of the hot path over one batch of synthetic input of the named shape
 (configs[1] of BASELINE.json: 337 months x 22 factor ETFs / 13 fund indices / rf; the notebook's
-sweep L = 1..21, deterministic row order so every fit runs all 1000 epochs; all 13 funds x 145
-rolling windows evaluated per fit): kernel (b) fits S x 21 autoencoders, kernel (c) scores them.
-S = 1 seed per GPU by default (configs[1]); every rank of a multi-GPU run takes its own seeds
-(weak scaling, no data-path collective; one result all-gather outside the hot path).
-The 64-seed ensemble of configs[2] is measured in the same run and reported under "ensemble".
+sweep L = 1..21, one seed, deterministic row order, EarlyStopping(patience 5) on as in the reference
+— run lengths are data dependent, `config.epochs_run_mean` reports them; all 13 funds x 145 rolling
+windows evaluated per fit): kernel (b) fits 21 autoencoders, kernel (c) scores them.
+Multi-GPU (`--gpus N`, one rank per GPU): every rank runs that sweep for ITS OWN seed (123 + rank):
+distinct fits, no data-path collective, `value` = all ranks' fits / the slowest rank's time (weak
+scaling).  The same line carries `sharded`: configs[2] (L = 1..21 x 64 seeds = 1 344 fits) dealt
+cyclically over the N ranks through the public API with host buffers, finished by the one NCCL
+all-gather of result records, timed end to end.  At N = 1 the line also carries the throughput
+regime (`ensemble`), the HBM-bound kernels (`hbm_kernels`), configs[3] (`wide`) and configs[4]
+(`paths`) samples and the CPU baselines.
 
-`--impl reference` times the CPU restatement of the reference path (oracle/ae_oracle.py; the
-reference itself cannot travel to the GPU box and Keras is not installable) on all host cores.
+`--impl reference` times the CPU restatement of the reference path (oracle/ae_oracle.py — the
+reference itself needs Keras, which cannot be installed, and cannot travel to the GPU box) on
+`--cpu-procs` host processes (default 16, fewer if the box has fewer cores).
 """
 from __future__ import annotations
 
@@ -34,6 +40,7 @@ UNIT = "fits/s"
 T_ALL, E, F, WINDOW = 337, 22, 13, 24
 LATENTS = list(range(1, 22))
 EPOCHS = 1000
+WORKLOAD = "cfg2: 13 indices x 145 windows x L=1..21 x 1 seed per GPU (Mode R), synthetic 337x(22+13+1)"
 # dram__bytes_read.sum + dram__bytes_write.sum per fit_kernel launch of the cfg2 sweep, from the committed
 # `ncu --set full` capture (profiles/r1_ncu_full_cfg2_summary.txt): the kernel is shared-memory resident.
 NCU_DRAM_BYTES_PER_FIT_LAUNCH = 80e3
@@ -51,7 +58,7 @@ def synthetic_returns(seed=20240611):
     return etf, hfd, rf
 
 
-def flops_per_epoch(L, T_fit=126, T_val=42, batch=48):
+def flops_per_epoch(L, T_fit=126, T_val=42, batch=48, E=E):
     """Algorithmic flop of one epoch of one fit."""
     steps = -(-T_fit // batch)
     mm = 10 * T_fit * E * L + 4 * T_val * E * L
@@ -68,37 +75,44 @@ def _cpu_task(args):
     We0, Wd0 = fitcore.initial_weights(seed, E, L)
     cfg = fitcore.FitConfig(epochs=EPOCHS, early_stop=True)
     t = time.perf_counter()
-    ae_oracle.run_task(etf[:168], hfd[:168], etf[168:], hfd[168:], rf, etf, L, We0, Wd0, cfg=cfg)
-    return time.perf_counter() - t
+    out = ae_oracle.run_task(etf[:168], hfd[:168], etf[168:], hfd[168:], rf, etf, L, We0, Wd0, cfg=cfg)
+    return time.perf_counter() - t, int(out["epochs_run"])
+
+
+CPU_IMPL = ("oracle/ae_oracle.py: the fit as compiled C in the canonical summation order (oracle/c/fit_oracle.c, one thread "
+            "per task — the reference pins TF to one thread, helper.py:38), every evaluation stage in numpy float64")
 
 
 def cpu_reference_arm(args):
-    """The reference path's CPU restatement on all host cores: each step = the 21-fit sweep."""
+    """The reference path's CPU restatement on --cpu-procs host processes: each step = the 21-fit sweep."""
     import multiprocessing as mp
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     cores = len(os.sched_getaffinity(0))
+    procs = max(1, min(args.cpu_procs, cores, len(LATENTS)))
     tasks = [(L, 123) for L in LATENTS]
     ctx = mp.get_context("fork")
-    times = []
-    with ctx.Pool(min(cores, len(tasks))) as pool:
+    times, epochs = [], []
+    with ctx.Pool(procs) as pool:
         for i in range(args.warmup + args.steps):
             t = time.perf_counter()
-            pool.map(_cpu_task, tasks, chunksize=1)
+            res = pool.map(_cpu_task, tasks, chunksize=1)
             dt = time.perf_counter() - t
             if i >= args.warmup:
                 times.append(dt)
+                epochs = [e for _, e in res]
     total = sum(times)
     value = len(tasks) * len(times) / total
-    sample = f"{len(times)} x full sweep L=1..21 (21 fits, 1000 epochs each, all evaluation stages), numpy float32/float64"
+    sample = (f"{len(times)} x full sweep L=1..21 (21 fits, up to {EPOCHS} epochs with early stopping: {np.mean(epochs):.0f} run on "
+              f"average; all evaluation stages) on {procs} processes of {cores} usable cores; {CPU_IMPL}")
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": 1e3 * total / len(times), "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": "cfg2: 13 indices x 145 windows x L=1..21 x 1 seed (Mode R), synthetic 337x(22+13+1)",
-                   "epochs": EPOCHS, "shuffle": False},
-        "cpu_baseline": {"value": value, "unit": UNIT, "cores": min(cores, len(tasks)), "kind": "port", "sample": sample},
+        "config": {"workload": WORKLOAD, "epochs": EPOCHS, "epochs_run_mean": float(np.mean(epochs)), "shuffle": False,
+                   "early_stop": True},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": procs, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     print(json.dumps(line))
@@ -107,20 +121,22 @@ def cpu_reference_arm(args):
 def cpu_baseline_single_core(budget_s=20.):
     """Oracle port on ONE core over a bounded sample of the same sweep (about `budget_s` seconds)."""
     sample, spent = [], 0.
-    for L in (1, 4, 8, 11, 14, 18, 21, 2, 6, 16, 20, 3, 9, 12, 5, 7, 10, 13, 15, 17, 19):
-        dt = _cpu_task((L, 123))
-        sample.append(L)
-        spent += dt
-        if spent > budget_s:
-            break
+    order = (1, 4, 8, 11, 14, 18, 21, 2, 6, 16, 20, 3, 9, 12, 5, 7, 10, 13, 15, 17, 19)
+    while spent < budget_s:
+        for L in order:
+            dt, _ = _cpu_task((L, 123))
+            sample.append(L)
+            spent += dt
+            if spent > budget_s:
+                break
     return {"value": len(sample) / spent, "unit": UNIT, "cores": 1, "kind": "port",
-            "sample": f"L in {sorted(sample)} of the cfg2 sweep, full pipeline, {spent:.1f} s on one core"}
+            "sample": f"{len(sample)} fits (widths cycling through L = 1..21) of the cfg2 sweep, full pipeline, {spent:.1f} s on one core; {CPU_IMPL}"}
 
 
 def cpu_best_effort():
-    """the fit alone as compiled C (oracle/c/fit_oracle.c, gcc -O2 -march=native, OpenMP over the 21
-    tasks of the sweep) on all host cores — shown so the speed-up is not only "Python overhead removed".  The
-    evaluation stages are NOT included, so this over-states the CPU's task-fits/sec."""
+    """the fit alone as compiled C in its natural loop order (oracle/c/fit_oracle.c, gcc -O3 -march=native,
+    OpenMP over the 21 tasks of the sweep) on all host cores — shown so the speed-up is not only "Python overhead
+    removed".  The evaluation stages are NOT included, so this over-states the CPU's task-fits/sec."""
     try:
         from oracle import c_oracle, fitcore, ae_oracle
         etf, _, _ = synthetic_returns()
@@ -179,6 +195,13 @@ class ClockSampler:
 
 
 # --------------------------------------------------------------------------------------- GPU arm
+def measured_peaks():
+    try:
+        return json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except OSError:
+        return {}
+
+
 def gpu_arm(args):
     import torch
     import torch.distributed as dist
@@ -191,20 +214,18 @@ def gpu_arm(args):
     torch.cuda.set_device(local)
     dev = torch.device(f"cuda:{local}")
     if world > 1:
+        if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
+            os.environ["NCCL_DEBUG"] = "WARN"            # keep NCCL's version banner off stdout: the line below is the output
         dist.init_process_group("nccl", device_id=dev)
 
     etf, hfd, rf = synthetic_returns()
-    # Weak scaling needs the same work on every GPU.  Early stopping makes a sweep's length depend on its seeds (measured:
-    # 7.1 to 8.8 ms per 21-fit sweep over four seeds), so every rank runs the sweep of the SAME seeds; the ranks' results are
-    # still separate task executions (the job's aggregate counts n_gpus x fits_per_step_per_gpu fits per step).
-    seeds = [123 + s for s in range(args.seeds)]
+    seeds = [123 + rank]                    # every rank its own seed: distinct fits, fixed fit count per GPU
     data = hfrep.ReplicationData(etf, hfd, rf, window=WINDOW, device=dev)
-    tasks = sorted(((L, s) for s in seeds for L in LATENTS), key=lambda t: -((t[0] + 3) // 4))   # widest first
+    tasks = engine.mode_r_tasks(LATENTS, seeds)
     n_tasks = len(tasks)
     w_stride = 2 * E * max(LATENTS)
     W0_host = engine.pack_weights([engine.initial_weights(s, E, L) for L, s in tasks], E, w_stride)
-    W0_pinned = torch.from_numpy(W0_host).pin_memory()
-    W0d = W0_pinned.to(dev)
+    W0d = engine.to_device(W0_host, dev)
     task_L = [L for L, _ in tasks]
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)      # > 126 MB L2
     n_buckets = len({(L + 3) // 4 for L in task_L})
@@ -219,12 +240,13 @@ def gpu_arm(args):
         return fit, ev
 
     def e2e_step():
-        """Through the public API with HOST buffers: H2D of the returns + initial kernels, D2H of the results."""
+        """Through the public API with HOST buffers: H2D of the returns + initial kernels, D2H of everything a caller of
+        the reference's AE objects reads — histories, trained kernels, quality series, replicas, turnover, metrics."""
         d = hfrep.ReplicationData(etf, hfd, rf, window=WINDOW, device=dev)
         _, fit, ev = hfrep.run_mode_r(d, LATENTS, seeds=seeds, W0=W0_host)      # same widest-first task order as W0_host
-        out = [t.cpu() for t in (ev.ante, ev.post, ev.turnover, ev.metrics, ev.quality, fit.epochs_run)]
-        h2d = d.h2d_bytes + W0_host.nbytes
-        return h2d, sum(t.numel() * t.element_size() for t in out)
+        out = engine.to_host([ev.ante, ev.post, ev.turnover, ev.metrics, ev.quality, fit.epochs_run, fit.status, fit.loss,
+                              fit.val_loss, fit.W])
+        return d.h2d_bytes + W0_host.nbytes, sum(a.nbytes for a in out)
 
     def barrier():
         if world > 1:
@@ -242,7 +264,8 @@ def gpu_arm(args):
         resident_step()                      # more (untimed) warm-up until the sampler has seen the GPU under this load
         flush.fill_(1)
         torch.cuda.synchronize()
-    e2e_step()
+    for _ in range(2):
+        e2e_step()
     barrier()
 
     # ---- timed: K steps, device time per step from CUDA events (L2 flushed between steps, flush not timed)
@@ -259,8 +282,8 @@ def gpu_arm(args):
     total_ms = float(sum(step_ms))
     fit, ev = last
     epochs_run = fit.epochs_run.cpu().numpy()
-    assert int(fit.status.abs().sum()) == 0 and int(ev.status.abs().sum()) == 0
-    assert bool(torch.isfinite(ev.ante).all())
+    assert int(fit.status.abs().sum()) == 0 and bool(torch.isfinite(ev.ante).all())
+    eval_status = sorted(set(int(v) for v in ev.status.cpu().numpy()))       # 2 = a rank-deficient window took the pinv path
 
     # ---- kernel (b) alone (its evaluation is otherwise queued behind it, bucket by bucket): the roofline's duration
     fit_ms = []
@@ -282,15 +305,19 @@ def gpu_arm(args):
     e2e_s = time.perf_counter() - t0
     clocks = sampler.stop(t_timed)
 
+    # ---- the sharded job: configs[2] dealt over the ranks, one all-gather of result records, host buffers in and out
+    sharded = sharded_job(args, hfrep, engine, dist, torch, dev, rank, world, (etf, hfd, rf), barrier)
+
     # ---- max over ranks
     tt = torch.tensor([total_ms, e2e_s * 1e3, float(np.mean(fit_ms))], dtype=torch.float64, device=dev)
     per_rank = None
     if world > 1:
-        # per-rank step time and SM clock (diagnostic: which rank the max comes from, and whether its clock differs)
-        mine = torch.tensor([total_ms / args.steps, clocks["sm_mhz"] or -1.], dtype=torch.float64, device=dev)
+        # per-rank step time, run length and SM clock (diagnostic: which rank the max comes from, and why)
+        mine = torch.tensor([total_ms / args.steps, clocks["sm_mhz"] or -1., float(epochs_run.mean())], dtype=torch.float64, device=dev)
         allr = [torch.zeros_like(mine) for _ in range(world)]
         dist.all_gather(allr, mine)
-        per_rank = {"ms_per_step": [round(float(t[0]), 4) for t in allr], "sm_mhz": [float(t[1]) for t in allr]}
+        per_rank = {"ms_per_step": [round(float(t[0]), 4) for t in allr], "sm_mhz": [float(t[1]) for t in allr],
+                    "epochs_run_mean": [round(float(t[2]), 1) for t in allr]}
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
     total_ms, e2e_ms, fit_ms_mean = (float(v) for v in tt.cpu())
     value = world * n_tasks * args.steps / (total_ms * 1e-3)
@@ -325,75 +352,21 @@ def gpu_arm(args):
                 "algorithmic_flop_per_launch": flop, "ms_per_launch": fit_ms_mean,
                 "note": f"{n_tasks} fits on {n_buckets} concurrent launches: cfg2 exposes only 21 sequential chains, so this is latency-, not FFMA-bound; see 'ensemble'"}
 
-    # ---- the 64-seed ensemble (configs[2]) on this GPU: the throughput regime of the same kernels
-    ens = None
-    if args.ensemble_seeds > 0:
-        es = [1000 + s for s in range(args.ensemble_seeds)]
-        et = sorted(((L, s) for s in es for L in LATENTS), key=lambda t: -((t[0] + 3) // 4))
-        eW0 = engine.to_device(engine.pack_weights([engine.initial_weights(s, E, L) for L, s in et], E, w_stride), dev)
-        eL = [L for L, _ in et]
-        times = []
-        for i in range(3):
-            a, b2, c = (torch.cuda.Event(enable_timing=True) for _ in range(3))
-            a.record()
-            f2 = engine.fit_batched(data.Xtr32, eL, eW0, E=E, T=data.n_train, early_stop=1)
-            b2.record()
-            torch.cuda.synchronize()
-            flush.fill_(i)
-            c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            c0.record()
-            engine.fit_and_score(data, eL, eW0, early_stop=1)
-            c1.record()
-            torch.cuda.synchronize()
-            flush.fill_(i)
-            times.append((a.elapsed_time(b2), c0.elapsed_time(c1)))
-        fms, sms = min(t[0] for t in times[1:]), min(t[1] for t in times[1:])
-        eflop = float(sum(flops_per_epoch(L) * int(n) for L, n in zip(eL, f2.epochs_run.cpu().numpy())))
-        ens = {"workload": f"cfg3 shape on one GPU: L=1..21 x {args.ensemble_seeds} seeds = {len(et)} fits",
-               "value": len(et) / (sms * 1e-3), "unit": UNIT, "ms_per_step": sms, "fit_ms": fms,
-               "roofline": {"bound": "fp32_ffma", "achieved": eflop / (fms * 1e-3) / 1e12, "peak": peak,
-                            "unit": "TFLOP/s", "frac": eflop / (fms * 1e-3) / 1e12 / peak}}
-
-    # ---- a bounded sample of configs[3] (500 ETFs, 252-day windows, rolling refit) through the wide kernels
-    wide = None
-    if args.wide_windows > 0 and rank == 0:
-        wT, wE, wF, wW, wL, wep = 5000, 500, args.wide_funds, 252, 8, 100
-        wr = np.random.default_rng(20240611)                         # SURVEY 8d cfg 4 factor model
-        fac = wr.normal(size=(wT, 10)) * .01
-        wetf = fac @ wr.normal(size=(10, wE)) + wr.normal(size=(wT, wE)) * .005
-        idx = wr.integers(0, wE, size=(wF, 5))
-        wts = wr.uniform(.06, .2, size=(wF, 5))
-        whfd = sum(wetf[:, idx[:, j]] * wts[:, j] for j in range(5)) + wr.normal(size=(wT, wF)) * .003
-        wins = np.linspace(0, wT - wW - 2, args.wide_windows).astype(int)
-        best_t = None
-        for i in range(3):
-            tm = {}
-            torch.cuda.synchronize()
-            t0 = time.perf_counter()
-            wo = hfrep.run_mode_w_wide(wetf, whfd, np.full(wT, 1e-4), train_window=wW, latent_dim=wL, seeds=(1,), windows=wins,
-                                       device=dev, max_epochs=wep, early_stop=0, timings=tm)
-            torch.cuda.synchronize()
-            tm["e2e_ms"] = (time.perf_counter() - t0) * 1e3
-            if best_t is None or tm["fit_ms"] < best_t["fit_ms"]:
-                best_t = tm
-        wflop = float(args.wide_windows) * wep * (10 * 189 * wE * wL + 4 * 63 * wE * wL)
-        wide = {"workload": f"cfg4 sample: {args.wide_windows} of 4747 windows x {wF} funds, 500 ETFs, L={wL}, {wep} epochs, rolling refit",
-                "fit_ms": best_t["fit_ms"], "eval_ms": best_t["eval_ms"], "e2e_ms_with_h2d": best_t["e2e_ms"],
-                "fits_per_s": args.wide_windows / (best_t["fit_ms"] * 1e-3),
-                "results_per_s_e2e": args.wide_windows * wF / (best_t["e2e_ms"] * 1e-3),
-                "status_ok": bool(int(wo["fit"].status.abs().sum()) == 0 and torch.isfinite(wo["replica"]).all()),
-                "roofline": {"bound": "fp32_ffma", "kernel": "fit_wide2_kernel", "achieved": wflop / (best_t["fit_ms"] * 1e-3) / 1e12,
-                             "peak": peak, "unit": "TFLOP/s", "frac": wflop / (best_t["fit_ms"] * 1e-3) / 1e12 / peak}}
+    extras = world == 1 and not args.no_extras
+    ens = ensemble_record(args, hfrep, engine, torch, data, dev, flush, peak, w_stride) if extras else None
+    hbm = hbm_kernels_record(hfrep, engine, torch, data, dev, flush, task_L, last) if extras else None
+    wide = wide_record(args, hfrep, torch, dev, peak) if (extras and args.wide_windows > 0) else None
+    paths = paths_record(args, hfrep, engine, torch, dev, peak) if (extras and args.path_tasks > 0) else None
 
     cpu = cpu_baseline_single_core() if (world == 1 and not args.no_cpu_baseline) else None
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
         "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"cfg2: 13 indices x 145 windows x L=1..21 x {args.seeds} seed(s) per GPU (Mode R), synthetic 337x(22+13+1)",
-                   "fits_per_step_per_gpu": n_tasks, "triples_per_step_per_gpu": n_tasks * F * 145,
-                   "epochs": EPOCHS, "epochs_run_mean": float(epochs_run.mean()), "shuffle": False,
-                   "seeds_per_rank": "the same on every rank (fixed work per GPU; run lengths under early stopping depend on the seed)",
+        "config": {"workload": WORKLOAD, "fits_per_step_per_gpu": n_tasks, "triples_per_step_per_gpu": n_tasks * F * 145,
+                   "epochs": EPOCHS, "epochs_run_mean": float(epochs_run.mean()), "shuffle": False, "early_stop": True,
+                   "seeds_per_rank": "rank r fits seed 123 + r (distinct fits on every GPU; run lengths under early stopping depend on the seed: see per_rank)",
+                   "eval_status_values": eval_status,
                    "l2": "flushed between steps (256 MiB write, not timed); inputs are KB-sized and smem-resident"},
         "clocks": clocks,
         "per_rank": per_rank,
@@ -401,10 +374,14 @@ def gpu_arm(args):
                 "ms_per_step": e2e_ms / args.steps},
         "gpu_launches": args.steps * 2 * n_buckets,      # fit_kernel + eval_kernel per width bucket
         "roofline": roofline,
+        "parity": "kernel (b) bit-identical to the CPU oracle (canonical summation order) over whole runs; everything else <= 1e-5 (tests/)",
         "cpu_baseline": cpu,
         "cpu_best_effort": cpu_best_effort() if cpu is not None else None,
+        "sharded": sharded,
         "ensemble": ens,
+        "hbm_kernels": hbm,
         "wide": wide,
+        "paths": paths,
         "wall_s_timed_region": wall,
     }
     print(json.dumps(line))
@@ -412,21 +389,228 @@ def gpu_arm(args):
         dist.destroy_process_group()
 
 
+def sharded_job(args, hfrep, engine, dist, torch, dev, rank, world, returns, barrier):
+    """configs[2]: the L = 1..21 x S-seed ensemble as ONE job over all ranks, through the public API: host buffers in
+    (returns matrices replicated to every GPU, the rank's share of the initial kernels), cyclic task split, fit + score,
+    ONE all-gather of packed result records (NCCL over NVLink), host results out on rank 0.  No data-path collective."""
+    S = args.sharded_seeds
+    if S <= 0:
+        return None
+    etf, hfd, rf = returns
+    es = [1000 + s for s in range(S)]
+    tasks = engine.mode_r_tasks(LATENTS, es)
+    w_stride = 2 * E * max(LATENTS)
+    W0 = engine.pack_weights([engine.initial_weights(s, E, L) for L, s in tasks], E, w_stride)
+    recs = []
+    for i in range(1 + args.sharded_steps):
+        barrier()
+        t0 = time.perf_counter()
+        d = hfrep.ReplicationData(etf, hfd, rf, window=WINDOW, device=dev)
+        tm = {}
+        _, fit, ev = hfrep.run_mode_r(d, LATENTS, seeds=es, W0=W0, sharded=world > 1, timings=tm)
+        d2h = 0
+        if rank == 0:
+            out = engine.to_host([ev.ante, ev.post, ev.turnover, ev.metrics, ev.quality, fit.epochs_run, fit.status, fit.loss,
+                                  fit.val_loss, fit.W])
+            d2h = sum(a.nbytes for a in out)
+        torch.cuda.synchronize()
+        t_local = time.perf_counter() - t0
+        barrier()
+        t_all = time.perf_counter() - t0
+        if i > 0:
+            recs.append((t_all, t_local, tm["compute_ms"], tm["gather_ms"], d2h, tm["record_bytes_per_task"]))
+    t_all = float(np.mean([r[0] for r in recs]))
+    mine = torch.tensor([np.mean([r[2] for r in recs]), np.mean([r[3] for r in recs]), t_all * 1e3,
+                         np.mean([r[1] for r in recs]) * 1e3], dtype=torch.float64, device=dev)
+    allr = [mine]
+    if world > 1:
+        allr = [torch.zeros_like(mine) for _ in range(world)]
+        dist.all_gather(allr, mine)
+    t_max = max(float(t[2]) for t in allr) * 1e-3
+    ok = bool(int(fit.status.abs().sum()) == 0 and fit.W.shape[0] == len(tasks) and torch.isfinite(ev.ante).all())
+    compute = [round(float(t[0]), 3) for t in allr]
+    gather = [round(float(t[1]), 3) for t in allr]
+    spread = (max(compute) - min(compute)) / max(compute)
+    return {"workload": f"cfg3: L=1..21 x {S} seeds = {len(tasks)} fits dealt cyclically over {world} GPU(s), early stopping on, "
+                        "host buffers in, gathered results to the host on rank 0",
+            "value": len(tasks) / t_max, "unit": UNIT, "ms_per_job": t_max * 1e3, "steps": args.sharded_steps,
+            "compute_ms_per_rank": compute, "gather_ms_per_rank": gather,
+            "local_ms_per_rank": [round(float(t[3]), 3) for t in allr],
+            "gathered_bytes_per_rank": int(recs[-1][5]) * len(tasks) if world > 1 else 0,
+            "d2h_bytes_rank0": int(recs[-1][4]), "h2d_bytes_per_rank": int(d.h2d_bytes + W0.nbytes // world),
+            "results_complete_and_finite": ok,
+            "limiter": ("the all-gather" if max(gather) > .25 * max(compute) else
+                        ("early-stop raggedness between ranks" if spread > .08 else "kernel (b) on each rank's share")) +
+                       f" (compute spread over ranks {100 * spread:.1f} %, gather {max(gather):.2f} ms of {t_max * 1e3:.1f} ms)"}
+
+
+def ensemble_record(args, hfrep, engine, torch, data, dev, flush, peak, w_stride):
+    """The 64-seed ensemble (configs[2]) on ONE GPU, inputs resident: the throughput regime of kernels (b) and (c)."""
+    if args.ensemble_seeds <= 0:
+        return None
+    es = [1000 + s for s in range(args.ensemble_seeds)]
+    et = engine.mode_r_tasks(LATENTS, es)
+    eW0 = engine.to_device(engine.pack_weights([engine.initial_weights(s, E, L) for L, s in et], E, w_stride), dev)
+    eL = [L for L, _ in et]
+    times = []
+    for i in range(3):
+        a, b2 = (torch.cuda.Event(enable_timing=True) for _ in range(2))
+        a.record()
+        f2 = engine.fit_batched(data.Xtr32, eL, eW0, E=E, T=data.n_train, early_stop=1)
+        b2.record()
+        torch.cuda.synchronize()
+        flush.fill_(i)
+        c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        c0.record()
+        engine.fit_and_score(data, eL, eW0, early_stop=1)
+        c1.record()
+        torch.cuda.synchronize()
+        flush.fill_(i)
+        times.append((a.elapsed_time(b2), c0.elapsed_time(c1)))
+    fms, sms = min(t[0] for t in times[1:]), min(t[1] for t in times[1:])
+    eflop = float(sum(flops_per_epoch(L) * int(n) for L, n in zip(eL, f2.epochs_run.cpu().numpy())))
+    return {"workload": f"cfg3 shape on one GPU: L=1..21 x {args.ensemble_seeds} seeds = {len(et)} fits",
+            "value": len(et) / (sms * 1e-3), "unit": UNIT, "ms_per_step": sms, "fit_ms": fms,
+            "roofline": {"bound": "fp32_ffma", "achieved": eflop / (fms * 1e-3) / 1e12, "peak": peak,
+                         "unit": "TFLOP/s", "frac": eflop / (fms * 1e-3) / 1e12 / peak}}
+
+
+def hbm_kernels_record(hfrep, engine, torch, data, dev, flush, task_L, last):
+    """The HBM-bound kernels against the measured copy bandwidth (MEASURED_PEAKS.json hbm_gbs): kernel (a) on the
+    configs[3] window set (296 windows x 252 rows x 500 ETFs, plain and with the per-window MinMax, float32 and float64
+    source) and the output side of kernel (c).  Algorithmic bytes = bytes written + the same read (kernel (a): overlapping
+    windows re-read from L2 count as read), CUDA events, L2 flushed before every launch, best of 5."""
+    peak = measured_peaks().get("hbm_gbs") or 6450.9
+
+    def timed(fn, reps=5):
+        best = float("inf")
+        for i in range(reps):
+            flush.fill_(i)
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            fn()
+            b.record()
+            torch.cuda.synchronize()
+            best = min(best, a.elapsed_time(b))
+        return best
+
+    lib, ptr, check, sp = hfrep._lib.lib, hfrep._lib.ptr, hfrep._lib.check, hfrep._lib.stream_ptr
+    rng = np.random.default_rng(3)
+    T, C, W = 5000, 500, 252
+    R32 = engine.to_device((rng.normal(size=(T, C)) * .01).astype(np.float32), dev)
+    R64 = R32.to(torch.float64)
+    out = {"peak_gbs": peak, "peak_source": "MEASURED_PEAKS.json hbm_gbs (copy, read+write bytes)"}
+    for n_win in (296, 4747):
+        starts = torch.from_numpy(np.linspace(0, T - W - 2, n_win).astype(np.int32)).to(dev)
+        dst = torch.empty((n_win, W, C), dtype=torch.float32, device=dev)
+        for name, src, mm in (("plain_f32", R32, 0), ("minmax_f32", R32, 1), ("minmax_f64", R64, 1)):
+            if n_win == 4747 and name == "plain_f32":
+                continue
+            fn = lib.hfrep_window_gather if src.dtype == torch.float32 else lib.hfrep_window_gather_f64
+            rb = n_win * W * C * (4. + src.element_size()) * (1. + .5 * mm)      # minmax reads every window twice (min/max, scale)
+            ms = timed(lambda: check(fn(ptr(src), T, C, ptr(starts), n_win, W, 0, C, mm, ptr(dst), sp())))   # the C ABI call: no host checks in the timed region
+            out[f"window_gather_{name}_{n_win}w"] = {"ms": ms, "algorithmic_bytes": rb, "gbs": rb / (ms * 1e-3) / 1e9,
+                                                     "frac": rb / (ms * 1e-3) / 1e9 / peak}
+        del dst
+    # kernel (c), output side: what one launch over many tasks writes (replicas, ex-post, turnover, metrics, quality, masks,
+    # beta, norm, status) / its duration — the kernel is compute-bound (float64 QR + quality loops), so this is small
+    n = 4096
+    fit, _ = last
+    W_rep = fit.W[:1].repeat(n, 1).contiguous()
+    tL = [task_L[0]] * n
+    r, launch = hfrep.predict_metrics(data.Xtr64, data.Xte64, data.Yte64, data.rf64, data.sigma, tL, W_rep, window=WINDOW,
+                                      want_oos=False, launch=False)
+    wb = sum(t.numel() * t.element_size() for t in (r.ante, r.post, r.turnover, r.metrics, r.mask, r.beta, r.norm, r.status))
+    stream = torch.cuda.current_stream(dev).cuda_stream
+    ms = timed(lambda: launch(0, n, stream), reps=3)
+    out["eval_kernel_output_side_4096_tasks"] = {
+        "ms": ms, "bytes_written": wb, "gbs": wb / (ms * 1e-3) / 1e9, "frac": wb / (ms * 1e-3) / 1e9 / peak,
+        "note": "kernel (c) writes 37 KB per task and is bound by its float64 QR / statistics, not by HBM"}
+    return out
+
+
+def wide_record(args, hfrep, torch, dev, peak):
+    """A bounded sample of configs[3] (500 ETFs, 10 000 funds, 252-day windows, rolling refit) through the wide kernels."""
+    wT, wE, wF, wW, wL, wep = 5000, 500, args.wide_funds, 252, 8, 100
+    wr = np.random.default_rng(20240611)                         # SURVEY 8d cfg 4 factor model
+    fac = wr.normal(size=(wT, 10)) * .01
+    wetf = fac @ wr.normal(size=(10, wE)) + wr.normal(size=(wT, wE)) * .005
+    idx = wr.integers(0, wE, size=(wF, 5))
+    wts = wr.uniform(.06, .2, size=(wF, 5))
+    whfd = np.zeros((wT, wF))
+    for j in range(5):
+        whfd += wetf[:, idx[:, j]] * wts[:, j]
+    whfd += wr.normal(size=(wT, wF)) * .003
+    wins = np.linspace(0, wT - wW - 2, args.wide_windows).astype(int)
+    best_t = None
+    for i in range(3):
+        tm = {}
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        wo = hfrep.run_mode_w_wide(wetf, whfd, np.full(wT, 1e-4), train_window=wW, latent_dim=wL, seeds=(1,), windows=wins,
+                                   device=dev, max_epochs=wep, early_stop=0, timings=tm)
+        torch.cuda.synchronize()
+        tm["e2e_ms"] = (time.perf_counter() - t0) * 1e3
+        if best_t is None:
+            best_t = tm
+        else:
+            best_t = {k: min(best_t[k], tm[k]) for k in tm}
+    wflop = float(args.wide_windows) * wep * flops_per_epoch(wL, 189, 63, 48, wE)
+    return {"workload": f"cfg4 sample: {args.wide_windows} of 4747 windows x {wF} funds, 500 ETFs, L={wL}, {wep} epochs, rolling refit",
+            "fit_ms": best_t["fit_ms"], "eval_ms": best_t["eval_ms"], "e2e_ms_with_h2d": best_t["e2e_ms"],
+            "h2d_bytes": int(whfd.nbytes + wetf.nbytes),
+            "fits_per_s": args.wide_windows / (best_t["fit_ms"] * 1e-3),
+            "results_per_s_e2e": args.wide_windows * wF / (best_t["e2e_ms"] * 1e-3),
+            "status_ok": bool(int(wo["fit"].status.abs().sum()) == 0 and torch.isfinite(wo["replica"]).all()),
+            "roofline": {"bound": "fp32_ffma", "kernel": "fit_wide2_kernel", "achieved": wflop / (best_t["fit_ms"] * 1e-3) / 1e12,
+                         "peak": peak, "unit": "TFLOP/s", "frac": wflop / (best_t["fit_ms"] * 1e-3) / 1e12 / peak}}
+
+
+def paths_record(args, hfrep, engine, torch, dev, peak):
+    """A bounded sample of configs[4]: generated paths (168 x 36, MinMax space; the generator's file is absent, so
+    clip(N(.61, .2), -.13, 1.26) as in SURVEY §8d) as augmented training tasks — every path its own training block
+    (`task_x`), L = 8, through the same batched fit (batch-tile mode).  Fixed epochs (no early stop) so the flop count is exact."""
+    n, T, L, ep = args.path_tasks, 168, 8, args.path_epochs
+    g = torch.Generator(device=dev)
+    g.manual_seed(7)
+    X = torch.empty((n, T, E), dtype=torch.float32, device=dev)
+    X.normal_(.61, .2, generator=g).clamp_(-.13, 1.26)
+    W0 = engine.to_device(engine.pack_weights([engine.initial_weights(5, E, L)], E, 2 * E * L), dev).repeat(n, 1).contiguous()
+    tx = torch.arange(n, dtype=torch.int32, device=dev)
+    best = float("inf")
+    for i in range(3):
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        fit = engine.fit_batched(X, [L] * n, W0, E=E, T=T, task_x=tx, max_epochs=ep, early_stop=0)
+        b.record()
+        torch.cuda.synchronize()
+        best = min(best, a.elapsed_time(b))
+    flop = float(n) * ep * flops_per_epoch(L)
+    return {"workload": f"cfg5 sample: {n} generated paths (168 x 22 ETF columns each, own training block per task), L={L}, {ep} epochs",
+            "fit_ms": best, "fits_per_s": n / (best * 1e-3), "fits_per_s_at_1000_epochs": n / (best * 1e-3) * ep / 1000.,
+            "blocks_bytes": int(X.numel() * 4), "status_ok": bool(int(fit.status.abs().sum()) == 0 and torch.isfinite(fit.W).all()),
+            "roofline": {"bound": "fp32_ffma", "kernel": "fit_kernel (batch-tile mode)", "achieved": flop / (best * 1e-3) / 1e12,
+                         "peak": peak, "unit": "TFLOP/s", "frac": flop / (best * 1e-3) / 1e12 / peak}}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--seeds", type=int, default=1, help="seeds per GPU (1 = configs[1]; 64 = configs[2] on one GPU)")
+    ap.add_argument("--sharded-seeds", type=int, default=64, help="seeds of the sharded configs[2] job (0: skip)")
+    ap.add_argument("--sharded-steps", type=int, default=3)
     ap.add_argument("--ensemble-seeds", type=int, default=64)
     ap.add_argument("--wide-windows", type=int, default=296, help="windows of the configs[3] sample through the wide kernels (0: skip)")
-    ap.add_argument("--wide-funds", type=int, default=2000, help="funds of that sample (configs[3] has 10 000: 400 MB of float64 H2D)")
+    ap.add_argument("--wide-funds", type=int, default=10000, help="funds of that sample (configs[3]: 10 000 = 400 MB of float64 H2D)")
+    ap.add_argument("--path-tasks", type=int, default=100000, help="tasks of the configs[4] sample (0: skip)")
+    ap.add_argument("--path-epochs", type=int, default=100)
     ap.add_argument("--impl", default="native", choices=["native", "reference"])
+    ap.add_argument("--cpu-procs", type=int, default=16, help="host processes of the --impl reference arm")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="skip the ensemble / hbm_kernels / wide / paths records")
     args = ap.parse_args()
     if args.impl == "reference":
-        args.steps = min(args.steps, 3)
-        args.warmup = min(args.warmup, 1)
         cpu_reference_arm(args)
     else:
         gpu_arm(args)

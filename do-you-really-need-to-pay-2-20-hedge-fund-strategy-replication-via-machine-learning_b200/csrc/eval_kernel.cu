@@ -661,7 +661,7 @@ extern "C" int hfrep_predict_metrics(const hfrep_eval_cfg* c, const double* Xtr,
     const size_t smem = dbl * 8 + flt * 4 + (size_t)p.n_oos * c->E + 16;
     HFREP_REQUIRE(smem <= 227 * 1024, "predict_metrics: %zu bytes of shared memory needed (T_test=%d too long)", smem,
                   c->T_test);
-    HFREP_CUDA_OK(cudaFuncSetAttribute(eval_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024)));
+    HFREP_CUDA_OK(allow_max_dynamic_smem(eval_kernel));
     // few tasks: spread each task's 167 expanding-prefix evaluations over several CTAs so the whole GPU works
     p.qsplit = 1;
     if (quality && c->want_oos) {

@@ -42,6 +42,10 @@
 
 namespace hfrep {
 
+#ifndef HFREP_CHAIN_UNROLL
+#define HFREP_CHAIN_UNROLL 4
+#endif
+constexpr int kChainUnroll = HFREP_CHAIN_UNROLL;   // a row class has 8 rows in a 48-row batch, 5 in the 30-row one
 constexpr int EP = 24;    // padded ETF width
 constexpr int XS = 28;    // row stride of Xs and dZy (8 consecutive rows -> 8 distinct 16-byte bank groups)
 constexpr int WDS = 28;   // row stride of Wd
@@ -401,7 +405,7 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
             auto class_chain = [&](int c, float2 (&acc)[4][2]) {
 #pragma unroll
                 for (int i = 0; i < 4; ++i) acc[i][0] = acc[i][1] = make_float2(0.f, 0.f);
-#pragma unroll 8
+#pragma unroll kChainUnroll
                 for (int q = c; q < nb; q += 6) {
                     const int ao = dec ? q * HS : (XT ? q * XS : xoff[q]);
                     const float4 a = ld4(Xs + a0 + ao);
@@ -429,26 +433,38 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
                 for (int i = 0; i < 4; ++i)
                     st4(dst + i * (NT5 * 4) + t * 4, make_float4(v[i][0].x, v[i][0].y, v[i][1].x, v[i][1].y));   // lanes -> consecutive 16 B
             };
+            // One copy of the chain code per kernel: the classes of this warp are walked by run-time loops.
             float2 acc[4][2];
             if constexpr (KS >= 3) {                     // every class sum goes to shared memory; the update phase combines
+#pragma unroll 1
+                for (int c = kq; c < 6; c += KS) {
+                    class_chain(c, acc);
+                    store(c, acc);
+                }
+            } else {                                     // a parity's sum (p_c + p_c+2) + p_c+4.  KS = 2: this warp's parity.
+                float2 par[4][2];                        // KS = 1: both, the even sum parked in the slot meanwhile
+#pragma unroll 1
+                for (int p0 = kq; p0 < 2; p0 += KS) {
+#pragma unroll 1
+                    for (int c = p0; c < 6; c += 2) {
+                        class_chain(c, acc);
+                        if (c == p0) {
 #pragma unroll
-                for (int c = 0; c < 6 / KS; ++c) {
-                    class_chain(kq + c * KS, acc);
-                    store(kq + c * KS, acc);
+                            for (int i = 0; i < 4; ++i) { par[i][0] = acc[i][0]; par[i][1] = acc[i][1]; }
+                        } else {
+                            add_to(par, acc);
+                        }
+                    }
+                    if (p0 != kq) {                      // T_even + T_odd
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) {
+                            const float4 ev = ld4(part + kq * NEL + i * (NT5 * 4) + t * 4);
+                            acc[i][0] = make_float2(ev.x, ev.y); acc[i][1] = make_float2(ev.z, ev.w);
+                        }
+                        add_to(par, acc);
+                    }
+                    store(kq, par);
                 }
-            } else {                                     // KS = 2: this warp's parity (p_kq + p_kq+2) + p_kq+4;  KS = 1: both
-                float2 par[4][2];
-                class_chain(kq, par);
-                class_chain(kq + 2, acc); add_to(par, acc);
-                class_chain(kq + 4, acc); add_to(par, acc);
-                if constexpr (KS == 1) {
-                    float2 odd[4][2];
-                    class_chain(1, odd);
-                    class_chain(3, acc); add_to(odd, acc);
-                    class_chain(5, acc); add_to(odd, acc);
-                    add_to(par, odd);
-                }
-                store(kq, par);
             }
         }
     };
@@ -474,25 +490,29 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
             return ld4(pq);
         }
     };
-    // Keras 2.7 Nadam._resource_apply_dense, operation by operation (oracle/fitcore.py Nadam.step):
-    // sa = {1 - m_schedule_new, 1 - m_schedule_next, 1 - beta_2^t, 1 - mu_t}, sb.x = mu_{t+1}
-    auto update_quad = [&](int qd, float4& m4, float4& v4, const float4& sa, const float4& sb) {
+    // Nadam in Keras' operation order with IEEE-exact division and square root (common.cuh: nadam_delta).  The fast
+    // sequences run unconditionally; if the smallest non-zero operand of the quad is below 2^-64 (never seen: gradients
+    // and moments of these fits stay above 1e-14) the quad is redone with the compiler's range-checked operations.
+    const NadamK nk{p.b1, omb1, p.b2, omb2, p.lr, p.eps};
+    auto update_quad = [&](int qd, float4& m4, float4& v4, const float4& sa, const float4& sb, const float3& rc) {
         const float4 g = quad_gradient(qd);
-        auto delta = [&](float gk, float& m, float& v) -> float {
-            const float g_prime = __fdiv_rn(gk, sa.x);
-            m = __fadd_rn(__fmul_rn(p.b1, m), __fmul_rn(omb1, gk));
-            const float m_prime = __fdiv_rn(m, sa.y);
-            v = __fadd_rn(__fmul_rn(p.b2, v), __fmul_rn(omb2, __fmul_rn(gk, gk)));
-            const float v_prime = __fdiv_rn(v, sa.z);
-            const float m_bar = __fadd_rn(__fmul_rn(sa.w, g_prime), __fmul_rn(sb.x, m_prime));
-            return __fdiv_rn(__fmul_rn(p.lr, m_bar), __fadd_rn(__fsqrt_rn(v_prime), p.eps));
-        };
         const int o = woff[qd];
         float4 wv = ld4(We + o);
-        wv.x = __fsub_rn(wv.x, delta(g.x, m4.x, v4.x));
-        wv.y = __fsub_rn(wv.y, delta(g.y, m4.y, v4.y));
-        wv.z = __fsub_rn(wv.z, delta(g.z, m4.z, v4.z));
-        wv.w = __fsub_rn(wv.w, delta(g.w, m4.w, v4.w));
+        nadam_moments(g.x, m4.x, v4.x, nk); nadam_moments(g.y, m4.y, v4.y, nk);
+        nadam_moments(g.z, m4.z, v4.z, nk); nadam_moments(g.w, m4.w, v4.w, nk);
+        unsigned lo = 0xffffffffu;
+        float4 d;
+        d.x = nadam_decrement<true>(g.x, m4.x, v4.x, sa, sb.x, rc, nk, lo);
+        d.y = nadam_decrement<true>(g.y, m4.y, v4.y, sa, sb.x, rc, nk, lo);
+        d.z = nadam_decrement<true>(g.z, m4.z, v4.z, sa, sb.x, rc, nk, lo);
+        d.w = nadam_decrement<true>(g.w, m4.w, v4.w, sa, sb.x, rc, nk, lo);
+        if (lo < kNadamSmallBits) {
+            d.x = nadam_decrement<false>(g.x, m4.x, v4.x, sa, sb.x, rc, nk, lo);
+            d.y = nadam_decrement<false>(g.y, m4.y, v4.y, sa, sb.x, rc, nk, lo);
+            d.z = nadam_decrement<false>(g.z, m4.z, v4.z, sa, sb.x, rc, nk, lo);
+            d.w = nadam_decrement<false>(g.w, m4.w, v4.w, sa, sb.x, rc, nk, lo);
+        }
+        wv.x = __fsub_rn(wv.x, d.x); wv.y = __fsub_rn(wv.y, d.y); wv.z = __fsub_rn(wv.z, d.z); wv.w = __fsub_rn(wv.w, d.w);
         st4(We + o, wv);
     };
     // test hook (cfg.dump_step): the summed gradient of one step, unpadded, to global memory.  Kept out of the update
@@ -516,15 +536,16 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
     };
     auto update_phase = [&](int step, const float4& sa, const float4& sb) {
         if (p.grad_out != nullptr && step == p.dump_step) dump_gradient();
+        const float3 rc = make_float3(rcp_refined(sa.x), rcp_refined(sa.y), rcp_refined(sa.z));
         if constexpr (MVREG) {
 #pragma unroll
             for (int j = 0; j < QPL; ++j)
-                if (NQ % NTH == 0 || tl + j * NTH < NQ) update_quad(tl + j * NTH, m4r[j], v4r[j], sa, sb);
+                if (NQ % NTH == 0 || tl + j * NTH < NQ) update_quad(tl + j * NTH, m4r[j], v4r[j], sa, sb, rc);
         } else {
 #pragma unroll 2
             for (int qd = tl; qd < NQ; qd += NTH) {
                 float4 m4 = mv[2 * qd], v4 = mv[2 * qd + 1];
-                update_quad(qd, m4, v4, sa, sb);
+                update_quad(qd, m4, v4, sa, sb, rc);
                 mv[2 * qd] = m4; mv[2 * qd + 1] = v4;
             }
         }
@@ -684,7 +705,14 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
         }
     }
 
+    // the caller's buffers need no initialisation: history entries past the last epoch run read NaN, the kernel row's tail
+    // (the task's own L packs 2*E*L of the w_stride floats) reads zero
+    for (int e2 = epochs_run + tl; e2 < p.max_epochs; e2 += NTH) {
+        p.loss_hist[(size_t)task * p.max_epochs + e2] = NAN;
+        p.val_hist[(size_t)task * p.max_epochs + e2] = NAN;
+    }
     float* wo = p.W_out + (size_t)task * p.w_stride;
+    for (int idx = 2 * E * L + tl; idx < p.w_stride; idx += NTH) wo[idx] = 0.f;
     for (int idx = tl; idx < E * L; idx += NTH) {
         const int e = idx / L, l = idx - e * L;
         wo[idx] = We[e * LP + l];
@@ -721,7 +749,7 @@ static int launch_fit_mode(const FitParams& p, cudaStream_t stream) {
     HFREP_REQUIRE(smem <= kMaxSmem, "fit: %zu bytes of shared memory needed (batch=%d too large for the narrow kernel)", smem,
                   p.batch);
     auto kern = fit_kernel<LP, NW, TPC, FULL, XT>;
-    HFREP_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024)));
+    HFREP_CUDA_OK(allow_max_dynamic_smem(kern));
     const int grid = (p.n_tasks + tpc - 1) / tpc;
     kern<<<grid, 32 * NW * tpc, smem, stream>>>(p);
     HFREP_CUDA_OK(cudaGetLastError());
@@ -742,19 +770,23 @@ static int launch_fit(const FitParams& p, cudaStream_t stream) {
 //      shared memory admits to hide its latency; 3 sits between 2 and 6 and wins nowhere on the measured sweep.
 template <int LP>
 static int dispatch_mapping(const FitParams& p, int wpt, cudaStream_t stream) {
+#ifndef HFREP_SLIM                                   // (HFREP_SLIM: experiment builds with the two main mappings only)
     if (wpt == 1) return launch_fit<LP, 1, 8, false>(p, stream);
-    if (wpt == 2) return launch_fit<LP, 2, 6, false>(p, stream);
     if (wpt == 3) return launch_fit<LP, 3, (LP <= 8 ? 8 : 6), false>(p, stream);
+#endif
+    if (wpt == 2) return launch_fit<LP, 2, 6, false>(p, stream);
     return launch_fit<LP, 6, 1, true>(p, stream);
 }
 
 int fit_dispatch(const FitParams& p, int L_max, int wpt, cudaStream_t stream) {
     const int LP = (L_max + 3) & ~3;
     switch (LP) {
+#ifndef HFREP_SLIM
         case 4: return dispatch_mapping<4>(p, wpt, stream);
-        case 8: return dispatch_mapping<8>(p, wpt, stream);
         case 12: return dispatch_mapping<12>(p, wpt, stream);
         case 16: return dispatch_mapping<16>(p, wpt, stream);
+#endif
+        case 8: return dispatch_mapping<8>(p, wpt, stream);
         case 20: return dispatch_mapping<20>(p, wpt, stream);
         case 24: return dispatch_mapping<24>(p, wpt, stream);
     }

@@ -33,17 +33,15 @@ struct WideFitParams {
     float alpha, lr, b1, b2, eps;
 };
 
-// Keras 2.7 Nadam._resource_apply_dense, operation by operation, each rounded on its own (SURVEY App. A.4;
-// oracle/fitcore.py Nadam.step).  sa = {1 - m_schedule_new, 1 - m_schedule_next, 1 - beta_2^t, 1 - mu_t}, mu1 = mu_{t+1}.
-__device__ __forceinline__ float nadam_step(float w, float g, float& m, float& v, const float4& sa, float mu1, float b1,
-                                            float omb1, float b2, float omb2, float lr, float eps) {
-    const float g_prime = __fdiv_rn(g, sa.x);
-    m = __fadd_rn(__fmul_rn(b1, m), __fmul_rn(omb1, g));
-    const float m_prime = __fdiv_rn(m, sa.y);
-    v = __fadd_rn(__fmul_rn(b2, v), __fmul_rn(omb2, __fmul_rn(g, g)));
-    const float v_prime = __fdiv_rn(v, sa.z);
-    const float m_bar = __fadd_rn(__fmul_rn(sa.w, g_prime), __fmul_rn(mu1, m_prime));
-    return __fsub_rn(w, __fdiv_rn(__fmul_rn(lr, m_bar), __fadd_rn(__fsqrt_rn(v_prime), eps)));
+// One Nadam step of a weight (common.cuh — Keras' operation order, IEEE-exact division and square root: the fast
+// sequences, evaluated again with the compiler's range-checked operations if an operand is non-zero and below 2^-64).
+__device__ __forceinline__ float nadam_step(float w, float g, float& m, float& v, const float4& sa, float mu1, const float3& rc,
+                                            const NadamK& k) {
+    nadam_moments(g, m, v, k);
+    unsigned lo = 0xffffffffu;
+    float d = nadam_decrement<true>(g, m, v, sa, mu1, rc, k, lo);
+    if (lo < kNadamSmallBits) d = nadam_decrement<false>(g, m, v, sa, mu1, rc, k, lo);
+    return __fsub_rn(w, d);
 }
 
 __device__ __forceinline__ float block_sum(float v, float* red) {
@@ -124,6 +122,8 @@ __global__ void __launch_bounds__(WIDE_THREADS) fit_wide_kernel(const WideFitPar
         // gradients + Nadam, element-wise over the 2*E*L weights
         const float4 sa = __ldg(p.sched + 2 * step);
         const float mu1 = __ldg(p.sched + 2 * step + 1).x;
+        const float3 rc = make_float3(rcp_refined(sa.x), rcp_refined(sa.y), rcp_refined(sa.z));
+        const NadamK nk{p.b1, omb1, p.b2, omb2, p.lr, p.eps};
         for (size_t i = tid; i < 2 * EL; i += WIDE_THREADS) {
             float g = 0.f;
             float *w, *m, *v;
@@ -138,7 +138,7 @@ __global__ void __launch_bounds__(WIDE_THREADS) fit_wide_kernel(const WideFitPar
                 w = We + j; m = mWe + j; v = vWe + j;
             }
             float mm = *m, vv = *v;
-            *w = nadam_step(*w, g, mm, vv, sa, mu1, p.b1, omb1, p.b2, omb2, p.lr, p.eps);
+            *w = nadam_step(*w, g, mm, vv, sa, mu1, rc, nk);
             *m = mm; *v = vv;
         }
         ++step;
@@ -270,11 +270,13 @@ __global__ void __launch_bounds__(512 / EPT) fit_wide2_kernel(const WideFitParam
     };
     const float4* sched = p.sched;
     float mu1 = 0.f;
+    float3 rc = make_float3(1.f, 1.f, 1.f);
+    const NadamK nk{p.b1, omb1, p.b2, omb2, p.lr, p.eps};
     auto upd = [&](float& w, float g, int slot, const float4& sa) {
         float* mp = mv + (size_t)slot * NT + tid;
         float* vp = mv + (size_t)(NS + slot) * NT + tid;
         float mm = *mp, vv = *vp;
-        w = nadam_step(w, g, mm, vv, sa, mu1, p.b1, omb1, p.b2, omb2, p.lr, p.eps);
+        w = nadam_step(w, g, mm, vv, sa, mu1, rc, nk);
         *mp = mm; *vp = vv;
     };
 
@@ -376,6 +378,7 @@ __global__ void __launch_bounds__(512 / EPT) fit_wide2_kernel(const WideFitParam
         // ---- Nadam on the thread's own weights (Wd now: its gradient is complete and pass 3 does not read Wd)
         const float4 sc = __ldg(sched + 2 * step);
         mu1 = __ldg(sched + 2 * step + 1).x;
+        rc = make_float3(rcp_refined(sc.x), rcp_refined(sc.y), rcp_refined(sc.z));
 #pragma unroll
         for (int j = 0; j < LH; ++j)
 #pragma unroll
@@ -649,7 +652,7 @@ static int launch_fit_wide2(const WideFitParams& p, int NT, cudaStream_t stream)
     const size_t smem = sizeof(float) * ((size_t)(2 + NWARP) * BP * LP + BP + 32 + (LP * EPT > 16 ? (size_t)BP * NT * EPT : 0));
     HFREP_REQUIRE(smem <= 227 * 1024, "fit_wide: %zu bytes of shared memory needed (batch too large)", smem);
     auto kern = fit_wide2_kernel<LP, EPT>;
-    HFREP_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024)));
+    HFREP_CUDA_OK(allow_max_dynamic_smem(kern));
     kern<<<p.n_tasks, NT, smem, stream>>>(p);
     HFREP_CUDA_OK(cudaGetLastError());
     return HFREP_OK;
@@ -687,7 +690,7 @@ extern "C" int hfrep_fit_wide(const hfrep_fit_cfg* c, const float* X, int n_task
     }
     const size_t smem = sizeof(float) * (2 * (size_t)c->batch * L + (size_t)c->batch * c->E + c->batch + 16);
     HFREP_REQUIRE(smem <= 227 * 1024, "fit_wide: %zu bytes of shared memory needed (batch x E too large)", smem);
-    HFREP_CUDA_OK(cudaFuncSetAttribute(fit_wide_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024)));
+    HFREP_CUDA_OK(allow_max_dynamic_smem(fit_wide_kernel));
     fit_wide_kernel<<<n_tasks, WIDE_THREADS, smem, (cudaStream_t)stream>>>(p);
     HFREP_CUDA_OK(cudaGetLastError());
     return HFREP_OK;
@@ -706,7 +709,7 @@ extern "C" int hfrep_predict_wide(const double* etf, const double* hfd, const do
     p.etf = etf; p.hfd = hfd; p.rf = rf; p.task_row0 = task_row0; p.W = W; p.replica = replica; p.status = status;
     p.n_tasks = n_tasks; p.E = E; p.F = F; p.L = L; p.window = window; p.alpha = alpha;
     const size_t smem = sizeof(double) * (2 * (size_t)window * L + 3 * L) + sizeof(float) * (size_t)(window + 2) * L + E + 16;
-    HFREP_CUDA_OK(cudaFuncSetAttribute(eval_wide_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024)));
+    HFREP_CUDA_OK(allow_max_dynamic_smem(eval_wide_kernel));
     eval_wide_kernel<<<n_tasks, WIDE_THREADS, smem, (cudaStream_t)stream>>>(p);
     HFREP_CUDA_OK(cudaGetLastError());
     return HFREP_OK;

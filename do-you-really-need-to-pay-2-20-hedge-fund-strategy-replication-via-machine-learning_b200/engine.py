@@ -104,12 +104,78 @@ def _dev(device=None):
     return torch.device(device if device is not None else f"cuda:{torch.cuda.current_device()}")
 
 
+class _Staging:
+    """Pinned host staging buffers, reused: `tensor.pin_memory()` allocates page-locked memory on every call (hundreds
+    of microseconds each — most of the host overhead of a small end-to-end step).  A buffer is handed out again only
+    after the copy that last read it has completed (one CUDA event per buffer)."""
+
+    def __init__(self):
+        self.free = []                       # [(uint8 pinned tensor, event of its last copy)]
+
+    def take(self, nbytes: int):
+        for i, (buf, ev) in enumerate(self.free):
+            if buf.numel() >= nbytes and ev.query():
+                return self.free.pop(i)
+        if len(self.free) > 32:
+            self.free = [(b, e) for b, e in self.free if not e.query()]      # drop idle buffers; busy ones stay alive
+        return torch.empty(max(nbytes, 1 << 16), dtype=torch.uint8).pin_memory(), torch.cuda.Event()
+
+    def give(self, buf, ev):
+        self.free.append((buf, ev))
+
+
+_STAGING = _Staging()
+
+
 def to_device(a: np.ndarray, device, dtype=None) -> torch.Tensor:
-    """Host array -> pinned staging -> device (async on the current stream)."""
+    """Host array -> pinned staging (pooled) -> device, asynchronous on the current stream."""
     t = torch.from_numpy(np.ascontiguousarray(a))
     if dtype is not None:
         t = t.to(dtype)
-    return t.pin_memory().to(device, non_blocking=True)
+    if t.numel() == 0:
+        return t.to(device)
+    nbytes = t.numel() * t.element_size()
+    buf, ev = _STAGING.take(nbytes)
+    host = buf[:nbytes].view(t.dtype).reshape(t.shape)
+    host.copy_(t)
+    out = host.to(device, non_blocking=True)
+    ev.record(torch.cuda.current_stream(out.device))
+    _STAGING.give(buf, ev)
+    return out
+
+
+def to_host(tensors) -> list:
+    """Device tensors -> host numpy arrays with ONE device-to-host copy: the tensors' bytes are concatenated on the
+    device (one kernel), copied into one page-locked buffer (torch's caching host allocator: no cudaHostAlloc after
+    the first call) and handed out as views of it (None entries stay None)."""
+    live = [t for t in tensors if t is not None]
+    if not live:
+        return [None for _ in tensors]
+    dev = live[0].device
+    flat, off = [], 0
+    for t in live:                                     # every field starts 16-byte aligned in the packed buffer
+        f = t.contiguous().reshape(-1).view(torch.uint8)
+        pad = (-off) & 15
+        if pad:
+            flat.append(torch.zeros(pad, dtype=torch.uint8, device=dev))
+            off += pad
+        flat.append(f)
+        off += f.numel()
+    packed = torch.cat(flat)
+    host = torch.empty(packed.numel(), dtype=torch.uint8, pin_memory=True)
+    host.copy_(packed, non_blocking=True)
+    torch.cuda.current_stream(dev).synchronize()
+    out, off, it = [], 0, iter(live)
+    for t in tensors:
+        if t is None:
+            out.append(None)
+            continue
+        tt = next(it)
+        off += (-off) & 15
+        n = tt.numel() * tt.element_size()
+        out.append(host[off:off + n].view(tt.dtype).reshape(tt.shape).numpy())
+        off += n
+    return out
 
 
 _SCHED_CACHE: dict = {}
@@ -211,13 +277,15 @@ def fit_batched(X: torch.Tensor, task_L, W0: torch.Tensor, *, E: int, T: int, n_
         tseed = _device_ints(np.asarray(shuffle_seeds, np.uint32)[order].view(np.int32), device)
 
     if W_out is None:
-        W_out = torch.zeros_like(W0s)      # rows are packed with each task's own L; the tail stays zero
+        W_out = torch.empty_like(W0s)      # the kernel writes every float of a row (the tail past the task's own L: zero)
     if after_bucket is not None and not identity:
         raise ValueError("after_bucket needs the tasks ordered widest-first (see run_mode_r)")
-    loss = torch.full((n, cfg.max_epochs), float("nan"), dtype=torch.float32, device=device)
-    val = torch.full((n, cfg.max_epochs), float("nan"), dtype=torch.float32, device=device)
-    epochs_run = torch.zeros(n, dtype=torch.int32, device=device)
-    status = torch.zeros(n, dtype=torch.int32, device=device)
+    # one allocation for both histories, one for the two int vectors; nothing to initialise (the kernel writes NaN past
+    # the last epoch run, and epochs_run / status of every task)
+    hist = torch.empty((2, n, cfg.max_epochs), dtype=torch.float32, device=device)
+    loss, val = hist[0], hist[1]
+    ints = torch.empty((2, n), dtype=torch.int32, device=device)
+    epochs_run, status = ints[0], ints[1]
     grads = torch.zeros_like(W0s) if dump_step is not None else None
 
     LP = (L_sorted + 3) // 4 * 4
@@ -350,15 +418,20 @@ class ReplicationData:
         self.n_train, self.n_test = split_rows(len(etf), test_size)
         self.E, self.F, self.window = etf.shape[1], hfd.shape[1], window
         self.n_oos = self.n_test - window - 1
+        ntr, nte, E, F = self.n_train, self.n_test, self.E, self.F
         with torch.cuda.device(self.device):
-            self.Xtr64 = to_device(minmax_scale(etf[:self.n_train]), self.device)
-            self.Xtr32 = self.Xtr64.to(torch.float32).reshape(1, self.n_train, self.E).contiguous()
-            self.Xte64 = to_device(etf[self.n_train:], self.device)
-            self.Yte64 = to_device(hfd[self.n_train:], self.device)
-            self.rf64 = to_device(rf[self.n_train:], self.device)
-            tail = to_device(etf[len(etf) - self.n_oos - window:], self.device)        # Autoencoder_encapsulate.py:206
+            # one host-to-device copy for the whole data set: [scaled train block | test ETFs | test funds | test rf]
+            host = np.concatenate([minmax_scale(etf[:ntr]).ravel(), etf[ntr:].ravel(), hfd[ntr:].ravel(), rf[ntr:]])
+            d = to_device(host, self.device)
+            o1, o2, o3 = ntr * E, ntr * E + nte * E, ntr * E + nte * E + nte * F
+            self.Xtr64 = d[:o1].view(ntr, E)
+            self.Xtr32 = self.Xtr64.to(torch.float32).reshape(1, ntr, E).contiguous()
+            self.Xte64 = d[o1:o2].view(nte, E)
+            self.Yte64 = d[o2:o3].view(nte, F)
+            self.rf64 = d[o3:]
+            tail = self.Xte64[nte - self.n_oos - window:]        # the last n_oos+window ETF rows (Autoencoder_encapsulate.py:206)
             starts, _ = window_index("expost", self.n_oos + window, window)               # helper.py:120
-            self.sigma = rolling_sigma(tail, torch.from_numpy(starts).to(self.device), window)
+            self.sigma = rolling_sigma(tail, _device_ints(starts, self.device), window)
         self.h2d_bytes = (etf.nbytes + hfd.nbytes + rf.nbytes)
 
 
@@ -366,7 +439,7 @@ def fit_and_score(data: "ReplicationData", task_L, W0d: torch.Tensor, *, perm=No
                   warps_per_task=0, **fit_kw):
     """Kernel (b) then kernel (c) for tasks ordered widest-first: every width bucket's evaluation is queued on the
     bucket's own stream right behind its fit, so it overlaps the fits of the other buckets."""
-    W_out = torch.zeros_like(W0d)
+    W_out = torch.empty_like(W0d)
     ev, score = predict_metrics(data.Xtr64, data.Xte64, data.Yte64, data.rf64, data.sigma, task_L, W_out,
                                 window=data.window, want_oos=want_oos, want_weights=want_weights,
                                 alpha=fit_kw.get("alpha", .2), launch=False)

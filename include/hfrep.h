@@ -112,8 +112,9 @@ int hfrep_nadam_schedule(const hfrep_fit_cfg* cfg, int n_steps, float* sched_hos
  *            perm is NULL and task_seed is not, every epoch's row order is the stable argsort of the hash keys
  *            fmix32(seed*0x9E3779B1 ^ (epoch+1)*0x85EBCA77 ^ (row+1)*0xC2B2AE3D) of the task's seed (murmur3 finaliser)
  *   sched    f32 [>= max_epochs*ceil(n_fit/batch)][HFREP_SCHED_STRIDE]  from hfrep_nadam_schedule, on the device, 16-byte aligned
- *   W_out    f32 [n_tasks][w_stride]       final kernels, same packing
- *   loss_hist/val_hist f32 [n_tasks][max_epochs]   history.history['loss'|'val_loss']
+ *   W_out    f32 [n_tasks][w_stride]       final kernels, same packing (floats past 2*E*L of a row are written as zero)
+ *   loss_hist/val_hist f32 [n_tasks][max_epochs]   history.history['loss'|'val_loss']; entries past epochs_run are
+ *            written as NaN — no output buffer needs initialising
  *   epochs_run int32 [n_tasks];  status int32 [n_tasks] (0 ok, 1 non-finite loss)
  *   grad_out f32 [n_tasks][w_stride] | NULL   gradients (dWe, dWd) of step cfg->dump_step
  * Every sum that feeds the weights follows one fixed order in every mapping (fused chains over the ETFs / latent
