@@ -16,6 +16,7 @@ MAX_E, MAX_L, MAX_F = 24, 24, 32
 STATIC_SCRATCH_BYTES = 4 << 20     # HFREP_STATIC_SCRATCH_BYTES
 N_STATS = 11                       # HFREP_N_STATS
 SCHED_STRIDE = 8                   # HFREP_SCHED_STRIDE
+WPT_CLUSTER = 60                   # HFREP_WPT_CLUSTER: warps_per_task value of the six-CTA cluster mapping
 STAT_NAMES = ("sharpe", "tracking_error", "correlation", "omega0", "omega10", "cvar5", "ceq2", "ceq5", "ceq10",
               "skewness", "kurtosis")
 

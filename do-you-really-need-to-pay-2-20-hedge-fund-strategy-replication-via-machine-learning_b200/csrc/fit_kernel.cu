@@ -33,6 +33,7 @@
 // window gather — shuffled orders cost nothing extra).
 // LP = L rounded up to 4; zero padding is exactly neutral (zero activations, zero gradients, Nadam(0)=0).
 #include "common.cuh"
+#include "fit_params.cuh"
 
 #include <algorithm>
 #include <atomic>
@@ -46,31 +47,7 @@ namespace hfrep {
 #define HFREP_CHAIN_UNROLL 4
 #endif
 constexpr int kChainUnroll = HFREP_CHAIN_UNROLL;   // a row class has 8 rows in a 48-row batch, 5 in the 30-row one
-constexpr int EP = 24;    // padded ETF width
-constexpr int XS = 28;    // row stride of Xs and dZy (8 consecutive rows -> 8 distinct 16-byte bank groups)
-constexpr int WDS = 28;   // row stride of Wd
-
-struct FitParams {
-    const float* X;
-    const int* task_L;
-    const int* task_x;
-    const float* W0;
-    const int* perm;
-    const unsigned* task_seed;   // per-task shuffle stream (device-side epoch permutations) or NULL
-    const float4* sched;
-    float* W_out;
-    float* loss_hist;
-    float* val_hist;
-    int* epochs_run;
-    int* status;
-    float* grad_out;
-    long long perm_task_stride;
-    int PS;              // ints reserved per team for the device-side shuffle (0 or 2*n_fit rounded up to 4)
-    int n_tasks, E, T, n_fit, n_val, batch, BP, max_epochs, patience, early_stop, w_stride, shared_x, dump_step;
-    int force_tile;      // testing: batch-tile mode even when the block could be resident (env HFREP_FORCE_TILE)
-    int debug_skip;      // profiling only (env HFREP_DEBUG_SKIP): bit0 rows, bit1 grads, bit2 update phases skipped
-    float alpha, lr, b1, b2, eps;
-};
+// (EP, XS, WDS, FitParams: fit_params.cuh)
 
 template <int LP>
 struct Lay {
@@ -126,11 +103,7 @@ __device__ __forceinline__ float team_sum(float v, float* red, int team, int tl)
     }
 }
 
-__device__ __forceinline__ float4 ld4(const float* p) { return *reinterpret_cast<const float4*>(p); }
-__device__ __forceinline__ void st4(float* p, float4 v) { *reinterpret_cast<float4*>(p) = v; }
 
-__device__ __forceinline__ float2 ld2(const float* p) { return *reinterpret_cast<const float2*>(p); }
-__device__ __forceinline__ void st2(float* p, float2 v) { *reinterpret_cast<float2*>(p) = v; }
 
 // LP: padded latent width; NW: warps per team (1, 2, 3 or 6: 2*NW lane classes must divide the 12 ETF float2 pieces);
 // TPC: most teams per CTA (the launch picks blockDim.x / (32*NW) <= TPC teams from the shared-memory budget);
@@ -866,11 +839,19 @@ static int fit_batched_impl(const hfrep_fit_cfg* c, const float* X, int n_tasks,
     int wpt = c->warps_per_task;
     if (wpt == 0) {                                  // pick the mapping from the amount of parallel work in THIS call
         const int sms = sm_count();                  // (callers that split a job over several calls pass it explicitly)
-        // measured on the L = 1..21 sweep x seeds (profiles/README.md): 6 warps win up to ~5 tasks per SM, 2 warps beyond
-        // (narrow tasks in large numbers: one warp per task — L = 8 x 4096 tasks 6.6 vs 7.8 ms per 100 epochs; L = 20: 14.8 vs 12.1)
-        wpt = n_tasks <= 5 * sms ? 6 : ((c->L_max <= 8 && n_tasks >= 10 * sms) ? 1 : 2);
+        // measured on the L = 1..21 sweep x seeds (profiles/README.md): a six-CTA cluster per task while every cluster has
+        // its own SMs; 6 warps win up to ~5 tasks per SM, 2 warps beyond (narrow tasks in large numbers: one warp per task
+        // — L = 8 x 4096 tasks 6.6 vs 7.8 ms per 100 epochs; L = 20: 14.8 vs 12.1)
+        wpt = n_tasks * 6 <= sms ? HFREP_WPT_CLUSTER
+                                 : (n_tasks <= 5 * sms ? 6 : ((c->L_max <= 8 && n_tasks >= 10 * sms) ? 1 : 2));
     }
-    HFREP_REQUIRE(wpt == 1 || wpt == 2 || wpt == 3 || wpt == 6, "fit_batched: warps_per_task=%d (0, 1, 2, 3 or 6)", wpt);
+    HFREP_REQUIRE(wpt == 1 || wpt == 2 || wpt == 3 || wpt == 6 || wpt == HFREP_WPT_CLUSTER,
+                  "fit_batched: warps_per_task=%d (0, 1, 2, 3, 6 or HFREP_WPT_CLUSTER)", wpt);
+    if (wpt == HFREP_WPT_CLUSTER) {
+        if (fit_cluster_takes(p, c->L_max) && !getenv("HFREP_NO_CLUSTER"))
+            return fit_cluster_dispatch(p, c->L_max, (cudaStream_t)stream);
+        wpt = 6;                                     // long blocks, batches over 48 rows: the one-CTA latency mapping
+    }
     return fit_dispatch(p, c->L_max, wpt, (cudaStream_t)stream);
 }
 

@@ -230,6 +230,8 @@ def warps_per_task_for(n_tasks: int, device) -> int:
     """Kernel (b) mapping for a job of n_tasks fits running at the same time (all width groups together): the same
     rule hfrep_fit_batched applies to a single call (csrc/fit_kernel.cu, dispatch_mapping)."""
     sms = torch.cuda.get_device_properties(device).multi_processor_count
+    if n_tasks * 6 <= sms:
+        return _lib.WPT_CLUSTER         # so few tasks that each gets a cluster of six SMs
     return 6 if n_tasks <= 5 * sms else 2
 
 

@@ -89,9 +89,13 @@ typedef struct hfrep_fit_cfg {
     float lr, beta_1, beta_2, epsilon, schedule_decay, decay_base;  /* Nadam(): 1e-3,.9,.999,1e-7,.004,.96 */
     int32_t n_x;          /* number of training blocks in X; 1 = all tasks share block 0 */
     int32_t warps_per_task; /* 0 = choose from this call's n_tasks; 1, 2, 3 = throughput mappings (1 needs many tasks
-                               per SM); 6 = latency mapping for a handful of tasks */
+                               per SM); 6 = latency mapping for a handful of tasks (one CTA per task);
+                               HFREP_WPT_CLUSTER = a cluster of six CTAs (six SMs) per task, for so few tasks that every
+                               cluster has SMs of its own (falls back to 6 for shapes it does not take) */
     int32_t dump_step;    /* global step (0-based) whose gradients go to grad_out, if grad_out != NULL */
 } hfrep_fit_cfg;
+
+#define HFREP_WPT_CLUSTER 60
 
 void hfrep_fit_cfg_default(hfrep_fit_cfg* cfg);
 

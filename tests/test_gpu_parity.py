@@ -38,7 +38,7 @@ def _fit_golden(hf, data, g, **kw):
 
 
 @pytest.mark.parametrize("L", [2, 8, 21])
-@pytest.mark.parametrize("wpt", [1, 2, 3, 6])
+@pytest.mark.parametrize("wpt", [1, 2, 3, 6, 60])
 def test_fit_matches_reference_run(hf, data, L, wpt):
     """Full 1000-epoch fit, deterministic order: history and final kernels vs the reference run."""
     g = load_golden(f"ref_modeR_L{L}")
@@ -67,7 +67,7 @@ def test_shuffled_fit_with_early_stopping(hf, data):
     g = load_golden("ref_modeR_L8_shuffled")
     perm = hf.engine.epoch_permutations(int(g["perm_seed"]), 1000, 126)
     permd = hf.engine.to_device(perm, data.device)
-    for wpt in (1, 2, 3, 6):
+    for wpt in (1, 2, 3, 6, 60):
         res, L = _fit_golden(hf, data, g, perm=permd, warps_per_task=wpt, patience=5)
         n = int(res.epochs_run[0])
         assert n == int(g["epochs_run"])
@@ -242,7 +242,7 @@ def test_fit_vs_oracle_synthetic(hf, E, L, T, batch):
     dev = torch.device("cuda:0")
     X = hf.engine.to_device(x.astype(np.float32)[None], dev)
     W0 = hf.engine.to_device(hf.engine.pack_weights([(We0, Wd0)], E, 2 * E * L), dev)
-    for wpt in (1, 2, 3, 6):
+    for wpt in (1, 2, 3, 6, 60):
         res = hf.fit_batched(X, [L], W0, E=E, T=T, max_epochs=40, batch=batch, early_stop=0, warps_per_task=wpt)
         assert np.max(np.abs(res.loss[0, :40].cpu().numpy() - o["loss"]) / o["loss"]) < TOL
         assert np.max(np.abs(res.val_loss[0, :40].cpu().numpy() - o["val_loss"]) / o["val_loss"]) < TOL
@@ -429,13 +429,18 @@ def test_batch_tile_mode_matches_resident(hf, data, monkeypatch):
     numbers as the resident mode: same arithmetic, different staging."""
     g = load_golden("ref_modeR_L8_shuffled")
     perm = hf.engine.to_device(hf.engine.epoch_permutations(int(g["perm_seed"]), 1000, 126), data.device)
-    for wpt in (1, 2, 3, 6):
+    for wpt in (1, 2, 3, 6, 60):
         ref, L = _fit_golden(hf, data, g, perm=perm, warps_per_task=wpt, patience=5)
         monkeypatch.setenv("HFREP_FORCE_TILE", "1")
         til, _ = _fit_golden(hf, data, g, perm=perm, warps_per_task=wpt, patience=5)
         monkeypatch.delenv("HFREP_FORCE_TILE")
         assert int(til.epochs_run[0]) == int(ref.epochs_run[0]) == int(g["epochs_run"])
-        assert torch.equal(til.W, ref.W) and torch.equal(til.loss.nan_to_num(), ref.loss.nan_to_num())
+        assert torch.equal(til.W, ref.W)
+        if wpt == 60:      # the cluster mapping has no tile mode: the forced-tile run is the one-CTA kernel, which sums the
+            n = int(ref.epochs_run[0])      # reported loss in another order (the weights above are the same bits)
+            assert rel_err(til.loss[0, :n].cpu().numpy(), ref.loss[0, :n].cpu().numpy()) < TOL
+        else:
+            assert torch.equal(til.loss.nan_to_num(), ref.loss.nan_to_num())
 
 
 def test_long_training_block_stacked_rows(hf):
@@ -452,7 +457,7 @@ def test_long_training_block_stacked_rows(hf):
     dev = torch.device("cuda:0")
     X = hf.engine.to_device(x.astype(np.float32)[None], dev)
     W0 = hf.engine.to_device(hf.engine.pack_weights([(We0, Wd0)], E, 2 * E * L), dev)
-    for wpt in (1, 2, 3, 6):
+    for wpt in (1, 2, 3, 6, 60):
         res = hf.fit_batched(X, [L], W0, E=E, T=T, max_epochs=6, early_stop=0, warps_per_task=wpt)
         assert np.max(np.abs(res.loss[0, :6].cpu().numpy() - o["loss"]) / o["loss"]) < TOL
         assert np.max(np.abs(res.val_loss[0, :6].cpu().numpy() - o["val_loss"]) / o["val_loss"]) < TOL
@@ -472,7 +477,7 @@ def test_device_side_shuffle(hf, data):
     assert sorted(tabs[0][3].tolist()) == list(range(126)) and not np.array_equal(tabs[0][3], tabs[1][3])
     E, L = data.E, 8
     W0 = hf.engine.to_device(hf.engine.pack_weights([(g["We0"], g["Wd0"])] * 2, E, 2 * E * L), data.device)
-    for wpt in (1, 2, 3, 6):
+    for wpt in (1, 2, 3, 6, 60):
         res = hf.fit_batched(data.Xtr32, [L, L], W0, E=E, T=168, max_epochs=40, patience=3, shuffle_seeds=seeds,
                              warps_per_task=wpt)
         for i, tab in enumerate(tabs):
