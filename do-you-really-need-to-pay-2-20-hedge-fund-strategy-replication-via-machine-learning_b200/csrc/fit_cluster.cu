@@ -317,8 +317,9 @@ __global__ void __launch_bounds__(CTH, 1) fit_cluster_kernel(const FitParams p) 
         float dx = nadam_decrement<true>(g.x, m2.x, v2.x, sa, sb.x, rc, nk, lo);
         float dy = nadam_decrement<true>(g.y, m2.y, v2.y, sa, sb.x, rc, nk, lo);
         if (lo < kNadamSmallBits) {
-            dx = nadam_decrement<false>(g.x, m2.x, v2.x, sa, sb.x, rc, nk, lo);
-            dy = nadam_decrement<false>(g.y, m2.y, v2.y, sa, sb.x, rc, nk, lo);
+            const float4 d4 = nadam_decrement_checked4(make_float4(g.x, g.y, 0.f, 0.f), make_float4(m2.x, m2.y, 0.f, 0.f),
+                                                       make_float4(v2.x, v2.y, 1.f, 1.f), sa, sb.x, nk);
+            dx = d4.x; dy = d4.y;
         }
         wv = make_float2(__fsub_rn(wv.x, dx), __fsub_rn(wv.y, dy));
 #pragma unroll

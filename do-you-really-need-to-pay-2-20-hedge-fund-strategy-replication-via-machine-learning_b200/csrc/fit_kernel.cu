@@ -479,12 +479,7 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
         d.y = nadam_decrement<true>(g.y, m4.y, v4.y, sa, sb.x, rc, nk, lo);
         d.z = nadam_decrement<true>(g.z, m4.z, v4.z, sa, sb.x, rc, nk, lo);
         d.w = nadam_decrement<true>(g.w, m4.w, v4.w, sa, sb.x, rc, nk, lo);
-        if (lo < kNadamSmallBits) {
-            d.x = nadam_decrement<false>(g.x, m4.x, v4.x, sa, sb.x, rc, nk, lo);
-            d.y = nadam_decrement<false>(g.y, m4.y, v4.y, sa, sb.x, rc, nk, lo);
-            d.z = nadam_decrement<false>(g.z, m4.z, v4.z, sa, sb.x, rc, nk, lo);
-            d.w = nadam_decrement<false>(g.w, m4.w, v4.w, sa, sb.x, rc, nk, lo);
-        }
+        if (lo < kNadamSmallBits) d = nadam_decrement_checked4(g, m4, v4, sa, sb.x, nk);
         wv.x = __fsub_rn(wv.x, d.x); wv.y = __fsub_rn(wv.y, d.y); wv.z = __fsub_rn(wv.z, d.z); wv.w = __fsub_rn(wv.w, d.w);
         st4(We + o, wv);
     };

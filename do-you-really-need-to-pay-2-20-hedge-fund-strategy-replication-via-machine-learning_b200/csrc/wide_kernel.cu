@@ -40,7 +40,8 @@ __device__ __forceinline__ float nadam_step(float w, float g, float& m, float& v
     nadam_moments(g, m, v, k);
     unsigned lo = 0xffffffffu;
     float d = nadam_decrement<true>(g, m, v, sa, mu1, rc, k, lo);
-    if (lo < kNadamSmallBits) d = nadam_decrement<false>(g, m, v, sa, mu1, rc, k, lo);
+    if (lo < kNadamSmallBits)
+        d = nadam_decrement_checked4(make_float4(g, 0.f, 0.f, 0.f), make_float4(m, 0.f, 0.f, 0.f), make_float4(v, 1.f, 1.f, 1.f), sa, mu1, k).x;
     return __fsub_rn(w, d);
 }
 

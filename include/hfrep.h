@@ -251,6 +251,19 @@ int hfrep_series_metrics(const double* series, const double* fund, const double*
 int hfrep_ex_post_return(const double* ante, const double* weights, const double* sigma, int T, int F, int E,
                          double param, double phi, double* post, void* stream);
 
+/* Generator inference: the forward pass of the reference's saved LSTM generator — GAN/MTSS_WGAN_GP.py:221-235
+ * `build_generator`, the Keras model the notebook loads and runs at autoencoder_v4.ipynb:1277-1291 — fused in one kernel:
+ * LSTM(units; sigmoid activation and recurrent activation; return_sequences) [-> LeakyReLU(alpha)] -> LayerNormalization(ln_eps)
+ * -> LSTM [-> LeakyReLU] -> LayerNormalization -> Dense(F_out).  Keras 2.7 semantics (gate order i, f, c, o; biased variance).
+ *   weights f32 [hfrep_generator_weight_count(F_in, units, F_out)], packed in this order:
+ *     W1 [F_in][4u], U1 [u][4u], b1 [4u], gamma1 [u], beta1 [u], W2 [u][4u], U2 [u][4u], b2 [4u], gamma2 [u], beta2 [u],
+ *     K [u][F_out], bias [F_out]                      (Keras kernel layout: in x out)
+ *   noise f32 [n_paths][T][F_in]  ->  out f32 [n_paths][T][F_out].   F_in, units, F_out <= 128. */
+size_t hfrep_generator_weight_count(int F_in, int units, int F_out);
+int hfrep_generator_forward(const float* weights, int F_in, int units, int F_out, int lrelu_after_lstm1,
+                            int lrelu_after_lstm2, float alpha, float ln_eps, const float* noise, int n_paths, int T,
+                            float* out, void* stream);
+
 /* FP32 peak micro-benchmark used as the roofline denominator of kernel (b) (MEASURED_PEAKS.json has no FP32
  * figure).  Runs `iters` rounds of 8 independent packed FMAs (FFMA2, fma.rn.f32x2) per thread on a full grid and returns
  * the flop count through *flops_host; time it with CUDA events on `stream`.  sink f32 [>=1]. */

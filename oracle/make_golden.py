@@ -119,6 +119,22 @@ def run_reference_stacked(ae_mod, helper, keras, data, L, seed):
     return res
 
 
+def generator_fixture():
+    """The reference's saved generator (GAN/trained_generator/MTTS_GAN_GP20220621_02-49-32.h5, the file the notebook loads at
+    autoencoder_v4.ipynb:1277) read with the package's own HDF5 reader: layer list (the file's model_config JSON) and
+    float32 weights, so the GPU box — which has neither the file nor h5py — can rebuild the model."""
+    import json
+    import importlib
+    gen = importlib.import_module("hfrep").generator
+    path = os.path.join(refbridge.REFERENCE_ROOT, "GAN", "trained_generator", "MTTS_GAN_GP20220621_02-49-32.h5")
+    layers = gen.read_keras_model(path)
+    out = {"layers_json": np.array(json.dumps([[c, cfg] for c, cfg, _ in layers]))}
+    for i, (_, _, ws) in enumerate(layers):
+        for j, w in enumerate(ws):
+            out[f"w_{i}_{j}"] = w
+    return out
+
+
 def helper_vectors(helper):
     """Outputs of the reference's numeric helpers on seeded random inputs."""
     import random
@@ -225,6 +241,7 @@ def main():
     res = run_reference_stacked(ae_mod, helper, keras, (etf, hfd, rf), 8, seed=123)
     np.savez_compressed(os.path.join(OUT, "ref_stacked_L8.npz"), **res)
     print(f"stacked rows L=8: {res['n_train_rows']} rows, epochs_run={res['epochs_run']} is_r2={res['is_r2']:.4f}")
+    np.savez_compressed(os.path.join(OUT, "ref_generator.npz"), **generator_fixture())
     np.savez_compressed(os.path.join(OUT, "ref_helpers.npz"), **helper_vectors(helper))
     np.savez_compressed(os.path.join(OUT, "ref_ff_factors.npz"), **ff_factor_fixture())
     refbridge.unload()

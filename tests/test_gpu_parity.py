@@ -162,6 +162,28 @@ def test_stacked_rows_flow_on_reference_generated_paths(hf, ref_inputs, monkeypa
     assert rel_err(ae.post(etf).values, g["post"]) < TOL
 
 
+@pytest.mark.parametrize("n", [3, 700, 2600])
+def test_generator_inference(hf, n):
+    """The reference's saved LSTM generator (autoencoder_v4.ipynb:1277-1291) on the GPU against the numpy restatement of
+    its Keras layers, for path counts that take each of the kernel's paths-per-CTA variants (2, 8, 16), ragged last CTA
+    included.  float32 both sides, different summation order: 2e-5 of the output range over 168 recurrent steps."""
+    import os
+    from oracle import gen_oracle
+    layers = hf.generator.layers_from_fixture(np.load(os.path.join(os.path.dirname(__file__), "golden", "ref_generator.npz")))
+    gen = hf.generator.Generator(layers, device="cuda:0")
+    noise = np.random.default_rng(n).normal(0, 1, (n, 168, 36)).astype(np.float32)
+    out = gen.predict(noise, verbose=0)
+    assert out.shape == (n, 168, 36) and np.isfinite(out).all()
+    pick = np.unique(np.r_[0, 1, n // 2, n - 2, n - 1])
+    want = gen_oracle.forward(layers, noise[pick])
+    assert np.max(np.abs(out[pick] - want)) < 2e-5 * np.max(np.abs(want))
+    # the device path used as the producer of augmented training tasks: columns 0..21 of a path are its ETF block
+    dev_out = gen.predict_device(torch.from_numpy(noise[:2]).to("cuda:0"))
+    assert torch.equal(dev_out.cpu(), torch.from_numpy(out[:2]))
+    with pytest.raises(NotImplementedError):
+        hf.generator.Generator([l for l in layers if l[0] != "Dense"])
+
+
 def test_mode_r_end_to_end(hf, data, ref_inputs):
     """Fit + evaluation in one pass (three widths at once, bucketed launches) vs the reference runs."""
     gs = {L: load_golden(f"ref_modeR_L{L}") for L in (2, 8, 21)}

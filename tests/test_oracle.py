@@ -56,6 +56,48 @@ def test_portable_oracle_stacked_rows_run(ref_inputs):
     assert rel_err(ae.ante(rf), g["ante"]) < 1e-10 and rel_err(ae.post(etf), g["post"]) < 1e-10
 
 
+def test_generator_restatement_against_the_references_stored_paths():
+    """oracle/gen_oracle.py (Keras LSTM / LeakyReLU / LayerNormalization / Dense restated) with the reference's saved
+    generator weights on fresh N(0, 1) noise against GAN/generated_data2022-07-09.pkl — what the reference's own Keras run
+    of that generator produced (autoencoder_v4.ipynb:1291; its noise was not saved, so only distributions can agree):
+    overall mean / spread, every column's mean, the range."""
+    import hfrep
+    from oracle import gen_oracle
+    layers = hfrep.generator.layers_from_fixture(np.load(os.path.join(os.path.dirname(__file__), "golden", "ref_generator.npz")))
+    ref = load_golden("ref_stacked_L8")["gen_data"]                       # (10, 168, 36) float32
+    out = gen_oracle.forward(layers, np.random.default_rng(0).normal(0, 1, (40, 168, 36)))
+    assert out.shape == (40, 168, 36) and out.dtype == np.float32
+    assert abs(out.mean() - ref.mean()) < 5e-3 and abs(out.std() / ref.std() - 1) < .05
+    assert np.max(np.abs(out.mean((0, 1)) - ref.mean((0, 1)))) < .015
+    assert ref.min() - .15 < out.min() < 0 and 1 < out.max() < ref.max() + .15
+
+
+@pytest.mark.skipif(not refbridge.available(), reason="reference checkout not present on this machine")
+def test_hdf5_reader_on_the_references_model_files():
+    """hfrep.h5lite (no h5py here) on every generator the reference saved: groups, attributes (fixed and variable-length
+    strings), float32 datasets; the fixture the GPU tests use equals the file's content."""
+    import glob
+    import json
+    import hfrep
+    files = sorted(glob.glob(os.path.join(refbridge.REFERENCE_ROOT, "GAN", "trained_generator", "**", "*.h5"), recursive=True))
+    assert len(files) == 8
+    for path in files:
+        f = hfrep.h5lite.File(path)
+        a = f.root.attrs
+        assert a["keras_version"] == "2.7.0" and a["backend"] == "tensorflow"
+        cfg = json.loads(a["model_config"])
+        assert cfg["class_name"] in ("Functional", "Sequential")
+        data = f.root["model_weights"].datasets()
+        assert data and all(v.dtype == np.float32 and np.isfinite(v).all() for v in data.values())
+    layers = hfrep.generator.read_keras_model(os.path.join(refbridge.REFERENCE_ROOT, "GAN", "trained_generator",
+                                                            "MTTS_GAN_GP20220621_02-49-32.h5"))
+    fix = hfrep.generator.layers_from_fixture(np.load(os.path.join(os.path.dirname(__file__), "golden", "ref_generator.npz")))
+    assert [c for c, _, _ in layers] == [c for c, _, _ in fix]
+    for (_, _, a), (_, _, b) in zip(layers, fix):
+        assert len(a) == len(b) and all(np.array_equal(x, y) for x, y in zip(a, b))
+    assert [w.shape for w in layers[1][2]] == [(36, 400), (100, 400), (400,)]       # LSTM(100) on 36 features
+
+
 def test_structural_constants(ref_inputs):
     """Window bookkeeping pinned by the notebook."""
     g = load_golden("ref_modeR_L2")
