@@ -402,7 +402,9 @@ def sharded_job(args, hfrep, engine, dist, torch, dev, rank, world, returns, bar
     w_stride = 2 * E * max(LATENTS)
     W0 = engine.pack_weights([engine.initial_weights(s, E, L) for L, s in tasks], E, w_stride)
     recs = []
+    out = None
     for i in range(1 + args.sharded_steps):
+        out = None                               # the previous job's host results are released (their page-locked buffer is reused)
         barrier()
         t0 = time.perf_counter()
         d = hfrep.ReplicationData(etf, hfd, rf, window=WINDOW, device=dev)
@@ -431,6 +433,10 @@ def sharded_job(args, hfrep, engine, dist, torch, dev, rank, world, returns, bar
     compute = [round(float(t[0]), 3) for t in allr]
     gather = [round(float(t[1]), 3) for t in allr]
     spread = (max(compute) - min(compute)) / max(compute)
+    d2h_ms = float(allr[0][3]) - compute[0] - gather[0]      # rank 0: what follows its compute and the gather (result download)
+    parts = {"kernel (b)/(c) on each rank's share (a fit is a chain of up to 1000 dependent epochs: with few fits per SM the job "
+             "cannot be shorter than the longest fit)": max(compute), "the all-gather": max(gather),
+             "rank 0's download of the gathered results to the host": d2h_ms}
     return {"workload": f"cfg3: L=1..21 x {S} seeds = {len(tasks)} fits dealt cyclically over {world} GPU(s), early stopping on, "
                         "host buffers in, gathered results to the host on rank 0",
             "value": len(tasks) / t_max, "unit": UNIT, "ms_per_job": t_max * 1e3, "steps": args.sharded_steps,
@@ -439,9 +445,9 @@ def sharded_job(args, hfrep, engine, dist, torch, dev, rank, world, returns, bar
             "gathered_bytes_per_rank": int(recs[-1][5]) * len(tasks) if world > 1 else 0,
             "d2h_bytes_rank0": int(recs[-1][4]), "h2d_bytes_per_rank": int(d.h2d_bytes + W0.nbytes // world),
             "results_complete_and_finite": ok,
-            "limiter": ("the all-gather" if max(gather) > .25 * max(compute) else
-                        ("early-stop raggedness between ranks" if spread > .08 else "kernel (b) on each rank's share")) +
-                       f" (compute spread over ranks {100 * spread:.1f} %, gather {max(gather):.2f} ms of {t_max * 1e3:.1f} ms)"}
+            "fits_per_rank": -(-len(tasks) // world), "result_download_ms_rank0": round(d2h_ms, 3),
+            "limiter": max(parts, key=parts.get) + f" — compute {max(compute):.1f} ms (spread over ranks {100 * spread:.1f} %: early-stop "
+                       f"raggedness), all-gather {max(gather):.2f} ms, host download {d2h_ms:.1f} ms of {t_max * 1e3:.1f} ms"}
 
 
 def ensemble_record(args, hfrep, engine, torch, data, dev, flush, peak, w_stride):
