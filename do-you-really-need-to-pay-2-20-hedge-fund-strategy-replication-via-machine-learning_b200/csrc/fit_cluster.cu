@@ -17,8 +17,13 @@
 //   all-gather      writes the new weights into all six CTAs' weight copies (st.async again).
 // Per step: two DSMEM exchanges (~4 KB in, ~4 KB out per CTA each), no cluster-wide barrier: an mbarrier per exchange,
 // armed for its next phase BEFORE this CTA does anything that lets a peer start producing that phase.
-// Per epoch: one more small exchange — every CTA's share of the epoch's squared error goes to every CTA, summed in rank
-// order, so all six take the same early-stopping decision from the same bits.
+// Validation is DEFERRED and runs beside training: the weights after an epoch's last update are the weights its validation
+// needs AND the weights the next epoch's first step starts from, so three more warps per CTA (the validation warps) run the
+// validation rows through the forward pass while the training warps do that first step's rows and gradients; each CTA's
+// share of the epoch's squared errors (train, validation) rides along with the step's class sums (8 more bytes per peer),
+// every CTA sums the six shares in rank order and takes the same early-stopping decision from the same bits BEFORE the
+// step's update — a run that stops leaves the weights of its last epoch untouched.  Only the last epoch of a run that
+// never stops needs a validation pass and an exchange of its own.
 //
 // Every wait is bounded (a clock64 deadline, then a trap): a protocol error would end the launch with an error, not hang the GPU.
 // DSMEM here is this GPU's shared memory only; nothing in this file touches another GPU's memory.
@@ -30,7 +35,8 @@
 namespace hfrep {
 
 constexpr int CL = 6;                 // CTAs per cluster = row classes of the canonical order
-constexpr int CTH = 96;               // threads per CTA: 8 rows x 12 float2 column pieces
+constexpr int RTH = 96;               // threads of a role: 8 rows x 12 float2 column pieces
+constexpr int CTH = 2 * RTH;          // threads per CTA: three training warps + three validation warps
 constexpr int RPC = 8;                // rows of a mini-batch pass per CTA (batch <= 48)
 
 // ---- PTX helpers (cluster, mbarrier, asynchronous DSMEM stores)
@@ -53,9 +59,12 @@ __device__ __forceinline__ void mbar_arm(unsigned bar, unsigned tx_bytes) {     
 __device__ __forceinline__ void mbar_arrive(unsigned bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
 }
+// (default semantics: acquire at CTA scope.  The data this CTA waits for are asynchronous stores INTO ITS OWN shared memory,
+// made visible by the barrier's transaction count — the same contract as a TMA load; a cluster-scope acquire would add an
+// L1 invalidation (CCTL.IVALL) to every wait.)
 __device__ __forceinline__ bool mbar_try(unsigned bar, unsigned parity) {
     unsigned ok;
-    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
+    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
                  "selp.u32 %0, 1, 0, p;\n\t}" : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
     return ok != 0;
 }
@@ -75,12 +84,11 @@ struct CLay {
     static constexpr int NT5 = 12 * CT;            // weight tiles (4x4): dWd (CT x 6) then dWe (6 x CT); <= 72 <= CTH
     static constexpr int NQ = 12 * LP;             // slot quads, tile-major [i][tile] as in fit_kernel.cu
     static constexpr int QPC = NQ / CL;            // quads owned by a CTA (2*LP)
-    static constexpr int NPAIR = 2 * QPC;          // float2 slot pairs owned by a CTA (4*LP <= 96 = CTH)
-    static_assert(NT5 <= CTH && NPAIR <= CTH, "one tile / one owned pair per thread");
+    static_assert(NT5 <= RTH && 2 * QPC <= RTH, "one tile / one owned slot pair per training thread");
     __host__ __device__ static size_t floats(int T, int PS) {
         return (size_t)(T + 1) * XS                // Xs: the training block, row T all-zero
                + (size_t)EP * LP + (size_t)LP * WDS          // We, Wd
-               + 2 * (size_t)(RPC + 1) * HS + (size_t)(RPC + 1) * XS   // H, dZh, dZy (row RPC = scratch)
+               + 3 * (size_t)(RPC + 1) * HS + (size_t)(RPC + 1) * XS   // H, dZh, H of the validation warps, dZy (row RPC = scratch)
                + (size_t)CL * QPC * 4              // part_in [source][owned quad][4]
                + NQ                                // woff
                + 2 * (size_t)((T + 3) & ~3)        // xoff tables
@@ -93,7 +101,7 @@ template <int LP>
 __global__ void __launch_bounds__(CTH, 1) fit_cluster_kernel(const FitParams p) {
     extern __shared__ __align__(16) float smem[];
     using Y = CLay<LP>;
-    constexpr int HS = Y::HS, CT = Y::CT, NT5 = Y::NT5, NQ = Y::NQ, QPC = Y::QPC, NPAIR = Y::NPAIR;
+    constexpr int HS = Y::HS, CT = Y::CT, NT5 = Y::NT5, NQ = Y::NQ, QPC = Y::QPC;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const unsigned c = cluster_rank();                       // this CTA's row class and slot share
     const int task = blockIdx.x / CL;
@@ -106,7 +114,8 @@ __global__ void __launch_bounds__(CTH, 1) fit_cluster_kernel(const FitParams p) 
     float* Wd = We + EP * LP;
     float* H = Wd + LP * WDS;
     float* dZh = H + (RPC + 1) * HS;
-    float* dZy = dZh + (RPC + 1) * HS;
+    float* Hv = dZh + (RPC + 1) * HS;                        // the validation warps' H
+    float* dZy = Hv + (RPC + 1) * HS;
     float* part_in = dZy + (RPC + 1) * XS;                   // [CL][QPC][4]
     int* woff = reinterpret_cast<int*>(part_in + CL * QPC * 4);
     const int TP = (T + 3) & ~3;
@@ -119,7 +128,7 @@ __global__ void __launch_bounds__(CTH, 1) fit_cluster_kernel(const FitParams p) 
     const int zero_row = T * XS;
     const unsigned barP = smem_u32(bars), barW = smem_u32(bars + 1), barE = smem_u32(bars + 2);
     const unsigned TX_SLOTS = (CL - 1) * QPC * 16u;           // bytes a CTA receives per exchange: five peers' share
-    const unsigned TX_EPOCH = (CL - 1) * 8u;
+    const unsigned TX_EPOCH = (CL - 1) * 8u;                  // ... plus, when an epoch's losses ride along, 8 bytes per peer
 
     // ---- stage the block, the kernels, the slot table
     const int xb = p.task_x ? p.task_x[task] : 0;
@@ -175,15 +184,19 @@ __global__ void __launch_bounds__(CTH, 1) fit_cluster_kernel(const FitParams p) 
     const float omb1 = 1.f - p.b1, omb2 = 1.f - p.b2;
     const NadamK nk{p.b1, omb1, p.b2, omb2, p.lr, p.eps};
 
-    // thread -> (local row rl, column piece pc): a warp holds 8 rows x 4 consecutive pieces
-    const int rl = lane & 7, pc = 4 * warp + (lane >> 3);
-    // owned slot pair of this thread (update phase): quad uq of this CTA's share, half uh
-    const bool owner = tid < NPAIR;
+    // roles: warps 0-2 train, warps 3-5 validate.  thread -> (local row rl, column piece pc): a warp holds 8 rows x 4 pieces
+    const bool val_role = warp >= RTH / 32;
+    const int rwarp = val_role ? warp - RTH / 32 : warp;
+    const int rl = lane & 7, pc = 4 * rwarp + (lane >> 3);
+    float* Hrole = val_role ? Hv : H;
+    auto role_sync = [&]() { asm volatile("bar.sync %0, %1;" ::"r"(val_role ? 2 : 1), "n"(RTH) : "memory"); };
+    // owned slot pair of this thread (update phase, training threads): quad uq of this CTA's share, half uh
+    const bool owner = tid < 2 * QPC;
     const int uq = tid >> 1, uh = tid & 1;
     const int my_qd = (int)c * QPC + uq;                     // global slot quad
     float2 m2 = make_float2(0.f, 0.f), v2 = make_float2(0.f, 0.f);   // Nadam moments of the owned pair
     // remote addresses of the six CTAs' copies of: the owned pair's weights, the barriers, this CTA's mailbox slots
-    unsigned peer_w[CL], peer_barW[CL], peer_barE[CL], peer_eloss[CL];
+    unsigned peer_w[CL], peer_barW[CL], peer_barE[CL], peer_eloss[CL];       // (compile-time indices only: registers)
 #pragma unroll
     for (int r = 0; r < CL; ++r) {
         peer_barW[r] = map_to_rank(barW, r); peer_barE[r] = map_to_rank(barE, r);
@@ -201,37 +214,41 @@ __global__ void __launch_bounds__(CTH, 1) fit_cluster_kernel(const FitParams p) 
         float2 zh = make_float2(0.f, 0.f);
         if (pc < LP / 2) {                                   // latent piece: zh = x . We[:, 2pc..2pc+1], fused chain over the ETFs
             const float* Wl = We + 2 * pc;
+            float2 ze = make_float2(0.f, 0.f), zo = make_float2(0.f, 0.f);      // chains over the even / the odd ETFs
 #pragma unroll
             for (int e4 = 0; e4 < EP / 4; ++e4) {
                 const float4 xv = ld4(xr + 4 * e4);
-                zh = __ffma2_rn(make_float2(xv.x, xv.x), ld2(Wl + (4 * e4 + 0) * LP), zh);
-                zh = __ffma2_rn(make_float2(xv.y, xv.y), ld2(Wl + (4 * e4 + 1) * LP), zh);
-                zh = __ffma2_rn(make_float2(xv.z, xv.z), ld2(Wl + (4 * e4 + 2) * LP), zh);
-                zh = __ffma2_rn(make_float2(xv.w, xv.w), ld2(Wl + (4 * e4 + 3) * LP), zh);
+                ze = __ffma2_rn(make_float2(xv.x, xv.x), ld2(Wl + (4 * e4 + 0) * LP), ze);
+                zo = __ffma2_rn(make_float2(xv.y, xv.y), ld2(Wl + (4 * e4 + 1) * LP), zo);
+                ze = __ffma2_rn(make_float2(xv.z, xv.z), ld2(Wl + (4 * e4 + 2) * LP), ze);
+                zo = __ffma2_rn(make_float2(xv.w, xv.w), ld2(Wl + (4 * e4 + 3) * LP), zo);
             }
-            st2(H + rs * HS + 2 * pc, make_float2(lrelu(zh.x, alpha), lrelu(zh.y, alpha)));
+            zh = make_float2(__fadd_rn(ze.x, zo.x), __fadd_rn(ze.y, zo.y));
+            st2(Hrole + rs * HS + 2 * pc, make_float2(lrelu(zh.x, alpha), lrelu(zh.y, alpha)));
         }
-        __syncthreads();
+        role_sync();
         // ETF piece: zy = h . Wd[:, 2pc..2pc+1], fused chain over the latent units
         float2 zy = make_float2(0.f, 0.f);
         {
             const float* Wy = Wd + 2 * pc;
-            const float* hr = H + rs * HS;
+            const float* hr = Hrole + rs * HS;
+            float2 ze = make_float2(0.f, 0.f), zo = make_float2(0.f, 0.f);      // chains over the even / the odd latent units
 #pragma unroll
             for (int l4 = 0; l4 < CT; ++l4) {
                 const float4 hv = ld4(hr + 4 * l4);
-                zy = __ffma2_rn(make_float2(hv.x, hv.x), ld2(Wy + (4 * l4 + 0) * WDS), zy);
-                zy = __ffma2_rn(make_float2(hv.y, hv.y), ld2(Wy + (4 * l4 + 1) * WDS), zy);
-                zy = __ffma2_rn(make_float2(hv.z, hv.z), ld2(Wy + (4 * l4 + 2) * WDS), zy);
-                zy = __ffma2_rn(make_float2(hv.w, hv.w), ld2(Wy + (4 * l4 + 3) * WDS), zy);
+                ze = __ffma2_rn(make_float2(hv.x, hv.x), ld2(Wy + (4 * l4 + 0) * WDS), ze);
+                zo = __ffma2_rn(make_float2(hv.y, hv.y), ld2(Wy + (4 * l4 + 1) * WDS), zo);
+                ze = __ffma2_rn(make_float2(hv.z, hv.z), ld2(Wy + (4 * l4 + 2) * WDS), ze);
+                zo = __ffma2_rn(make_float2(hv.w, hv.w), ld2(Wy + (4 * l4 + 3) * WDS), zo);
             }
+            zy = make_float2(__fadd_rn(ze.x, zo.x), __fadd_rn(ze.y, zo.y));
         }
         const float2 xv = ld2(xr + 2 * pc);
         const float dx = lrelu(zy.x, alpha) - xv.x, dy = lrelu(zy.y, alpha) - xv.y;
         const float sse = valid ? fmaf(dy, dy, dx * dx) : 0.f;
-        if (!train) return sse;
+        if (!train) { role_sync(); return sse; }             // (H may be overwritten by the next chunk after this)
         st2(dZy + rs * XS + 2 * pc, make_float2(lrelu_grad(zy.x, coef * dx, alpha), lrelu_grad(zy.y, coef * dy, alpha)));
-        __syncthreads();
+        role_sync();
         if (pc < LP / 2) {                                   // dzh of the own latent columns: S_even + S_odd per column
             float2 a0 = make_float2(0.f, 0.f), a1 = make_float2(0.f, 0.f);
             const float* dr = dZy + rs * XS;
@@ -248,8 +265,7 @@ __global__ void __launch_bounds__(CTH, 1) fit_cluster_kernel(const FitParams p) 
             st2(dZh + rs * HS + 2 * pc, make_float2(lrelu_grad(zh.x, __fadd_rn(a0.x, a0.y), alpha),
                                                    lrelu_grad(zh.y, __fadd_rn(a1.x, a1.y), alpha)));
         }
-        __syncthreads();
-        return sse;
+        return sse;                                          // (the caller's CTA-wide barrier makes dZh visible to both roles)
     };
 
     // ---- grads phase + reduce-scatter: this CTA's class sum of every weight slot, sent to the slots' owners
@@ -289,11 +305,11 @@ __global__ void __launch_bounds__(CTH, 1) fit_cluster_kernel(const FitParams p) 
         }
     };
 
-    // ---- update of the owned pair + all-gather of the new weights
+    // ---- update of the owned pair + all-gather of the new weights (two weight slots per training thread)
     auto quad_gradient2 = [&]() -> float2 {                  // canonical combination of the six class sums
         const float* pq = part_in + (size_t)uq * 4 + 2 * uh;
-        auto at = [&](int s) { return ld2(pq + (size_t)s * QPC * 4); };
-        auto add2 = [](float2 a, float2 b) { return make_float2(__fadd_rn(a.x, b.x), __fadd_rn(a.y, b.y)); };
+        auto at = [&](int s2) { return ld2(pq + (size_t)s2 * QPC * 4); };
+        auto add2 = [](float2 x, float2 y) { return make_float2(__fadd_rn(x.x, y.x), __fadd_rn(x.y, y.y)); };
         const float2 even = add2(add2(at(0), at(2)), at(4));
         const float2 odd = add2(add2(at(1), at(3)), at(5));
         return add2(even, odd);
@@ -331,7 +347,7 @@ __global__ void __launch_bounds__(CTH, 1) fit_cluster_kernel(const FitParams p) 
 
     // ---- training run (same segment loop as fit_kernel.cu, resident mode)
     const int n_fit = p.n_fit, n_val = p.n_val, batch = p.batch;
-    const int n_tb = (n_fit + batch - 1) / batch, n_vb = (n_val + batch - 1) / batch, n_seg = n_tb + n_vb;
+    const int n_tb = (n_fit + batch - 1) / batch, n_vb = (n_val + batch - 1) / batch;
     int step = 0, wait_cnt = 0, epochs_run = 0, st = 0, cur = 0;
     unsigned phP = 0, phW = 0, phE = 0;                      // phase parities of the three barriers
     float best = INFINITY;
@@ -370,76 +386,26 @@ __global__ void __launch_bounds__(CTH, 1) fit_cluster_kernel(const FitParams p) 
 #else
 #define TICK(i) do { } while (0)
 #endif
-    for (int epoch = 0; epoch < p.max_epochs; ++epoch) {
-        float lsum = 0.f, vsum = 0.f;
-#pragma unroll 1
-        for (int seg = 0; seg < n_seg; ++seg) {
-            const bool train = seg < n_tb;
-            const int lo = (train ? seg : seg - n_tb) * batch;
-            const int nb = min(batch, (train ? n_fit : n_val) - lo);
-            const int* xoff = xoff_tab + cur * TP + (train ? lo : n_fit + lo);
-            const bool last = seg + 1 == n_seg;
-            if (last && !ident) {                            // next epoch's order into the other table
-                const int ne = epoch + 1 < p.max_epochs ? epoch + 1 : epoch;
-                if (dev_shuffle) make_perm(ne);
-                fill_order(xoff_tab + (cur ^ 1) * TP, ne);
-            }
-            float4 sa = make_float4(1.f, 1.f, 1.f, 0.f), sb = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (train) {
-                asm volatile("ld.global.nc.v4.f32 {%0,%1,%2,%3}, [%4];"
-                             : "=f"(sa.x), "=f"(sa.y), "=f"(sa.z), "=f"(sa.w) : "l"(p.sched + 2 * step));
-                asm volatile("ld.global.nc.v4.f32 {%0,%1,%2,%3}, [%4];"
-                             : "=f"(sb.x), "=f"(sb.y), "=f"(sb.z), "=f"(sb.w) : "l"(p.sched + 2 * step + 1));
-            }
-            TICK(0);
-            const float sse = rows_phase(xoff, nb, train, 2.f / (float)(nb * E));
-            TICK(1);
-            if (train) {
-                lsum += sse;
-                grads_and_send(xoff, nb);
-                __syncthreads();                             // the own class sums are in part_in
-                TICK(2);
-                wait(barP, phP); phP ^= 1;                   // ... and the five peers' sums of the slots this CTA owns
-                arm(barP, TX_SLOTS);
-                TICK(3);
-                update_and_send(step, sa, sb);
-                __syncthreads();                             // own weights written
-                TICK(4);
-                wait(barW, phW); phW ^= 1;                   // all six shares of the new weights are here
-                arm(barW, TX_SLOTS);
-                TICK(5);
-                ++step;
-            } else {
-                vsum += sse;
-            }
-            if (last && !ident) cur ^= 1;
-            __syncthreads();
+    // squared-error shares of one epoch: this role's warps reduce theirs (train: `tr`, validation: `va`) into red[0..5]
+    auto reduce_shares = [&](float tr, float va) {
+        const float v = warp_sum(val_role ? va : tr);
+        if (lane == 0) red[warp] = v;
+    };
+    auto own_share = [&]() { return make_float2((red[0] + red[1]) + red[2], (red[3] + red[4]) + red[5]); };
+    // the validation rows through the forward pass (validation warps; same weights as the training step beside them)
+    auto validate = [&]() -> float {
+        float vs = 0.f;
+        for (int vb = 0; vb < n_vb; ++vb) {
+            const int lo = vb * batch, nb = min(batch, n_val - lo);
+            vs += rows_phase(xoff_tab + n_fit + lo, nb, false, 0.f);      // (the validation rows' offsets are the same in both tables)
         }
-        // ---- epoch losses: this CTA's share (fixed-order block sum), then every CTA's share in rank order
-        TICK(0);
-        {
-            const float l1 = warp_sum(lsum), v1 = warp_sum(vsum);
-            if (lane == 0) { red[warp] = l1; red[8 + warp] = v1; }
-            __syncthreads();
-            if (tid == 0) {
-                float ls = 0.f, vs = 0.f;
-                for (int w = 0; w < CTH / 32; ++w) { ls += red[w]; vs += red[8 + w]; }
-                const float2 mine = make_float2(ls, vs);
-#pragma unroll
-                for (int r = 0; r < CL; ++r) {
-                    if (r == (int)c) eloss[c] = mine;
-                    else st_async_v2(peer_eloss[r], mine, peer_barE[r]);
-                }
-            }
-            __syncthreads();
-            wait(barE, phE); phE ^= 1;
-            arm(barE, TX_EPOCH);
-        }
+        return vs;
+    };
+    // every CTA's shares are in: the epoch's losses, its history entry, the early-stopping rule.  Returns true to stop.
+    auto close_epoch = [&](int epoch, float2 mine) -> bool {
         float loss = 0.f, val = 0.f;
 #pragma unroll
-        for (int r = 0; r < CL; ++r) { const float2 e2 = eloss[r]; loss += e2.x; val += e2.y; }
-        __syncthreads();                                     // everyone has read the mailbox before the next epoch refills it
-        TICK(6);
+        for (int r = 0; r < CL; ++r) { const float2 e2 = r == (int)c ? mine : eloss[r]; loss += e2.x; val += e2.y; }
         loss = loss / (float)(E * n_fit);
         val = n_val > 0 ? val / (float)(E * n_val) : NAN;
         if (c == 0 && tid == 0) {
@@ -451,15 +417,88 @@ __global__ void __launch_bounds__(CTH, 1) fit_cluster_kernel(const FitParams p) 
         if (p.early_stop && n_val > 0) {                     // EarlyStopping.on_epoch_end (App. A.6), identical on all six CTAs
             ++wait_cnt;
             if (val < best) { best = val; wait_cnt = 0; }
-            if (wait_cnt >= p.patience && epoch > 0) break;
+            if (wait_cnt >= p.patience && epoch > 0) return true;
         }
+        return false;
+    };
+
+    float lsum = 0.f;                                        // training threads: squared error of the epoch being trained
+    bool stopped = false;
+    for (int epoch = 0; epoch < p.max_epochs && !stopped; ++epoch) {
+#pragma unroll 1
+        for (int seg = 0; seg < n_tb; ++seg) {
+            const int lo = seg * batch;
+            const int nb = min(batch, n_fit - lo);
+            const int* xoff = xoff_tab + cur * TP + lo;
+            const bool last = seg + 1 == n_tb;
+            const bool closing = seg == 0 && epoch > 0;      // this step also validates and closes epoch - 1
+            if (last && !ident) {                            // next epoch's order into the other table
+                const int ne = epoch + 1 < p.max_epochs ? epoch + 1 : epoch;
+                if (dev_shuffle) make_perm(ne);
+                fill_order(xoff_tab + (cur ^ 1) * TP, ne);
+            }
+            float4 sa, sb;
+            asm volatile("ld.global.nc.v4.f32 {%0,%1,%2,%3}, [%4];"
+                         : "=f"(sa.x), "=f"(sa.y), "=f"(sa.z), "=f"(sa.w) : "l"(p.sched + 2 * step));
+            asm volatile("ld.global.nc.v4.f32 {%0,%1,%2,%3}, [%4];"
+                         : "=f"(sb.x), "=f"(sb.y), "=f"(sb.z), "=f"(sb.w) : "l"(p.sched + 2 * step + 1));
+            TICK(0);
+            if (!val_role) {
+                const float sse = rows_phase(xoff, nb, true, 2.f / (float)(nb * E));
+                if (closing) { reduce_shares(lsum, 0.f); lsum = 0.f; }
+                lsum += sse;
+            } else if (closing) {
+                reduce_shares(0.f, validate());
+            }
+            __syncthreads();                                 // H, dZy, dZh of the batch rows are complete
+            TICK(1);
+            grads_and_send(xoff, nb);                        // (training threads)
+            __syncthreads();                                 // the own class sums are in part_in, the shares in red
+            float2 mine = make_float2(0.f, 0.f);
+            if (closing) {
+                mine = own_share();
+                if (tid == 0) {
+#pragma unroll
+                    for (int r = 0; r < CL; ++r)
+                        if (r != (int)c) st_async_v2(peer_eloss[r], mine, map_to_rank(barP, r));
+                }
+            }
+            TICK(2);
+            wait(barP, phP); phP ^= 1;                       // the five peers' sums of the slots this CTA owns (+ their shares)
+            arm(barP, TX_SLOTS + (last ? TX_EPOCH : 0u));    // the next step closes an epoch iff this one ends one
+            TICK(3);
+            if (closing && close_epoch(epoch - 1, mine)) { stopped = true; break; }      // before the update: weights stay
+            update_and_send(step, sa, sb);
+            __syncthreads();                                 // own weights written
+            TICK(4);
+            wait(barW, phW); phW ^= 1;                       // all six shares of the new weights are here
+            arm(barW, TX_SLOTS);
+            TICK(5);
+            ++step;
+            if (last && !ident) cur ^= 1;
+            __syncthreads();
+        }
+    }
+    if (!stopped) {                                          // the last epoch of a run that never stopped: its own validation pass
+        TICK(0);
+        reduce_shares(lsum, val_role ? validate() : 0.f);
+        __syncthreads();
+        const float2 mine = own_share();
+        if (tid == 0) {
+#pragma unroll
+            for (int r = 0; r < CL; ++r)
+                if (r != (int)c) st_async_v2(peer_eloss[r], mine, peer_barE[r]);
+        }
+        wait(barE, phE); phE ^= 1;
+        close_epoch(p.max_epochs - 1, mine);
+        TICK(6);
     }
 
 #ifdef HFREP_CLUSTER_TIMING
     if (tid == 0 && blockIdx.x < CL)
-        printf("cluster timing LP=%d cta=%u steps=%d epochs=%d: rows %lld grads+send %lld waitP %lld update+send %lld waitW %lld epoch-exchange %lld (cycles/step; epoch part per epoch)\n",
-               LP, c, step, epochs_run, tk[1] / (step + epochs_run * n_vb), tk[2] / max(step, 1), tk[3] / max(step, 1), tk[4] / max(step, 1),
-               tk[5] / max(step, 1), tk[6] / max(epochs_run, 1));
+        printf("cluster timing LP=%d cta=%u steps=%d epochs=%d: rows %lld grads+send %lld waitP %lld update+send %lld waitW %lld (cycles/step)\n",
+               LP, c, step, epochs_run, tk[1] / max(step, 1), tk[2] / max(step, 1), tk[3] / max(step, 1), tk[4] / max(step, 1),
+               tk[5] / max(step, 1));
 #endif
     if (c == 0) {
         for (int e2 = epochs_run + tid; e2 < p.max_epochs; e2 += CTH) {

@@ -19,7 +19,8 @@
 // that feeds the weights has one fixed order in every mapping, so a run's weight trajectory is bit-identical across the
 // mappings and to the CPU oracle — a LeakyReLU pre-activation within rounding of zero would otherwise send two correct
 // float32 implementations down different branches (3e-5 jumps in the loss history).
-//   zh[r][l]  fused chain over e = 0..E-1;  zy[r][e]  fused chain over l = 0..L-1   (padding adds exact zeros)
+//   zh[r][l] = Z_even + Z_odd, fused chains over the even / the odd ETFs in ascending order; zy[r][e] likewise over the
+//   latent units   (padding adds exact zeros)
 //   dzy = lrelu'(zy) * (coef * (y - x)), coef = 2 / (rows * E) rounded once
 //   dh[r][l] = S_even + S_odd, fused chains over the even / the odd ETFs, ascending
 //   dWd, dWe = (p0 + p2 + p4) + (p1 + p3 + p5), p_c = fused chain over the batch positions q = c, c+6, c+12, ...
@@ -238,27 +239,39 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
                 rs[j] = valid ? r : BP;
             }
             // ---- zh pieces = x . We[:, own pieces]
+            // two fused chains per output, over the even and over the odd ETFs, then their sum (canonical order)
             float2 zh[R][NPL];
+            {
+                float2 zc[2][R][NPL];
 #pragma unroll
-            for (int j = 0; j < R; ++j)
+                for (int h = 0; h < 2; ++h)
 #pragma unroll
-                for (int i = 0; i < NPL; ++i) zh[j][i] = make_float2(0.f, 0.f);
+                    for (int j = 0; j < R; ++j)
+#pragma unroll
+                        for (int i = 0; i < NPL; ++i) zc[h][j][i] = make_float2(0.f, 0.f);
 #pragma unroll (FULL ? EP / 4 : 2)
-            for (int e4 = 0; e4 < EP / 4; ++e4) {
-                float xe[R][4];
+                for (int e4 = 0; e4 < EP / 4; ++e4) {
+                    float xe[R][4];
 #pragma unroll
-                for (int j = 0; j < R; ++j) {
-                    const float4 v = ld4(xr[j] + 4 * e4);
-                    xe[j][0] = v.x; xe[j][1] = v.y; xe[j][2] = v.z; xe[j][3] = v.w;
+                    for (int j = 0; j < R; ++j) {
+                        const float4 v = ld4(xr[j] + 4 * e4);
+                        xe[j][0] = v.x; xe[j][1] = v.y; xe[j][2] = v.z; xe[j][3] = v.w;
+                    }
+#pragma unroll
+                    for (int k = 0; k < 4; ++k)
+#pragma unroll
+                        for (int i = 0; i < NPL; ++i) {
+                            const float2 w = ld2(Wl + (4 * e4 + k) * LP + 2 * NC * i);
+#pragma unroll
+                            for (int j = 0; j < R; ++j)
+                                zc[k & 1][j][i] = __ffma2_rn(make_float2(xe[j][k], xe[j][k]), w, zc[k & 1][j][i]);
+                        }
                 }
 #pragma unroll
-                for (int k = 0; k < 4; ++k)
+                for (int j = 0; j < R; ++j)
 #pragma unroll
-                    for (int i = 0; i < NPL; ++i) {
-                        const float2 w = ld2(Wl + (4 * e4 + k) * LP + 2 * NC * i);
-#pragma unroll
-                        for (int j = 0; j < R; ++j) zh[j][i] = __ffma2_rn(make_float2(xe[j][k], xe[j][k]), w, zh[j][i]);
-                    }
+                    for (int i = 0; i < NPL; ++i)
+                        zh[j][i] = make_float2(__fadd_rn(zc[0][j][i].x, zc[1][j][i].x), __fadd_rn(zc[0][j][i].y, zc[1][j][i].y));
             }
 #pragma unroll
             for (int i = 0; i < NPL; ++i)
@@ -270,26 +283,37 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
             team_sync<NW>(team);
             // ---- zy pieces = h . Wd[:, own pieces]
             float2 zy[R][NPE];
+            {
+                float2 zc[2][R][NPE];          // chains over the even / the odd latent units
 #pragma unroll
-            for (int j = 0; j < R; ++j)
+                for (int h = 0; h < 2; ++h)
 #pragma unroll
-                for (int i = 0; i < NPE; ++i) zy[j][i] = make_float2(0.f, 0.f);
+                    for (int j = 0; j < R; ++j)
+#pragma unroll
+                        for (int i = 0; i < NPE; ++i) zc[h][j][i] = make_float2(0.f, 0.f);
 #pragma unroll (FULL ? CT : 2)
-            for (int l4 = 0; l4 < CT; ++l4) {
-                float hl[R][4];
+                for (int l4 = 0; l4 < CT; ++l4) {
+                    float hl[R][4];
 #pragma unroll
-                for (int j = 0; j < R; ++j) {
-                    const float4 v = ld4(H + rs[j] * HS + 4 * l4);
-                    hl[j][0] = v.x; hl[j][1] = v.y; hl[j][2] = v.z; hl[j][3] = v.w;
+                    for (int j = 0; j < R; ++j) {
+                        const float4 v = ld4(H + rs[j] * HS + 4 * l4);
+                        hl[j][0] = v.x; hl[j][1] = v.y; hl[j][2] = v.z; hl[j][3] = v.w;
+                    }
+#pragma unroll
+                    for (int k = 0; k < 4; ++k)
+#pragma unroll
+                        for (int i = 0; i < NPE; ++i) {
+                            const float2 w = ld2(Wy + (4 * l4 + k) * WDS + 2 * NC * i);
+#pragma unroll
+                            for (int j = 0; j < R; ++j)
+                                zc[k & 1][j][i] = __ffma2_rn(make_float2(hl[j][k], hl[j][k]), w, zc[k & 1][j][i]);
+                        }
                 }
 #pragma unroll
-                for (int k = 0; k < 4; ++k)
+                for (int j = 0; j < R; ++j)
 #pragma unroll
-                    for (int i = 0; i < NPE; ++i) {
-                        const float2 w = ld2(Wy + (4 * l4 + k) * WDS + 2 * NC * i);
-#pragma unroll
-                        for (int j = 0; j < R; ++j) zy[j][i] = __ffma2_rn(make_float2(hl[j][k], hl[j][k]), w, zy[j][i]);
-                    }
+                    for (int i = 0; i < NPE; ++i)
+                        zy[j][i] = make_float2(__fadd_rn(zc[0][j][i].x, zc[1][j][i].x), __fadd_rn(zc[0][j][i].y, zc[1][j][i].y));
             }
             // ---- squared error and dLoss/dzy on the lane's pieces
 #pragma unroll

@@ -11,8 +11,8 @@
  *   1  the CANONICAL ORDER of DESIGN.md §5, the one every mapping of the CUDA fit kernel follows, so that the weight
  *      trajectory of a run is bit-identical on both sides (a LeakyReLU pre-activation within rounding of zero otherwise
  *      lets two correct float32 implementations take different branches — see DESIGN.md):
- *        zh[r][l]   fused multiply-add chain over the ETFs e = 0..E-1, from 0
- *        zy[r][e]   fused multiply-add chain over the latent units l = 0..L-1, from 0
+ *        zh[r][l]   Z_even + Z_odd, fused multiply-add chains over the even / the odd ETFs in ascending order, from 0
+ *        zy[r][e]   the same over the even / the odd latent units
  *        dzy        lrelu'(zy) * (coef * (y - x)),  coef = 2 / (rows * E) rounded once
  *        dh[r][l]   S_even + S_odd, each a fused chain over the even / odd ETFs in ascending order
  *        dWd, dWe   (p0 + p2 + p4) + (p1 + p3 + p5), p_c = fused chain over the batch positions q = c, c+6, c+12, ...
@@ -83,16 +83,24 @@ int FIT_ONE(const fit_cfg* c, const float* x, float* We, float* Wd, const int* p
                     memcpy(Xb + (size_t)r * E, xr, sizeof(float) * E);
                     for (int l = 0; l < L; ++l) {
                         float z = 0.f;
-                        if (canon) for (int e = 0; e < E; ++e) z = fmaf(xr[e], We[e * L + l], z);
-                        else for (int e = 0; e < E; ++e) z += xr[e] * We[e * L + l];
+                        if (canon) {
+                            float z0 = 0.f, z1 = 0.f;
+                            for (int e = 0; e < E; e += 2) z0 = fmaf(xr[e], We[e * L + l], z0);
+                            for (int e = 1; e < E; e += 2) z1 = fmaf(xr[e], We[e * L + l], z1);
+                            z = z0 + z1;
+                        } else for (int e = 0; e < E; ++e) z += xr[e] * We[e * L + l];
                         Zh[r * L + l] = z;
                         H[r * L + l] = lrelu(z, c->alpha);
                     }
                     float row = 0.f;
                     for (int e = 0; e < E; ++e) {
                         float z = 0.f;
-                        if (canon) for (int l = 0; l < L; ++l) z = fmaf(H[r * L + l], Wd[l * E + e], z);
-                        else for (int l = 0; l < L; ++l) z += H[r * L + l] * Wd[l * E + e];
+                        if (canon) {
+                            float z0 = 0.f, z1 = 0.f;
+                            for (int l = 0; l < L; l += 2) z0 = fmaf(H[r * L + l], Wd[l * E + e], z0);
+                            for (int l = 1; l < L; l += 2) z1 = fmaf(H[r * L + l], Wd[l * E + e], z1);
+                            z = z0 + z1;
+                        } else for (int l = 0; l < L; ++l) z += H[r * L + l] * Wd[l * E + e];
                         Zy[r * E + e] = z;
                         const float d = lrelu(z, c->alpha) - xr[e];
                         row += d * d;

@@ -111,10 +111,16 @@ def class_sum(a, b):
     return ((p[0] + p[2]) + p[4]) + ((p[1] + p[3]) + p[5])
 
 
+def chain2(a, b):
+    """Canonical order of a layer's pre-activation: fused chains over the even and over the odd terms, then their sum."""
+    K = a.shape[1]
+    return (chain(a, b, range(0, K, 2)) + chain(a, b, range(1, K, 2))).astype(F32)
+
+
 def forward_canonical(x, We, Wd, alpha):
-    zh = chain(x, We, range(x.shape[1]))
+    zh = chain2(x, We)
     h = lrelu(zh, alpha)
-    zy = chain(h, Wd, range(h.shape[1]))
+    zy = chain2(h, Wd)
     return zh, h, zy, lrelu(zy, alpha)
 
 

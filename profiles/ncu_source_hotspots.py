@@ -12,7 +12,8 @@ for r in rows:
     if cur is None: continue
     if r[0]=="Line No": cur['hdr']=r; continue
     cur['rows'].append((fname,r))
-src=open('/root/repo/do-you-really-need-to-pay-2-20-hedge-fund-strategy-replication-via-machine-learning_b200/csrc/fit_kernel.cu').read().split('\n')
+import os
+SRC={f: open('/root/repo/do-you-really-need-to-pay-2-20-hedge-fund-strategy-replication-via-machine-learning_b200/csrc/'+f).read().split('\n') for f in ('fit_kernel.cu','fit_cluster.cu','common.cuh','fit_params.cuh')}
 agg=collections.Counter(); inst=collections.Counter(); sass={}
 for b in blocks:
     if key in b['name']:
@@ -24,7 +25,7 @@ for b in blocks:
                 if a not in sass: sass[a]=[r[so], int(r[si]), int(r[ie]) if r[ie].isdigit() else 0, f, r[0]]
 tot=sum(agg.values()); ti=sum(inst.values()); print(key, 'total samples', tot, 'total warp-inst', ti)
 for (f,l),v in agg.most_common(topn):
-    text = src[int(l)-1].strip()[:100] if f=='fit_kernel.cu' and l.isdigit() else ''
+    text = SRC[f][int(l)-1].strip()[:100] if f in SRC and l.isdigit() else ''
     print(f"  {v*100/tot:5.1f}%  inst={inst[(f,l)]*100/ti:5.1f}% {f}:{l:>4s}  {text}")
 print("top sass")
 for a,v in sorted(sass.items(), key=lambda kv:-kv[1][1])[:15]:
