@@ -41,9 +41,10 @@ T_ALL, E, F, WINDOW = 337, 22, 13, 24
 LATENTS = list(range(1, 22))
 EPOCHS = 1000
 WORKLOAD = "cfg2: 13 indices x 145 windows x L=1..21 x 1 seed per GPU (Mode R), synthetic 337x(22+13+1)"
-# dram__bytes_read.sum + dram__bytes_write.sum per fit_kernel launch of the cfg2 sweep, from the committed
-# `ncu --set full` capture (profiles/r1_ncu_full_cfg2_summary.txt): the kernel is shared-memory resident.
-NCU_DRAM_BYTES_PER_FIT_LAUNCH = 80e3
+# dram__bytes_read.sum + dram__bytes_write.sum per fit_cluster_kernel launch of the cfg2 sweep, from the committed
+# `ncu --set full` capture (profiles/r2_ncu_full_cfg2_summary.txt: 92-140 KB per launch, 0 B written): every CTA of a
+# cluster stages its task's 15 KB training block; the run itself is shared-memory resident.
+NCU_DRAM_BYTES_PER_FIT_LAUNCH = 110e3
 
 
 def synthetic_returns(seed=20240611):
@@ -75,12 +76,13 @@ def _cpu_task(args):
     We0, Wd0 = fitcore.initial_weights(seed, E, L)
     cfg = fitcore.FitConfig(epochs=EPOCHS, early_stop=True)
     t = time.perf_counter()
-    out = ae_oracle.run_task(etf[:168], hfd[:168], etf[168:], hfd[168:], rf, etf, L, We0, Wd0, cfg=cfg)
+    out = ae_oracle.run_task(etf[:168], hfd[:168], etf[168:], hfd[168:], rf, etf, L, We0, Wd0, cfg=cfg, order="blas")
     return time.perf_counter() - t, int(out["epochs_run"])
 
 
-CPU_IMPL = ("oracle/ae_oracle.py: the fit as compiled C in the canonical summation order (oracle/c/fit_oracle.c, one thread "
-            "per task — the reference pins TF to one thread, helper.py:38), every evaluation stage in numpy float64")
+CPU_IMPL = ("oracle/ae_oracle.py: the fit as a float32 numpy step loop over BLAS matmuls — the structure of Keras' fit without its "
+            "per-step dispatch cost, as in round 1 — and every evaluation stage in numpy float64; one thread per task (the "
+            "reference pins TF to one thread, helper.py:38).  cpu_best_effort is the fit alone as compiled C on all cores")
 
 
 def cpu_reference_arm(args):
@@ -346,7 +348,7 @@ def gpu_arm(args):
     peak = ffma_peak()
     flop = float(sum(flops_per_epoch(L) * int(n) for L, n in zip(task_L, epochs_run)))
     achieved = flop / (fit_ms_mean * 1e-3) / 1e12
-    roofline = {"bound": "fp32_ffma", "kernel": "fit_kernel", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
+    roofline = {"bound": "fp32_ffma", "kernel": "fit_cluster_kernel", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
                 "frac": achieved / peak, "traffic": NCU_DRAM_BYTES_PER_FIT_LAUNCH,
                 "peak_source": "measured live: hfrep_ffma_peak (8 packed FFMA2 chains/thread, full grid; scalar FFMA reaches 64.4 on the same box); MEASURED_PEAKS.json has no FP32 figure; nominal 148*128*2*1.965 GHz = 74.4",
                 "algorithmic_flop_per_launch": flop, "ms_per_launch": fit_ms_mean,

@@ -193,9 +193,9 @@ class AEOracle:
         self.We = self.Wd = None
 
     # :72-96
-    def train(self, We0, Wd0, patience=5, perm=None, cfg=None, record_grads_at=()):
+    def train(self, We0, Wd0, patience=5, perm=None, cfg=None, record_grads_at=(), order="canonical"):
         cfg = cfg or fitcore.FitConfig(patience=patience)
-        out = fitcore.fit(self.x_train_scaled, We0, Wd0, cfg, perm=perm, record_grads_at=record_grads_at)
+        out = fitcore.fit(self.x_train_scaled, We0, Wd0, cfg, perm=perm, record_grads_at=record_grads_at, order=order)
         self.We, self.Wd, self.fit_out = out["We"], out["Wd"], out
         return out
 
@@ -287,11 +287,11 @@ class AEOracle:
 
 
 def run_task(x_train, y_train, x_test, y_test, rf, etf_all, L, We0, Wd0, perm=None, cfg=None,
-             with_oos=True):
+             with_oos=True, order="canonical"):
     """One complete task-fit the way the notebook sweeps it (autoencoder_v4.ipynb:158-165,
     :896-901): fit, IS/OOS quality, ante, turnover, post, metrics.  Returns a dict of arrays."""
     ae = AEOracle(x_train, y_train, x_test, y_test, L)
-    fo = ae.train(We0, Wd0, perm=perm, cfg=cfg)
+    fo = ae.train(We0, Wd0, perm=perm, cfg=cfg, order=order)
     out = dict(We=ae.We, Wd=ae.Wd, loss=fo["loss"], val_loss=fo["val_loss"], epochs_run=fo["epochs_run"],
                is_r2=ae.model_IS_r2(), is_rmse=ae.model_IS_RMSE())
     if with_oos:
