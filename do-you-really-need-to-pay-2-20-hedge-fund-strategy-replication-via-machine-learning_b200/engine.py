@@ -88,8 +88,20 @@ def unpack_weights(row: np.ndarray, E: int, L: int):
     return row[:E * L].reshape(E, L).copy(), row[E * L:2 * E * L].reshape(L, E).copy()
 
 
+_WINDOW_TABLES: dict = {}
+
+
 def window_index(kind: str, T: int, window: int):
-    """Bit-exact window tables from the C ABI: returns (starts, lens) int32."""
+    """Bit-exact window tables from the C ABI: returns (starts, lens) int32 (cached per argument set)."""
+    hit = _WINDOW_TABLES.get((kind, T, window))
+    if hit is not None:
+        return hit[0].copy(), hit[1].copy()
+    starts, lens = _window_index(kind, T, window)
+    _WINDOW_TABLES[(kind, T, window)] = (starts.copy(), lens.copy())
+    return starts, lens
+
+
+def _window_index(kind: str, T: int, window: int):
     k = {"rolling": 0, "expanding": 1, "expost": 2}[kind]
     n = check(lib.hfrep_window_index(k, T, window, None, None, 0))
     starts, lens = np.zeros(n, np.int32), np.zeros(n, np.int32)
@@ -144,6 +156,9 @@ def to_device(a: np.ndarray, device, dtype=None) -> torch.Tensor:
     return out
 
 
+_PAD: dict = {}
+
+
 def to_host(tensors) -> list:
     """Device tensors -> host numpy arrays with ONE device-to-host copy: the tensors' bytes are concatenated on the
     device (one kernel), copied into one page-locked buffer (torch's caching host allocator: no cudaHostAlloc after
@@ -152,12 +167,15 @@ def to_host(tensors) -> list:
     if not live:
         return [None for _ in tensors]
     dev = live[0].device
+    zeros = _PAD.get(dev)
+    if zeros is None:
+        zeros = _PAD[dev] = torch.zeros(16, dtype=torch.uint8, device=dev)
     flat, off = [], 0
     for t in live:                                     # every field starts 16-byte aligned in the packed buffer
         f = t.contiguous().reshape(-1).view(torch.uint8)
         pad = (-off) & 15
         if pad:
-            flat.append(torch.zeros(pad, dtype=torch.uint8, device=dev))
+            flat.append(zeros[:pad])
             off += pad
         flat.append(f)
         off += f.numel()

@@ -272,6 +272,37 @@ def test_fit_vs_oracle_synthetic(hf, E, L, T, batch):
         assert np.array_equal(We, o["We"]) and np.array_equal(Wd, o["Wd"])
 
 
+def test_fit_bit_exact_on_random_shapes(hf):
+    """Sixty random shapes (ETF count, latent width, block length, batch size, validation split, shuffled or fixed order,
+    early stopping on or off) through a random mapping each: trained kernels, stop epoch — the oracle's bits."""
+    from oracle import fitcore
+    rng = np.random.default_rng(2024)
+    dev = torch.device("cuda:0")
+    for trial in range(60):
+        E, L = int(rng.integers(2, 25)), int(rng.integers(1, 25))
+        T, batch = int(rng.integers(12, 200)), int(rng.integers(3, 49))
+        split = float(rng.choice([.25, .1, .4]))
+        epochs = int(rng.integers(3, 40))
+        wpt = int(rng.choice([1, 2, 3, 6, 60]))
+        early = bool(rng.integers(0, 2))
+        x = rng.uniform(0, 1, (T, E))
+        n_fit = fitcore.split_at(T, split)
+        perm = fitcore.make_perm(trial, epochs, n_fit) if rng.integers(0, 2) else None
+        We0, Wd0 = fitcore.initial_weights(trial, E, L)
+        cfg = fitcore.FitConfig(epochs=epochs, batch_size=batch, validation_split=split, patience=2, early_stop=early)
+        o = fitcore.fit(x, We0, Wd0, cfg, perm=perm)
+        X = hf.engine.to_device(x.astype(np.float32)[None], dev)
+        W0 = hf.engine.to_device(hf.engine.pack_weights([(We0, Wd0)], E, 2 * E * L), dev)
+        res = hf.fit_batched(X, [L], W0, E=E, T=T, n_fit=n_fit, max_epochs=epochs, batch=batch, patience=2, early_stop=int(early),
+                             perm=None if perm is None else hf.engine.to_device(perm, dev), warps_per_task=wpt)
+        tag = (trial, E, L, T, batch, split, epochs, wpt, early, perm is not None)
+        assert int(res.epochs_run[0]) == o["epochs_run"], tag
+        We, Wd = hf.engine.unpack_weights(res.W[0].cpu().numpy(), E, L)
+        assert np.array_equal(We, o["We"]) and np.array_equal(Wd, o["Wd"]), tag
+        n = o["epochs_run"]
+        assert np.max(np.abs(res.loss[0, :n].cpu().numpy() - o["loss"]) / o["loss"]) < TOL, tag
+
+
 def test_per_task_blocks_and_perms(hf):
     """n_x > 1 (each task its own training block, cfg-5 style) with per-task permutation tables."""
     from oracle import fitcore
