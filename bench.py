@@ -12,9 +12,10 @@ Multi-GPU (`--gpus N`, one rank per GPU): every rank runs that sweep for ITS OWN
 distinct fits, no data-path collective, `value` = all ranks' fits / the slowest rank's time (weak
 scaling).  The same line carries `sharded`: configs[2] (L = 1..21 x 64 seeds = 1 344 fits) dealt
 cyclically over the N ranks through the public API with host buffers, finished by the one NCCL
-all-gather of result records, timed end to end.  At N = 1 the line also carries the throughput
-regime (`ensemble`), the HBM-bound kernels (`hbm_kernels`), configs[3] (`wide`) and configs[4]
-(`paths`) samples and the CPU baselines.
+all-gather of result records, timed end to end; `wide`: configs[3] at its stated size (4 747 windows x
+10 000 funds x 500 ETFs) and `paths`: configs[4] (1 000 000 generated paths as tasks), their windows /
+paths dealt over the N ranks.  At N = 1 the line also carries the throughput regime (`ensemble`), the
+HBM-bound kernels (`hbm_kernels`) and the CPU baselines.
 
 `--impl reference` times the CPU restatement of the reference path (oracle/ae_oracle.py — the
 reference itself needs Keras, which cannot be installed, and cannot travel to the GPU box) on
@@ -310,6 +311,10 @@ def gpu_arm(args):
     # ---- the sharded job: configs[2] dealt over the ranks, one all-gather of result records, host buffers in and out
     sharded = sharded_job(args, hfrep, engine, dist, torch, dev, rank, world, (etf, hfd, rf), barrier)
 
+    # ---- configs[3] and configs[4] at their stated sizes, their units dealt over the ranks
+    wide_raw = wide_job(args, hfrep, torch, dist, dev, rank, world, barrier) if (args.wide_windows > 0 and not args.no_extras) else None
+    paths_raw = paths_job(args, hfrep, engine, torch, dist, dev, rank, world, barrier) if (args.path_tasks > 0 and not args.no_extras) else None
+
     # ---- max over ranks
     tt = torch.tensor([total_ms, e2e_s * 1e3, float(np.mean(fit_ms))], dtype=torch.float64, device=dev)
     per_rank = None
@@ -354,11 +359,11 @@ def gpu_arm(args):
                 "algorithmic_flop_per_launch": flop, "ms_per_launch": fit_ms_mean,
                 "note": f"{n_tasks} fits on {n_buckets} concurrent launches: cfg2 exposes only 21 sequential chains, so this is latency-, not FFMA-bound; see 'ensemble'"}
 
-    extras = world == 1 and not args.no_extras
+    extras = world == 1 and not args.no_extras           # single-GPU records (ensemble, HBM kernels)
     ens = ensemble_record(args, hfrep, engine, torch, data, dev, flush, peak, w_stride) if extras else None
     hbm = hbm_kernels_record(hfrep, engine, torch, data, dev, flush, task_L, last) if extras else None
-    wide = wide_record(args, hfrep, torch, dev, peak) if (extras and args.wide_windows > 0) else None
-    paths = paths_record(args, hfrep, engine, torch, dev, peak) if (extras and args.path_tasks > 0) else None
+    wide = wide_record(wide_raw, peak) if wide_raw else None
+    paths = paths_record(paths_raw, peak) if paths_raw else None
 
     cpu = cpu_baseline_single_core() if (world == 1 and not args.no_cpu_baseline) else None
     line = {
@@ -537,10 +542,20 @@ def hbm_kernels_record(hfrep, engine, torch, data, dev, flush, task_L, last):
     return out
 
 
-def wide_record(args, hfrep, torch, dev, peak):
-    """A bounded sample of configs[3] (500 ETFs, 10 000 funds, 252-day windows, rolling refit) through the wide kernels."""
+def _max_over_ranks(torch, dist, dev, world, values):
+    t = torch.tensor(values, dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return [float(v) for v in t.cpu()]
+
+
+def wide_job(args, hfrep, torch, dist, dev, rank, world, barrier):
+    """configs[3] (500 ETFs, 10 000 funds, 5 000-day history, 252-day windows, rolling refit: 4 747 windows, L = 8, 100
+    epochs as SURVEY §8d fixes it) through the wide kernels, the windows dealt cyclically over the ranks, every rank's
+    replica rows all-gathered at the end.  Every rank builds the same synthetic history (SURVEY §8d cfg 4 factor model)."""
+    from hfrep import distributed
     wT, wE, wF, wW, wL, wep = 5000, 500, args.wide_funds, 252, 8, 100
-    wr = np.random.default_rng(20240611)                         # SURVEY 8d cfg 4 factor model
+    wr = np.random.default_rng(20240611)
     fac = wr.normal(size=(wT, 10)) * .01
     wetf = fac @ wr.normal(size=(10, wE)) + wr.normal(size=(wT, wE)) * .005
     idx = wr.integers(0, wE, size=(wF, 5))
@@ -549,78 +564,109 @@ def wide_record(args, hfrep, torch, dev, peak):
     for j in range(5):
         whfd += wetf[:, idx[:, j]] * wts[:, j]
     whfd += wr.normal(size=(wT, wF)) * .003
-    wins = np.linspace(0, wT - wW - 2, args.wide_windows).astype(int)
-    best_t = None
+    n_all = wT - wW - 1                                              # 4 747 windows
+    n_win = min(args.wide_windows, n_all)
+    wins = np.arange(n_all) if n_win == n_all else np.linspace(0, n_all - 1, n_win).astype(int)
+    mine = wins[rank::world]
+    W0 = hfrep.engine.pack_weights([hfrep.engine.initial_weights(100003 + int(wi), wE, wL) for wi in mine], wE, 2 * wE * wL)
+    best, ok = None, True
     for i in range(3):
         tm = {}
-        torch.cuda.synchronize()
+        barrier()
         t0 = time.perf_counter()
-        wo = hfrep.run_mode_w_wide(wetf, whfd, np.full(wT, 1e-4), train_window=wW, latent_dim=wL, seeds=(1,), windows=wins,
-                                   device=dev, max_epochs=wep, early_stop=0, timings=tm)
+        wo = hfrep.run_mode_w_wide(wetf, whfd, np.full(wT, 1e-4), train_window=wW, latent_dim=wL, seeds=(1,), windows=mine,
+                                   device=dev, W0=W0, max_epochs=wep, early_stop=0, timings=tm)
+        g0 = torch.cuda.Event(enable_timing=True); g1 = torch.cuda.Event(enable_timing=True)
+        g0.record()
+        replica = distributed.gather_results(wo["replica"][0], n_win, rank, world) if world > 1 else wo["replica"][0]
+        g1.record()
         torch.cuda.synchronize()
-        tm["e2e_ms"] = (time.perf_counter() - t0) * 1e3
-        if best_t is None:
-            best_t = tm
-        else:
-            best_t = {k: min(best_t[k], tm[k]) for k in tm}
-    wflop = float(args.wide_windows) * wep * flops_per_epoch(wL, 189, 63, 48, wE)
-    return {"workload": f"cfg4 sample: {args.wide_windows} of 4747 windows x {wF} funds, 500 ETFs, L={wL}, {wep} epochs, rolling refit",
-            "fit_ms": best_t["fit_ms"], "eval_ms": best_t["eval_ms"], "e2e_ms_with_h2d": best_t["e2e_ms"],
-            "h2d_bytes": int(whfd.nbytes + wetf.nbytes),
-            "fits_per_s": args.wide_windows / (best_t["fit_ms"] * 1e-3),
-            "results_per_s_e2e": args.wide_windows * wF / (best_t["e2e_ms"] * 1e-3),
-            "status_ok": bool(int(wo["fit"].status.abs().sum()) == 0 and torch.isfinite(wo["replica"]).all()),
-            "roofline": {"bound": "fp32_ffma", "kernel": "fit_wide2_kernel", "achieved": wflop / (best_t["fit_ms"] * 1e-3) / 1e12,
-                         "peak": peak, "unit": "TFLOP/s", "frac": wflop / (best_t["fit_ms"] * 1e-3) / 1e12 / peak}}
+        tm["gather_ms"] = g0.elapsed_time(g1)
+        barrier()
+        tm["job_ms"] = (time.perf_counter() - t0) * 1e3
+        ok = ok and bool(int(wo["fit"].status.abs().sum()) == 0 and replica.shape[0] == n_win and torch.isfinite(replica).all())
+        best = tm if best is None else {k: min(best[k], tm[k]) for k in tm}
+    fit_ms, eval_ms, gather_ms, job_ms = _max_over_ranks(torch, dist, dev, world, [best["fit_ms"], best["eval_ms"], best["gather_ms"], best["job_ms"]])
+    return dict(n_win=n_win, n_all=n_all, wF=wF, wE=wE, wL=wL, wep=wep, world=world, fit_ms=fit_ms, eval_ms=eval_ms, gather_ms=gather_ms,
+                job_ms=job_ms, ok=ok, h2d=int(whfd.nbytes + wetf.nbytes), gathered=int(n_win * wF * 8))
 
 
-def paths_record(args, hfrep, engine, torch, dev, peak):
-    """A bounded sample of configs[4]: generated paths (168 x 36, MinMax space; the generator's file is absent, so
-    clip(N(.61, .2), -.13, 1.26) as in SURVEY §8d) as augmented training tasks — every path its own training block
-    (`task_x`), L = 8, through the same batched fit (batch-tile mode).  Fixed epochs (no early stop) so the flop count is exact."""
-    n, T, L, ep = args.path_tasks, 168, 8, args.path_epochs
+def wide_record(r, peak):
+    wflop = float(r["n_win"]) * r["wep"] * flops_per_epoch(r["wL"], 189, 63, 48, r["wE"])
+    per_gpu_flops = wflop / r["world"] / (r["fit_ms"] * 1e-3) / 1e12
+    return {"workload": f"cfg4: {r['n_win']} of {r['n_all']} windows x {r['wF']} funds, 500 ETFs, L={r['wL']}, {r['wep']} epochs, rolling refit, "
+                        f"windows dealt over {r['world']} GPU(s), replica rows all-gathered",
+            "fit_ms": r["fit_ms"], "eval_ms": r["eval_ms"], "gather_ms": r["gather_ms"], "job_ms_with_h2d": r["job_ms"],
+            "h2d_bytes_per_rank": r["h2d"], "gathered_bytes": r["gathered"] if r["world"] > 1 else 0,
+            "fits_per_s": r["n_win"] / (r["fit_ms"] * 1e-3), "results_per_s_e2e": r["n_win"] * r["wF"] / (r["job_ms"] * 1e-3),
+            "status_ok": r["ok"],
+            "roofline": {"bound": "fp32_ffma", "kernel": "fit_wide2_kernel", "achieved": per_gpu_flops, "peak": peak, "unit": "TFLOP/s",
+                         "frac": per_gpu_flops / peak, "note": "per GPU"}}
+
+
+def paths_job(args, hfrep, engine, torch, dist, dev, rank, world, barrier):
+    """configs[4]: generated paths (168 x 36 in MinMax space) as augmented training tasks — every path its own training
+    block (`task_x`), L = 8, through the same batched fit (batch-tile mode), the paths dealt over the ranks.  The paths come
+    from the reference's own saved generator (weights carried in tests/golden) run on each rank's GPU; without that file,
+    from clip(N(.61, .2), -.13, 1.26) as in SURVEY §8d.  Fixed epochs (no early stop) so the flop count is exact."""
+    n_all, T, L, ep = args.path_tasks, 168, 8, args.path_epochs
+    n = len(range(rank, n_all, world))
     g = torch.Generator(device=dev)
-    g.manual_seed(7)
+    g.manual_seed(7 + rank)
     X = torch.empty((n, T, E), dtype=torch.float32, device=dev)
-    gen_rec = None
+    gen_ms = None
     fixture = os.path.join(ROOT, "tests", "golden", "ref_generator.npz")
     if os.path.isfile(fixture):
-        # the paths come from the reference's own saved generator (weights carried in tests/golden), run on this GPU:
-        # N(0, 1) noise (n, 168, 36) -> paths (n, 168, 36) in MinMax space; columns 0..21 are a task's ETF block
         gen = hfrep.generator.Generator(hfrep.generator.layers_from_fixture(np.load(fixture)), device=dev)
-        chunk, ms = 20000, 0.
+        chunk, gen_ms = 20000, 0.
         for lo in range(0, n, chunk):
             m = min(chunk, n - lo)
             noise = torch.empty((m, T, 36), dtype=torch.float32, device=dev).normal_(0., 1., generator=g)
             a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             a.record()
-            paths = gen.predict_device(noise)
+            paths = gen.predict_device(noise)                       # (m, 168, 36); columns 0..21 are a task's ETF block
             b.record()
             torch.cuda.synchronize()
-            ms += a.elapsed_time(b)
+            gen_ms += a.elapsed_time(b)
             X[lo:lo + m] = paths[:, :, :E]
-        gflop = n * T * 2. * ((36 + 100) * 400 + 200 * 400 + 100 * 36) / 1e9
-        gen_rec = {"kernel": "generator_kernel (LSTM 36->100->100->36, 168 steps)", "ms": ms, "paths_per_s": n / (ms * 1e-3),
-                   "tflops": gflop / ms, "frac_of_fp32_peak": gflop / ms / peak}
+            del noise, paths
     else:
         X.normal_(.61, .2, generator=g).clamp_(-.13, 1.26)
     W0 = engine.to_device(engine.pack_weights([engine.initial_weights(5, E, L)], E, 2 * E * L), dev).repeat(n, 1).contiguous()
     tx = torch.arange(n, dtype=torch.int32, device=dev)
-    best = float("inf")
-    for i in range(3):
+    best, ok = float("inf"), True
+    for i in range(2):
+        barrier()
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         a.record()
         fit = engine.fit_batched(X, [L] * n, W0, E=E, T=T, task_x=tx, max_epochs=ep, early_stop=0)
         b.record()
         torch.cuda.synchronize()
         best = min(best, a.elapsed_time(b))
-    flop = float(n) * ep * flops_per_epoch(L)
-    return {"workload": f"cfg5 sample: {n} generated paths (168 x 22 ETF columns each, own training block per task), L={L}, {ep} epochs",
-            "paths_from": "the reference's saved generator run on this GPU" if gen_rec else "clip(N(.61, .2), -.13, 1.26) stand-in",
-            "generator": gen_rec, "fit_ms": best, "fits_per_s": n / (best * 1e-3), "fits_per_s_at_1000_epochs": n / (best * 1e-3) * ep / 1000.,
-            "blocks_bytes": int(X.numel() * 4), "status_ok": bool(int(fit.status.abs().sum()) == 0 and torch.isfinite(fit.W).all()),
-            "roofline": {"bound": "fp32_ffma", "kernel": "fit_kernel (batch-tile mode)", "achieved": flop / (best * 1e-3) / 1e12,
-                         "peak": peak, "unit": "TFLOP/s", "frac": flop / (best * 1e-3) / 1e12 / peak}}
+        ok = ok and bool(int(fit.status.abs().sum()) == 0 and torch.isfinite(fit.W).all())
+        del fit
+    fit_ms, gen_max = _max_over_ranks(torch, dist, dev, world, [best, gen_ms or 0.])
+    return dict(n_all=n_all, L=L, ep=ep, world=world, fit_ms=fit_ms, gen_ms=gen_max if gen_ms is not None else None, ok=ok,
+                blocks_bytes=int(X.numel() * 4))
+
+
+def paths_record(r, peak):
+    n, ep, w = r["n_all"], r["ep"], r["world"]
+    flop = float(n) * ep * flops_per_epoch(r["L"])
+    gen_rec = None
+    if r["gen_ms"] is not None:
+        gflop = n * 168 * 2. * ((36 + 100) * 400 + 200 * 400 + 100 * 36) / 1e9
+        gen_rec = {"kernel": "generator_kernel (LSTM 36->100->100->36, 168 steps)", "ms": r["gen_ms"], "paths_per_s": n / (r["gen_ms"] * 1e-3),
+                   "tflops_per_gpu": gflop / w / r["gen_ms"], "frac_of_fp32_peak": gflop / w / r["gen_ms"] / peak}
+    per_gpu = flop / w / (r["fit_ms"] * 1e-3) / 1e12
+    return {"workload": f"cfg5: {n} generated paths (168 x 22 ETF columns each, own training block per task), L={r['L']}, {ep} epochs, "
+                        f"paths dealt over {w} GPU(s)",
+            "paths_from": "the reference's saved generator run on the GPU(s)" if gen_rec else "clip(N(.61, .2), -.13, 1.26) stand-in",
+            "generator": gen_rec, "fit_ms": r["fit_ms"], "fits_per_s": n / (r["fit_ms"] * 1e-3),
+            "fits_per_s_at_1000_epochs": n / (r["fit_ms"] * 1e-3) * ep / 1000.,
+            "blocks_bytes_per_rank": r["blocks_bytes"], "status_ok": r["ok"],
+            "roofline": {"bound": "fp32_ffma", "kernel": "fit_kernel (batch-tile mode)", "achieved": per_gpu, "peak": peak,
+                         "unit": "TFLOP/s", "frac": per_gpu / peak, "note": "per GPU"}}
 
 
 def main():
@@ -631,9 +677,9 @@ def main():
     ap.add_argument("--sharded-seeds", type=int, default=64, help="seeds of the sharded configs[2] job (0: skip)")
     ap.add_argument("--sharded-steps", type=int, default=3)
     ap.add_argument("--ensemble-seeds", type=int, default=64)
-    ap.add_argument("--wide-windows", type=int, default=296, help="windows of the configs[3] sample through the wide kernels (0: skip)")
+    ap.add_argument("--wide-windows", type=int, default=4747, help="windows of configs[3] through the wide kernels (4 747 = all; 0: skip)")
     ap.add_argument("--wide-funds", type=int, default=10000, help="funds of that sample (configs[3]: 10 000 = 400 MB of float64 H2D)")
-    ap.add_argument("--path-tasks", type=int, default=100000, help="tasks of the configs[4] sample (0: skip)")
+    ap.add_argument("--path-tasks", type=int, default=1000000, help="path tasks of configs[4] (1 000 000 = the stated size; 0: skip)")
     ap.add_argument("--path-epochs", type=int, default=100)
     ap.add_argument("--impl", default="native", choices=["native", "reference"])
     ap.add_argument("--cpu-procs", type=int, default=16, help="host processes of the --impl reference arm")
