@@ -32,7 +32,7 @@ struct EvalParams {
     int n_tasks, w_stride, E, F, T_train, T_test, window, want_oos, n_oos, n_pre, acols;
     int rolling, nq, wsz; // beta_rolling: OLS of every window (nq warps, one workspace of wsz doubles each)
     int series_dbl;       // doubles reserved for ante/post/turnover [3][n_oos][F] (>= the quality phase's prediction buffers)
-    int qsplit;           // CTAs per task: CTA (task, part) scores prefixes part, part+qsplit, ...; part 0 also builds the replica
+    int qsplit;           // CTAs per task: 1, or part 0 builds the replica while parts 1.. share the quality work
     int off_float;        // byte offset of the float32 region inside dynamic shared memory (16-byte aligned)
     float alpha;
     double cost_param, phi;
@@ -239,11 +239,14 @@ __global__ void __launch_bounds__(NTH_EVAL, 2) eval_kernel(const EvalParams p) {
     if (tid == 0) s_status = 0;
     __syncthreads();
 
-    // ---- quality: in-sample block (warp 0) and the expanding prefixes (all warps, incremental column stats)
-    if (p.quality) {
+    // ---- quality: in-sample block (warp 0) and the expanding prefixes (all warps, incremental column stats).  With
+    // several CTAs per task the quality work belongs to CTAs 1.. and CTA 0 goes straight to the replica stages, so a
+    // task's two halves run side by side (the latency of a handful of tasks is their sum otherwise).
+    const int qq = p.qsplit > 1 ? qpart - 1 : 0, nqq = p.qsplit > 1 ? p.qsplit - 1 : 1;
+    if (p.quality && (p.qsplit == 1 || qpart > 0)) {
         double* q = p.quality + (size_t)task * (2 + 2 * p.n_pre);
         double* cs = cstat + warp * 3 * HFREP_MAX_E;
-        if (warp == 0 && qpart == 0) {
+        if (warp == 0 && qq == 0) {
             if (lane < HFREP_MAX_E) {
                 double s = 0.;
                 if (lane < E) for (int r = 0; r < p.T_train; ++r) s += p.Xtr[(size_t)r * E + lane];
@@ -258,7 +261,7 @@ __global__ void __launch_bounds__(NTH_EVAL, 2) eval_kernel(const EvalParams p) {
         if (p.want_oos) {
             double lo = INFINITY, hi = -INFINITY, sum = 0.;
             int seen = 0;                                         // rows [0, seen) folded into lo/hi/sum (lane = column)
-            for (int j = qpart * NW + warp; j < p.n_pre; j += NW * p.qsplit) {
+            for (int j = qq * NW + warp; j < p.n_pre; j += NW * nqq) {
                 const int n = j + 2;                              // prefix x_test[:n]
                 if (lane < E)
                     for (; seen < n; ++seen) {
