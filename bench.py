@@ -242,14 +242,21 @@ def gpu_arm(args):
             record[2].record()
         return fit, ev
 
+    plan = hfrep.SweepPlan(etf.shape[0], E, hfd.shape[1], LATENTS, seeds, window=WINDOW, device=dev, early_stop=1)
+
     def e2e_step():
-        """Through the public API with HOST buffers: H2D of the returns + initial kernels, D2H of everything a caller of
-        the reference's AE objects reads — histories, trained kernels, quality series, replicas, turnover, metrics."""
+        """Through the public API with HOST buffers — the recorded sweep (`hfrep.SweepPlan.run`: one CUDA graph): H2D of the
+        returns + initial kernels, D2H of everything a caller of the reference's AE objects reads — histories, trained
+        kernels, quality series, replicas, turnover, metrics."""
+        r = plan.run(etf, hfd, rf, W0=W0_host)
+        return r.h2d_bytes, r.d2h_bytes
+
+    def one_shot_step():
+        """The same job launch by launch (`hfrep.run_mode_r`, no recorded graph: what a first call costs)."""
         d = hfrep.ReplicationData(etf, hfd, rf, window=WINDOW, device=dev)
         _, fit, ev = hfrep.run_mode_r(d, LATENTS, seeds=seeds, W0=W0_host)      # same widest-first task order as W0_host
-        out = engine.to_host([ev.ante, ev.post, ev.turnover, ev.metrics, ev.quality, fit.epochs_run, fit.status, fit.loss,
-                              fit.val_loss, fit.W])
-        return d.h2d_bytes + W0_host.nbytes, sum(a.nbytes for a in out)
+        engine.to_host([ev.ante, ev.post, ev.turnover, ev.metrics, ev.quality, ev.status, fit.epochs_run, fit.status, fit.loss,
+                        fit.val_loss, fit.W])
 
     def barrier():
         if world > 1:
@@ -269,6 +276,7 @@ def gpu_arm(args):
         torch.cuda.synchronize()
     for _ in range(2):
         e2e_step()
+        one_shot_step()
     barrier()
 
     # ---- timed: K steps, device time per step from CUDA events (L2 flushed between steps, flush not timed)
@@ -306,6 +314,11 @@ def gpu_arm(args):
         h2d, d2h = e2e_step()
     barrier()
     e2e_s = time.perf_counter() - t0
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        one_shot_step()
+    barrier()
+    one_shot_s = time.perf_counter() - t0
     clocks = sampler.stop(t_timed)
 
     # ---- the sharded job: configs[2] dealt over the ranks, one all-gather of result records, host buffers in and out
@@ -378,7 +391,8 @@ def gpu_arm(args):
         "clocks": clocks,
         "per_rank": per_rank,
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
-                "ms_per_step": e2e_ms / args.steps},
+                "ms_per_step": e2e_ms / args.steps, "api": "hfrep.SweepPlan.run (the sweep recorded once as a CUDA graph, replayed per step)",
+                "one_shot_ms_per_step": one_shot_s * 1e3 / args.steps, "one_shot_api": "hfrep.ReplicationData + hfrep.run_mode_r + engine.to_host, launch by launch (this rank)"},
         "gpu_launches": args.steps * 2 * n_buckets,      # fit_kernel + eval_kernel per width bucket
         "roofline": roofline,
         "parity": "kernel (b) bit-identical to the CPU oracle (canonical summation order) over whole runs; everything else <= 1e-5 (tests/)",

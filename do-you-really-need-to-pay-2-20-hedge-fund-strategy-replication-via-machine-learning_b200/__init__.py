@@ -12,10 +12,10 @@ import os as _os
 from . import _lib                      # noqa: F401  (fails loudly when the CUDA library is missing)
 from . import engine, helper, distributed, generator, h5lite
 from .Autoencoder_encapsulate import AE, Autoencoder, config
-from .engine import (ReplicationData, run_mode_r, run_mode_w, run_mode_w_wide, fit_batched, fit_windows, predict_metrics,
+from .engine import (ReplicationData, SweepPlan, run_mode_r, run_mode_w, run_mode_w_wide, fit_batched, fit_windows, predict_metrics,
                      window_gather, window_index)
 
 DROPIN_PATH = _os.path.join(_os.path.dirname(_os.path.abspath(__file__)), "dropin")
 LIB_PATH = _lib.LIB_PATH
-__all__ = ["AE", "Autoencoder", "config", "helper", "engine", "distributed", "generator", "h5lite", "ReplicationData", "run_mode_r", "run_mode_w", "run_mode_w_wide", "fit_windows",
+__all__ = ["AE", "Autoencoder", "config", "helper", "engine", "distributed", "generator", "h5lite", "ReplicationData", "SweepPlan", "run_mode_r", "run_mode_w", "run_mode_w_wide", "fit_windows",
            "fit_batched", "predict_metrics", "window_gather", "window_index", "DROPIN_PATH", "LIB_PATH"]

@@ -219,6 +219,28 @@ def test_mode_r_end_to_end(hf, data, ref_inputs):
                 assert abs(m[which, j, f] - want[nm]) <= 1e-9 * abs(want[nm]) + 1e-11, (which, nm, f, m[which, j, f], want[nm])
 
 
+def test_sweep_plan_replays_run_mode_r(hf, ref_inputs):
+    """The recorded sweep (one CUDA graph: upload, fits, evaluations, packed download) against the launch-by-launch
+    path on the same host inputs, twice with different data through the same plan: every output bit for bit."""
+    etf, hfd, rf = ref_inputs["etf"], ref_inputs["hfd"], ref_inputs["rf"].reshape(-1)
+    latents, seeds = [21, 8, 5, 2], (123, 7)
+    plan = hf.SweepPlan(etf.shape[0], etf.shape[1], hfd.shape[1], latents, seeds, max_epochs=60)
+    rng = np.random.default_rng(5)
+    for trial in range(2):
+        e = etf if trial == 0 else etf + rng.normal(size=etf.shape) * 1e-3
+        h = hfd if trial == 0 else hfd[::-1].copy()
+        got = plan.run(e, h, rf)
+        data = hf.ReplicationData(e, h, rf)
+        tasks, fit, ev = hf.run_mode_r(data, latents, seeds=seeds, max_epochs=60)
+        assert got.tasks == tasks
+        for name, t in (("ante", ev.ante), ("post", ev.post), ("turnover", ev.turnover), ("metrics", ev.metrics),
+                        ("quality", ev.quality), ("eval_status", ev.status), ("epochs_run", fit.epochs_run),
+                        ("status", fit.status), ("loss", fit.loss), ("val_loss", fit.val_loss), ("W", fit.W)):
+            assert np.array_equal(getattr(got, name), t.cpu().numpy(), equal_nan=True), (trial, name)
+    with pytest.raises(hf._lib.HfrepError):
+        plan.run(etf[:-1], hfd[:-1], rf[:-1])
+
+
 def test_known_answer_table(hf, ref_inputs):
     """hfd_res of autoencoder_v4.ipynb:1015 (deterministic, the reference's own printed output): statistics of the 13 real
     indices over the last 144 months, through the GPU series-statistics kernel and the notebook-level data_analysis."""
