@@ -213,7 +213,7 @@ __device__ __forceinline__ float warp_scatter_sum(float (&v)[32], int lane, int&
     }
 }
 
-template <int LP, int EPT>
+template <int LP, int EPT, bool MVS>
 __global__ void __launch_bounds__(512 / EPT) fit_wide2_kernel(const WideFitParams p) {
     extern __shared__ __align__(16) float sm[];
     constexpr int RG = 32 / LP;                 // batch rows per reduction group (32 values per lane)
@@ -248,7 +248,8 @@ __global__ void __launch_bounds__(512 / EPT) fit_wide2_kernel(const WideFitParam
         }
     // Nadam state: slot s of thread t at mv[s*NT + t] (m) and mv[(NS + s)*NT + t] (v); slots = We then Wd
     constexpr int NS = 2 * EPT * LP;
-    float* mv = p.ws + (size_t)task * (2 * NS) * NT;
+    // (in shared memory when it fits beside the tiles — LP <= 16: 64 / 128 KB — else in the caller's workspace, L2-resident)
+    float* mv = MVS ? dzyS + (SPLIT ? (size_t)BP * NT * EPT : 0) : p.ws + (size_t)task * (2 * NS) * NT;
     for (int s = 0; s < 2 * NS; ++s) mv[(size_t)s * NT + tid] = 0.f;
 
     const int* perm_t = p.perm ? p.perm + (size_t)task * p.perm_task_stride : nullptr;
@@ -652,9 +653,16 @@ static int launch_fit_wide2(const WideFitParams& p, int NT, cudaStream_t stream)
     const int BP = (p.batch + 3) & ~3, NWARP = NT / 32;
     const size_t smem = sizeof(float) * ((size_t)(2 + NWARP) * BP * LP + BP + 32 + (LP * EPT > 16 ? (size_t)BP * NT * EPT : 0));
     HFREP_REQUIRE(smem <= 227 * 1024, "fit_wide: %zu bytes of shared memory needed (batch too large)", smem);
-    auto kern = fit_wide2_kernel<LP, EPT>;
-    HFREP_CUDA_OK(allow_max_dynamic_smem(kern));
-    kern<<<p.n_tasks, NT, smem, stream>>>(p);
+    const size_t mv_bytes = sizeof(float) * 4 * EPT * LP * (size_t)NT;       // Nadam's m and v of the thread's 2*EPT*LP weights
+    if (smem + mv_bytes <= 227 * 1024 && !getenv("HFREP_WIDE_MV_GLOBAL")) {
+        auto kern = fit_wide2_kernel<LP, EPT, true>;
+        HFREP_CUDA_OK(allow_max_dynamic_smem(kern));
+        kern<<<p.n_tasks, NT, smem + mv_bytes, stream>>>(p);
+    } else {
+        auto kern = fit_wide2_kernel<LP, EPT, false>;
+        HFREP_CUDA_OK(allow_max_dynamic_smem(kern));
+        kern<<<p.n_tasks, NT, smem, stream>>>(p);
+    }
     HFREP_CUDA_OK(cudaGetLastError());
     return HFREP_OK;
 }
