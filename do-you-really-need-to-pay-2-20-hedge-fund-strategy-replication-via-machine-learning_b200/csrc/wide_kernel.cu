@@ -7,8 +7,9 @@
 //
 // Two fit kernels: fit_wide_kernel (v1: correct first, any E <= 4096 and L <= 64, weights in the global workspace) and
 // fit_wide2_kernel (E <= 512, L <= 32: ETF columns dealt to threads, weights in registers, packed FFMA2, shuffle
-// scatter-reductions over the ETFs; 4.3-4.6x faster than v1).  The tcgen05 / TMA version (seeds batched along N so the
-// encoder GEMM becomes [rows x 500].[500 x (L*S)], 3xTF32) is the next step and is NOT what this file is yet.
+// scatter-reductions over the ETFs; 4.3-4.6x faster than v1) and, for L <= 8 (configs[3]'s width), fit_wide3_kernel: the
+// same ownership, the two contractions over the ETFs as row-mapped register tiles over a shared mini-batch tile (1.55x
+// faster than v2).  All FP32 FFMA2: no tensor-core version (DESIGN.md section 4 says why).
 #include "common.cuh"
 
 #include <cmath>
@@ -472,6 +473,349 @@ __global__ void __launch_bounds__(512 / EPT) fit_wide2_kernel(const WideFitParam
     if (tid == 0) { p.epochs_run[task] = epochs_run; p.status[task] = st; }
 }
 
+// ------------------------------------------------------------------------------------------------ wide fit, v3
+// v2 spends two fifths of its instructions on the shuffle scatter-reductions of the two contractions that sum over the
+// ETFs (zh = x We, dzh = dzy Wd^T).  v3 (LP = 8: configs[3]'s width) keeps v2's ownership for everything thread-local
+// — thread t owns ETF columns 2t, 2t+1: its weights in registers, zy / dWd / dWe / Nadam as before — and runs those two
+// contractions as ROW-mapped register tiles instead: the mini-batch sits in a shared tile [48][516] (cp.async; 516 = 4
+// mod 32 words, so eight lanes reading eight different rows with LDS.128 touch eight different bank groups), shared copies
+// of We [e][8] and Wd^T [e][8] are rewritten by their owners after every update, thread (row triple, 32-ETF chunk)
+// accumulates 3 x 8 partial sums over its chunk (per 4 ETFs: 3 LDS.128 of x, 8 broadcast LDS.128 of weights, 48 FFMA2)
+// and the 16 chunks' partial sums meet in shared memory in chunk order.  Pass 2 overwrites the tile's x with dzy in place
+// (each thread the elements it just read), so dzh's pass reads it back row-mapped; dWe re-reads x from global memory
+// (L1/L2, coalesced) as in v2.  Nadam's m, v sit in shared memory.  220 KB of shared memory, one CTA of 256 threads per SM.
+constexpr int W3_TS = 516;          // tile row stride (floats)
+constexpr int W3_EP = 512;          // ETF capacity
+constexpr int W3_BP = 48;           // batch rows (16 row triples)
+constexpr int W3_NCH = 16;          // 32-ETF chunks whose partial sums meet in shared memory
+
+__device__ __forceinline__ void cp_async16(float* dst_smem, const float* src) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((unsigned)__cvta_generic_to_shared(dst_smem)), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+
+// EPT = ETF columns per thread: 2 (256 threads) or 1 (512 threads: twice the warps to hide the dependent-issue latency of
+// the short chains, for about a sixth more instructions — every thread loads the h / dzh rows it multiplies with)
+template <int EPT>
+__global__ void __launch_bounds__(512 / EPT) fit_wide3_kernel(const WideFitParams p) {
+    extern __shared__ __align__(16) float sm[];
+    constexpr int LP = 8, LH = 4, NT = 512 / EPT, BP = W3_BP, TS = W3_TS;
+    constexpr int CW = 16 * EPT;                    // ETFs of a thread's chunk in the row-mapped contractions
+    constexpr int NS = 2 * EPT * LP;                                   // weight slots per thread
+    const int task = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int E = p.E, L = p.L, B = p.batch;
+    float* H = sm;                                  // [BP][LP]
+    float* dZh = H + BP * LP;                       // [BP][LP]
+    float* part = dZh + BP * LP;                    // [NCH][BP][LP]
+    int* rows2 = reinterpret_cast<int*>(part + W3_NCH * BP * LP);      // [2][BP] rows of this batch and of the next
+    float* red = reinterpret_cast<float*>(rows2 + 2 * BP);             // [32]
+    float* tile = red + 32;                         // [BP][TS]   x of the mini-batch, then dzy
+    float* WeS = tile + BP * TS;                    // [EP][LP]   We rows
+    float* WdT = WeS + W3_EP * LP;                  // [EP][LP]   Wd columns
+    float* mv = WdT + W3_EP * LP;                   // [2*NS][NT] Nadam m then v, slot-major
+
+    const size_t EL = (size_t)E * L;
+    const float* X = p.X + (size_t)(p.task_x ? p.task_x[task] : 0) * p.T * E;
+    const float* w0 = p.W0 + (size_t)task * 2 * EL;
+    const int e0 = tid * EPT;
+    float2 We[EPT][LH], Wd[LH][EPT];
+    auto w_at = [&](size_t base, int idx, bool in) { return in ? w0[base + idx] : 0.f; };
+#pragma unroll
+    for (int k = 0; k < EPT; ++k)
+#pragma unroll
+        for (int j = 0; j < LH; ++j) {
+            const bool ine = e0 + k < E;
+            We[k][j] = make_float2(w_at(0, (e0 + k) * L + 2 * j, ine && 2 * j < L), w_at(0, (e0 + k) * L + 2 * j + 1, ine && 2 * j + 1 < L));
+            Wd[j][k] = make_float2(w_at(EL, 2 * j * E + e0 + k, ine && 2 * j < L), w_at(EL, (2 * j + 1) * E + e0 + k, ine && 2 * j + 1 < L));
+        }
+    auto publish_We = [&]() {
+#pragma unroll
+        for (int k = 0; k < EPT; ++k) {
+            float4* d = reinterpret_cast<float4*>(WeS + (e0 + k) * LP);
+            d[0] = make_float4(We[k][0].x, We[k][0].y, We[k][1].x, We[k][1].y);
+            d[1] = make_float4(We[k][2].x, We[k][2].y, We[k][3].x, We[k][3].y);
+        }
+    };
+    auto publish_Wd = [&]() {
+#pragma unroll
+        for (int k = 0; k < EPT; ++k) {
+            float4* d = reinterpret_cast<float4*>(WdT + (e0 + k) * LP);
+            d[0] = make_float4(Wd[0][k].x, Wd[0][k].y, Wd[1][k].x, Wd[1][k].y);
+            d[1] = make_float4(Wd[2][k].x, Wd[2][k].y, Wd[3][k].x, Wd[3][k].y);
+        }
+    };
+    publish_We();
+    publish_Wd();
+    for (int s = 0; s < 2 * NS; ++s) mv[s * NT + tid] = 0.f;
+    for (int i = tid; i < BP * TS; i += NT) tile[i] = 0.f;              // columns past E and rows past the batch stay zero
+
+    const int* perm_t = p.perm ? p.perm + (size_t)task * p.perm_task_stride : nullptr;
+    const float alpha = p.alpha, omb1 = 1.f - p.b1, omb2 = 1.f - p.b2;
+    const int n_fit = p.n_fit, n_val = p.n_val;
+    int step = 0, wait = 0, epochs_run = 0, st = 0;
+    float best = INFINITY;
+    const float4* sched = p.sched;
+    float mu1 = 0.f;
+    float3 rc = make_float3(1.f, 1.f, 1.f);
+    const NadamK nk{p.b1, omb1, p.b2, omb2, p.lr, p.eps};
+    auto upd = [&](float& w, float g, int slot, const float4& sa) {
+        float* mp = mv + slot * NT + tid;
+        float* vp = mv + (NS + slot) * NT + tid;
+        float mm = *mp, vv = *vp;
+        w = nadam_step(w, g, mm, vv, sa, mu1, rc, nk);
+        *mp = mm; *vp = vv;
+    };
+    const bool vec_rows = (E & 3) == 0;             // 16-byte row pieces (rows of X start 16-byte aligned)
+    const int E4 = (E + 3) >> 2;
+
+    // a mini-batch's rows into the tile (rows past nb: zeros); asynchronous: cp_async_wait_all + barrier before use
+    auto fill_tile = [&](const int* rows, int nb) {
+        for (int r = warp; r < BP; r += NT / 32) {                     // a warp per row, lanes over its 16-byte pieces
+            float* d0 = tile + r * TS;
+            if (r < nb) {
+                const float* src = X + (size_t)rows[r] * E;
+                for (int c4 = lane; c4 < E4; c4 += 32) {
+                    if (vec_rows) cp_async16(d0 + 4 * c4, src + 4 * c4);
+                    else {
+#pragma unroll
+                        for (int q = 0; q < 4; ++q) d0[4 * c4 + q] = 4 * c4 + q < E ? __ldg(src + 4 * c4 + q) : 0.f;
+                    }
+                }
+            } else {
+                for (int c4 = lane; c4 < E4; c4 += 32) *reinterpret_cast<float4*>(d0 + 4 * c4) = make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+        }
+    };
+    // part[ch][r][l] = sum over chunk ch's ETFs of tile[r][e] * Ws[e][l]  for the thread's row triple
+    const int rt = tid & 15, ch = tid >> 4;          // row triple, chunk of CW ETFs (EPT = 1: 32 chunks, lane pairs l, l^16 add up)
+    auto row_contract = [&](const float* Ws) {
+        float2 acc[3][LH];
+#pragma unroll
+        for (int i = 0; i < 3; ++i)
+#pragma unroll
+            for (int j = 0; j < LH; ++j) acc[i][j] = make_float2(0.f, 0.f);
+        const float* t0 = tile + (3 * rt) * TS + CW * ch;
+        const float* wb = Ws + (CW * ch) * LP;
+#pragma unroll 2
+        for (int e4 = 0; e4 < CW / 4; ++e4) {
+            float4 xv[3];
+#pragma unroll
+            for (int i = 0; i < 3; ++i) xv[i] = *reinterpret_cast<const float4*>(t0 + i * TS + 4 * e4);
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const float4 wa = *reinterpret_cast<const float4*>(wb + (4 * e4 + q) * LP);
+                const float4 wc = *reinterpret_cast<const float4*>(wb + (4 * e4 + q) * LP + 4);
+#pragma unroll
+                for (int i = 0; i < 3; ++i) {
+                    const float xe = q == 0 ? xv[i].x : (q == 1 ? xv[i].y : (q == 2 ? xv[i].z : xv[i].w));
+                    const float2 xx = make_float2(xe, xe);
+                    acc[i][0] = __ffma2_rn(xx, make_float2(wa.x, wa.y), acc[i][0]);
+                    acc[i][1] = __ffma2_rn(xx, make_float2(wa.z, wa.w), acc[i][1]);
+                    acc[i][2] = __ffma2_rn(xx, make_float2(wc.x, wc.y), acc[i][2]);
+                    acc[i][3] = __ffma2_rn(xx, make_float2(wc.z, wc.w), acc[i][3]);
+                }
+            }
+        }
+        if constexpr (EPT == 1) {                    // the two 16-ETF chunks of a warp: lower chunk + upper chunk
+#pragma unroll
+            for (int i = 0; i < 3; ++i)
+#pragma unroll
+                for (int j = 0; j < LH; ++j) {
+                    const float ox = __shfl_xor_sync(0xffffffffu, acc[i][j].x, 16), oy = __shfl_xor_sync(0xffffffffu, acc[i][j].y, 16);
+                    acc[i][j] = (lane & 16) ? make_float2(ox + acc[i][j].x, oy + acc[i][j].y) : make_float2(acc[i][j].x + ox, acc[i][j].y + oy);
+                }
+        }
+        if (EPT == 2 || lane < 16) {
+            const int pc = EPT == 2 ? ch : (ch >> 1);
+#pragma unroll
+            for (int i = 0; i < 3; ++i) {
+                float4* d = reinterpret_cast<float4*>(part + (pc * BP + 3 * rt + i) * LP);
+                d[0] = make_float4(acc[i][0].x, acc[i][0].y, acc[i][1].x, acc[i][1].y);
+                d[1] = make_float4(acc[i][2].x, acc[i][2].y, acc[i][3].x, acc[i][3].y);
+            }
+        }
+    };
+    auto chunk_sum = [&](int o) -> float {           // the 16 chunks' sums for output o, in chunk order
+        float sacc = 0.f;
+#pragma unroll
+        for (int c = 0; c < W3_NCH; ++c) sacc += part[c * BP * LP + o];
+        return sacc;
+    };
+
+    // Batches of an epoch in order: the training mini-batches, then the validation chunks.  The tile of batch b + 1 is
+    // requested as soon as batch b has no more use for the tile (after dzh's pass; after pass 2 of a validation chunk),
+    // so the copies run under the Nadam updates and dWe's pass.
+    const int ntb = (n_fit + B - 1) / B, nvb = (n_val + B - 1) / B, nbt = ntb + nvb;
+    auto batch_of = [&](int b, int& lo, int& nb, bool& train) {       // b in [0, nbt)
+        train = b < ntb;
+        lo = train ? b * B : n_fit + (b - ntb) * B;
+        nb = train ? min(B, n_fit - b * B) : min(B, n_val - (b - ntb) * B);
+    };
+    auto write_rows = [&](int* rows, int epoch, int b) {              // (made visible by the next barrier)
+        int lo, nb; bool train;
+        batch_of(b, lo, nb, train);
+        for (int q = tid; q < nb; q += NT)
+            rows[q] = (train && perm_t) ? __ldg(perm_t + (size_t)epoch * n_fit + lo + q) : lo + q;
+    };
+    auto prefetch_next = [&](int epoch, int b) {                      // the tile is free: request batch b + 1 (or the next epoch's first)
+        int e2 = epoch, b2 = b + 1;
+        if (b2 == nbt) { b2 = 0; ++e2; }
+        if (e2 >= p.max_epochs) return;
+        int lo, nb; bool train;
+        batch_of(b2, lo, nb, train);
+        fill_tile(rows2 + ((e2 * nbt + b2) & 1) * BP, nb);
+    };
+
+    auto run_batch = [&](int epoch, int b) -> float {
+        int lo_, nb; bool train;
+        batch_of(b, lo_, nb, train);
+        const int* rows = rows2 + ((epoch * nbt + b) & 1) * BP;
+        {   // the next batch's rows (read by prefetch_next after at least one barrier)
+            int e2 = epoch, b2 = b + 1;
+            if (b2 == nbt) { b2 = 0; ++e2; }
+            if (e2 < p.max_epochs) write_rows(rows2 + ((e2 * nbt + b2) & 1) * BP, e2, b2);
+        }
+        cp_async_wait_all();
+        __syncthreads();
+        // ---- pass 1: zh = x We (row-mapped), h
+        row_contract(WeS);
+        __syncthreads();
+        for (int o = tid; o < BP * LP; o += NT) H[o] = lrelu(chunk_sum(o), alpha);
+        __syncthreads();
+        // ---- pass 2 (owner-mapped): zy = h Wd, error, dzy -> tile in place; dWd += h^T dzy
+        const float coef = 2.f / (float)(nb * E);
+        float sse = 0.f;
+        float2 gWd[LH][EPT];
+#pragma unroll
+        for (int j = 0; j < LH; ++j)
+#pragma unroll
+            for (int k = 0; k < EPT; ++k) gWd[j][k] = make_float2(0.f, 0.f);
+#pragma unroll 2
+        for (int r = 0; r < nb; ++r) {
+            const float4 h0 = *reinterpret_cast<const float4*>(H + r * LP), h1 = *reinterpret_cast<const float4*>(H + r * LP + 4);
+            const float2 h[LH] = {make_float2(h0.x, h0.y), make_float2(h0.z, h0.w), make_float2(h1.x, h1.y), make_float2(h1.z, h1.w)};
+            float* tp = tile + r * TS + e0;
+            float x[EPT], dzy[EPT];
+            if constexpr (EPT == 2) { const float2 xv = *reinterpret_cast<const float2*>(tp); x[0] = xv.x; x[1] = xv.y; }
+            else x[0] = *tp;
+#pragma unroll
+            for (int k = 0; k < EPT; ++k) {
+                float2 a = make_float2(0.f, 0.f);
+#pragma unroll
+                for (int j = 0; j < LH; ++j) a = __ffma2_rn(h[j], Wd[j][k], a);
+                const float zy = a.x + a.y;
+                const float d = lrelu(zy, alpha) - x[k];                 // columns past E: zy = x = 0
+                sse = fmaf(d, d, sse);
+                dzy[k] = lrelu_grad(zy, coef * d, alpha);
+            }
+            if (train) {
+                if constexpr (EPT == 2) *reinterpret_cast<float2*>(tp) = make_float2(dzy[0], dzy[1]);
+                else *tp = dzy[0];
+#pragma unroll
+                for (int j = 0; j < LH; ++j)
+#pragma unroll
+                    for (int k = 0; k < EPT; ++k) gWd[j][k] = __ffma2_rn(h[j], make_float2(dzy[k], dzy[k]), gWd[j][k]);
+            }
+        }
+        if (!train) { __syncthreads(); prefetch_next(epoch, b); return sse; }
+        __syncthreads();
+        // ---- pass 2b: dzh = (dzy Wd^T) o lrelu'(zh), row-mapped, with the forward pass's Wd
+        row_contract(WdT);
+        __syncthreads();
+        prefetch_next(epoch, b);
+        for (int o = tid; o < BP * LP; o += NT) dZh[o] = lrelu_grad(H[o], chunk_sum(o), alpha);   // sign(h) == sign(zh)
+        // ---- Nadam on Wd (its gradient is complete; nothing reads WdT before the next step's pass 2b)
+        const float4 sc = __ldg(sched + 2 * step);
+        mu1 = __ldg(sched + 2 * step + 1).x;
+        rc = make_float3(rcp_refined(sc.x), rcp_refined(sc.y), rcp_refined(sc.z));
+#pragma unroll
+        for (int j = 0; j < LH; ++j)
+#pragma unroll
+            for (int k = 0; k < EPT; ++k) {
+                upd(Wd[j][k].x, gWd[j][k].x, EPT * LP + (2 * j) * EPT + k, sc);
+                upd(Wd[j][k].y, gWd[j][k].y, EPT * LP + (2 * j + 1) * EPT + k, sc);
+            }
+        publish_Wd();
+        __syncthreads();
+        // ---- pass 3 (owner-mapped): dWe = x^T dzh, x from global memory (the tile holds dzy now)
+        float2 gWe[EPT][LH];
+#pragma unroll
+        for (int k = 0; k < EPT; ++k)
+#pragma unroll
+            for (int j = 0; j < LH; ++j) gWe[k][j] = make_float2(0.f, 0.f);
+#pragma unroll 8
+        for (int r = 0; r < nb; ++r) {
+            const float* xr = X + (size_t)rows[r] * E + e0;
+            float x[EPT];
+#pragma unroll
+            for (int k = 0; k < EPT; ++k) x[k] = e0 + k < E ? __ldg(xr + k) : 0.f;
+            const float4 g0 = *reinterpret_cast<const float4*>(dZh + r * LP), g1 = *reinterpret_cast<const float4*>(dZh + r * LP + 4);
+#pragma unroll
+            for (int k = 0; k < EPT; ++k) {
+                const float2 xx = make_float2(x[k], x[k]);
+                gWe[k][0] = __ffma2_rn(xx, make_float2(g0.x, g0.y), gWe[k][0]);
+                gWe[k][1] = __ffma2_rn(xx, make_float2(g0.z, g0.w), gWe[k][1]);
+                gWe[k][2] = __ffma2_rn(xx, make_float2(g1.x, g1.y), gWe[k][2]);
+                gWe[k][3] = __ffma2_rn(xx, make_float2(g1.z, g1.w), gWe[k][3]);
+            }
+        }
+#pragma unroll
+        for (int k = 0; k < EPT; ++k)
+#pragma unroll
+            for (int j = 0; j < LH; ++j) {
+                upd(We[k][j].x, gWe[k][j].x, k * LP + 2 * j, sc);
+                upd(We[k][j].y, gWe[k][j].y, k * LP + 2 * j + 1, sc);
+            }
+        publish_We();
+        ++step;
+        __syncthreads();
+        return sse;
+    };
+
+    write_rows(rows2, 0, 0);
+    __syncthreads();
+    {
+        int lo, nb; bool train;
+        batch_of(0, lo, nb, train);
+        fill_tile(rows2, nb);
+    }
+    for (int epoch = 0; epoch < p.max_epochs; ++epoch) {
+        float lsum = 0.f, vsum = 0.f;
+        for (int b = 0; b < ntb; ++b) lsum += run_batch(epoch, b);
+        for (int b = ntb; b < nbt; ++b) vsum += run_batch(epoch, b);
+        const float l1 = warp_sum(lsum), v1 = warp_sum(vsum);
+        if (lane == 0) { red[warp] = l1; red[16 + warp] = v1; }
+        __syncthreads();
+        float loss = 0.f, val = 0.f;
+        for (int w = 0; w < NT / 32; ++w) { loss += red[w]; val += red[16 + w]; }
+        __syncthreads();
+        loss = loss / ((float)E * n_fit);
+        val = n_val > 0 ? val / ((float)E * n_val) : NAN;
+        if (tid == 0) {
+            p.loss_hist[(size_t)task * p.max_epochs + epoch] = loss;
+            p.val_hist[(size_t)task * p.max_epochs + epoch] = val;
+        }
+        epochs_run = epoch + 1;
+        if (!isfinite(loss)) st = 1;
+        if (p.early_stop && n_val > 0) {         // no validation rows: no val_loss, Keras never stops (see fit_kernel.cu)
+            ++wait;
+            if (val < best) { best = val; wait = 0; }
+            if (wait >= p.patience && epoch > 0) break;
+        }
+    }
+    cp_async_wait_all();                             // (a requested tile may still be in flight after an early stop)
+    float* wo = p.W_out + (size_t)task * 2 * EL;
+#pragma unroll
+    for (int k = 0; k < EPT; ++k)
+#pragma unroll
+        for (int j = 0; j < LH; ++j)
+            if (e0 + k < E) {
+                if (2 * j < L) { wo[(size_t)(e0 + k) * L + 2 * j] = We[k][j].x; wo[EL + (size_t)(2 * j) * E + e0 + k] = Wd[j][k].x; }
+                if (2 * j + 1 < L) { wo[(size_t)(e0 + k) * L + 2 * j + 1] = We[k][j].y; wo[EL + (size_t)(2 * j + 1) * E + e0 + k] = Wd[j][k].y; }
+            }
+    if (tid == 0) { p.epochs_run[task] = epochs_run; p.status[task] = st; }
+}
+
 // ------------------------------------------------------------------------------------------------ wide evaluation
 struct WideEvalParams {
     const double* etf; const double* hfd; const double* rf;   // full histories [T][E], [T][F], [T]
@@ -693,6 +1037,20 @@ extern "C" int hfrep_fit_wide(const hfrep_fit_cfg* c, const float* X, int n_task
     const Wide2Geom g = getenv("HFREP_WIDE_V1") ? Wide2Geom{0, 0, 0} : wide2_geom(c->E, L, n_tasks);
     if (g.NT) {
         cudaStream_t st = (cudaStream_t)stream;
+        if (g.LP == 8 && c->batch <= W3_BP && !getenv("HFREP_WIDE_V2")) {      // row-mapped reductions (v3)
+            const int ept = getenv("HFREP_WIDE3_EPT") ? atoi(getenv("HFREP_WIDE3_EPT")) : 2;     // (1: measured equal — 28.3 vs 28.7 ms on 592 windows)
+            const size_t smem = sizeof(float) * ((size_t)(2 + W3_NCH) * W3_BP * 8 + 2 * W3_BP + 32 + (size_t)W3_BP * W3_TS +
+                                                 2 * (size_t)W3_EP * 8 + 64 * (size_t)256);
+            if (ept == 2) {
+                HFREP_CUDA_OK(allow_max_dynamic_smem(fit_wide3_kernel<2>));
+                fit_wide3_kernel<2><<<n_tasks, 256, smem, st>>>(p);
+            } else {
+                HFREP_CUDA_OK(allow_max_dynamic_smem(fit_wide3_kernel<1>));
+                fit_wide3_kernel<1><<<n_tasks, 512, smem, st>>>(p);
+            }
+            HFREP_CUDA_OK(cudaGetLastError());
+            return HFREP_OK;
+        }
         if (g.LP == 8) return launch_fit_wide2<8, 2>(p, g.NT, st);
         if (g.LP == 16) return launch_fit_wide2<16, 1>(p, g.NT, st);
         return launch_fit_wide2<32, 1>(p, g.NT, st);

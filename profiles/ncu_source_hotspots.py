@@ -13,7 +13,7 @@ for r in rows:
     if r[0]=="Line No": cur['hdr']=r; continue
     cur['rows'].append((fname,r))
 import os
-SRC={f: open('/root/repo/do-you-really-need-to-pay-2-20-hedge-fund-strategy-replication-via-machine-learning_b200/csrc/'+f).read().split('\n') for f in ('fit_kernel.cu','fit_cluster.cu','common.cuh','fit_params.cuh')}
+SRC={f: open('/root/repo/do-you-really-need-to-pay-2-20-hedge-fund-strategy-replication-via-machine-learning_b200/csrc/'+f).read().split('\n') for f in ('fit_kernel.cu','fit_cluster.cu','common.cuh','fit_params.cuh','wide_kernel.cu')}
 agg=collections.Counter(); inst=collections.Counter(); sass={}
 for b in blocks:
     if key in b['name']:
@@ -30,3 +30,12 @@ for (f,l),v in agg.most_common(topn):
 print("top sass")
 for a,v in sorted(sass.items(), key=lambda kv:-kv[1][1])[:15]:
     print(f"  {v[1]*100/tot:5.2f}% inst={v[2]:>9d} {v[3]}:{v[4]:>4s} {v[0][:90]}")
+print("opcode mix (warp instructions executed)")
+ops=collections.Counter()
+for a,v in sass.items():
+    t=v[0].strip().split()
+    if not t: continue
+    op = t[1] if t[0].startswith('@') and len(t) > 1 else t[0]
+    ops[op.split('.')[0]] += v[2]
+for op,n in ops.most_common(28):
+    print(f"  {n*100/ti:5.1f}%  {op}")

@@ -29,10 +29,11 @@ for rep in range(2):
     torch.cuda.synchronize()
     t0 = time.perf_counter()
     out = hfrep.run_mode_w_wide(etf, hfd, rf, train_window=W, latent_dim=L, seeds=(1,), windows=windows, device="cuda:0",
-                                max_epochs=epochs, early_stop=0)
+                                max_epochs=epochs, early_stop=0, timings=(tm := {}))
     torch.cuda.synchronize()
     dt = time.perf_counter() - t0
     ok = int(out["fit"].status.abs().sum()) == 0 and bool(torch.isfinite(out["replica"]).all())
     flop = n_win * epochs * (10 * 189 * E * L + 4 * 63 * E * L)
     print(f"rep {rep}: {n_win} windows x {F} funds, L={L}, {epochs} epochs: {dt * 1e3:.0f} ms end to end (incl. {etf.nbytes + hfd.nbytes >> 20} MiB H2D) "
-          f"-> {n_win / dt:.0f} fits/s, {n_win * F / dt / 1e6:.2f} M triples/s, >= {flop / dt / 1e12:.2f} TFLOP/s; ok={ok}")
+          f"-> {n_win / dt:.0f} fits/s, {n_win * F / dt / 1e6:.2f} M triples/s, >= {flop / dt / 1e12:.2f} TFLOP/s; ok={ok}; "
+          f"fit {tm['fit_ms']:.1f} ms ({flop / tm['fit_ms'] / 1e9:.2f} TFLOP/s), eval {tm['eval_ms']:.1f} ms")
