@@ -45,7 +45,8 @@ class EvalCfg(C.Structure):
 EXPORTS = ("hfrep_last_error", "hfrep_version", "hfrep_window_index", "hfrep_window_gather", "hfrep_window_gather_f64",
            "hfrep_rolling_sigma", "hfrep_fit_cfg_default", "hfrep_nadam_schedule", "hfrep_fit_batched", "hfrep_fit_windows_workspace", "hfrep_fit_windows", "hfrep_fit_windows_static", "hfrep_fit_wide_workspace", "hfrep_fit_wide", "hfrep_predict_wide",
            "hfrep_eval_cfg_default", "hfrep_predict_metrics", "hfrep_series_metrics", "hfrep_ex_post_return", "hfrep_forward",
-           "hfrep_ffma_peak", "hfrep_generator_weight_count", "hfrep_generator_forward")
+           "hfrep_ffma_peak", "hfrep_generator_weight_count", "hfrep_generator_forward", "hfrep_tc_selftest",
+           "hfrep_generator_tc_weight_bytes", "hfrep_generator_tc_prepare", "hfrep_generator_forward_tc")
 
 
 def _load():
@@ -86,6 +87,12 @@ def _load():
     lib.hfrep_forward.argtypes = [vp, C.c_int, C.c_int, vp, C.c_int, C.c_int, C.c_float, vp, vp]
     lib.hfrep_ffma_peak.argtypes = [C.c_int, vp, C.POINTER(C.c_double), vp]
     lib.hfrep_generator_weight_count.argtypes = [C.c_int, C.c_int, C.c_int]
+    lib.hfrep_generator_tc_weight_bytes.argtypes = [C.c_int, C.c_int, C.c_int]
+    lib.hfrep_generator_tc_weight_bytes.restype = C.c_size_t
+    lib.hfrep_generator_tc_prepare.argtypes = [vp, C.c_int, C.c_int, C.c_int, vp, vp]
+    lib.hfrep_generator_forward_tc.argtypes = [vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, vp, C.c_int,
+                                               C.c_int, vp, vp]
+    lib.hfrep_tc_selftest.argtypes = [vp, vp, C.c_int, vp, vp]
     lib.hfrep_generator_forward.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, vp, C.c_int,
                                             C.c_int, vp, vp]
     for name in EXPORTS:

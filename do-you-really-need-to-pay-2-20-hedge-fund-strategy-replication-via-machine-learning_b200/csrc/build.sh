@@ -7,7 +7,7 @@ here="$(cd "$(dirname "$0")" && pwd)"
 out="$here/../libhfrep.so"
 mkdir -p "$here/build"
 flags="-std=c++17 -O3 -gencode arch=compute_100a,code=sm_100a -lineinfo -Xcompiler -fPIC"
-for f in common fit_kernel fit_cluster eval_kernel gather_kernel wide_kernel gen_kernel; do
+for f in common fit_kernel fit_cluster eval_kernel gather_kernel wide_kernel gen_kernel gen_tc; do
     extra=""
     case "$f" in fit_kernel|fit_cluster) extra="-fmad=false";; esac
     nvcc $flags $extra "$@" -c "$here/$f.cu" -o "$here/build/$f.o" &

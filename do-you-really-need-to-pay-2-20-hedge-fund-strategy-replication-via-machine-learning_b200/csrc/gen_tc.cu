@@ -1,0 +1,426 @@
+// Tensor-core (tcgen05) path of the generator's recurrent contractions.
+//   hfrep_tc_selftest: D[64 x 400] = A[64 x K] * B[400 x K]^T in 3xTF32 on one CTA — operands written by threads in the
+//   canonical un-swizzled K-major layout, accumulators in tensor memory, read back with tcgen05.ld.  It pins the
+//   descriptor fields, the M = 64 accumulator layout (row r -> lane 32*(r/16) + r%16) and the error of the 3xTF32 split
+//   that the generator kernel builds on (tests/test_gpu_parity.py).
+#include "common.cuh"
+#include "tc.cuh"
+
+namespace hfrep {
+
+constexpr int TCM = 64;            // rows (paths) per CTA
+constexpr int TCN = 400;           // gate columns
+constexpr int TCN0 = 256, TCN1 = TCN - TCN0;
+
+__global__ void __launch_bounds__(128) tc_selftest_kernel(const float* A, const float* B, int K, float* D) {
+    extern __shared__ __align__(128) unsigned char smraw[];
+    __shared__ __align__(8) uint64_t bar;
+    __shared__ uint32_t tmem_slot;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    unsigned char* a_hi = smraw;
+    unsigned char* a_lo = a_hi + TCM * K * 4;
+    unsigned char* b_hi = a_lo + TCM * K * 4;
+    unsigned char* b_lo = b_hi + TCN * K * 4;
+
+    if (warp == 0) tc::tmem_alloc<512>(&tmem_slot);
+    if (tid == 0) { tc::mbar_init(&bar, 1); tc::fence_barrier_init(); }
+    for (int i = tid; i < TCM * K; i += blockDim.x) {
+        const int r = i / K, k = i - r * K;
+        float hi, lo;
+        tc::split_tf32(A[i], hi, lo);
+        *reinterpret_cast<float*>(a_hi + tc::kmajor_off(r, k, K)) = hi;
+        *reinterpret_cast<float*>(a_lo + tc::kmajor_off(r, k, K)) = lo;
+    }
+    for (int i = tid; i < TCN * K; i += blockDim.x) {
+        const int r = i / K, k = i - r * K;
+        float hi, lo;
+        tc::split_tf32(B[i], hi, lo);
+        *reinterpret_cast<float*>(b_hi + tc::kmajor_off(r, k, K)) = hi;
+        *reinterpret_cast<float*>(b_lo + tc::kmajor_off(r, k, K)) = lo;
+    }
+    tc::fence_async_smem();
+    tc::tc_fence_before();
+    __syncthreads();
+    tc::tc_fence_after();
+    const uint32_t tmem = tmem_slot;
+
+    if (tid == 0) {
+        const uint32_t sbo = (uint32_t)(K >> 2) * 128u, lbo = 128u;
+        const uint32_t i0 = tc::idesc_tf32(TCM, TCN0), i1 = tc::idesc_tf32(TCM, TCN1);
+        bool acc = false;
+        for (int ks = 0; ks < K / 8; ++ks) {
+            const uint32_t koff = (uint32_t)ks * 256u;
+            const unsigned char* as[3] = {a_hi, a_lo, a_hi};
+            const unsigned char* bs[3] = {b_hi, b_hi, b_lo};
+            for (int t = 0; t < 3; ++t) {
+                const uint64_t ad = tc::smem_desc(tc::smem_u32(as[t]) + koff, lbo, sbo);
+                const uint64_t bd0 = tc::smem_desc(tc::smem_u32(bs[t]) + koff, lbo, sbo);
+                const uint64_t bd1 = tc::smem_desc(tc::smem_u32(bs[t]) + koff + (TCN0 / 8) * sbo, lbo, sbo);
+                tc::mma_tf32(tmem, ad, bd0, i0, acc);
+                tc::mma_tf32(tmem + TCN0, ad, bd1, i1, acc);
+                acc = true;
+            }
+        }
+        tc::mma_commit(&bar);
+    }
+    tc::mbar_wait(&bar, 0);
+    tc::tc_fence_after();
+    // warp w reads TMEM lanes 32w .. 32w+31; rows 16w + lane live in its lanes 0..15
+    for (int c0 = 0; c0 < TCN; c0 += 8) {
+        float v[8];
+        tc::tmem_ld8(tmem + ((uint32_t)(32 * warp) << 16) + (uint32_t)c0, v);
+        if (lane < 16) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) D[(size_t)(16 * warp + lane) * TCN + c0 + i] = v[i];
+        }
+    }
+    tc::tc_fence_before();
+    __syncthreads();
+    if (warp == 0) tc::tmem_free<512>(tmem);
+}
+
+// =====================================================================================================================
+// The generator forward on tensor cores (units = 100: what GAN/MTSS_WGAN_GP.py:221-235 builds).
+// One CTA carries 64 paths through all T steps.  Per step and LSTM layer the gate pre-activations
+//   Z[64 x 400] = [x_t | h_{t-1}] [W; U]           (K = 40 + 104 for layer 1, 104 + 104 for layer 2, zero padded)
+// are one chain of kind::tf32 MMAs (M = 64, N = 256 + 144, K = 8 each) in 3xTF32 — a_hi b_hi + a_lo b_hi + a_hi b_lo,
+// FP32 accumulators in tensor memory — with
+//   * the A operands (x_t / a1_t, h1, h2: TF32 hi and lo planes, canonical un-swizzled K-major layout) resident in shared
+//     memory and rewritten in place by the epilogue threads every step,
+//   * the B operands (the weights, split into hi / lo planes and laid out per K = 8 step by hfrep_generator_tc_prepare,
+//     gate columns permuted so that a unit's four gates are adjacent) streamed from L2 through a two-stage ring of 25.6 KB
+//     bulk copies (cp.async.bulk, THIS GPU's memory, no multicast), one mbarrier pair per stage,
+//   * warps 0-7: epilogue (TMEM -> registers, gates, cell state in registers, LayerNorm, operands of the next MMA chain,
+//     Dense, output), warp 8: MMA issue (one thread), warp 9: weight loader (one thread).
+// M = 64 accumulators occupy lanes 0-15 of each 32-lane TMEM quarter; the epilogue warps hand half of what they load to
+// their lanes 16-31 by shuffle, so every lane works on (row, 25 units).
+// =====================================================================================================================
+constexpr int GU = 100, GG = 400, GKX = 40, GKH = 104;
+constexpr int G_NKS1 = (GKX + GKH) / 8, G_NKS2 = (GKH + GKH) / 8, G_NKS = G_NKS1 + G_NKS2;       // 18, 26, 44 K-steps per time step
+constexpr uint32_t G_PLANE_B = GG * 8 * 4, G_STAGE = 2 * G_PLANE_B;                               // 12 800, 25 600 bytes
+constexpr uint32_t G_SBO_B = 256, G_LBO = 128;
+constexpr uint32_t G_SBO_A = (GKH / 4) * 128, G_PLANE_A = 8 * G_SBO_A;                            // 3 328, 26 624 bytes
+constexpr int G_EPI = 256;                                                                       // epilogue threads
+constexpr int G_UPL = 25;                                                                        // units per lane
+
+struct GenTcParams {
+    const float* W;        // packed weights (hfrep.h): biases, LayerNorm, Dense read from here
+    const unsigned char* tcw;   // prepared B blocks: [G_NKS][hi plane | lo plane]
+    const float* noise; float* out;
+    int n, T, F_in, F_out, lrelu1, lrelu2;
+    float alpha, ln_eps;
+};
+
+__device__ __forceinline__ float sigmoid_fast(float x) { return __fdividef(1.f, 1.f + __expf(-x)); }
+__device__ __forceinline__ uint32_t a_off(int row, int k) {            // element (row, k) of a 64 x 104 operand plane
+    return (uint32_t)(row >> 3) * G_SBO_A + (uint32_t)(k >> 2) * 128u + (uint32_t)(row & 7) * 16u + (uint32_t)(k & 3) * 4u;
+}
+__device__ __forceinline__ void epi_sync() { asm volatile("bar.sync 1, %0;" ::"n"(G_EPI) : "memory"); }
+
+__global__ void __launch_bounds__(320, 1) generator_tc_kernel(const GenTcParams p) {
+    extern __shared__ __align__(128) unsigned char smraw[];
+    __shared__ __align__(8) uint64_t bar_full[2], bar_empty[2], bar_z, bar_a;
+    __shared__ uint32_t tmem_slot;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    unsigned char* H1 = smraw;                          // [hi | lo] planes of h1
+    unsigned char* AX = H1 + 2 * G_PLANE_A;             // x_t during layer 1's MMAs, a1_t during layer 2's
+    unsigned char* H2 = AX + 2 * G_PLANE_A;
+    unsigned char* ring = H2 + 2 * G_PLANE_A;           // 2 stages of B
+    float* b1p = reinterpret_cast<float*>(ring + 2 * G_STAGE);    // [400] permuted gate biases
+    float* b2p = b1p + GG;
+    float* lng = b2p + GG;                              // gamma1, beta1, gamma2, beta2 [100 each]
+    float* bd = lng + 4 * GU;                           // [64]
+    float* lnA = bd + 64;                               // [64][4]
+    float* lnB = lnA + 256;                             // [64][4]
+    float* dpart = lnB + 256;                           // [64][36+] Dense partial sums of the upper warp pair
+
+    const int U = GU, G = GG, F_in = p.F_in, F_out = p.F_out, T = p.T;
+    const float* W1 = p.W;
+    const float* b1 = W1 + (size_t)F_in * G + (size_t)U * G;
+    const float* g1 = b1 + G;
+    const float* W2 = g1 + 2 * U;
+    const float* b2 = W2 + 2 * (size_t)U * G;
+    const float* g2 = b2 + G;
+    const float* Kd = g2 + 2 * U;
+    const float* bdg = Kd + (size_t)U * F_out;
+
+    if (warp == 0) tc::tmem_alloc<512>(&tmem_slot);
+    if (tid == 0) {
+        tc::mbar_init(&bar_full[0], 1); tc::mbar_init(&bar_full[1], 1);
+        tc::mbar_init(&bar_empty[0], 1); tc::mbar_init(&bar_empty[1], 1);
+        tc::mbar_init(&bar_z, 1); tc::mbar_init(&bar_a, G_EPI / 32);
+        tc::fence_barrier_init();
+    }
+    for (int i = tid; i < G; i += blockDim.x) {
+        const int u = i >> 2, g = i & 3;
+        b1p[i] = __ldg(b1 + g * U + u);
+        b2p[i] = __ldg(b2 + g * U + u);
+    }
+    for (int i = tid; i < 2 * U; i += blockDim.x) { lng[i] = __ldg(g1 + i); lng[2 * U + i] = __ldg(g2 + i); }
+    for (int i = tid; i < 64; i += blockDim.x) bd[i] = i < F_out ? __ldg(bdg + i) : 0.f;
+    for (int i = tid; i < (int)(6 * G_PLANE_A / 4); i += blockDim.x) reinterpret_cast<float*>(smraw)[i] = 0.f;   // h1 = h2 = 0, pads
+    tc::tc_fence_before();
+    __syncthreads();
+    tc::tc_fence_after();
+    const uint32_t tmem = tmem_slot;
+    const int path0 = blockIdx.x * 64;
+
+    if (warp < G_EPI / 32) {
+        // ============================================================ epilogue threads
+        const int s = warp & 3, pr = warp >> 2, l16 = lane & 15, hh = lane >> 4;
+        const int row = 16 * s + l16, q = 2 * pr + hh, u0 = G_UPL * q;
+        const int path = path0 + row;
+        const bool live = path < p.n;
+        const uint32_t trow = tmem + ((uint32_t)(32 * s) << 16);
+        const float alpha = p.alpha;
+        float c1[G_UPL], c2[G_UPL];
+#pragma unroll
+        for (int j = 0; j < G_UPL; ++j) c1[j] = c2[j] = 0.f;
+        unsigned par_z = 0;
+        const int kx0 = 10 * q;                                        // this thread's 10 columns of the x operand
+        auto put = [&](unsigned char* region, int k, float v) {
+            float hi, lo;
+            tc::split_tf32(v, hi, lo);
+            const uint32_t o = a_off(row, k);
+            *reinterpret_cast<float*>(region + o) = hi;
+            *reinterpret_cast<float*>(region + G_PLANE_A + o) = lo;
+        };
+        auto load_x = [&](int t, float (&xv)[10]) {
+#pragma unroll
+            for (int i = 0; i < 10; ++i) {
+                const int k = kx0 + i;
+                xv[i] = (live && k < F_in) ? __ldg(p.noise + ((size_t)path * T + t) * F_in + k) : 0.f;
+            }
+        };
+        auto store_x = [&](const float (&xv)[10]) {
+#pragma unroll
+            for (int i = 0; i < 10; ++i) put(AX, kx0 + i, xv[i]);
+        };
+        auto signal_operands = [&]() {                                 // operands written, accumulators read: the MMA thread may go on
+            tc::fence_async_smem();
+            tc::tc_fence_before();
+            __syncwarp();
+            if (lane == 0) tc::mbar_arrive(&bar_a);
+        };
+        // one LSTM layer's epilogue: gates -> cell -> h (region Hreg) -> [LeakyReLU] LayerNorm -> a[] (registers)
+        auto layer = [&](float (&c)[G_UPL], const float* bp, unsigned char* Hreg, int lrelu, const float* gamma, const float* beta,
+                         float (&a)[G_UPL]) {
+            float hv[G_UPL];
+            float ssum = 0.f;
+#pragma unroll
+            for (int j = 0; j < G_UPL; ++j) {
+                float za[4], zb[4], z[4];
+                tc::tmem_ld4(trow + (uint32_t)(4 * (2 * G_UPL * pr + j)), za);             // range 2*pr     (lanes 0-15 keep it)
+                tc::tmem_ld4(trow + (uint32_t)(4 * (2 * G_UPL * pr + G_UPL + j)), zb);     // range 2*pr + 1 (handed to lanes 16-31)
+#pragma unroll
+                for (int g = 0; g < 4; ++g) {
+                    const float o = __shfl_sync(0xffffffffu, zb[g], l16);
+                    z[g] = (hh ? o : za[g]) + bp[4 * (u0 + j) + g];
+                }
+                const float ig = sigmoid_fast(z[0]), fg = sigmoid_fast(z[1]), cand = sigmoid_fast(z[2]), og = sigmoid_fast(z[3]);
+                c[j] = fg * c[j] + ig * cand;
+                const float h = og * sigmoid_fast(c[j]);
+                put(Hreg, u0 + j, h);
+                hv[j] = (lrelu && !(h > 0.f)) ? alpha * h : h;
+                ssum += hv[j];
+            }
+            lnA[row * 4 + q] = ssum;
+            epi_sync();
+            const float mean = ((lnA[row * 4] + lnA[row * 4 + 1]) + (lnA[row * 4 + 2] + lnA[row * 4 + 3])) / (float)GU;
+            float ss = 0.f;
+#pragma unroll
+            for (int j = 0; j < G_UPL; ++j) { const float d = hv[j] - mean; ss = fmaf(d, d, ss); }
+            lnB[row * 4 + q] = ss;
+            epi_sync();
+            const float inv = rsqrtf(((lnB[row * 4] + lnB[row * 4 + 1]) + (lnB[row * 4 + 2] + lnB[row * 4 + 3])) / (float)GU + p.ln_eps);
+#pragma unroll
+            for (int j = 0; j < G_UPL; ++j) a[j] = (hv[j] - mean) * inv * gamma[u0 + j] + beta[u0 + j];
+        };
+
+        {   // x_0, then the first operands are ready
+            float xv[10];
+            load_x(0, xv);
+            store_x(xv);
+            signal_operands();
+        }
+        for (int t = 0; t < T; ++t) {
+            float xn[10];
+            if (t + 1 < T) load_x(t + 1, xn);                          // (in flight under the first layer's epilogue)
+            // ---- layer 1
+            tc::mbar_wait(&bar_z, par_z); par_z ^= 1;
+            tc::tc_fence_after();
+            float a[G_UPL];
+            layer(c1, b1p, H1, p.lrelu1, lng, lng + GU, a);
+#pragma unroll
+            for (int j = 0; j < G_UPL; ++j) put(AX, u0 + j, a[j]);
+            signal_operands();
+            // ---- layer 2
+            tc::mbar_wait(&bar_z, par_z); par_z ^= 1;
+            tc::tc_fence_after();
+            layer(c2, b2p, H2, p.lrelu2, lng + 2 * GU, lng + 3 * GU, a);
+            if (t + 1 < T) {                                           // layer 2's MMAs are complete: the x / a1 region is free
+                store_x(xn);
+                signal_operands();
+            }
+            // ---- Dense on the registers: out[row][j] = bd[j] + sum_u a2[u] Kd[u][j], the row's four unit ranges added up
+            float acc[36];
+#pragma unroll
+            for (int j = 0; j < 36; ++j) acc[j] = 0.f;
+            if (F_out == 36) {
+#pragma unroll 5
+                for (int i = 0; i < G_UPL; ++i) {
+                    const float4* kr = reinterpret_cast<const float4*>(Kd + (size_t)(u0 + i) * 36);
+#pragma unroll
+                    for (int j4 = 0; j4 < 9; ++j4) {
+                        const float4 w = __ldg(kr + j4);
+                        acc[4 * j4] = fmaf(a[i], w.x, acc[4 * j4]); acc[4 * j4 + 1] = fmaf(a[i], w.y, acc[4 * j4 + 1]);
+                        acc[4 * j4 + 2] = fmaf(a[i], w.z, acc[4 * j4 + 2]); acc[4 * j4 + 3] = fmaf(a[i], w.w, acc[4 * j4 + 3]);
+                    }
+                }
+            } else {
+                for (int i = 0; i < G_UPL; ++i)
+#pragma unroll
+                    for (int j = 0; j < 36; ++j)
+                        if (j < F_out) acc[j] = fmaf(a[i], __ldg(Kd + (size_t)(u0 + i) * F_out + j), acc[j]);
+            }
+#pragma unroll
+            for (int j = 0; j < 36; ++j) acc[j] += __shfl_xor_sync(0xffffffffu, acc[j], 16);
+            if (pr == 1 && hh == 0) {
+#pragma unroll
+                for (int j = 0; j < 36; ++j) dpart[row * 36 + j] = acc[j];
+            }
+            epi_sync();
+            if (pr == 0 && hh == 0 && live) {
+                float* o = p.out + ((size_t)path * T + t) * F_out;
+#pragma unroll
+                for (int j = 0; j < 36; ++j)
+                    if (j < F_out) o[j] = (acc[j] + dpart[row * 36 + j]) + bd[j];
+            }
+            epi_sync();                                                // dpart is free again
+        }
+    } else if (warp == G_EPI / 32) {
+        // ============================================================ MMA issue
+        if (lane == 0) {
+            const uint32_t i0 = tc::idesc_tf32(64, TCN0), i1 = tc::idesc_tf32(64, TCN1);
+            const uint32_t h1a = tc::smem_u32(H1), axa = tc::smem_u32(AX), h2a = tc::smem_u32(H2), rga = tc::smem_u32(ring);
+            unsigned par_a = 0;
+            uint32_t g = 0;
+            for (int t = 0; t < T; ++t) {
+                for (int layer = 0; layer < 2; ++layer) {
+                    tc::mbar_wait(&bar_a, par_a); par_a ^= 1;
+                    tc::tc_fence_after();
+                    const int nks = layer ? G_NKS2 : G_NKS1, nfirst = layer ? GKH / 8 : GKX / 8;
+                    for (int ks = 0; ks < nks; ++ks, ++g) {
+                        const uint32_t st = g & 1;
+                        tc::mbar_wait(&bar_full[st], (g >> 1) & 1);
+                        tc::tc_fence_after();
+                        const uint32_t abase = ks < nfirst ? axa + (uint32_t)ks * 256u
+                                                           : (layer ? h2a : h1a) + (uint32_t)(ks - nfirst) * 256u;
+                        const uint32_t bbase = rga + st * G_STAGE;
+#pragma unroll
+                        for (int c = 0; c < 3; ++c) {
+                            const uint32_t aa = abase + (c == 1 ? G_PLANE_A : 0u), bb = bbase + (c == 2 ? G_PLANE_B : 0u);
+                            const uint64_t ad = tc::smem_desc(aa, G_LBO, G_SBO_A);
+                            tc::mma_tf32(tmem, ad, tc::smem_desc(bb, G_LBO, G_SBO_B), i0, ks > 0 || c > 0);
+                            tc::mma_tf32(tmem + TCN0, ad, tc::smem_desc(bb + (TCN0 / 8) * G_SBO_B, G_LBO, G_SBO_B), i1, ks > 0 || c > 0);
+                        }
+                        tc::mma_commit(&bar_empty[st]);                 // the stage is free once these MMAs have read it
+                    }
+                    tc::mma_commit(&bar_z);                             // the layer's accumulators are complete
+                }
+            }
+        }
+        __syncwarp();
+    } else {
+        // ============================================================ weight loader
+        if (lane == 0) {
+            const uint32_t total = (uint32_t)T * G_NKS;
+            for (uint32_t g = 0; g < total; ++g) {
+                const uint32_t st = g & 1;
+                tc::mbar_wait(&bar_empty[st], ((g >> 1) & 1) ^ 1);
+                tc::mbar_expect_tx(&bar_full[st], G_STAGE);
+                tc::bulk_g2s(ring + st * G_STAGE, p.tcw + (size_t)(g % G_NKS) * G_STAGE, G_STAGE, &bar_full[st]);
+            }
+        }
+        __syncwarp();
+    }
+    tc::tc_fence_before();
+    __syncthreads();
+    if (warp == 0) tc::tmem_free<512>(tmem);
+}
+
+// B blocks of the two LSTM layers for generator_tc_kernel: block b = K-step b of a time step (18 of layer 1: x rows 0..39,
+// then h1 rows 0..103; 26 of layer 2: a1 rows, then h2 rows; rows past the real input sizes are zero), each [hi | lo] plane
+// 400 gate columns x 8 K in the canonical K-major layout, gate column 4u+g <- Keras column g*U+u.
+__global__ void generator_tc_prepare_kernel(const float* W, int F_in, unsigned char* tcw) {
+    const int U = GU, G = GG;
+    const float* W1 = W;
+    const float* U1 = W1 + (size_t)F_in * G;
+    const float* W2 = U1 + (size_t)U * G + G + 2 * U;
+    const float* U2 = W2 + (size_t)U * G;
+    const int total = G_NKS * 8 * G;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+        const int n = i % G, kk = (i / G) % 8, b = i / (8 * G);
+        const int u = n >> 2, g = n & 3, col = g * U + u;
+        float v = 0.f;
+        if (b < G_NKS1) {
+            const int k = b * 8 + kk;
+            if (k < GKX) { if (k < F_in) v = W1[(size_t)k * G + col]; }
+            else if (k - GKX < U) v = U1[(size_t)(k - GKX) * G + col];
+        } else {
+            const int k = (b - G_NKS1) * 8 + kk;
+            if (k < GKH) { if (k < U) v = W2[(size_t)k * G + col]; }
+            else if (k - GKH < U) v = U2[(size_t)(k - GKH) * G + col];
+        }
+        float hi, lo;
+        tc::split_tf32(v, hi, lo);
+        const size_t o = (size_t)b * G_STAGE + (size_t)(n >> 3) * G_SBO_B + (size_t)(kk >> 2) * 128 + (size_t)(n & 7) * 16 + (size_t)(kk & 3) * 4;
+        *reinterpret_cast<float*>(tcw + o) = hi;
+        *reinterpret_cast<float*>(tcw + G_PLANE_B + o) = lo;
+    }
+}
+
+}  // namespace hfrep
+
+using namespace hfrep;
+
+extern "C" int hfrep_tc_selftest(const float* A, const float* B, int K, float* D, void* stream) {
+    HFREP_REQUIRE(A && B && D, "tc_selftest: null argument");
+    HFREP_REQUIRE(K >= 8 && K % 8 == 0 && K <= 48, "tc_selftest: K=%d (a multiple of 8 up to 48)", K);
+    const size_t smem = (size_t)2 * (TCM + TCN) * K * 4;
+    HFREP_CUDA_OK(allow_max_dynamic_smem(tc_selftest_kernel));
+    tc_selftest_kernel<<<1, 128, smem, (cudaStream_t)stream>>>(A, B, K, D);
+    HFREP_CUDA_OK(cudaGetLastError());
+    return HFREP_OK;
+}
+
+extern "C" size_t hfrep_generator_tc_weight_bytes(int F_in, int units, int F_out) {
+    if (units != GU || F_in < 1 || F_in > GKX || F_out < 1 || F_out > 36) return 0;       // shapes the tensor-core kernel takes
+    return (size_t)G_NKS * G_STAGE;
+}
+
+extern "C" int hfrep_generator_tc_prepare(const float* weights, int F_in, int units, int F_out, void* tc_weights, void* stream) {
+    HFREP_REQUIRE(weights && tc_weights, "generator_tc_prepare: null argument");
+    HFREP_REQUIRE(hfrep_generator_tc_weight_bytes(F_in, units, F_out) != 0, "generator_tc_prepare: F_in=%d units=%d F_out=%d (units = %d, F_in <= %d, F_out <= 36)",
+                  F_in, units, F_out, GU, GKX);
+    generator_tc_prepare_kernel<<<148, 256, 0, (cudaStream_t)stream>>>(weights, F_in, (unsigned char*)tc_weights);
+    HFREP_CUDA_OK(cudaGetLastError());
+    return HFREP_OK;
+}
+
+extern "C" int hfrep_generator_forward_tc(const float* weights, const void* tc_weights, int F_in, int units, int F_out,
+                                          int lrelu_after_lstm1, int lrelu_after_lstm2, float alpha, float ln_eps,
+                                          const float* noise, int n_paths, int T, float* out, void* stream) {
+    HFREP_REQUIRE(weights && tc_weights && noise && out, "generator_forward_tc: null argument");
+    HFREP_REQUIRE(hfrep_generator_tc_weight_bytes(F_in, units, F_out) != 0, "generator_forward_tc: F_in=%d units=%d F_out=%d not taken", F_in, units, F_out);
+    HFREP_REQUIRE(n_paths >= 0 && T >= 1, "generator_forward_tc: n_paths=%d T=%d", n_paths, T);
+    if (n_paths == 0) return HFREP_OK;
+    GenTcParams p;
+    p.W = weights; p.tcw = (const unsigned char*)tc_weights; p.noise = noise; p.out = out; p.n = n_paths; p.T = T;
+    p.F_in = F_in; p.F_out = F_out; p.lrelu1 = lrelu_after_lstm1; p.lrelu2 = lrelu_after_lstm2; p.alpha = alpha; p.ln_eps = ln_eps;
+    const size_t smem = 6 * (size_t)G_PLANE_A + 2 * (size_t)G_STAGE + sizeof(float) * (2 * GG + 4 * GU + 64 + 512 + 64 * 36);
+    HFREP_CUDA_OK(allow_max_dynamic_smem(generator_tc_kernel));
+    generator_tc_kernel<<<(n_paths + 63) / 64, 320, smem, (cudaStream_t)stream>>>(p);
+    HFREP_CUDA_OK(cudaGetLastError());
+    return HFREP_OK;
+}

@@ -11,6 +11,7 @@ from __future__ import annotations
 
 import ctypes as C
 import json
+import os
 
 import numpy as np
 import torch
@@ -79,20 +80,39 @@ class Generator:
         self._packed_host = packed.astype(np.float32)
         self._device = device
         self._packed_dev = None
+        self._tc_dev = None
 
-    def predict_device(self, noise: torch.Tensor) -> torch.Tensor:
-        """noise f32 [n][T][F_in] on the GPU -> paths f32 [n][T][F_out] on the GPU (no host round trip)."""
+    def predict_device(self, noise: torch.Tensor, tensor_cores: bool | None = None) -> torch.Tensor:
+        """noise f32 [n][T][F_in] on the GPU -> paths f32 [n][T][F_out] on the GPU (no host round trip).
+        tensor_cores: True = the tcgen05 kernel (3xTF32 products, FP32 accumulation; the reference's shape only), False = the
+        FP32 FFMA kernel, None = tensor cores when the shape allows and there are enough paths to fill the GPU's CTAs."""
         dev = noise.device
         if self._packed_dev is None or self._packed_dev.device != dev:
             self._packed_dev = engine.to_device(self._packed_host, dev)
+            self._tc_dev = None
         noise = noise.contiguous().to(torch.float32)
         n, T, Fi = noise.shape
         if Fi != self.F_in:
             raise ValueError(f"expected (n, T, {self.F_in}) noise, got {tuple(noise.shape)}")
         out = torch.empty((n, T, self.F_out), dtype=torch.float32, device=dev)
+        tc_bytes = lib.hfrep_generator_tc_weight_bytes(self.F_in, self.units, self.F_out)
+        if tensor_cores is None:
+            tensor_cores = tc_bytes != 0 and n >= 64 * torch.cuda.get_device_properties(dev).multi_processor_count \
+                and os.environ.get("HFREP_GEN_FFMA") is None
+        if tensor_cores and tc_bytes == 0:
+            raise NotImplementedError("the tensor-core generator kernel takes units = 100, F_in <= 40, F_out <= 36")
         with torch.cuda.device(dev):
-            check(lib.hfrep_generator_forward(ptr(self._packed_dev), self.F_in, self.units, self.F_out, self.lrelu1, self.lrelu2,
-                                              self.alpha, self.ln_eps, ptr(noise), n, T, ptr(out), stream_ptr()))
+            if tensor_cores:
+                if self._tc_dev is None:
+                    self._tc_dev = torch.empty(tc_bytes, dtype=torch.uint8, device=dev)
+                    check(lib.hfrep_generator_tc_prepare(ptr(self._packed_dev), self.F_in, self.units, self.F_out, ptr(self._tc_dev),
+                                                         stream_ptr()))
+                check(lib.hfrep_generator_forward_tc(ptr(self._packed_dev), ptr(self._tc_dev), self.F_in, self.units, self.F_out,
+                                                     self.lrelu1, self.lrelu2, self.alpha, self.ln_eps, ptr(noise), n, T, ptr(out),
+                                                     stream_ptr()))
+            else:
+                check(lib.hfrep_generator_forward(ptr(self._packed_dev), self.F_in, self.units, self.F_out, self.lrelu1, self.lrelu2,
+                                                  self.alpha, self.ln_eps, ptr(noise), n, T, ptr(out), stream_ptr()))
         return out
 
     def predict(self, x, verbose=0, **kwargs):

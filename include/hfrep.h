@@ -264,6 +264,25 @@ int hfrep_generator_forward(const float* weights, int F_in, int units, int F_out
                             int lrelu_after_lstm2, float alpha, float ln_eps, const float* noise, int n_paths, int T,
                             float* out, void* stream);
 
+/* The same forward pass on the tensor cores (csrc/gen_tc.cu: tcgen05 kind::tf32 MMAs in 3xTF32 — every product formed as
+ * a_hi b_hi + a_lo b_hi + a_hi b_lo with FP32 accumulation in tensor memory; gate activations with ex2.approx / rcp.approx;
+ * results agree with hfrep_generator_forward to about 1e-6 of the output range per step) for the reference's generator
+ * shape: units = 100, F_in <= 40, F_out <= 36.  hfrep_generator_tc_weight_bytes returns 0 for any other shape.
+ * hfrep_generator_tc_prepare lays the LSTM kernels out once (TF32 hi / lo planes per K = 8 step, gate columns permuted)
+ * into tc_weights (device, hfrep_generator_tc_weight_bytes bytes, 16-byte aligned); hfrep_generator_forward_tc takes both the
+ * packed weights (biases, LayerNorm, Dense) and tc_weights.  One CTA per 64 paths. */
+size_t hfrep_generator_tc_weight_bytes(int F_in, int units, int F_out);
+int hfrep_generator_tc_prepare(const float* weights, int F_in, int units, int F_out, void* tc_weights, void* stream);
+int hfrep_generator_forward_tc(const float* weights, const void* tc_weights, int F_in, int units, int F_out,
+                               int lrelu_after_lstm1, int lrelu_after_lstm2, float alpha, float ln_eps, const float* noise,
+                               int n_paths, int T, float* out, void* stream);
+
+/* tcgen05 self-test (the building blocks of the tensor-core generator path, csrc/tc.cuh): D f32 [64][400] =
+ * A f32 [64][K] * B f32 [400][K]^T in 3xTF32 on one CTA — operands split into TF32 hi/lo pairs and written in the canonical
+ * un-swizzled K-major shared-memory layout, kind::tf32 MMAs (M = 64, N = 256 + 144), FP32 accumulators in tensor memory.
+ * K a multiple of 8, <= 48.  All pointers device memory. */
+int hfrep_tc_selftest(const float* A, const float* B, int K, float* D, void* stream);
+
 /* FP32 peak micro-benchmark used as the roofline denominator of kernel (b) (MEASURED_PEAKS.json has no FP32
  * figure).  Runs `iters` rounds of 8 independent packed FMAs (FFMA2, fma.rn.f32x2) per thread on a full grid and returns
  * the flop count through *flops_host; time it with CUDA events on `stream`.  sink f32 [>=1]. */

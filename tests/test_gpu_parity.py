@@ -184,6 +184,41 @@ def test_generator_inference(hf, n):
         hf.generator.Generator([l for l in layers if l[0] != "Dense"])
 
 
+def test_tcgen05_selftest(hf):
+    """The tensor-core building blocks (csrc/tc.cuh): a 64 x 400 x K product in 3xTF32 on one CTA — shared-memory matrix
+    descriptors of the un-swizzled K-major layout, kind::tf32 MMAs with M = 64, the accumulator's lane layout in tensor
+    memory — against float64.  Error of the hi/lo split: a few 1e-7 of the result's scale (plain TF32 would be 1e-3)."""
+    from hfrep._lib import lib, check, ptr
+    rng = np.random.default_rng(1)
+    for K in (8, 16, 40):
+        A, B = rng.normal(size=(64, K)).astype(np.float32), rng.normal(size=(400, K)).astype(np.float32)
+        D = torch.full((64, 400), float("nan"), device="cuda:0")
+        check(lib.hfrep_tc_selftest(ptr(torch.from_numpy(A).cuda()), ptr(torch.from_numpy(B).cuda()), K, ptr(D), None))
+        want = A.astype(np.float64) @ B.astype(np.float64).T
+        assert np.max(np.abs(D.cpu().numpy() - want)) < 1e-6 * np.max(np.abs(want))
+
+
+def test_generator_tensor_cores(hf):
+    """The tcgen05 generator kernel (3xTF32 MMAs, FP32 accumulation in tensor memory, weights streamed by bulk copies)
+    against the numpy restatement and against the FP32 FFMA kernel, ragged last CTA included.  Same bound as the FFMA
+    kernel's own test: 2e-5 of the output range over 168 recurrent steps (measured: 2.4e-6)."""
+    import os
+    from oracle import gen_oracle
+    layers = hf.generator.layers_from_fixture(np.load(os.path.join(os.path.dirname(__file__), "golden", "ref_generator.npz")))
+    gen = hf.generator.Generator(layers, device="cuda:0")
+    n = 150
+    noise = np.random.default_rng(n).normal(0, 1, (n, 168, 36)).astype(np.float32)
+    nd = torch.from_numpy(noise).to("cuda:0")
+    tc = gen.predict_device(nd, tensor_cores=True).cpu().numpy()
+    ff = gen.predict_device(nd, tensor_cores=False).cpu().numpy()
+    assert np.isfinite(tc).all()
+    pick = np.unique(np.r_[0, 1, 63, 64, n // 2, n - 2, n - 1])
+    want = gen_oracle.forward(layers, noise[pick])
+    scale = np.max(np.abs(want))
+    assert np.max(np.abs(tc[pick] - want)) < 2e-5 * scale
+    assert np.max(np.abs(tc - ff)) < 2e-5 * scale
+
+
 def test_mode_r_end_to_end(hf, data, ref_inputs):
     """Fit + evaluation in one pass (three widths at once, bucketed launches) vs the reference runs."""
     gs = {L: load_golden(f"ref_modeR_L{L}") for L in (2, 8, 21)}
