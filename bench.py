@@ -632,7 +632,8 @@ def paths_job(args, hfrep, engine, torch, dist, dev, rank, world, barrier):
     fixture = os.path.join(ROOT, "tests", "golden", "ref_generator.npz")
     if os.path.isfile(fixture):
         gen = hfrep.generator.Generator(hfrep.generator.layers_from_fixture(np.load(fixture)), device=dev)
-        chunk, gen_ms = 20000, 0.
+        sms = torch.cuda.get_device_properties(dev).multi_processor_count
+        chunk, gen_ms = 64 * sms * 4, 0.                          # whole waves of the tensor-core kernel's 64-path CTAs
         for lo in range(0, n, chunk):
             m = min(chunk, n - lo)
             noise = torch.empty((m, T, 36), dtype=torch.float32, device=dev).normal_(0., 1., generator=g)
@@ -670,8 +671,15 @@ def paths_record(r, peak):
     gen_rec = None
     if r["gen_ms"] is not None:
         gflop = n * 168 * 2. * ((36 + 100) * 400 + 200 * 400 + 100 * 36) / 1e9
-        gen_rec = {"kernel": "generator_kernel (LSTM 36->100->100->36, 168 steps)", "ms": r["gen_ms"], "paths_per_s": n / (r["gen_ms"] * 1e-3),
-                   "tflops_per_gpu": gflop / w / r["gen_ms"], "frac_of_fp32_peak": gflop / w / r["gen_ms"] / peak}
+        # tensor-pipe work the tcgen05 kernel issues: 3 TF32 MMAs per product, K padded to 144 / 208, 64-row MMAs
+        tc_gflop = n * 168 * 3 * 2. * 400 * (144 + 208) / 1e9
+        tf32_peak = (measured_peaks().get("bf16_tflops_sustained") or 1404.3) / 2.
+        gen_rec = {"kernel": "generator_tc_kernel (LSTM 36->100->100->36, 168 steps; tcgen05 kind::tf32 in 3xTF32, FP32 accumulators in TMEM)",
+                   "ms": r["gen_ms"], "paths_per_s": n / (r["gen_ms"] * 1e-3),
+                   "fp32_equivalent_tflops_per_gpu": gflop / w / r["gen_ms"],
+                   "roofline": {"bound": "tensor", "achieved": tc_gflop / w / r["gen_ms"], "peak": tf32_peak, "unit": "TFLOP/s",
+                                "frac": tc_gflop / w / r["gen_ms"] / tf32_peak,
+                                "note": "issued TF32 MMA flops per GPU against half the measured sustained bf16 rate (MEASURED_PEAKS.json has no TF32 figure)"}}
     per_gpu = flop / w / (r["fit_ms"] * 1e-3) / 1e12
     return {"workload": f"cfg5: {n} generated paths (168 x 22 ETF columns each, own training block per task), L={r['L']}, {ep} epochs, "
                         f"paths dealt over {w} GPU(s)",

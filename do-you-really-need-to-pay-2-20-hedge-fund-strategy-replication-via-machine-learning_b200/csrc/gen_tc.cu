@@ -6,6 +6,8 @@
 #include "common.cuh"
 #include "tc.cuh"
 
+#include <cstdlib>
+
 namespace hfrep {
 
 constexpr int TCM = 64;            // rows (paths) per CTA
@@ -93,7 +95,9 @@ __global__ void __launch_bounds__(128) tc_selftest_kernel(const float* A, const 
 //   * warps 0-7: epilogue (TMEM -> registers, gates, cell state in registers, LayerNorm, operands of the next MMA chain,
 //     Dense, output), warp 8: MMA issue (one thread), warp 9: weight loader (one thread).
 // M = 64 accumulators occupy lanes 0-15 of each 32-lane TMEM quarter; the epilogue warps hand half of what they load to
-// their lanes 16-31 by shuffle, so every lane works on (row, 25 units).
+// their lanes 16-31 by shuffle, so every lane works on (row, 25 units): lane (row, q) owns units 4i + q, i < 25 (their
+// operand columns are then compile-time offsets), and gate column n = 200*(q/2) + 8i + 4*(q%2) + g holds gate g of unit
+// 4i + q, so that one 32-column TMEM load brings four units of both lane halves.
 // =====================================================================================================================
 constexpr int GU = 100, GG = 400, GKX = 40, GKH = 104;
 constexpr int G_NKS1 = (GKX + GKH) / 8, G_NKS2 = (GKH + GKH) / 8, G_NKS = G_NKS1 + G_NKS2;       // 18, 26, 44 K-steps per time step
@@ -109,9 +113,14 @@ struct GenTcParams {
     const float* noise; float* out;
     int n, T, F_in, F_out, lrelu1, lrelu2;
     float alpha, ln_eps;
+    int debug;             // timing experiments only, wrong results (1: no weight streaming after the first two stages,
+                           // 2: no epilogue arithmetic, 4: no MMAs)
 };
 
-__device__ __forceinline__ float sigmoid_fast(float x) { return __fdividef(1.f, 1.f + __expf(-x)); }
+__device__ __forceinline__ float rcp_fast(float x) { float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+// gate column n -> (unit, gate): n = 200*pr + 8*i + 4*hh + g  <->  unit 4*i + 2*pr + hh
+__host__ __device__ constexpr int gate_col_unit(int n) { return 4 * ((n % 200) >> 3) + 2 * (n / 200) + ((n >> 2) & 1); }
+__host__ __device__ constexpr int gate_col_gate(int n) { return n & 3; }
 __device__ __forceinline__ uint32_t a_off(int row, int k) {            // element (row, k) of a 64 x 104 operand plane
     return (uint32_t)(row >> 3) * G_SBO_A + (uint32_t)(k >> 2) * 128u + (uint32_t)(row & 7) * 16u + (uint32_t)(k & 3) * 4u;
 }
@@ -129,10 +138,9 @@ __global__ void __launch_bounds__(320, 1) generator_tc_kernel(const GenTcParams 
     float* b1p = reinterpret_cast<float*>(ring + 2 * G_STAGE);    // [400] permuted gate biases
     float* b2p = b1p + GG;
     float* lng = b2p + GG;                              // gamma1, beta1, gamma2, beta2 [100 each]
-    float* bd = lng + 4 * GU;                           // [64]
-    float* lnA = bd + 64;                               // [64][4]
+    float* lnA = lng + 4 * GU;                          // [64][4]
     float* lnB = lnA + 256;                             // [64][4]
-    float* dpart = lnB + 256;                           // [64][36+] Dense partial sums of the upper warp pair
+    float* KdS = lnB + 256;                             // [100][36] Dense kernel (rows past F_out columns: unused)
 
     const int U = GU, G = GG, F_in = p.F_in, F_out = p.F_out, T = p.T;
     const float* W1 = p.W;
@@ -152,12 +160,15 @@ __global__ void __launch_bounds__(320, 1) generator_tc_kernel(const GenTcParams 
         tc::fence_barrier_init();
     }
     for (int i = tid; i < G; i += blockDim.x) {
-        const int u = i >> 2, g = i & 3;
+        const int u = gate_col_unit(i), g = gate_col_gate(i);
         b1p[i] = __ldg(b1 + g * U + u);
         b2p[i] = __ldg(b2 + g * U + u);
     }
-    for (int i = tid; i < 2 * U; i += blockDim.x) { lng[i] = __ldg(g1 + i); lng[2 * U + i] = __ldg(g2 + i); }
-    for (int i = tid; i < 64; i += blockDim.x) bd[i] = i < F_out ? __ldg(bdg + i) : 0.f;
+    for (int i = tid; i < 4 * U; i += blockDim.x) {               // gamma1, beta1, gamma2, beta2, each stored [q][i] for unit 4i + q
+        const int arr = i / U, r = i - arr * U, qq = r / G_UPL, ii = r - qq * G_UPL;
+        lng[i] = __ldg((arr < 2 ? g1 : g2) + (arr & 1) * U + 4 * ii + qq);
+    }
+    for (int i = tid; i < U * 36; i += blockDim.x) { const int u = i / 36, j = i - u * 36; KdS[i] = j < F_out ? __ldg(Kd + (size_t)u * F_out + j) : 0.f; }
     for (int i = tid; i < (int)(6 * G_PLANE_A / 4); i += blockDim.x) reinterpret_cast<float*>(smraw)[i] = 0.f;   // h1 = h2 = 0, pads
     tc::tc_fence_before();
     __syncthreads();
@@ -168,7 +179,7 @@ __global__ void __launch_bounds__(320, 1) generator_tc_kernel(const GenTcParams 
     if (warp < G_EPI / 32) {
         // ============================================================ epilogue threads
         const int s = warp & 3, pr = warp >> 2, l16 = lane & 15, hh = lane >> 4;
-        const int row = 16 * s + l16, q = 2 * pr + hh, u0 = G_UPL * q;
+        const int row = 16 * s + l16, q = 2 * pr + hh;             // this lane: units 4i + q, i < 25
         const int path = path0 + row;
         const bool live = path < p.n;
         const uint32_t trow = tmem + ((uint32_t)(32 * s) << 16);
@@ -184,6 +195,13 @@ __global__ void __launch_bounds__(320, 1) generator_tc_kernel(const GenTcParams 
             const uint32_t o = a_off(row, k);
             *reinterpret_cast<float*>(region + o) = hi;
             *reinterpret_cast<float*>(region + G_PLANE_A + o) = lo;
+        };
+        const uint32_t unit_base = a_off(row, q);                      // operand column of unit 4i + q: + 128 i bytes
+        auto put_unit = [&](unsigned char* region, int i, float v) {
+            float hi, lo;
+            tc::split_tf32(v, hi, lo);
+            *reinterpret_cast<float*>(region + unit_base + 128 * i) = hi;
+            *reinterpret_cast<float*>(region + G_PLANE_A + unit_base + 128 * i) = lo;
         };
         auto load_x = [&](int t, float (&xv)[10]) {
 #pragma unroll
@@ -203,26 +221,43 @@ __global__ void __launch_bounds__(320, 1) generator_tc_kernel(const GenTcParams 
             if (lane == 0) tc::mbar_arrive(&bar_a);
         };
         // one LSTM layer's epilogue: gates -> cell -> h (region Hreg) -> [LeakyReLU] LayerNorm -> a[] (registers)
+        const uint32_t zcol = trow + (uint32_t)(200 * pr);             // this warp pair's 200 gate columns
         auto layer = [&](float (&c)[G_UPL], const float* bp, unsigned char* Hreg, int lrelu, const float* gamma, const float* beta,
                          float (&a)[G_UPL]) {
             float hv[G_UPL];
             float ssum = 0.f;
-#pragma unroll
-            for (int j = 0; j < G_UPL; ++j) {
-                float za[4], zb[4], z[4];
-                tc::tmem_ld4(trow + (uint32_t)(4 * (2 * G_UPL * pr + j)), za);             // range 2*pr     (lanes 0-15 keep it)
-                tc::tmem_ld4(trow + (uint32_t)(4 * (2 * G_UPL * pr + G_UPL + j)), zb);     // range 2*pr + 1 (handed to lanes 16-31)
+            const float* bq = bp + 200 * pr + 4 * hh;                   // + 8 i: the four gate biases of unit 4i + q
+            // gates of one unit: lanes 0-15 keep the first four of a unit pair's eight columns, lanes 16-31 get the other four
+            auto unit = [&](int i, const uint32_t* r8) {
+                float z[4];
+                const float4 b4 = *reinterpret_cast<const float4*>(bq + 8 * i);
+                const float bb[4] = {b4.x, b4.y, b4.z, b4.w};
 #pragma unroll
                 for (int g = 0; g < 4; ++g) {
-                    const float o = __shfl_sync(0xffffffffu, zb[g], l16);
-                    z[g] = (hh ? o : za[g]) + bp[4 * (u0 + j) + g];
+                    const uint32_t o = __shfl_sync(0xffffffffu, r8[4 + g], l16);
+                    z[g] = __uint_as_float(hh ? o : r8[g]) + bb[g];
                 }
-                const float ig = sigmoid_fast(z[0]), fg = sigmoid_fast(z[1]), cand = sigmoid_fast(z[2]), og = sigmoid_fast(z[3]);
-                c[j] = fg * c[j] + ig * cand;
-                const float h = og * sigmoid_fast(c[j]);
-                put(Hreg, u0 + j, h);
-                hv[j] = (lrelu && !(h > 0.f)) ? alpha * h : h;
-                ssum += hv[j];
+                // sigmoids with 5 ex2 + 3 rcp: i*cand and o*sigmoid(c) share a reciprocal each
+                const float ei = __expf(-z[0]), ef = __expf(-z[1]), ec = __expf(-z[2]), eo = __expf(-z[3]);
+                c[i] = fmaf(rcp_fast(1.f + ef), c[i], rcp_fast((1.f + ei) * (1.f + ec)));
+                const float h = rcp_fast((1.f + eo) * (1.f + __expf(-c[i])));
+                put_unit(Hreg, i, h);
+                hv[i] = (lrelu && !(h > 0.f)) ? alpha * h : h;
+                ssum += hv[i];
+            };
+#pragma unroll
+            for (int i0 = 0; i0 < 24; i0 += 4) {                        // four units of both lane halves per 32-column load
+                uint32_t r[32];
+                tc::tmem_ld32_nowait(zcol + (uint32_t)(8 * i0), r);
+                tc::tmem_ld_wait();
+#pragma unroll
+                for (int k = 0; k < 4; ++k) unit(i0 + k, r + 8 * k);
+            }
+            {
+                uint32_t r[8];
+                tc::tmem_ld8_nowait(zcol + 8u * 24u, r);
+                tc::tmem_ld_wait();
+                unit(24, r);
             }
             lnA[row * 4 + q] = ssum;
             epi_sync();
@@ -234,7 +269,7 @@ __global__ void __launch_bounds__(320, 1) generator_tc_kernel(const GenTcParams 
             epi_sync();
             const float inv = rsqrtf(((lnB[row * 4] + lnB[row * 4 + 1]) + (lnB[row * 4 + 2] + lnB[row * 4 + 3])) / (float)GU + p.ln_eps);
 #pragma unroll
-            for (int j = 0; j < G_UPL; ++j) a[j] = (hv[j] - mean) * inv * gamma[u0 + j] + beta[u0 + j];
+            for (int j = 0; j < G_UPL; ++j) a[j] = (hv[j] - mean) * inv * gamma[G_UPL * q + j] + beta[G_UPL * q + j];
         };
 
         {   // x_0, then the first operands are ready
@@ -250,14 +285,14 @@ __global__ void __launch_bounds__(320, 1) generator_tc_kernel(const GenTcParams 
             tc::mbar_wait(&bar_z, par_z); par_z ^= 1;
             tc::tc_fence_after();
             float a[G_UPL];
-            layer(c1, b1p, H1, p.lrelu1, lng, lng + GU, a);
+            if (!(p.debug & 2)) layer(c1, b1p, H1, p.lrelu1, lng, lng + GU, a);
 #pragma unroll
-            for (int j = 0; j < G_UPL; ++j) put(AX, u0 + j, a[j]);
+            for (int j = 0; j < G_UPL; ++j) put_unit(AX, j, a[j]);
             signal_operands();
             // ---- layer 2
             tc::mbar_wait(&bar_z, par_z); par_z ^= 1;
             tc::tc_fence_after();
-            layer(c2, b2p, H2, p.lrelu2, lng + 2 * GU, lng + 3 * GU, a);
+            if (!(p.debug & 2)) layer(c2, b2p, H2, p.lrelu2, lng + 2 * GU, lng + 3 * GU, a);
             if (t + 1 < T) {                                           // layer 2's MMAs are complete: the x / a1 region is free
                 store_x(xn);
                 signal_operands();
@@ -266,37 +301,48 @@ __global__ void __launch_bounds__(320, 1) generator_tc_kernel(const GenTcParams 
             float acc[36];
 #pragma unroll
             for (int j = 0; j < 36; ++j) acc[j] = 0.f;
-            if (F_out == 36) {
+            if (!(p.debug & 2)) {
 #pragma unroll 5
                 for (int i = 0; i < G_UPL; ++i) {
-                    const float4* kr = reinterpret_cast<const float4*>(Kd + (size_t)(u0 + i) * 36);
+                    const float4* kr = reinterpret_cast<const float4*>(KdS + (4 * i + q) * 36);
 #pragma unroll
                     for (int j4 = 0; j4 < 9; ++j4) {
-                        const float4 w = __ldg(kr + j4);
+                        const float4 w = kr[j4];
                         acc[4 * j4] = fmaf(a[i], w.x, acc[4 * j4]); acc[4 * j4 + 1] = fmaf(a[i], w.y, acc[4 * j4 + 1]);
                         acc[4 * j4 + 2] = fmaf(a[i], w.z, acc[4 * j4 + 2]); acc[4 * j4 + 3] = fmaf(a[i], w.w, acc[4 * j4 + 3]);
                     }
                 }
-            } else {
-                for (int i = 0; i < G_UPL; ++i)
-#pragma unroll
-                    for (int j = 0; j < 36; ++j)
-                        if (j < F_out) acc[j] = fmaf(a[i], __ldg(Kd + (size_t)(u0 + i) * F_out + j), acc[j]);
             }
 #pragma unroll
             for (int j = 0; j < 36; ++j) acc[j] += __shfl_xor_sync(0xffffffffu, acc[j], 16);
-            if (pr == 1 && hh == 0) {
+            // the upper warp pair's sums cross to the lower pair through spare TMEM columns of the row's own lane
+            const uint32_t dcol = trow + 400u;
+            if (pr == 1) {
 #pragma unroll
-                for (int j = 0; j < 36; ++j) dpart[row * 36 + j] = acc[j];
+                for (int j4 = 0; j4 < 9; ++j4) {
+                    const float v4[4] = {acc[4 * j4], acc[4 * j4 + 1], acc[4 * j4 + 2], acc[4 * j4 + 3]};
+                    tc::tmem_st4(dcol + 4u * j4, v4);
+                }
+                tc::tmem_st_wait();
             }
+            tc::tc_fence_before();
             epi_sync();
-            if (pr == 0 && hh == 0 && live) {
-                float* o = p.out + ((size_t)path * T + t) * F_out;
+            tc::tc_fence_after();
+            if (pr == 0) {
+                uint32_t r[32];
+                float r4[4];
+                tc::tmem_ld32_nowait(dcol, r);
+                tc::tmem_ld4(dcol + 32u, r4);                          // (its wait covers both loads)
+                if (hh == 0 && live) {
+                    float* o = p.out + ((size_t)path * T + t) * F_out;
 #pragma unroll
-                for (int j = 0; j < 36; ++j)
-                    if (j < F_out) o[j] = (acc[j] + dpart[row * 36 + j]) + bd[j];
+                    for (int j = 0; j < 36; ++j)
+                        if (j < F_out) o[j] = (acc[j] + (j < 32 ? __uint_as_float(r[j]) : r4[j - 32])) + __ldg(bdg + j);
+                }
             }
-            epi_sync();                                                // dpart is free again
+            tc::tc_fence_before();
+            epi_sync();                                                // the spare columns are free again
+            tc::tc_fence_after();
         }
     } else if (warp == G_EPI / 32) {
         // ============================================================ MMA issue
@@ -312,19 +358,19 @@ __global__ void __launch_bounds__(320, 1) generator_tc_kernel(const GenTcParams 
                     const int nks = layer ? G_NKS2 : G_NKS1, nfirst = layer ? GKH / 8 : GKX / 8;
                     for (int ks = 0; ks < nks; ++ks, ++g) {
                         const uint32_t st = g & 1;
-                        tc::mbar_wait(&bar_full[st], (g >> 1) & 1);
+                        if (!(p.debug & 1) || g < 2) tc::mbar_wait(&bar_full[st], (g >> 1) & 1);
                         tc::tc_fence_after();
                         const uint32_t abase = ks < nfirst ? axa + (uint32_t)ks * 256u
                                                            : (layer ? h2a : h1a) + (uint32_t)(ks - nfirst) * 256u;
                         const uint32_t bbase = rga + st * G_STAGE;
 #pragma unroll
-                        for (int c = 0; c < 3; ++c) {
+                        for (int c = 0; c < ((p.debug & 4) ? 0 : 3); ++c) {
                             const uint32_t aa = abase + (c == 1 ? G_PLANE_A : 0u), bb = bbase + (c == 2 ? G_PLANE_B : 0u);
                             const uint64_t ad = tc::smem_desc(aa, G_LBO, G_SBO_A);
                             tc::mma_tf32(tmem, ad, tc::smem_desc(bb, G_LBO, G_SBO_B), i0, ks > 0 || c > 0);
                             tc::mma_tf32(tmem + TCN0, ad, tc::smem_desc(bb + (TCN0 / 8) * G_SBO_B, G_LBO, G_SBO_B), i1, ks > 0 || c > 0);
                         }
-                        tc::mma_commit(&bar_empty[st]);                 // the stage is free once these MMAs have read it
+                        if (!(p.debug & 1)) tc::mma_commit(&bar_empty[st]);     // the stage is free once these MMAs have read it
                     }
                     tc::mma_commit(&bar_z);                             // the layer's accumulators are complete
                 }
@@ -334,7 +380,7 @@ __global__ void __launch_bounds__(320, 1) generator_tc_kernel(const GenTcParams 
     } else {
         // ============================================================ weight loader
         if (lane == 0) {
-            const uint32_t total = (uint32_t)T * G_NKS;
+            const uint32_t total = (p.debug & 1) ? 2u : (uint32_t)T * G_NKS;
             for (uint32_t g = 0; g < total; ++g) {
                 const uint32_t st = g & 1;
                 tc::mbar_wait(&bar_empty[st], ((g >> 1) & 1) ^ 1);
@@ -361,7 +407,7 @@ __global__ void generator_tc_prepare_kernel(const float* W, int F_in, unsigned c
     const int total = G_NKS * 8 * G;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
         const int n = i % G, kk = (i / G) % 8, b = i / (8 * G);
-        const int u = n >> 2, g = n & 3, col = g * U + u;
+        const int u = gate_col_unit(n), g = gate_col_gate(n), col = g * U + u;
         float v = 0.f;
         if (b < G_NKS1) {
             const int k = b * 8 + kk;
@@ -418,7 +464,8 @@ extern "C" int hfrep_generator_forward_tc(const float* weights, const void* tc_w
     GenTcParams p;
     p.W = weights; p.tcw = (const unsigned char*)tc_weights; p.noise = noise; p.out = out; p.n = n_paths; p.T = T;
     p.F_in = F_in; p.F_out = F_out; p.lrelu1 = lrelu_after_lstm1; p.lrelu2 = lrelu_after_lstm2; p.alpha = alpha; p.ln_eps = ln_eps;
-    const size_t smem = 6 * (size_t)G_PLANE_A + 2 * (size_t)G_STAGE + sizeof(float) * (2 * GG + 4 * GU + 64 + 512 + 64 * 36);
+    p.debug = getenv("HFREP_GEN_TC_DEBUG") ? atoi(getenv("HFREP_GEN_TC_DEBUG")) : 0;
+    const size_t smem = 6 * (size_t)G_PLANE_A + 2 * (size_t)G_STAGE + sizeof(float) * (2 * GG + 4 * GU + 512 + GU * 36);
     HFREP_CUDA_OK(allow_max_dynamic_smem(generator_tc_kernel));
     generator_tc_kernel<<<(n_paths + 63) / 64, 320, smem, (cudaStream_t)stream>>>(p);
     HFREP_CUDA_OK(cudaGetLastError());

@@ -13,7 +13,7 @@ for r in rows:
     if r[0]=="Line No": cur['hdr']=r; continue
     cur['rows'].append((fname,r))
 import os
-SRC={f: open('/root/repo/do-you-really-need-to-pay-2-20-hedge-fund-strategy-replication-via-machine-learning_b200/csrc/'+f).read().split('\n') for f in ('fit_kernel.cu','fit_cluster.cu','common.cuh','fit_params.cuh','wide_kernel.cu')}
+SRC={f: open('/root/repo/do-you-really-need-to-pay-2-20-hedge-fund-strategy-replication-via-machine-learning_b200/csrc/'+f).read().split('\n') for f in ('fit_kernel.cu','fit_cluster.cu','common.cuh','fit_params.cuh','wide_kernel.cu','gen_tc.cu','tc.cuh','gen_kernel.cu')}
 agg=collections.Counter(); inst=collections.Counter(); sass={}
 for b in blocks:
     if key in b['name']:

@@ -193,7 +193,8 @@ def test_tcgen05_selftest(hf):
     for K in (8, 16, 40):
         A, B = rng.normal(size=(64, K)).astype(np.float32), rng.normal(size=(400, K)).astype(np.float32)
         D = torch.full((64, 400), float("nan"), device="cuda:0")
-        check(lib.hfrep_tc_selftest(ptr(torch.from_numpy(A).cuda()), ptr(torch.from_numpy(B).cuda()), K, ptr(D), None))
+        Ad, Bd = torch.from_numpy(A).to("cuda:0"), torch.from_numpy(B).to("cuda:0")
+        check(lib.hfrep_tc_selftest(ptr(Ad), ptr(Bd), K, ptr(D), None))
         want = A.astype(np.float64) @ B.astype(np.float64).T
         assert np.max(np.abs(D.cpu().numpy() - want)) < 1e-6 * np.max(np.abs(want))
 
