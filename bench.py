@@ -614,7 +614,7 @@ def wide_record(r, peak):
             "h2d_bytes_per_rank": r["h2d"], "gathered_bytes": r["gathered"] if r["world"] > 1 else 0,
             "fits_per_s": r["n_win"] / (r["fit_ms"] * 1e-3), "results_per_s_e2e": r["n_win"] * r["wF"] / (r["job_ms"] * 1e-3),
             "status_ok": r["ok"],
-            "roofline": {"bound": "fp32_ffma", "kernel": "fit_wide2_kernel", "achieved": per_gpu_flops, "peak": peak, "unit": "TFLOP/s",
+            "roofline": {"bound": "fp32_ffma", "kernel": "fit_wide3_kernel", "achieved": per_gpu_flops, "peak": peak, "unit": "TFLOP/s",
                          "frac": per_gpu_flops / peak, "note": "per GPU"}}
 
 

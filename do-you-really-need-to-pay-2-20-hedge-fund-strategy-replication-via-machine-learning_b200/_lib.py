@@ -45,7 +45,7 @@ class EvalCfg(C.Structure):
 EXPORTS = ("hfrep_last_error", "hfrep_version", "hfrep_window_index", "hfrep_window_gather", "hfrep_window_gather_f64",
            "hfrep_rolling_sigma", "hfrep_fit_cfg_default", "hfrep_nadam_schedule", "hfrep_fit_batched", "hfrep_fit_windows_workspace", "hfrep_fit_windows", "hfrep_fit_windows_static", "hfrep_fit_wide_workspace", "hfrep_fit_wide", "hfrep_predict_wide",
            "hfrep_eval_cfg_default", "hfrep_predict_metrics", "hfrep_series_metrics", "hfrep_ex_post_return", "hfrep_forward",
-           "hfrep_ffma_peak", "hfrep_generator_weight_count", "hfrep_generator_forward", "hfrep_tc_selftest",
+           "hfrep_ffma_peak", "hfrep_generator_weight_count", "hfrep_generator_forward", "hfrep_tc_selftest", "hfrep_tc_mma_rate",
            "hfrep_generator_tc_weight_bytes", "hfrep_generator_tc_prepare", "hfrep_generator_forward_tc")
 
 
@@ -93,6 +93,7 @@ def _load():
     lib.hfrep_generator_forward_tc.argtypes = [vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, vp, C.c_int,
                                                C.c_int, vp, vp]
     lib.hfrep_tc_selftest.argtypes = [vp, vp, C.c_int, vp, vp]
+    lib.hfrep_tc_mma_rate.argtypes = [C.c_int, C.c_int, vp]
     lib.hfrep_generator_forward.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, vp, C.c_int,
                                             C.c_int, vp, vp]
     for name in EXPORTS:

@@ -81,6 +81,34 @@ __global__ void __launch_bounds__(128) tc_selftest_kernel(const float* A, const 
     if (warp == 0) tc::tmem_free<512>(tmem);
 }
 
+// MMA issue-rate probe: every CTA's thread 0 issues `iters` kind::tf32 MMAs (M = 64, N as given, K = 8) on zeroed operands,
+// commits, waits.  Timed from outside; tells what a small-N MMA costs next to a wide one (wide fit).
+__global__ void __launch_bounds__(128) tc_mma_rate_kernel(int N, int iters) {
+    extern __shared__ __align__(128) unsigned char smraw[];
+    __shared__ __align__(8) uint64_t bar;
+    __shared__ uint32_t tmem_slot;
+    const int tid = threadIdx.x, warp = tid >> 5;
+    if (warp == 0) tc::tmem_alloc<256>(&tmem_slot);
+    if (tid == 0) { tc::mbar_init(&bar, 1); tc::fence_barrier_init(); }
+    for (int i = tid; i < (64 + 256) * 8; i += blockDim.x) reinterpret_cast<float*>(smraw)[i] = 0.f;
+    tc::fence_async_smem();
+    tc::tc_fence_before();
+    __syncthreads();
+    tc::tc_fence_after();
+    const uint32_t tmem = tmem_slot;
+    if (tid == 0) {
+        const uint32_t idesc = tc::idesc_tf32(64, N);
+        const uint64_t ad = tc::smem_desc(tc::smem_u32(smraw), 128u, 256u);
+        const uint64_t bd = tc::smem_desc(tc::smem_u32(smraw) + 64 * 8 * 4, 128u, 256u);
+        for (int i = 0; i < iters; ++i) tc::mma_tf32(tmem, ad, bd, idesc, i > 0);
+        tc::mma_commit(&bar);
+    }
+    tc::mbar_wait(&bar, 0);
+    tc::tc_fence_before();
+    __syncthreads();
+    if (warp == 0) tc::tmem_free<256>(tmem);
+}
+
 // =====================================================================================================================
 // The generator forward on tensor cores (units = 100: what GAN/MTSS_WGAN_GP.py:221-235 builds).
 // One CTA carries 64 paths through all T steps.  Per step and LSTM layer the gate pre-activations
@@ -468,6 +496,13 @@ extern "C" int hfrep_generator_forward_tc(const float* weights, const void* tc_w
     const size_t smem = 6 * (size_t)G_PLANE_A + 2 * (size_t)G_STAGE + sizeof(float) * (2 * GG + 4 * GU + 512 + GU * 36);
     HFREP_CUDA_OK(allow_max_dynamic_smem(generator_tc_kernel));
     generator_tc_kernel<<<(n_paths + 63) / 64, 320, smem, (cudaStream_t)stream>>>(p);
+    HFREP_CUDA_OK(cudaGetLastError());
+    return HFREP_OK;
+}
+
+extern "C" int hfrep_tc_mma_rate(int N, int iters, void* stream) {
+    HFREP_REQUIRE(N >= 8 && N <= 256 && N % 8 == 0 && iters >= 1, "tc_mma_rate: N=%d iters=%d", N, iters);
+    tc_mma_rate_kernel<<<sm_count(), 128, (64 + 256) * 8 * 4, (cudaStream_t)stream>>>(N, iters);
     HFREP_CUDA_OK(cudaGetLastError());
     return HFREP_OK;
 }

@@ -282,6 +282,9 @@ int hfrep_generator_forward_tc(const float* weights, const void* tc_weights, int
  * un-swizzled K-major shared-memory layout, kind::tf32 MMAs (M = 64, N = 256 + 144), FP32 accumulators in tensor memory.
  * K a multiple of 8, <= 48.  All pointers device memory. */
 int hfrep_tc_selftest(const float* A, const float* B, int K, float* D, void* stream);
+/* MMA issue-rate probe: one CTA per SM, each issues `iters` kind::tf32 MMAs of M = 64, N (a multiple of 8, <= 256), K = 8 on
+ * zeroed operands; time it with CUDA events on `stream`. */
+int hfrep_tc_mma_rate(int N, int iters, void* stream);
 
 /* FP32 peak micro-benchmark used as the roofline denominator of kernel (b) (MEASURED_PEAKS.json has no FP32
  * figure).  Runs `iters` rounds of 8 independent packed FMAs (FFMA2, fma.rn.f32x2) per thread on a full grid and returns
