@@ -565,8 +565,8 @@ def _max_over_ranks(torch, dist, dev, world, values):
 
 def wide_job(args, hfrep, torch, dist, dev, rank, world, barrier):
     """configs[3] (500 ETFs, 10 000 funds, 5 000-day history, 252-day windows, rolling refit: 4 747 windows, L = 8, 100
-    epochs as SURVEY §8d fixes it) through the wide kernels, the windows dealt cyclically over the ranks, every rank's
-    replica rows all-gathered at the end.  Every rank builds the same synthetic history (SURVEY §8d cfg 4 factor model)."""
+    epochs as SURVEY §8d fixes it) through the wide kernels, the windows dealt over the ranks in runs of consecutive windows
+    (a rank uploads only its stretch of the histories), every rank's replica rows all-gathered at the end.  Every rank builds the same synthetic history (SURVEY §8d cfg 4 factor model)."""
     from hfrep import distributed
     wT, wE, wF, wW, wL, wep = 5000, 500, args.wide_funds, 252, 8, 100
     wr = np.random.default_rng(20240611)
@@ -581,7 +581,7 @@ def wide_job(args, hfrep, torch, dist, dev, rank, world, barrier):
     n_all = wT - wW - 1                                              # 4 747 windows
     n_win = min(args.wide_windows, n_all)
     wins = np.arange(n_all) if n_win == n_all else np.linspace(0, n_all - 1, n_win).astype(int)
-    mine = wins[rank::world]
+    mine = wins[distributed.shard_blocks(n_win, rank, world)]      # a run of consecutive windows: the rank uploads only its stretch
     W0 = hfrep.engine.pack_weights([hfrep.engine.initial_weights(100003 + int(wi), wE, wL) for wi in mine], wE, 2 * wE * wL)
     best, ok = None, True
     for i in range(3):
@@ -592,7 +592,7 @@ def wide_job(args, hfrep, torch, dist, dev, rank, world, barrier):
                                    device=dev, W0=W0, max_epochs=wep, early_stop=0, timings=tm)
         g0 = torch.cuda.Event(enable_timing=True); g1 = torch.cuda.Event(enable_timing=True)
         g0.record()
-        replica = distributed.gather_results(wo["replica"][0], n_win, rank, world) if world > 1 else wo["replica"][0]
+        replica = distributed.gather_results(wo["replica"][0], n_win, rank, world, order="blocks") if world > 1 else wo["replica"][0]
         g1.record()
         torch.cuda.synchronize()
         tm["gather_ms"] = g0.elapsed_time(g1)
@@ -602,7 +602,7 @@ def wide_job(args, hfrep, torch, dist, dev, rank, world, barrier):
         best = tm if best is None else {k: min(best[k], tm[k]) for k in tm}
     fit_ms, eval_ms, gather_ms, job_ms = _max_over_ranks(torch, dist, dev, world, [best["fit_ms"], best["eval_ms"], best["gather_ms"], best["job_ms"]])
     return dict(n_win=n_win, n_all=n_all, wF=wF, wE=wE, wL=wL, wep=wep, world=world, fit_ms=fit_ms, eval_ms=eval_ms, gather_ms=gather_ms,
-                job_ms=job_ms, ok=ok, h2d=int(whfd.nbytes + wetf.nbytes), gathered=int(n_win * wF * 8))
+                job_ms=job_ms, ok=ok, h2d=int(wo["h2d_bytes"]), gathered=int(n_win * wF * 8))
 
 
 def wide_record(r, peak):

@@ -25,15 +25,34 @@ def shard(n_tasks: int, rank: int, world_size: int) -> np.ndarray:
     return np.arange(rank, n_tasks, world_size, dtype=np.int64)
 
 
-def _global_order(n_tasks: int, world_size: int, per: int, device) -> torch.Tensor:
-    """Row of the rank-major gathered buffer [world][per] that holds global task i: rank i % world, slot i // world."""
+def shard_blocks(n_tasks: int, rank: int, world_size: int) -> np.ndarray:
+    """Contiguous assignment: rank r takes the r-th of world_size nearly equal runs of consecutive tasks (the first
+    n % world ranks one more).  For rolling windows of equal cost: a rank then needs only its own stretch of the history."""
+    base, extra = divmod(n_tasks, world_size)
+    lo = rank * base + min(rank, extra)
+    return np.arange(lo, lo + base + (1 if rank < extra else 0), dtype=np.int64)
+
+
+def _global_order(n_tasks: int, world_size: int, per: int, device, order: str = "cyclic") -> torch.Tensor:
+    """Row of the rank-major gathered buffer [world][per] that holds global task i — cyclic: rank i % world, slot
+    i // world; blocks: rank and slot of `shard_blocks`."""
     i = torch.arange(n_tasks, device=device)
-    return (i % world_size) * per + i // world_size
+    if order == "cyclic":
+        return (i % world_size) * per + i // world_size
+    if order != "blocks":
+        raise ValueError(f"order {order!r}: 'cyclic' or 'blocks'")
+    base, extra = divmod(n_tasks, world_size)
+    split = extra * (base + 1)                                   # tasks below `split` sit on the ranks that hold base + 1
+    r_hi = extra + (i - split) // max(base, 1)
+    r = torch.where(i < split, i // (base + 1), r_hi)
+    start = r * base + torch.clamp(r, max=extra)
+    return r * per + (i - start)
 
 
-def gather_results(local: torch.Tensor, n_tasks: int, rank: int | None = None, world_size: int | None = None):
-    """All-gather per-task result rows (first dim = this rank's tasks in `shard` order) and put
-    them back in global task order.  Ragged shards are padded to ceil(n/world) rows."""
+def gather_results(local: torch.Tensor, n_tasks: int, rank: int | None = None, world_size: int | None = None,
+                   order: str = "cyclic"):
+    """All-gather per-task result rows (first dim = this rank's tasks in `shard` order — or `shard_blocks` order with
+    order="blocks") and put them back in global task order.  Ragged shards are padded to ceil(n/world) rows."""
     r, w = world()
     rank = r if rank is None else rank
     world_size = w if world_size is None else world_size
@@ -44,7 +63,7 @@ def gather_results(local: torch.Tensor, n_tasks: int, rank: int | None = None, w
     pad[:local.shape[0]] = local
     full = torch.empty((world_size * per,) + tuple(local.shape[1:]), dtype=local.dtype, device=local.device)
     dist.all_gather_into_tensor(full, pad)
-    return full.index_select(0, _global_order(n_tasks, world_size, per, local.device))
+    return full.index_select(0, _global_order(n_tasks, world_size, per, local.device, order))
 
 
 def pack_records(tensors) -> tuple[torch.Tensor, list]:

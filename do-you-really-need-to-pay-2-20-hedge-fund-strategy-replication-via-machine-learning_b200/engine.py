@@ -674,7 +674,9 @@ def run_mode_w_wide(etf, hfd, rf, *, train_window: int, latent_dim: int, seeds=(
     """Rolling refit for wide shapes (hundreds of ETFs, thousands of funds: BASELINE configs[3]).  Same task definition
     and alignment as run_mode_w; kernel (a) builds the MinMax-scaled training windows, hfrep_fit_wide trains on them with
     weights in a global workspace, hfrep_predict_wide regresses every fund on the latent factors and returns the replica
-    return of row t+1.  `windows`: optional subset of window indices (a bounded sample of the 4 747 windows of configs[3])."""
+    return of row t+1.  `windows`: optional subset of window indices (a rank's share of the job, a bounded sample); only the
+    rows of the history those windows touch are uploaded, so a rank that takes a run of consecutive windows
+    (distributed.shard_blocks) uploads its own stretch of the histories and nothing else."""
     dev = _dev(device)
     src_f32 = np.asarray(etf).dtype == np.float32       # float32 history: windows are cut from it as it is; otherwise the
     etf = np.asarray(etf, np.float64)                   # MinMax runs on the float64 values (as the reference's AE does)
@@ -689,6 +691,10 @@ def run_mode_w_wide(etf, hfd, rf, *, train_window: int, latent_dim: int, seeds=(
     n_win = len(ts)
     tasks = [(wi, int(s)) for s in seeds for wi in range(n_win)]
     n = len(tasks)
+    t_out = ts
+    if n_win:                                            # only the stretch of the history these windows touch travels to the GPU:
+        r_lo, r_hi = int(ts.min()) - train_window, int(ts.max()) + 2      # rows [t - train_window, t + 2) of every window
+        etf, hfd, rf, ts, T = etf[r_lo:r_hi], hfd[r_lo:r_hi], rf[r_lo:r_hi], ts - r_lo, r_hi - r_lo
     with torch.cuda.device(dev):
         etf_d = to_device(etf, dev)
         Rsrc = etf_d.to(torch.float32) if src_f32 else etf_d
@@ -727,7 +733,8 @@ def run_mode_w_wide(etf, hfd, rf, *, train_window: int, latent_dim: int, seeds=(
             ev[2].synchronize()
             timings["fit_ms"] = ev[0].elapsed_time(ev[1])
             timings["eval_ms"] = ev[1].elapsed_time(ev[2])
-    return dict(t=ts, replica=replica.view(len(seeds), n_win, F), fit=fit, eval_status=est, blocks=blocks, tasks=tasks)
+    return dict(t=t_out, replica=replica.view(len(seeds), n_win, F), fit=fit, eval_status=est, blocks=blocks, tasks=tasks,
+                h2d_bytes=int(etf.nbytes + hfd.nbytes + rf.nbytes))
 
 
 def run_mode_w(etf, hfd, rf, *, train_window: int, latent_dim: int, seeds=(123,), ols_window: int = 24, device=None,

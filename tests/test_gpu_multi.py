@@ -45,6 +45,19 @@ kw = dict(train_window=40, latent_dim=3, seeds=(7, 8, 9), ols_window=12, device=
 w = hfrep.run_mode_w(etf, hfd, np.full(T, 1e-3), sharded=True, **kw)
 w1 = hfrep.run_mode_w(etf, hfd, np.full(T, 1e-3), **kw)
 assert torch.equal(w["replica"], w1["replica"]) and torch.equal(w["weights"], w1["weights"]) and torch.equal(w["fit"].W, w1["fit"].W)
+# wide rolling refit, windows dealt in runs of consecutive windows: a rank uploads only its stretch of the histories
+T, E, F = 300, 64, 40
+etf = rng.normal(size=(T, 5)) @ rng.normal(size=(5, E)) * .02 + rng.normal(size=(T, E)) * .01
+hfd = etf @ (rng.normal(size=(E, F)) * .1) + rng.normal(size=(T, F)) * .004
+kw = dict(train_window=252, latent_dim=6, seeds=(4,), ols_window=24, device=dev, max_epochs=6, early_stop=0)
+n_win = T - 252 - 1
+W0 = hfrep.engine.pack_weights([hfrep.engine.initial_weights(100 + wi, E, 6) for wi in range(n_win)], E, 2 * E * 6)
+mine = hfrep.distributed.shard_blocks(n_win, rank, world)
+part = hfrep.run_mode_w_wide(etf, hfd, np.full(T, 1e-3), windows=mine, W0=W0[mine], **kw)
+whole = hfrep.run_mode_w_wide(etf, hfd, np.full(T, 1e-3), W0=W0, **kw)
+assert part["h2d_bytes"] < whole["h2d_bytes"]
+got = hfrep.distributed.gather_results(part["replica"][0], n_win, order="blocks")
+assert torch.equal(got, whole["replica"][0])
 dist.barrier(); dist.destroy_process_group()
 print("ok", rank)
 """

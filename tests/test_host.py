@@ -140,6 +140,11 @@ local = torch.tensor([[float(i), float(i) * 2] for i in mine], dtype=torch.float
 full = D.gather_results(local, n)
 assert torch.equal(full[:, 0], torch.arange(n, dtype=torch.float64)), full
 assert torch.equal(full[:, 1], 2 * torch.arange(n, dtype=torch.float64))
+# runs of consecutive tasks (rolling windows): ragged too
+mine_b = D.shard_blocks(n, rank, world)
+assert len(mine_b) == (11 if rank == 0 else 10) and (np.diff(mine_b) == 1).all()
+full_b = D.gather_results(torch.from_numpy(mine_b).to(torch.float64)[:, None], n, order="blocks")
+assert torch.equal(full_b[:, 0], torch.arange(n, dtype=torch.float64)), full_b
 # the packed-record gather: several tensors of different dtypes and shapes (odd byte counts, a missing one) in ONE collective
 idx = torch.from_numpy(mine)
 fields = [idx.to(torch.float64)[:, None, None] * torch.ones(1, 3, 2, dtype=torch.float64), None,
