@@ -344,7 +344,9 @@ __global__ void __launch_bounds__(320, 1) generator_tc_kernel(const GenTcParams 
 #pragma unroll
             for (int j = 0; j < 36; ++j) acc[j] += __shfl_xor_sync(0xffffffffu, acc[j], 16);
             // the upper warp pair's sums cross to the lower pair through spare TMEM columns of the row's own lane
-            const uint32_t dcol = trow + 400u;
+            // (two sets of 40 columns, taken in turn: a set is rewritten two steps later, after the pair has met again — no
+            // barrier needed to free it; the pair meets on its own named barrier, not on the barrier of all eight warps)
+            const uint32_t dcol = trow + 400u + 40u * (uint32_t)(t & 1);
             if (pr == 1) {
 #pragma unroll
                 for (int j4 = 0; j4 < 9; ++j4) {
@@ -354,7 +356,7 @@ __global__ void __launch_bounds__(320, 1) generator_tc_kernel(const GenTcParams 
                 tc::tmem_st_wait();
             }
             tc::tc_fence_before();
-            epi_sync();
+            asm volatile("bar.sync %0, 64;" ::"r"(2 + s) : "memory");     // the two warps that share this TMEM quarter's rows
             tc::tc_fence_after();
             if (pr == 0) {
                 uint32_t r[32];
@@ -363,14 +365,23 @@ __global__ void __launch_bounds__(320, 1) generator_tc_kernel(const GenTcParams 
                 tc::tmem_ld4(dcol + 32u, r4);                          // (its wait covers both loads)
                 if (hh == 0 && live) {
                     float* o = p.out + ((size_t)path * T + t) * F_out;
+                    if (F_out == 36) {                                 // rows of 144 bytes, 16-byte aligned
 #pragma unroll
-                    for (int j = 0; j < 36; ++j)
-                        if (j < F_out) o[j] = (acc[j] + (j < 32 ? __uint_as_float(r[j]) : r4[j - 32])) + __ldg(bdg + j);
+                        for (int j4 = 0; j4 < 9; ++j4) {
+                            const float4 b4 = __ldg(reinterpret_cast<const float4*>(bdg) + j4);
+                            const float o0 = j4 < 8 ? __uint_as_float(r[4 * j4]) : r4[0], o1 = j4 < 8 ? __uint_as_float(r[4 * j4 + 1]) : r4[1];
+                            const float o2 = j4 < 8 ? __uint_as_float(r[4 * j4 + 2]) : r4[2], o3 = j4 < 8 ? __uint_as_float(r[4 * j4 + 3]) : r4[3];
+                            reinterpret_cast<float4*>(o)[j4] = make_float4((acc[4 * j4] + o0) + b4.x, (acc[4 * j4 + 1] + o1) + b4.y,
+                                                                           (acc[4 * j4 + 2] + o2) + b4.z, (acc[4 * j4 + 3] + o3) + b4.w);
+                        }
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 36; ++j)
+                            if (j < F_out) o[j] = (acc[j] + (j < 32 ? __uint_as_float(r[j]) : r4[j - 32])) + __ldg(bdg + j);
+                    }
                 }
             }
             tc::tc_fence_before();
-            epi_sync();                                                // the spare columns are free again
-            tc::tc_fence_after();
         }
     } else if (warp == G_EPI / 32) {
         // ============================================================ MMA issue
