@@ -92,7 +92,7 @@ def _load():
     lib.hfrep_generator_tc_prepare.argtypes = [vp, C.c_int, C.c_int, C.c_int, vp, vp]
     lib.hfrep_generator_forward_tc.argtypes = [vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, vp, C.c_int,
                                                C.c_int, vp, vp]
-    lib.hfrep_tc_selftest.argtypes = [vp, vp, C.c_int, vp, vp]
+    lib.hfrep_tc_selftest.argtypes = [vp, vp, C.c_int, vp, C.c_int, vp]
     lib.hfrep_tc_mma_rate.argtypes = [C.c_int, C.c_int, vp]
     lib.hfrep_generator_forward.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, vp, C.c_int,
                                             C.c_int, vp, vp]

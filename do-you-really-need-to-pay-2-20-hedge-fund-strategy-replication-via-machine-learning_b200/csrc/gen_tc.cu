@@ -14,7 +14,7 @@ constexpr int TCM = 64;            // rows (paths) per CTA
 constexpr int TCN = 400;           // gate columns
 constexpr int TCN0 = 256, TCN1 = TCN - TCN0;
 
-__global__ void __launch_bounds__(128) tc_selftest_kernel(const float* A, const float* B, int K, float* D) {
+__global__ void __launch_bounds__(128) tc_selftest_kernel(const float* A, const float* B, int K, float* D, int half) {
     extern __shared__ __align__(128) unsigned char smraw[];
     __shared__ __align__(8) uint64_t bar;
     __shared__ uint32_t tmem_slot;
@@ -44,7 +44,8 @@ __global__ void __launch_bounds__(128) tc_selftest_kernel(const float* A, const 
     tc::tc_fence_before();
     __syncthreads();
     tc::tc_fence_after();
-    const uint32_t tmem = tmem_slot;
+    // half = 1: the accumulator in lanes 16-31 of every TMEM quarter (the other half-subpartition an M = 64 tile may take)
+    const uint32_t tmem = tmem_slot + ((uint32_t)(16 * half) << 16);
 
     if (tid == 0) {
         const uint32_t sbo = (uint32_t)(K >> 2) * 128u, lbo = 128u;
@@ -70,15 +71,15 @@ __global__ void __launch_bounds__(128) tc_selftest_kernel(const float* A, const 
     // warp w reads TMEM lanes 32w .. 32w+31; rows 16w + lane live in its lanes 0..15
     for (int c0 = 0; c0 < TCN; c0 += 8) {
         float v[8];
-        tc::tmem_ld8(tmem + ((uint32_t)(32 * warp) << 16) + (uint32_t)c0, v);
-        if (lane < 16) {
+        tc::tmem_ld8(tmem_slot + ((uint32_t)(32 * warp) << 16) + (uint32_t)c0, v);
+        if ((lane >> 4) == half) {
 #pragma unroll
-            for (int i = 0; i < 8; ++i) D[(size_t)(16 * warp + lane) * TCN + c0 + i] = v[i];
+            for (int i = 0; i < 8; ++i) D[(size_t)(16 * warp + (lane & 15)) * TCN + c0 + i] = v[i];
         }
     }
     tc::tc_fence_before();
     __syncthreads();
-    if (warp == 0) tc::tmem_free<512>(tmem);
+    if (warp == 0) tc::tmem_free<512>(tmem_slot);
 }
 
 // MMA issue-rate probe: every CTA's thread 0 issues `iters` kind::tf32 MMAs (M = 64, N as given, K = 8) on zeroed operands,
@@ -250,20 +251,21 @@ __global__ void __launch_bounds__(320, 1) generator_tc_kernel(const GenTcParams 
         };
         // one LSTM layer's epilogue: gates -> cell -> h (region Hreg) -> [LeakyReLU] LayerNorm -> a[] (registers)
         const uint32_t zcol = trow + (uint32_t)(200 * pr);             // this warp pair's 200 gate columns
-        auto layer = [&](float (&c)[G_UPL], const float* bp, unsigned char* Hreg, int lrelu, const float* gamma, const float* beta,
-                         float (&a)[G_UPL]) {
+        auto layer = [&](int own, float (&c)[G_UPL], const float* bp, unsigned char* Hreg, int lrelu, const float* gamma,
+                         const float* beta, float (&a)[G_UPL]) {
             float hv[G_UPL];
             float ssum = 0.f;
             const float* bq = bp + 200 * pr + 4 * hh;                   // + 8 i: the four gate biases of unit 4i + q
-            // gates of one unit: lanes 0-15 keep the first four of a unit pair's eight columns, lanes 16-31 get the other four
+            // gates of one unit: the lanes that hold the TMEM rows (half `own`: 0 = lanes 0-15, layer 1; 1 = lanes 16-31, layer 2)
+            // keep their own four of a unit pair's eight columns and hand the other four to the other half
             auto unit = [&](int i, const uint32_t* r8) {
                 float z[4];
                 const float4 b4 = *reinterpret_cast<const float4*>(bq + 8 * i);
                 const float bb[4] = {b4.x, b4.y, b4.z, b4.w};
 #pragma unroll
                 for (int g = 0; g < 4; ++g) {
-                    const uint32_t o = __shfl_sync(0xffffffffu, r8[4 + g], l16);
-                    z[g] = __uint_as_float(hh ? o : r8[g]) + bb[g];
+                    const uint32_t o = __shfl_sync(0xffffffffu, r8[4 * (1 - own) + g], l16 + 16 * own);
+                    z[g] = __uint_as_float(hh == own ? r8[4 * own + g] : o) + bb[g];
                 }
                 // sigmoids with 5 ex2 + 3 rcp: i*cand and o*sigmoid(c) share a reciprocal each
                 const float ei = __expf(-z[0]), ef = __expf(-z[1]), ec = __expf(-z[2]), eo = __expf(-z[3]);
@@ -313,14 +315,14 @@ __global__ void __launch_bounds__(320, 1) generator_tc_kernel(const GenTcParams 
             tc::mbar_wait(&bar_z, par_z); par_z ^= 1;
             tc::tc_fence_after();
             float a[G_UPL];
-            if (!(p.debug & 2)) layer(c1, b1p, H1, p.lrelu1, lng, lng + GU, a);
+            if (!(p.debug & 2)) layer(0, c1, b1p, H1, p.lrelu1, lng, lng + GU, a);
 #pragma unroll
             for (int j = 0; j < G_UPL; ++j) put_unit(AX, j, a[j]);
             signal_operands();
             // ---- layer 2
             tc::mbar_wait(&bar_z, par_z); par_z ^= 1;
             tc::tc_fence_after();
-            if (!(p.debug & 2)) layer(c2, b2p, H2, p.lrelu2, lng + 2 * GU, lng + 3 * GU, a);
+            if (!(p.debug & 2)) layer(1, c2, b2p, H2, p.lrelu2, lng + 2 * GU, lng + 3 * GU, a);
             if (t + 1 < T) {                                           // layer 2's MMAs are complete: the x / a1 region is free
                 store_x(xn);
                 signal_operands();
@@ -389,30 +391,37 @@ __global__ void __launch_bounds__(320, 1) generator_tc_kernel(const GenTcParams 
             const uint32_t i0 = tc::idesc_tf32(64, TCN0), i1 = tc::idesc_tf32(64, TCN1);
             const uint32_t h1a = tc::smem_u32(H1), axa = tc::smem_u32(AX), h2a = tc::smem_u32(H2), rga = tc::smem_u32(ring);
             unsigned par_a = 0;
-            uint32_t g = 0;
-            for (int t = 0; t < T; ++t) {
-                for (int layer = 0; layer < 2; ++layer) {
-                    tc::mbar_wait(&bar_a, par_a); par_a ^= 1;
-                    tc::tc_fence_after();
-                    const int nks = layer ? G_NKS2 : G_NKS1, nfirst = layer ? GKH / 8 : GKX / 8;
-                    for (int ks = 0; ks < nks; ++ks, ++g) {
-                        const uint32_t st = g & 1;
-                        if (!(p.debug & 1) || g < 2) tc::mbar_wait(&bar_full[st], (g >> 1) & 1);
-                        tc::tc_fence_after();
-                        const uint32_t abase = ks < nfirst ? axa + (uint32_t)ks * 256u
-                                                           : (layer ? h2a : h1a) + (uint32_t)(ks - nfirst) * 256u;
-                        const uint32_t bbase = rga + st * G_STAGE;
+            uint32_t g = 0;                                            // K-steps issued so far: stage = g & 1
+            // one K = 8 step: three MMA pairs (3xTF32) on the stage the loader filled, then the stage is handed back
+            auto kstep = [&](uint32_t abase, uint32_t d, bool first) {
+                const uint32_t st = g & 1;
+                if (!(p.debug & 1) || g < 2) tc::mbar_wait(&bar_full[st], (g >> 1) & 1);
+                tc::tc_fence_after();
+                const uint32_t bbase = rga + st * G_STAGE;
 #pragma unroll
-                        for (int c = 0; c < ((p.debug & 4) ? 0 : 3); ++c) {
-                            const uint32_t aa = abase + (c == 1 ? G_PLANE_A : 0u), bb = bbase + (c == 2 ? G_PLANE_B : 0u);
-                            const uint64_t ad = tc::smem_desc(aa, G_LBO, G_SBO_A);
-                            tc::mma_tf32(tmem, ad, tc::smem_desc(bb, G_LBO, G_SBO_B), i0, ks > 0 || c > 0);
-                            tc::mma_tf32(tmem + TCN0, ad, tc::smem_desc(bb + (TCN0 / 8) * G_SBO_B, G_LBO, G_SBO_B), i1, ks > 0 || c > 0);
-                        }
-                        if (!(p.debug & 1)) tc::mma_commit(&bar_empty[st]);     // the stage is free once these MMAs have read it
-                    }
-                    tc::mma_commit(&bar_z);                             // the layer's accumulators are complete
+                for (int c = 0; c < ((p.debug & 4) ? 0 : 3); ++c) {
+                    const uint32_t aa = abase + (c == 1 ? G_PLANE_A : 0u), bb = bbase + (c == 2 ? G_PLANE_B : 0u);
+                    const uint64_t ad = tc::smem_desc(aa, G_LBO, G_SBO_A);
+                    tc::mma_tf32(d, ad, tc::smem_desc(bb, G_LBO, G_SBO_B), i0, !first || c > 0);
+                    tc::mma_tf32(d + TCN0, ad, tc::smem_desc(bb + (TCN0 / 8) * G_SBO_B, G_LBO, G_SBO_B), i1, !first || c > 0);
                 }
+                if (!(p.debug & 1)) tc::mma_commit(&bar_empty[st]);     // the stage is free once these MMAs have read it
+                ++g;
+            };
+            const uint32_t z1 = tmem, z2 = tmem + (16u << 16);         // layer 2's accumulators: lanes 16-31 of every TMEM quarter
+            for (int t = 0; t < T; ++t) {
+                // x_t and h1_{t-1} are in place; so are h2_{t-1} and the layer-2 lanes (the same signal, sent after layer 2's epilogue)
+                tc::mbar_wait(&bar_a, par_a); par_a ^= 1;
+                tc::tc_fence_after();
+                for (int ks = 0; ks < GKX / 8; ++ks) kstep(axa + (uint32_t)ks * 256u, z1, ks == 0);
+                for (int ks = 0; ks < GKH / 8; ++ks) kstep(h1a + (uint32_t)ks * 256u, z1, false);
+                tc::mma_commit(&bar_z);                                 // layer 1's accumulators are complete
+                // layer 2's recurrent half does not wait for layer 1's epilogue: it runs under it
+                for (int ks = 0; ks < GKH / 8; ++ks) kstep(h2a + (uint32_t)ks * 256u, z2, ks == 0);
+                tc::mbar_wait(&bar_a, par_a); par_a ^= 1;               // a1_t is in place
+                tc::tc_fence_after();
+                for (int ks = 0; ks < GKH / 8; ++ks) kstep(axa + (uint32_t)ks * 256u, z2, false);
+                tc::mma_commit(&bar_z);                                 // layer 2's accumulators are complete
             }
         }
         __syncwarp();
@@ -434,8 +443,8 @@ __global__ void __launch_bounds__(320, 1) generator_tc_kernel(const GenTcParams 
     if (warp == 0) tc::tmem_free<512>(tmem);
 }
 
-// B blocks of the two LSTM layers for generator_tc_kernel: block b = K-step b of a time step (18 of layer 1: x rows 0..39,
-// then h1 rows 0..103; 26 of layer 2: a1 rows, then h2 rows; rows past the real input sizes are zero), each [hi | lo] plane
+// B blocks of the two LSTM layers for generator_tc_kernel: block b = K-step b of a time step in issue order (18 of layer 1: x
+// rows 0..39, then h1 rows 0..103; 26 of layer 2: h2 rows first, then a1 rows; rows past the real input sizes are zero), each [hi | lo] plane
 // 400 gate columns x 8 K in the canonical K-major layout, gate column 4u+g <- Keras column g*U+u.
 __global__ void generator_tc_prepare_kernel(const float* W, int F_in, unsigned char* tcw) {
     const int U = GU, G = GG;
@@ -452,10 +461,12 @@ __global__ void generator_tc_prepare_kernel(const float* W, int F_in, unsigned c
             const int k = b * 8 + kk;
             if (k < GKX) { if (k < F_in) v = W1[(size_t)k * G + col]; }
             else if (k - GKX < U) v = U1[(size_t)(k - GKX) * G + col];
-        } else {
+        } else if (b < G_NKS1 + GKH / 8) {                             // layer 2, recurrent half first (issued under layer 1's epilogue)
             const int k = (b - G_NKS1) * 8 + kk;
-            if (k < GKH) { if (k < U) v = W2[(size_t)k * G + col]; }
-            else if (k - GKH < U) v = U2[(size_t)(k - GKH) * G + col];
+            if (k < U) v = U2[(size_t)k * G + col];
+        } else {
+            const int k = (b - G_NKS1 - GKH / 8) * 8 + kk;
+            if (k < U) v = W2[(size_t)k * G + col];
         }
         float hi, lo;
         tc::split_tf32(v, hi, lo);
@@ -469,12 +480,12 @@ __global__ void generator_tc_prepare_kernel(const float* W, int F_in, unsigned c
 
 using namespace hfrep;
 
-extern "C" int hfrep_tc_selftest(const float* A, const float* B, int K, float* D, void* stream) {
+extern "C" int hfrep_tc_selftest(const float* A, const float* B, int K, float* D, int lane_half, void* stream) {
     HFREP_REQUIRE(A && B && D, "tc_selftest: null argument");
     HFREP_REQUIRE(K >= 8 && K % 8 == 0 && K <= 48, "tc_selftest: K=%d (a multiple of 8 up to 48)", K);
     const size_t smem = (size_t)2 * (TCM + TCN) * K * 4;
     HFREP_CUDA_OK(allow_max_dynamic_smem(tc_selftest_kernel));
-    tc_selftest_kernel<<<1, 128, smem, (cudaStream_t)stream>>>(A, B, K, D);
+    tc_selftest_kernel<<<1, 128, smem, (cudaStream_t)stream>>>(A, B, K, D, lane_half ? 1 : 0);
     HFREP_CUDA_OK(cudaGetLastError());
     return HFREP_OK;
 }

@@ -280,8 +280,9 @@ int hfrep_generator_forward_tc(const float* weights, const void* tc_weights, int
 /* tcgen05 self-test (the building blocks of the tensor-core generator path, csrc/tc.cuh): D f32 [64][400] =
  * A f32 [64][K] * B f32 [400][K]^T in 3xTF32 on one CTA — operands split into TF32 hi/lo pairs and written in the canonical
  * un-swizzled K-major shared-memory layout, kind::tf32 MMAs (M = 64, N = 256 + 144), FP32 accumulators in tensor memory.
- * K a multiple of 8, <= 48.  All pointers device memory. */
-int hfrep_tc_selftest(const float* A, const float* B, int K, float* D, void* stream);
+ * K a multiple of 8, <= 48.  lane_half = 1 places the accumulator in lanes 16-31 of each TMEM quarter instead of lanes 0-15.
+ * All pointers device memory. */
+int hfrep_tc_selftest(const float* A, const float* B, int K, float* D, int lane_half, void* stream);
 /* MMA issue-rate probe: one CTA per SM, each issues `iters` kind::tf32 MMAs of M = 64, N (a multiple of 8, <= 256), K = 8 on
  * zeroed operands; time it with CUDA events on `stream`. */
 int hfrep_tc_mma_rate(int N, int iters, void* stream);

@@ -194,7 +194,11 @@ def test_tcgen05_selftest(hf):
         A, B = rng.normal(size=(64, K)).astype(np.float32), rng.normal(size=(400, K)).astype(np.float32)
         D = torch.full((64, 400), float("nan"), device="cuda:0")
         Ad, Bd = torch.from_numpy(A).to("cuda:0"), torch.from_numpy(B).to("cuda:0")
-        check(lib.hfrep_tc_selftest(ptr(Ad), ptr(Bd), K, ptr(D), None))
+        for half in (0, 1):
+            D.fill_(float("nan"))
+            check(lib.hfrep_tc_selftest(ptr(Ad), ptr(Bd), K, ptr(D), half, None))
+            want = A.astype(np.float64) @ B.astype(np.float64).T
+            assert np.max(np.abs(D.cpu().numpy() - want)) < 1e-6 * np.max(np.abs(want)), half
         want = A.astype(np.float64) @ B.astype(np.float64).T
         assert np.max(np.abs(D.cpu().numpy() - want)) < 1e-6 * np.max(np.abs(want))
 
