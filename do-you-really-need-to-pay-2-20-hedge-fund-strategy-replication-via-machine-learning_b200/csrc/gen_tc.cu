@@ -133,17 +133,17 @@ constexpr int G_NKS1 = (GKX + GKH) / 8, G_NKS2 = (GKH + GKH) / 8, G_NKS = G_NKS1
 constexpr uint32_t G_PLANE_B = GG * 8 * 4, G_STAGE = 2 * G_PLANE_B;                               // 12 800, 25 600 bytes
 constexpr uint32_t G_SBO_B = 256, G_LBO = 128;
 constexpr uint32_t G_SBO_A = (GKH / 4) * 128, G_PLANE_A = 8 * G_SBO_A;                            // 3 328, 26 624 bytes
+constexpr int G_ND = 40, G_NKD = GKH / 8;                                                       // Dense: N = 40 (36 + pad), 13 K-steps over a2
+constexpr uint32_t G_PLANE_D = G_ND * 8 * 4, G_BLOCK_D = 2 * G_PLANE_D;                          // 1 280, 2 560 bytes
 constexpr int G_EPI = 256;                                                                       // epilogue threads
 constexpr int G_UPL = 25;                                                                        // units per lane
 
 struct GenTcParams {
     const float* W;        // packed weights (hfrep.h): biases, LayerNorm, Dense read from here
-    const unsigned char* tcw;   // prepared B blocks: [G_NKS][hi plane | lo plane]
+    const unsigned char* tcw;   // prepared B blocks: [G_NKS][hi plane | lo plane] of the LSTM kernels, then [G_NKD] of the Dense kernel
     const float* noise; float* out;
     int n, T, F_in, F_out, lrelu1, lrelu2;
     float alpha, ln_eps;
-    int debug;             // timing experiments only, wrong results (1: no weight streaming after the first two stages,
-                           // 2: no epilogue arithmetic, 4: no MMAs)
 };
 
 __device__ __forceinline__ float rcp_fast(float x) { float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
@@ -169,7 +169,6 @@ __global__ void __launch_bounds__(320, 1) generator_tc_kernel(const GenTcParams 
     float* lng = b2p + GG;                              // gamma1, beta1, gamma2, beta2 [100 each]
     float* lnA = lng + 4 * GU;                          // [64][4]
     float* lnB = lnA + 256;                             // [64][4]
-    float* KdS = lnB + 256;                             // [100][36] Dense kernel (rows past F_out columns: unused)
 
     const int U = GU, G = GG, F_in = p.F_in, F_out = p.F_out, T = p.T;
     const float* W1 = p.W;
@@ -197,7 +196,6 @@ __global__ void __launch_bounds__(320, 1) generator_tc_kernel(const GenTcParams 
         const int arr = i / U, r = i - arr * U, qq = r / G_UPL, ii = r - qq * G_UPL;
         lng[i] = __ldg((arr < 2 ? g1 : g2) + (arr & 1) * U + 4 * ii + qq);
     }
-    for (int i = tid; i < U * 36; i += blockDim.x) { const int u = i / 36, j = i - u * 36; KdS[i] = j < F_out ? __ldg(Kd + (size_t)u * F_out + j) : 0.f; }
     for (int i = tid; i < (int)(6 * G_PLANE_A / 4); i += blockDim.x) reinterpret_cast<float*>(smraw)[i] = 0.f;   // h1 = h2 = 0, pads
     tc::tc_fence_before();
     __syncthreads();
@@ -308,132 +306,142 @@ __global__ void __launch_bounds__(320, 1) generator_tc_kernel(const GenTcParams 
             store_x(xv);
             signal_operands();
         }
+        const uint32_t dcol = trow + 400u;                             // the Dense layer's accumulators: 40 columns, lanes 0-15
         for (int t = 0; t < T; ++t) {
             float xn[10];
             if (t + 1 < T) load_x(t + 1, xn);                          // (in flight under the first layer's epilogue)
             // ---- layer 1
-            tc::mbar_wait(&bar_z, par_z); par_z ^= 1;
+            tc::mbar_wait<false>(&bar_z, par_z); par_z ^= 1;
             tc::tc_fence_after();
             float a[G_UPL];
-            if (!(p.debug & 2)) layer(0, c1, b1p, H1, p.lrelu1, lng, lng + GU, a);
+            layer(0, c1, b1p, H1, p.lrelu1, lng, lng + GU, a);
 #pragma unroll
             for (int j = 0; j < G_UPL; ++j) put_unit(AX, j, a[j]);
-            signal_operands();
+            signal_operands();                                         // A(t): a1_t, h1_t in place, layer 1's lanes read
             // ---- layer 2
-            tc::mbar_wait(&bar_z, par_z); par_z ^= 1;
+            tc::mbar_wait<false>(&bar_z, par_z); par_z ^= 1;
             tc::tc_fence_after();
-            if (!(p.debug & 2)) layer(1, c2, b2p, H2, p.lrelu2, lng + 2 * GU, lng + 3 * GU, a);
-            if (t + 1 < T) {                                           // layer 2's MMAs are complete: the x / a1 region is free
-                store_x(xn);
-                signal_operands();
-            }
-            // ---- Dense on the registers: out[row][j] = bd[j] + sum_u a2[u] Kd[u][j], the row's four unit ranges added up
-            float acc[36];
+            layer(1, c2, b2p, H2, p.lrelu2, lng + 2 * GU, lng + 3 * GU, a);
 #pragma unroll
-            for (int j = 0; j < 36; ++j) acc[j] = 0.f;
-            if (!(p.debug & 2)) {
-#pragma unroll 5
-                for (int i = 0; i < G_UPL; ++i) {
-                    const float4* kr = reinterpret_cast<const float4*>(KdS + (4 * i + q) * 36);
-#pragma unroll
-                    for (int j4 = 0; j4 < 9; ++j4) {
-                        const float4 w = kr[j4];
-                        acc[4 * j4] = fmaf(a[i], w.x, acc[4 * j4]); acc[4 * j4 + 1] = fmaf(a[i], w.y, acc[4 * j4 + 1]);
-                        acc[4 * j4 + 2] = fmaf(a[i], w.z, acc[4 * j4 + 2]); acc[4 * j4 + 3] = fmaf(a[i], w.w, acc[4 * j4 + 3]);
-                    }
-                }
-            }
-#pragma unroll
-            for (int j = 0; j < 36; ++j) acc[j] += __shfl_xor_sync(0xffffffffu, acc[j], 16);
-            // the upper warp pair's sums cross to the lower pair through spare TMEM columns of the row's own lane
-            // (two sets of 40 columns, taken in turn: a set is rewritten two steps later, after the pair has met again — no
-            // barrier needed to free it; the pair meets on its own named barrier, not on the barrier of all eight warps)
-            const uint32_t dcol = trow + 400u + 40u * (uint32_t)(t & 1);
-            if (pr == 1) {
-#pragma unroll
-                for (int j4 = 0; j4 < 9; ++j4) {
-                    const float v4[4] = {acc[4 * j4], acc[4 * j4 + 1], acc[4 * j4 + 2], acc[4 * j4 + 3]};
-                    tc::tmem_st4(dcol + 4u * j4, v4);
-                }
-                tc::tmem_st_wait();
-            }
-            tc::tc_fence_before();
-            asm volatile("bar.sync %0, 64;" ::"r"(2 + s) : "memory");     // the two warps that share this TMEM quarter's rows
+            for (int j = 0; j < G_UPL; ++j) put_unit(AX, j, a[j]);     // layer 2's a1-half is complete: a2_t takes the region
+            signal_operands();                                         // C(t): a2_t, h2_t in place, layer 2's lanes read
+            // ---- Dense: out = a2 Kd + bd, one more MMA chain; the two warps of a TMEM quarter store half the columns each
+            tc::mbar_wait<false>(&bar_z, par_z); par_z ^= 1;
             tc::tc_fence_after();
-            if (pr == 0) {
-                uint32_t r[32];
-                float r4[4];
+            {
+                uint32_t r[32], r8[8];
                 tc::tmem_ld32_nowait(dcol, r);
-                tc::tmem_ld4(dcol + 32u, r4);                          // (its wait covers both loads)
+                tc::tmem_ld8_nowait(dcol + 32u, r8);
+                tc::tmem_ld_wait();
                 if (hh == 0 && live) {
                     float* o = p.out + ((size_t)path * T + t) * F_out;
                     if (F_out == 36) {                                 // rows of 144 bytes, 16-byte aligned
 #pragma unroll
                         for (int j4 = 0; j4 < 9; ++j4) {
+                            if ((j4 < 5) != (pr == 0)) continue;
                             const float4 b4 = __ldg(reinterpret_cast<const float4*>(bdg) + j4);
-                            const float o0 = j4 < 8 ? __uint_as_float(r[4 * j4]) : r4[0], o1 = j4 < 8 ? __uint_as_float(r[4 * j4 + 1]) : r4[1];
-                            const float o2 = j4 < 8 ? __uint_as_float(r[4 * j4 + 2]) : r4[2], o3 = j4 < 8 ? __uint_as_float(r[4 * j4 + 3]) : r4[3];
-                            reinterpret_cast<float4*>(o)[j4] = make_float4((acc[4 * j4] + o0) + b4.x, (acc[4 * j4 + 1] + o1) + b4.y,
-                                                                           (acc[4 * j4 + 2] + o2) + b4.z, (acc[4 * j4 + 3] + o3) + b4.w);
+                            const uint32_t* v = j4 < 8 ? r + 4 * j4 : r8;
+                            reinterpret_cast<float4*>(o)[j4] = make_float4(__uint_as_float(v[0]) + b4.x, __uint_as_float(v[1]) + b4.y,
+                                                                           __uint_as_float(v[2]) + b4.z, __uint_as_float(v[3]) + b4.w);
                         }
-                    } else {
+                    } else if (pr == 0) {
 #pragma unroll
                         for (int j = 0; j < 36; ++j)
-                            if (j < F_out) o[j] = (acc[j] + (j < 32 ? __uint_as_float(r[j]) : r4[j - 32])) + __ldg(bdg + j);
+                            if (j < F_out) o[j] = __uint_as_float(j < 32 ? r[j] : r8[j - 32]) + __ldg(bdg + j);
                     }
                 }
             }
-            tc::tc_fence_before();
+            if (t + 1 < T) {                                           // the Dense chain is complete: x_{t+1} takes the region
+                store_x(xn);
+                signal_operands();                                     // B(t): x_{t+1} in place, the Dense lanes read
+            }
         }
+        tc::tc_fence_before();
     } else if (warp == G_EPI / 32) {
         // ============================================================ MMA issue
         if (lane == 0) {
-            const uint32_t i0 = tc::idesc_tf32(64, TCN0), i1 = tc::idesc_tf32(64, TCN1);
+            const uint32_t i0 = tc::idesc_tf32(64, TCN0), i1 = tc::idesc_tf32(64, TCN1), id = tc::idesc_tf32(64, G_ND);
             const uint32_t h1a = tc::smem_u32(H1), axa = tc::smem_u32(AX), h2a = tc::smem_u32(H2), rga = tc::smem_u32(ring);
             unsigned par_a = 0;
             uint32_t g = 0;                                            // K-steps issued so far: stage = g & 1
             // one K = 8 step: three MMA pairs (3xTF32) on the stage the loader filled, then the stage is handed back
             auto kstep = [&](uint32_t abase, uint32_t d, bool first) {
                 const uint32_t st = g & 1;
-                if (!(p.debug & 1) || g < 2) tc::mbar_wait(&bar_full[st], (g >> 1) & 1);
+                tc::mbar_wait<false>(&bar_full[st], (g >> 1) & 1);
                 tc::tc_fence_after();
                 const uint32_t bbase = rga + st * G_STAGE;
 #pragma unroll
-                for (int c = 0; c < ((p.debug & 4) ? 0 : 3); ++c) {
+                for (int c = 0; c < 3; ++c) {
                     const uint32_t aa = abase + (c == 1 ? G_PLANE_A : 0u), bb = bbase + (c == 2 ? G_PLANE_B : 0u);
                     const uint64_t ad = tc::smem_desc(aa, G_LBO, G_SBO_A);
                     tc::mma_tf32(d, ad, tc::smem_desc(bb, G_LBO, G_SBO_B), i0, !first || c > 0);
                     tc::mma_tf32(d + TCN0, ad, tc::smem_desc(bb + (TCN0 / 8) * G_SBO_B, G_LBO, G_SBO_B), i1, !first || c > 0);
                 }
-                if (!(p.debug & 1)) tc::mma_commit(&bar_empty[st]);     // the stage is free once these MMAs have read it
+                tc::mma_commit(&bar_empty[st]);                         // the stage is free once these MMAs have read it
                 ++g;
             };
-            const uint32_t z1 = tmem, z2 = tmem + (16u << 16);         // layer 2's accumulators: lanes 16-31 of every TMEM quarter
-            for (int t = 0; t < T; ++t) {
-                // x_t and h1_{t-1} are in place; so are h2_{t-1} and the layer-2 lanes (the same signal, sent after layer 2's epilogue)
-                tc::mbar_wait(&bar_a, par_a); par_a ^= 1;
+            auto kstep_dense = [&](uint32_t abase, uint32_t d, bool first) {
+                const uint32_t st = g & 1;
+                tc::mbar_wait<false>(&bar_full[st], (g >> 1) & 1);
                 tc::tc_fence_after();
-                for (int ks = 0; ks < GKX / 8; ++ks) kstep(axa + (uint32_t)ks * 256u, z1, ks == 0);
-                for (int ks = 0; ks < GKH / 8; ++ks) kstep(h1a + (uint32_t)ks * 256u, z1, false);
+                const uint32_t bbase = rga + st * G_STAGE;
+#pragma unroll
+                for (int c = 0; c < 3; ++c) {
+                    const uint32_t aa = abase + (c == 1 ? G_PLANE_A : 0u), bb = bbase + (c == 2 ? G_PLANE_D : 0u);
+                    tc::mma_tf32(d, tc::smem_desc(aa, G_LBO, G_SBO_A), tc::smem_desc(bb, G_LBO, G_SBO_B), id, !first || c > 0);
+                }
+                tc::mma_commit(&bar_empty[st]);
+                ++g;
+            };
+            const uint32_t z1 = tmem, z2 = tmem + (16u << 16), zd = tmem + 400u;   // layer 2: lanes 16-31 of every TMEM quarter
+            // Issue order (the loader streams the weight blocks in the same order).  Every chain starts with the half whose
+            // operand is ready first, so it runs under the epilogue that produces the other half's operand:
+            //   h1_{t-1} U1 | per step:  x_t W1 -> z1 ; h2_{t-1} U2 ; [A(t)] a1_t W2 -> z2 ; h1_t U1 (next step's) ; [C(t)] a2_t Kd -> zd ; [B(t)]
+            tc::mbar_wait<false>(&bar_a, par_a); par_a ^= 1;                   // x_0 and the zero states
+            tc::tc_fence_after();
+            for (int ks = 0; ks < GKH / 8; ++ks) kstep(h1a + (uint32_t)ks * 256u, z1, ks == 0);
+            for (int t = 0; t < T; ++t) {
+                if (t > 0) { tc::mbar_wait<false>(&bar_a, par_a); par_a ^= 1; tc::tc_fence_after(); }   // B(t-1)
+                for (int ks = 0; ks < GKX / 8; ++ks) kstep(axa + (uint32_t)ks * 256u, z1, false);
                 tc::mma_commit(&bar_z);                                 // layer 1's accumulators are complete
-                // layer 2's recurrent half does not wait for layer 1's epilogue: it runs under it
                 for (int ks = 0; ks < GKH / 8; ++ks) kstep(h2a + (uint32_t)ks * 256u, z2, ks == 0);
-                tc::mbar_wait(&bar_a, par_a); par_a ^= 1;               // a1_t is in place
+                tc::mbar_wait<false>(&bar_a, par_a); par_a ^= 1;               // A(t)
                 tc::tc_fence_after();
                 for (int ks = 0; ks < GKH / 8; ++ks) kstep(axa + (uint32_t)ks * 256u, z2, false);
                 tc::mma_commit(&bar_z);                                 // layer 2's accumulators are complete
+                if (t + 1 < T)
+                    for (int ks = 0; ks < GKH / 8; ++ks) kstep(h1a + (uint32_t)ks * 256u, z1, ks == 0);
+                tc::mbar_wait<false>(&bar_a, par_a); par_a ^= 1;               // C(t)
+                tc::tc_fence_after();
+                for (int ks = 0; ks < G_NKD; ++ks) kstep_dense(axa + (uint32_t)ks * 256u, zd, ks == 0);
+                tc::mma_commit(&bar_z);                                 // the Dense accumulators are complete
             }
         }
         __syncwarp();
     } else {
-        // ============================================================ weight loader
+        // ============================================================ weight loader (same order as the MMA issue)
         if (lane == 0) {
-            const uint32_t total = (p.debug & 1) ? 2u : (uint32_t)T * G_NKS;
-            for (uint32_t g = 0; g < total; ++g) {
+            uint32_t g = 0;
+            auto load = [&](const unsigned char* src, uint32_t bytes) {
                 const uint32_t st = g & 1;
                 tc::mbar_wait(&bar_empty[st], ((g >> 1) & 1) ^ 1);
-                tc::mbar_expect_tx(&bar_full[st], G_STAGE);
-                tc::bulk_g2s(ring + st * G_STAGE, p.tcw + (size_t)(g % G_NKS) * G_STAGE, G_STAGE, &bar_full[st]);
+                tc::mbar_expect_tx(&bar_full[st], bytes);
+                tc::bulk_g2s(ring + st * G_STAGE, src, bytes, &bar_full[st]);
+                ++g;
+            };
+            const unsigned char* bx = p.tcw;                                   // 5 blocks: W1 rows of x
+            const unsigned char* bh1 = bx + (size_t)(GKX / 8) * G_STAGE;       // 13: U1
+            const unsigned char* bh2 = bh1 + (size_t)(GKH / 8) * G_STAGE;      // 13: U2
+            const unsigned char* ba1 = bh2 + (size_t)(GKH / 8) * G_STAGE;      // 13: W2
+            const unsigned char* bkd = ba1 + (size_t)(GKH / 8) * G_STAGE;      // 13 small: Kd
+            for (int ks = 0; ks < GKH / 8; ++ks) load(bh1 + (size_t)ks * G_STAGE, G_STAGE);
+            for (int t = 0; t < T; ++t) {
+                for (int ks = 0; ks < GKX / 8; ++ks) load(bx + (size_t)ks * G_STAGE, G_STAGE);
+                for (int ks = 0; ks < GKH / 8; ++ks) load(bh2 + (size_t)ks * G_STAGE, G_STAGE);
+                for (int ks = 0; ks < GKH / 8; ++ks) load(ba1 + (size_t)ks * G_STAGE, G_STAGE);
+                if (t + 1 < T)
+                    for (int ks = 0; ks < GKH / 8; ++ks) load(bh1 + (size_t)ks * G_STAGE, G_STAGE);
+                for (int ks = 0; ks < G_NKD; ++ks) load(bkd + (size_t)ks * G_BLOCK_D, G_BLOCK_D);
             }
         }
         __syncwarp();
@@ -446,22 +454,25 @@ __global__ void __launch_bounds__(320, 1) generator_tc_kernel(const GenTcParams 
 // B blocks of the two LSTM layers for generator_tc_kernel: block b = K-step b of a time step in issue order (18 of layer 1: x
 // rows 0..39, then h1 rows 0..103; 26 of layer 2: h2 rows first, then a1 rows; rows past the real input sizes are zero), each [hi | lo] plane
 // 400 gate columns x 8 K in the canonical K-major layout, gate column 4u+g <- Keras column g*U+u.
-__global__ void generator_tc_prepare_kernel(const float* W, int F_in, unsigned char* tcw) {
+__global__ void generator_tc_prepare_kernel(const float* W, int F_in, int F_out, unsigned char* tcw) {
     const int U = GU, G = GG;
     const float* W1 = W;
     const float* U1 = W1 + (size_t)F_in * G;
     const float* W2 = U1 + (size_t)U * G + G + 2 * U;
     const float* U2 = W2 + (size_t)U * G;
+    const float* Kd = U2 + (size_t)U * G + G + 2 * U;
     const int total = G_NKS * 8 * G;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
         const int n = i % G, kk = (i / G) % 8, b = i / (8 * G);
         const int u = gate_col_unit(n), g = gate_col_gate(n), col = g * U + u;
         float v = 0.f;
-        if (b < G_NKS1) {
+        if (b < GKX / 8) {                                             // layer 1: x rows, then h1 rows
             const int k = b * 8 + kk;
-            if (k < GKX) { if (k < F_in) v = W1[(size_t)k * G + col]; }
-            else if (k - GKX < U) v = U1[(size_t)(k - GKX) * G + col];
-        } else if (b < G_NKS1 + GKH / 8) {                             // layer 2, recurrent half first (issued under layer 1's epilogue)
+            if (k < F_in) v = W1[(size_t)k * G + col];
+        } else if (b < G_NKS1) {
+            const int k = (b - GKX / 8) * 8 + kk;
+            if (k < U) v = U1[(size_t)k * G + col];
+        } else if (b < G_NKS1 + GKH / 8) {                             // layer 2: h2 rows (recurrent half), then a1 rows
             const int k = (b - G_NKS1) * 8 + kk;
             if (k < U) v = U2[(size_t)k * G + col];
         } else {
@@ -473,6 +484,19 @@ __global__ void generator_tc_prepare_kernel(const float* W, int F_in, unsigned c
         const size_t o = (size_t)b * G_STAGE + (size_t)(n >> 3) * G_SBO_B + (size_t)(kk >> 2) * 128 + (size_t)(n & 7) * 16 + (size_t)(kk & 3) * 4;
         *reinterpret_cast<float*>(tcw + o) = hi;
         *reinterpret_cast<float*>(tcw + G_PLANE_B + o) = lo;
+    }
+    // the Dense kernel: 13 blocks of [hi | lo] planes, 40 output columns (36 + zero padding) x 8 K
+    const int total_d = G_NKD * 8 * G_ND;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total_d; i += gridDim.x * blockDim.x) {
+        const int n = i % G_ND, kk = (i / G_ND) % 8, b = i / (8 * G_ND);
+        const int k = b * 8 + kk;
+        const float v = (k < U && n < F_out) ? Kd[(size_t)k * F_out + n] : 0.f;
+        float hi, lo;
+        tc::split_tf32(v, hi, lo);
+        const size_t o = (size_t)G_NKS * G_STAGE + (size_t)b * G_BLOCK_D + (size_t)(n >> 3) * G_SBO_B + (size_t)(kk >> 2) * 128 +
+                         (size_t)(n & 7) * 16 + (size_t)(kk & 3) * 4;
+        *reinterpret_cast<float*>(tcw + o) = hi;
+        *reinterpret_cast<float*>(tcw + G_PLANE_D + o) = lo;
     }
 }
 
@@ -492,14 +516,14 @@ extern "C" int hfrep_tc_selftest(const float* A, const float* B, int K, float* D
 
 extern "C" size_t hfrep_generator_tc_weight_bytes(int F_in, int units, int F_out) {
     if (units != GU || F_in < 1 || F_in > GKX || F_out < 1 || F_out > 36) return 0;       // shapes the tensor-core kernel takes
-    return (size_t)G_NKS * G_STAGE;
+    return (size_t)G_NKS * G_STAGE + (size_t)G_NKD * G_BLOCK_D;
 }
 
 extern "C" int hfrep_generator_tc_prepare(const float* weights, int F_in, int units, int F_out, void* tc_weights, void* stream) {
     HFREP_REQUIRE(weights && tc_weights, "generator_tc_prepare: null argument");
     HFREP_REQUIRE(hfrep_generator_tc_weight_bytes(F_in, units, F_out) != 0, "generator_tc_prepare: F_in=%d units=%d F_out=%d (units = %d, F_in <= %d, F_out <= 36)",
                   F_in, units, F_out, GU, GKX);
-    generator_tc_prepare_kernel<<<148, 256, 0, (cudaStream_t)stream>>>(weights, F_in, (unsigned char*)tc_weights);
+    generator_tc_prepare_kernel<<<148, 256, 0, (cudaStream_t)stream>>>(weights, F_in, F_out, (unsigned char*)tc_weights);
     HFREP_CUDA_OK(cudaGetLastError());
     return HFREP_OK;
 }
@@ -514,8 +538,7 @@ extern "C" int hfrep_generator_forward_tc(const float* weights, const void* tc_w
     GenTcParams p;
     p.W = weights; p.tcw = (const unsigned char*)tc_weights; p.noise = noise; p.out = out; p.n = n_paths; p.T = T;
     p.F_in = F_in; p.F_out = F_out; p.lrelu1 = lrelu_after_lstm1; p.lrelu2 = lrelu_after_lstm2; p.alpha = alpha; p.ln_eps = ln_eps;
-    p.debug = getenv("HFREP_GEN_TC_DEBUG") ? atoi(getenv("HFREP_GEN_TC_DEBUG")) : 0;
-    const size_t smem = 6 * (size_t)G_PLANE_A + 2 * (size_t)G_STAGE + sizeof(float) * (2 * GG + 4 * GU + 512 + GU * 36);
+    const size_t smem = 6 * (size_t)G_PLANE_A + 2 * (size_t)G_STAGE + sizeof(float) * (2 * GG + 4 * GU + 512);
     HFREP_CUDA_OK(allow_max_dynamic_smem(generator_tc_kernel));
     generator_tc_kernel<<<(n_paths + 63) / 64, 320, smem, (cudaStream_t)stream>>>(p);
     HFREP_CUDA_OK(cudaGetLastError());

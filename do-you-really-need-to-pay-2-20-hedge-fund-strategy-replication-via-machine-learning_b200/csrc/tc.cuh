@@ -27,12 +27,13 @@ __device__ __forceinline__ bool mbar_try(uint64_t* bar, unsigned parity) {
     return ok != 0;
 }
 // bounded wait: a barrier that never completes traps instead of hanging the GPU
+template <bool SLEEP = true>
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, unsigned parity) {
     if (mbar_try(bar, parity)) return;
     const long long t0 = clock64();
     while (!mbar_try(bar, parity)) {
-        __nanosleep(64);                               // a waiting thread leaves the issue slots to the warps that work
-        if (clock64() - t0 > (1ll << 31)) __trap();
+        if (SLEEP) __nanosleep(64);                    // a waiting thread leaves the issue slots to the warps that work
+        if (clock64() - t0 > (1ll << 31)) __trap();    // (SLEEP = false: waits on the critical path, where the wake-up lag counts)
     }
 }
 __device__ __forceinline__ void fence_barrier_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
