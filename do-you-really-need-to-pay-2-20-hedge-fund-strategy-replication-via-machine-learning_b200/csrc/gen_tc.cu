@@ -7,6 +7,7 @@
 #include "tc.cuh"
 
 #include <cstdlib>
+#include <type_traits>
 
 namespace hfrep {
 
@@ -146,6 +147,8 @@ struct GenTcParams {
     float alpha, ln_eps;
 };
 
+// 2^x; results below the normal range flush to zero (1 + e is 1 either way)
+__device__ __forceinline__ float ex2_fast(float x) { float r; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
 __device__ __forceinline__ float rcp_fast(float x) { float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
 // gate column n -> (unit, gate): n = 200*pr + 8*i + 4*hh + g  <->  unit 4*i + 2*pr + hh
 __host__ __device__ constexpr int gate_col_unit(int n) { return 4 * ((n % 200) >> 3) + 2 * (n / 200) + ((n >> 2) & 1); }
@@ -218,7 +221,7 @@ __global__ void __launch_bounds__(320, 1) generator_tc_kernel(const GenTcParams 
         const int kx0 = 10 * q;                                        // this thread's 10 columns of the x operand
         auto put = [&](unsigned char* region, int k, float v) {
             float hi, lo;
-            tc::split_tf32(v, hi, lo);
+            tc::split_tf32_trunc(v, hi, lo);
             const uint32_t o = a_off(row, k);
             *reinterpret_cast<float*>(region + o) = hi;
             *reinterpret_cast<float*>(region + G_PLANE_A + o) = lo;
@@ -226,7 +229,7 @@ __global__ void __launch_bounds__(320, 1) generator_tc_kernel(const GenTcParams 
         const uint32_t unit_base = a_off(row, q);                      // operand column of unit 4i + q: + 128 i bytes
         auto put_unit = [&](unsigned char* region, int i, float v) {
             float hi, lo;
-            tc::split_tf32(v, hi, lo);
+            tc::split_tf32_trunc(v, hi, lo);
             *reinterpret_cast<float*>(region + unit_base + 128 * i) = hi;
             *reinterpret_cast<float*>(region + G_PLANE_A + unit_base + 128 * i) = lo;
         };
@@ -256,36 +259,55 @@ __global__ void __launch_bounds__(320, 1) generator_tc_kernel(const GenTcParams 
             const float* bq = bp + 200 * pr + 4 * hh;                   // + 8 i: the four gate biases of unit 4i + q
             // gates of one unit: the lanes that hold the TMEM rows (half `own`: 0 = lanes 0-15, layer 1; 1 = lanes 16-31, layer 2)
             // keep their own four of a unit pair's eight columns and hand the other four to the other half
-            auto unit = [&](int i, const uint32_t* r8) {
-                float z[4];
-                const float4 b4 = *reinterpret_cast<const float4*>(bq + 8 * i);
-                const float bb[4] = {b4.x, b4.y, b4.z, b4.w};
+            // NU units at once, stage by stage: the compiler keeps a unit's ~20 dependent operations (shuffle, ex2, rcp, ...)
+            // in order, so written unit by unit the chains run one after the other; written across the units they overlap.
+            auto units = [&](auto nu_tag, int i0, const uint32_t* r) {
+                constexpr int NU = decltype(nu_tag)::value;
+                float z[NU][4];
 #pragma unroll
-                for (int g = 0; g < 4; ++g) {
-                    const uint32_t o = __shfl_sync(0xffffffffu, r8[4 * (1 - own) + g], l16 + 16 * own);
-                    z[g] = __uint_as_float(hh == own ? r8[4 * own + g] : o) + bb[g];
+                for (int k = 0; k < NU; ++k) {
+                    const float4 b4 = *reinterpret_cast<const float4*>(bq + 8 * (i0 + k));
+                    const float bb[4] = {b4.x, b4.y, b4.z, b4.w};
+#pragma unroll
+                    for (int g = 0; g < 4; ++g) {
+                        const uint32_t o = __shfl_sync(0xffffffffu, r[8 * k + 4 * (1 - own) + g], l16 + 16 * own);
+                        z[k][g] = __uint_as_float(hh == own ? r[8 * k + 4 * own + g] : o) + bb[g];
+                    }
                 }
-                // sigmoids with 5 ex2 + 3 rcp: i*cand and o*sigmoid(c) share a reciprocal each
-                const float ei = __expf(-z[0]), ef = __expf(-z[1]), ec = __expf(-z[2]), eo = __expf(-z[3]);
-                c[i] = fmaf(rcp_fast(1.f + ef), c[i], rcp_fast((1.f + ei) * (1.f + ec)));
-                const float h = rcp_fast((1.f + eo) * (1.f + __expf(-c[i])));
-                put_unit(Hreg, i, h);
-                hv[i] = (lrelu && !(h > 0.f)) ? alpha * h : h;
-                ssum += hv[i];
+                // sigmoids with 5 ex2 + 3 rcp per unit: i*cand and o*sigmoid(c) share a reciprocal each
+                float e[NU][4];
+#pragma unroll
+                for (int k = 0; k < NU; ++k)
+#pragma unroll
+                    for (int g = 0; g < 4; ++g) e[k][g] = ex2_fast(z[k][g] * -1.4426950408889634f);
+                float rf[NU], ric[NU];
+#pragma unroll
+                for (int k = 0; k < NU; ++k) { rf[k] = rcp_fast(1.f + e[k][1]); ric[k] = rcp_fast((1.f + e[k][0]) * (1.f + e[k][2])); }
+                float es[NU];
+#pragma unroll
+                for (int k = 0; k < NU; ++k) { c[i0 + k] = fmaf(rf[k], c[i0 + k], ric[k]); es[k] = ex2_fast(c[i0 + k] * -1.4426950408889634f); }
+                float h[NU];
+#pragma unroll
+                for (int k = 0; k < NU; ++k) h[k] = rcp_fast((1.f + e[k][3]) * (1.f + es[k]));
+#pragma unroll
+                for (int k = 0; k < NU; ++k) {
+                    put_unit(Hreg, i0 + k, h[k]);
+                    hv[i0 + k] = (lrelu && !(h[k] > 0.f)) ? alpha * h[k] : h[k];
+                    ssum += hv[i0 + k];
+                }
             };
 #pragma unroll
             for (int i0 = 0; i0 < 24; i0 += 4) {                        // four units of both lane halves per 32-column load
                 uint32_t r[32];
                 tc::tmem_ld32_nowait(zcol + (uint32_t)(8 * i0), r);
                 tc::tmem_ld_wait();
-#pragma unroll
-                for (int k = 0; k < 4; ++k) unit(i0 + k, r + 8 * k);
+                units(std::integral_constant<int, 4>{}, i0, r);
             }
             {
                 uint32_t r[8];
                 tc::tmem_ld8_nowait(zcol + 8u * 24u, r);
                 tc::tmem_ld_wait();
-                unit(24, r);
+                units(std::integral_constant<int, 1>{}, 24, r);
             }
             lnA[row * 4 + q] = ssum;
             epi_sync();

@@ -135,6 +135,13 @@ __device__ __forceinline__ void split_tf32(float x, float& hi, float& lo) {
     hi = tf32_rna(x);
     lo = tf32_rna(x - hi);
 }
+// the same by truncation: two logic operations and a subtraction instead of two emulated round-to-nearest conversions
+// (cvt.rna.tf32 is ~10 integer instructions here); hi + lo = x to 2^-21 |x| instead of 2^-22 |x|.  For operands that are
+// rewritten every step; weights, split once, use the rounded version.
+__device__ __forceinline__ void split_tf32_trunc(float x, float& hi, float& lo) {
+    hi = __uint_as_float(__float_as_uint(x) & 0xffffe000u);
+    lo = __uint_as_float(__float_as_uint(x - hi) & 0xffffe000u);
+}
 // byte offset of element (row, k) in the canonical K-major layout with all K pieces of an 8-row group contiguous:
 // lbo = 128, sbo = (K/4)*128
 __host__ __device__ constexpr uint32_t kmajor_off(int row, int k, int K) {
