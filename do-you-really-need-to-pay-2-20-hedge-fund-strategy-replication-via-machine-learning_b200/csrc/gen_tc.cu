@@ -121,9 +121,7 @@ __global__ void __launch_bounds__(128) tc_mma_rate_kernel(int N, int iters) {
 //     memory and rewritten in place by the epilogue threads every step,
 //   * the B operands (the weights, split into hi / lo planes and laid out per K = 8 step by hfrep_generator_tc_prepare,
 //     gate columns permuted so that a unit's four gates are adjacent) streamed from L2 through a two-stage ring of 25.6 KB
-//     bulk copies, one mbarrier pair per stage; the CTAs run in clusters of two and share the stream: each CTA's loader
-//     fetches half of every block (the hi plane, the lo plane) and multicasts it to both — half the L2 traffic, which is
-//     what bounded the MMA chains (7.5 TB/s drawn from L2 before),
+//     bulk copies (cp.async.bulk, THIS GPU's memory, no multicast), one mbarrier pair per stage,
 //   * warps 0-7: epilogue (TMEM -> registers, gates, cell state in registers, LayerNorm, operands of the next MMA chain,
 //     Dense, output), warp 8: MMA issue (one thread), warp 9: weight loader (one thread).
 // M = 64 accumulators occupy lanes 0-15 of each 32-lane TMEM quarter; the epilogue warps hand half of what they load to
@@ -188,7 +186,7 @@ __global__ void __launch_bounds__(320, 1) generator_tc_kernel(const GenTcParams 
     if (warp == 0) tc::tmem_alloc<512>(&tmem_slot);
     if (tid == 0) {
         tc::mbar_init(&bar_full[0], 1); tc::mbar_init(&bar_full[1], 1);
-        tc::mbar_init(&bar_empty[0], 2); tc::mbar_init(&bar_empty[1], 2);     // a stage is free when BOTH CTAs' MMAs have read it
+        tc::mbar_init(&bar_empty[0], 1); tc::mbar_init(&bar_empty[1], 1);
         tc::mbar_init(&bar_z, 1); tc::mbar_init(&bar_a, G_EPI / 32);
         tc::fence_barrier_init();
     }
@@ -204,11 +202,9 @@ __global__ void __launch_bounds__(320, 1) generator_tc_kernel(const GenTcParams 
     for (int i = tid; i < (int)(6 * G_PLANE_A / 4); i += blockDim.x) reinterpret_cast<float*>(smraw)[i] = 0.f;   // h1 = h2 = 0, pads
     tc::tc_fence_before();
     __syncthreads();
-    tc::cluster_sync();                                  // both CTAs' barriers exist before either loader or MMA thread signals the other
     tc::tc_fence_after();
     const uint32_t tmem = tmem_slot;
     const int path0 = blockIdx.x * 64;
-    const unsigned crank = tc::cluster_ctarank();
 
     if (warp < G_EPI / 32) {
         // ============================================================ epilogue threads
@@ -403,7 +399,7 @@ __global__ void __launch_bounds__(320, 1) generator_tc_kernel(const GenTcParams 
                     tc::mma_tf32(d, ad, tc::smem_desc(bb, G_LBO, G_SBO_B), i0, !first || c > 0);
                     tc::mma_tf32(d + TCN0, ad, tc::smem_desc(bb + (TCN0 / 8) * G_SBO_B, G_LBO, G_SBO_B), i1, !first || c > 0);
                 }
-                tc::mma_commit_multicast(&bar_empty[st], 3);            // this CTA is done with the stage: tell both loaders
+                tc::mma_commit(&bar_empty[st]);                         // the stage is free once these MMAs have read it
                 ++g;
             };
             auto kstep_dense = [&](uint32_t abase, uint32_t d, bool first) {
@@ -416,7 +412,7 @@ __global__ void __launch_bounds__(320, 1) generator_tc_kernel(const GenTcParams 
                     const uint32_t aa = abase + (c == 1 ? G_PLANE_A : 0u), bb = bbase + (c == 2 ? G_PLANE_D : 0u);
                     tc::mma_tf32(d, tc::smem_desc(aa, G_LBO, G_SBO_A), tc::smem_desc(bb, G_LBO, G_SBO_B), id, !first || c > 0);
                 }
-                tc::mma_commit_multicast(&bar_empty[st], 3);
+                tc::mma_commit(&bar_empty[st]);
                 ++g;
             };
             const uint32_t z1 = tmem, z2 = tmem + (16u << 16), zd = tmem + 400u;   // layer 2: lanes 16-31 of every TMEM quarter
@@ -448,13 +444,11 @@ __global__ void __launch_bounds__(320, 1) generator_tc_kernel(const GenTcParams 
         // ============================================================ weight loader (same order as the MMA issue)
         if (lane == 0) {
             uint32_t g = 0;
-            // this CTA fetches plane `crank` (0: hi, 1: lo) of the block and multicasts it into the same stage of both CTAs;
-            // its own barrier expects the whole block: the other plane arrives from the peer's loader
             auto load = [&](const unsigned char* src, uint32_t bytes) {
-                const uint32_t st = g & 1, half = bytes >> 1;
+                const uint32_t st = g & 1;
                 tc::mbar_wait(&bar_empty[st], ((g >> 1) & 1) ^ 1);
                 tc::mbar_expect_tx(&bar_full[st], bytes);
-                tc::bulk_g2s_multicast(ring + st * G_STAGE + crank * half, src + crank * half, half, &bar_full[st], 3);
+                tc::bulk_g2s(ring + st * G_STAGE, src, bytes, &bar_full[st]);
                 ++g;
             };
             const unsigned char* bx = p.tcw;                                   // 5 blocks: W1 rows of x
@@ -476,7 +470,6 @@ __global__ void __launch_bounds__(320, 1) generator_tc_kernel(const GenTcParams 
     }
     tc::tc_fence_before();
     __syncthreads();
-    tc::cluster_sync();                                  // neither CTA leaves while the peer could still write its stages or barriers
     if (warp == 0) tc::tmem_free<512>(tmem);
 }
 
@@ -568,26 +561,8 @@ extern "C" int hfrep_generator_forward_tc(const float* weights, const void* tc_w
     p.W = weights; p.tcw = (const unsigned char*)tc_weights; p.noise = noise; p.out = out; p.n = n_paths; p.T = T;
     p.F_in = F_in; p.F_out = F_out; p.lrelu1 = lrelu_after_lstm1; p.lrelu2 = lrelu_after_lstm2; p.alpha = alpha; p.ln_eps = ln_eps;
     const size_t smem = 6 * (size_t)G_PLANE_A + 2 * (size_t)G_STAGE + sizeof(float) * (2 * GG + 4 * GU + 512);
-    // the weight blocks are multicast to the CTAs of a cluster: they must be THIS GPU's memory
-    cudaPointerAttributes pa;
-    int dev = -1;
-    HFREP_CUDA_OK(cudaGetDevice(&dev));
-    HFREP_CUDA_OK(cudaPointerGetAttributes(&pa, tc_weights));
-    HFREP_REQUIRE(pa.type == cudaMemoryTypeDevice && pa.device == dev,
-                  "generator_forward_tc: tc_weights must be device memory of the current GPU (%d), got type %d on device %d", dev,
-                  (int)pa.type, pa.device);
     HFREP_CUDA_OK(allow_max_dynamic_smem(generator_tc_kernel));
-    cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3((unsigned)(((n_paths + 63) / 64 + 1) & ~1), 1, 1);           // clusters of two CTAs (a CTA past the paths runs idle rows)
-    cfg.blockDim = dim3(320, 1, 1);
-    cfg.dynamicSmemBytes = smem;
-    cfg.stream = (cudaStream_t)stream;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeClusterDimension;
-    attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
-    cfg.attrs = attr;
-    cfg.numAttrs = 1;
-    HFREP_CUDA_OK(cudaLaunchKernelEx(&cfg, generator_tc_kernel, p));
+    generator_tc_kernel<<<(n_paths + 63) / 64, 320, smem, (cudaStream_t)stream>>>(p);
     HFREP_CUDA_OK(cudaGetLastError());
     return HFREP_OK;
 }

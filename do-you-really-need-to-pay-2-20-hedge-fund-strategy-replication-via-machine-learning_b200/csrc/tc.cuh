@@ -1,8 +1,6 @@
 // tcgen05 building blocks (sm_100a): tensor-memory allocation, shared-memory matrix descriptors for the un-swizzled
 // K-major canonical layout, the TF32 MMA, commit-to-mbarrier, accumulator loads, and the 3xTF32 operand split.
-// MMAs and tensor memory are this CTA's (cta_group::1).  The one cluster operation is the multicast bulk copy of weight
-// blocks to the CTAs of a cluster: TMA multicast loads here read only this GPU's memory, since on B200 a TMA multicast load
-// from another GPU's memory hung the GPU (the host entry point checks where the pointer lives).
+// Everything here addresses THIS CTA's shared and tensor memory only (cta_group::1, no cluster, no multicast).
 #pragma once
 #include <cstdint>
 #include <cuda_runtime.h>
@@ -48,17 +46,6 @@ __device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src, unsign
                  ::"r"(smem_u32(dst_smem)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
 }
 
-// the same copy delivered to every CTA of `cta_mask` at the same shared-memory offset, each CTA's own barrier counting the
-// bytes.  Source: memory of THIS GPU only (see the header of this file).
-__device__ __forceinline__ void bulk_g2s_multicast(void* dst_smem, const void* src, unsigned bytes, uint64_t* bar, uint16_t cta_mask) {
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster [%0], [%1], %2, [%3], %4;"
-                 ::"r"(smem_u32(dst_smem)), "l"(src), "r"(bytes), "r"(smem_u32(bar)), "h"(cta_mask) : "memory");
-}
-__device__ __forceinline__ unsigned cluster_ctarank() { unsigned r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return r; }
-__device__ __forceinline__ void cluster_sync() {
-    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
-}
-
 // ---- tensor memory
 template <int COLS>
 __device__ __forceinline__ void tmem_alloc(uint32_t* slot_smem) {          // one full warp
@@ -95,11 +82,6 @@ __device__ __forceinline__ void mma_tf32(uint32_t d_tmem, uint64_t a_desc, uint6
 // all MMAs issued so far by this thread: when they complete, one arrival on `bar` (implies fence::before_thread_sync)
 __device__ __forceinline__ void mma_commit(uint64_t* bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
-}
-// ... one arrival on the barrier at this offset in every CTA of `cta_mask`
-__device__ __forceinline__ void mma_commit_multicast(uint64_t* bar, uint16_t cta_mask) {
-    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
-                 ::"r"(smem_u32(bar)), "h"(cta_mask) : "memory");
 }
 // accumulator rows of this warp's 32-lane quarter: lane i <- 8 / 4 consecutive columns of TMEM lane (base lane + i)
 __device__ __forceinline__ void tmem_ld8(uint32_t taddr, float (&v)[8]) {
