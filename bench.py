@@ -672,7 +672,7 @@ def paths_record(r, peak):
     if r["gen_ms"] is not None:
         gflop = n * 168 * 2. * ((36 + 100) * 400 + 200 * 400 + 100 * 36) / 1e9
         # tensor-pipe work the tcgen05 kernel issues: 3 TF32 MMAs per product, K padded to 144 / 208, 64-row MMAs
-        tc_gflop = n * 168 * 3 * 2. * 400 * (144 + 208) / 1e9
+        tc_gflop = n * 168 * 3 * 2. * (400 * (144 + 208) + 40 * 104) / 1e9      # (+ the Dense chain: N = 40, K = 104)
         tf32_peak = (measured_peaks().get("bf16_tflops_sustained") or 1404.3) / 2.
         gen_rec = {"kernel": "generator_tc_kernel (LSTM 36->100->100->36, 168 steps; tcgen05 kind::tf32 in 3xTF32, FP32 accumulators in TMEM)",
                    "ms": r["gen_ms"], "paths_per_s": n / (r["gen_ms"] * 1e-3),
