@@ -860,9 +860,10 @@ static int fit_batched_impl(const hfrep_fit_cfg* c, const float* X, int n_tasks,
         const int sms = sm_count();                  // (callers that split a job over several calls pass it explicitly)
         // measured on the L = 1..21 sweep x seeds (profiles/README.md): a six-CTA cluster per task while every cluster has
         // its own SMs; 6 warps win up to ~5 tasks per SM, 2 warps beyond (narrow tasks in large numbers: one warp per task
-        // — L = 8 x 4096 tasks 6.6 vs 7.8 ms per 100 epochs; L = 20: 14.8 vs 12.1)
+        // — L = 8 x 4096 tasks 6.6 vs 7.8 ms per 100 epochs; L = 20: 14.8 vs 12.1; with a training block per task (batch-tile
+        // staging) 2 warps stay ahead: 100 000 path tasks 207 vs 219 ms)
         wpt = n_tasks * 6 <= sms ? HFREP_WPT_CLUSTER
-                                 : (n_tasks <= 5 * sms ? 6 : ((c->L_max <= 8 && n_tasks >= 10 * sms) ? 1 : 2));
+                                 : (n_tasks <= 5 * sms ? 6 : ((c->L_max <= 8 && n_tasks >= 10 * sms && p.shared_x) ? 1 : 2));
     }
     HFREP_REQUIRE(wpt == 1 || wpt == 2 || wpt == 3 || wpt == 6 || wpt == HFREP_WPT_CLUSTER,
                   "fit_batched: warps_per_task=%d (0, 1, 2, 3, 6 or HFREP_WPT_CLUSTER)", wpt);
