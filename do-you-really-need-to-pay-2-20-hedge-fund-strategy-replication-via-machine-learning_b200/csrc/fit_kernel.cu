@@ -71,12 +71,13 @@ struct Lay {
     __host__ __device__ static constexpr bool mv_in_regs(int NW) { return NW >= 2; }
     // XT (batch-tile mode): the training block stays in global memory / L2 and only the current mini-batch's rows
     // sit in a per-team tile [BP+1][XS], refilled with cp.async; else the whole block is resident once per CTA.
-    __host__ __device__ static size_t team_floats(int BP, int NW, bool XT, int PS, int T) {
-        return (size_t)EP * LP + (size_t)LP * WDS + (size_t)(BP + 1) * HS * 2 + (size_t)(BP + 1) * XS +
+    // PRIV: resident mode with the training block per team instead of per CTA (tasks with their own blocks)
+    __host__ __device__ static size_t team_floats(int BP, int NW, bool XT, int PS, int T, bool PRIV = false) {
+        return (PRIV ? (size_t)(T + 1) * XS : 0) + (size_t)EP * LP + (size_t)LP * WDS + (size_t)(BP + 1) * HS * 2 + (size_t)(BP + 1) * XS +
                (size_t)npart(NW) * NEL + (mv_in_regs(NW) ? 0 : 2 * (size_t)NEL) + (XT ? 0 : 2 * (size_t)((T + 3) & ~3)) + 64 +
                (XT ? (size_t)(BP + 1) * XS : 0) + PS;
     }
-    __host__ __device__ static size_t cta_floats(int T, bool XT) { return (XT ? 0 : (size_t)(T + 1) * XS) + NEL / 4; }
+    __host__ __device__ static size_t cta_floats(int T, bool XT, bool PRIV = false) { return ((XT || PRIV) ? 0 : (size_t)(T + 1) * XS) + NEL / 4; }
 };
 
 template <int NW>
@@ -126,12 +127,13 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
     const bool active = task < p.n_tasks;
     const int T = p.T, E = p.E, BP = p.BP;
 
-    const size_t cf = Lay<LP>::cta_floats(T, XT);
-    const size_t tf = Lay<LP>::team_floats(BP, NW, XT, p.PS, T);
+    const bool priv = !XT && p.private_x;            // this team's own resident block
+    const size_t cf = Lay<LP>::cta_floats(T, XT, priv);
+    const size_t tf = Lay<LP>::team_floats(BP, NW, XT, p.PS, T, priv);
     // [Xs (resident mode only) | woff | team 0 | team 1 ...]
-    int* woff = reinterpret_cast<int*>(smem + (XT ? 0 : (size_t)(T + 1) * XS));
+    int* woff = reinterpret_cast<int*>(smem + ((XT || priv) ? 0 : (size_t)(T + 1) * XS));
     float* base = smem + cf + (size_t)team * tf;
-    float* We = base;
+    float* We = base + (priv ? (size_t)(T + 1) * XS : 0);
     float* Wd = We + EP * LP;
     float* H = Wd + LP * WDS;
     float* dZh = H + (BP + 1) * HS;
@@ -150,7 +152,7 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
     int* xoff_tab = reinterpret_cast<int*>(part + NPART * NEL + (MVREG ? 0 : 2 * NEL));
     float* red = reinterpret_cast<float*>(xoff_tab + 2 * TP);          // [2][32], double-buffered per epoch
     // Xs: what the phases address rows in — the resident block (row r at xoff[r]) or the team's batch tile (row r at r*XS)
-    float* Xs = XT ? red + 64 : smem;
+    float* Xs = XT ? red + 64 : (priv ? base : smem);
     unsigned* keyS = reinterpret_cast<unsigned*>(red + 64 + (XT ? (BP + 1) * XS : 0));   // [n_fit] shuffle keys
     int* permS = reinterpret_cast<int*>(keyS) + p.PS / 2;                                  // [n_fit] this epoch's row order
     const int zero_row = XT ? BP * XS : T * XS;      // all-zero row for idle lanes
@@ -163,7 +165,8 @@ __global__ void __launch_bounds__(32 * NW * TPC) fit_kernel(const FitParams p) {
             for (int idx = tl; idx < (BP + 1) * XS; idx += NTH) Xs[idx] = 0.f;   // pad columns and the zero row stay 0
         } else {
             const int n = (T + 1) * XS;
-            for (int idx = threadIdx.x; idx < n; idx += blockDim.x) {
+            const int i0 = priv ? tl : threadIdx.x, di = priv ? NTH : blockDim.x;     // own block: the team stages it
+            for (int idx = i0; idx < n; idx += di) {
                 const int r = idx / XS, c = idx - r * XS;
                 Xs[idx] = (r < T && c < E) ? __ldg(xg + (size_t)r * E + c) : 0.f;
             }
@@ -724,11 +727,13 @@ constexpr size_t kMaxSmem = 227 * 1024;
 
 template <int LP, int NW>
 static size_t fit_smem_bytes(const FitParams& p, int tpc, bool xt) {
-    return sizeof(float) * (Lay<LP>::cta_floats(p.T, xt) + tpc * Lay<LP>::team_floats(p.BP, NW, xt, p.PS, p.T));
+    const bool priv = !xt && p.private_x;
+    return sizeof(float) * (Lay<LP>::cta_floats(p.T, xt, priv) + tpc * Lay<LP>::team_floats(p.BP, NW, xt, p.PS, p.T, priv));
 }
 
-// Resident mode: teams of one CTA share the staged training block, so several teams per CTA need n_x == 1 and the block
-// must fit.  Batch-tile mode (own block per task, or a block too long for shared memory) has neither limit.  The launch
+// Resident mode: the training block sits in shared memory for the whole run — one copy shared by the CTA's teams when all
+// tasks train on the same block (n_x == 1), one copy per team when every task has its own (private_x).  Batch-tile mode (a
+// block too long for shared memory) stages only the current mini-batch's rows.  The launch
 // takes the largest team count (<= TPC) whose shared memory fits.
 template <int LP, int NW, int TPC, bool FULL, bool XT>
 static int launch_fit_mode(const FitParams& p, cudaStream_t stream) {
@@ -750,9 +755,13 @@ static int launch_fit_mode(const FitParams& p, cudaStream_t stream) {
 
 template <int LP, int NW, int TPC, bool FULL>
 static int launch_fit(const FitParams& p, cudaStream_t stream) {
-    const bool resident = p.shared_x && fit_smem_bytes<LP, NW>(p, 1, false) <= kMaxSmem && !p.force_tile;
-    return resident ? launch_fit_mode<LP, NW, TPC, FULL, false>(p, stream)
-                    : launch_fit_mode<LP, NW, TPC, FULL, true>(p, stream);
+    FitParams q = p;
+    q.private_x = !p.shared_x;                       // a block per task: resident per team when it fits, else batch tiles
+    const bool resident = fit_smem_bytes<LP, NW>(q, 1, false) <= kMaxSmem && !p.force_tile &&
+                          (p.shared_x || !getenv("HFREP_NO_PRIVATE_BLOCKS"));
+    if (!resident) q.private_x = 0;
+    return resident ? launch_fit_mode<LP, NW, TPC, FULL, false>(q, stream)
+                    : launch_fit_mode<LP, NW, TPC, FULL, true>(q, stream);
 }
 
 // warps per task (every mapping runs the same phases; they differ in how many warps share a task's columns):
@@ -853,6 +862,7 @@ static int fit_batched_impl(const hfrep_fit_cfg* c, const float* X, int n_tasks,
     p.w_stride = w_stride; p.shared_x = (c->n_x == 1); p.dump_step = c->dump_step;
     { const char* dbg = getenv("HFREP_DEBUG_SKIP"); p.debug_skip = dbg ? atoi(dbg) : 0; }
     p.force_tile = getenv("HFREP_FORCE_TILE") != nullptr;
+    p.private_x = 0;
     p.alpha = c->alpha; p.lr = c->lr; p.b1 = c->beta_1; p.b2 = c->beta_2; p.eps = c->epsilon;
 
     int wpt = c->warps_per_task;

@@ -27,6 +27,7 @@ struct FitParams {
     int PS;              // ints reserved per team for the device-side shuffle (0 or 2*n_fit rounded up to 4)
     int n_tasks, E, T, n_fit, n_val, batch, BP, max_epochs, patience, early_stop, w_stride, shared_x, dump_step;
     int force_tile;      // testing: batch-tile mode even when the block could be resident (env HFREP_FORCE_TILE)
+    int private_x;       // resident mode with a training block PER TEAM (tasks with their own blocks that fit shared memory)
     int debug_skip;      // profiling only (env HFREP_DEBUG_SKIP): bit0 rows, bit1 grads, bit2 update phases skipped
     float alpha, lr, b1, b2, eps;
 };
