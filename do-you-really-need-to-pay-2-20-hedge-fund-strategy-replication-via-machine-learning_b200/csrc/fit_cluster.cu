@@ -280,11 +280,12 @@ __global__ void __launch_bounds__(CTH, 1) fit_cluster_kernel(const FitParams p) 
             float2 acc[4][2];
 #pragma unroll
             for (int i = 0; i < 4; ++i) acc[i][0] = acc[i][1] = make_float2(0.f, 0.f);
-#pragma unroll 4
-            for (int r = 0; r < nrows; ++r) {                // ascending positions q = c + 6 r: the class chain
-                const int ao = dec ? r * HS : xoff[(int)c + CL * r];
-                const float4 a = ld4(Xs + a0 + ao);
-                const float4 b = ld4(Xs + b0 + r * bstr);
+#pragma unroll
+            for (int r = 0; r < RPC; ++r) {                  // ascending positions q = c + 6 r: the class chain.  Fixed trip count
+                const bool live = r < nrows;                 // (all loads issue up front); rows past the class read the zero row
+                const int ao = dec ? r * HS : xoff[live ? (int)c + CL * r : 0];
+                const float4 a = ld4(Xs + (live ? a0 + ao : zero_row));
+                const float4 b = ld4(Xs + (live ? b0 + r * bstr : zero_row));
                 const float av[4] = {a.x, a.y, a.z, a.w};
                 const float2 b01 = make_float2(b.x, b.y), b23 = make_float2(b.z, b.w);
 #pragma unroll
