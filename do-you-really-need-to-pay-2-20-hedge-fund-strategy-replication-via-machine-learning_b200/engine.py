@@ -256,7 +256,7 @@ def warps_per_task_for(n_tasks: int, device) -> int:
 def fit_batched(X: torch.Tensor, task_L, W0: torch.Tensor, *, E: int, T: int, n_fit: int | None = None,
                 perm: torch.Tensor | None = None, task_x: torch.Tensor | None = None, dump_step: int | None = None,
                 warps_per_task: int = 0, bucket: bool = True, W_out: torch.Tensor | None = None, after_bucket=None,
-                shuffle_seeds=None,
+                shuffle_seeds=None, hist: torch.Tensor | None = None, ints: torch.Tensor | None = None,
                 **cfg_kw) -> FitResult:
     """Kernel (b) for a batch of tasks.  X f32 [n_x][T][E] (device, scaled); task_L sequence of ints;
     W0 f32 [n][w_stride] (device).  Tasks are grouped by padded latent width (multiples of 4) and each
@@ -302,9 +302,11 @@ def fit_batched(X: torch.Tensor, task_L, W0: torch.Tensor, *, E: int, T: int, n_
         raise ValueError("after_bucket needs the tasks ordered widest-first (see run_mode_r)")
     # one allocation for both histories, one for the two int vectors; nothing to initialise (the kernel writes NaN past
     # the last epoch run, and epochs_run / status of every task)
-    hist = torch.empty((2, n, cfg.max_epochs), dtype=torch.float32, device=device)
+    if hist is None:                                   # (callers that pack results themselves pass both: SweepPlan)
+        hist = torch.empty((2, n, cfg.max_epochs), dtype=torch.float32, device=device)
     loss, val = hist[0], hist[1]
-    ints = torch.empty((2, n), dtype=torch.int32, device=device)
+    if ints is None:
+        ints = torch.empty((2, n), dtype=torch.int32, device=device)
     epochs_run, status = ints[0], ints[1]
     grads = torch.zeros_like(W0s) if dump_step is not None else None
 
@@ -368,7 +370,7 @@ def rolling_sigma(R64: torch.Tensor, starts: torch.Tensor, window: int) -> torch
 
 def predict_metrics(Xtr64, Xte64, Yte64, rf64, sigma, task_L, W, *, window=24, want_oos=True,
                     want_weights=False, alpha=.2, cost_param=.05, phi=.5, task_row0=None, T_test=None,
-                    want_quality=True, launch=True, beta_rolling=False):
+                    want_quality=True, launch=True, beta_rolling=False, out: dict | None = None):
     """Kernel (c) for a batch of trained tasks (all tensors on the device, float64 unless noted).
     launch=False only allocates the result and returns (result, launcher): launcher(a, b, stream) scores tasks
     [a, b) on `stream` — used to start a width bucket's evaluation right behind its fit, concurrently with the
@@ -384,13 +386,16 @@ def predict_metrics(Xtr64, Xte64, Yte64, rf64, sigma, task_L, W, *, window=24, w
     n_oos, n_pre = T_test - window - 1, T_test - 2
     tL = task_L if isinstance(task_L, torch.Tensor) else _device_ints(np.asarray(task_L, np.int32), device)
     f64 = dict(dtype=torch.float64, device=device)
+    o = out or {}                                      # preallocated result fields (SweepPlan: views of its download buffer)
+    nan_ = lambda key, shape: o[key].fill_(float("nan")) if key in o else torch.full(shape, float("nan"), **f64)
     r = EvalResult(
-        ante=torch.empty((n, n_oos, F), **f64), post=torch.empty((n, n_oos, F), **f64) if sigma is not None else None,
-        turnover=torch.empty((n, F), **f64), metrics=torch.full((n, 2, _lib.N_STATS, F), float("nan"), **f64),
-        quality=torch.full((n, 2 + 2 * n_pre), float("nan"), **f64) if want_quality else None,
+        ante=o.get("ante", None) if "ante" in o else torch.empty((n, n_oos, F), **f64),
+        post=(o["post"] if "post" in o else torch.empty((n, n_oos, F), **f64)) if sigma is not None else None,
+        turnover=o["turnover"] if "turnover" in o else torch.empty((n, F), **f64), metrics=nan_("metrics", (n, 2, _lib.N_STATS, F)),
+        quality=nan_("quality", (n, 2 + 2 * n_pre)) if want_quality else None,
         mask=torch.empty((n, n_oos, E), dtype=torch.uint8, device=device),
         beta=torch.empty((n, _lib.MAX_L, F), **f64), norm=torch.empty((n, F), **f64),
-        status=torch.zeros(n, dtype=torch.int32, device=device),
+        status=o["eval_status"].zero_() if "eval_status" in o else torch.zeros(n, dtype=torch.int32, device=device),
         weights=torch.empty((n, n_oos, E, F), **f64) if want_weights else None)
 
     def launcher(a, b, stream):
@@ -475,15 +480,16 @@ class ReplicationData:
 
 
 def fit_and_score(data: "ReplicationData", task_L, W0d: torch.Tensor, *, perm=None, want_oos=True, want_weights=False,
-                  warps_per_task=0, **fit_kw):
+                  warps_per_task=0, out: dict | None = None, **fit_kw):
     """Kernel (b) then kernel (c) for tasks ordered widest-first: every width bucket's evaluation is queued on the
     bucket's own stream right behind its fit, so it overlaps the fits of the other buckets."""
-    W_out = torch.empty_like(W0d)
+    o = out or {}
+    W_out = o["W"] if "W" in o else torch.empty_like(W0d)
     ev, score = predict_metrics(data.Xtr64, data.Xte64, data.Yte64, data.rf64, data.sigma, task_L, W_out,
                                 window=data.window, want_oos=want_oos, want_weights=want_weights,
-                                alpha=fit_kw.get("alpha", .2), launch=False)
+                                alpha=fit_kw.get("alpha", .2), launch=False, out=out)
     fit = fit_batched(data.Xtr32, task_L, W0d, E=data.E, T=data.n_train, perm=perm, warps_per_task=warps_per_task,
-                      W_out=W_out, after_bucket=score, **fit_kw)      # fit_kw may carry shuffle_seeds
+                      W_out=W_out, after_bucket=score, hist=o.get("hist"), ints=o.get("ints"), **fit_kw)      # fit_kw may carry shuffle_seeds
     return fit, ev
 
 
@@ -584,13 +590,37 @@ class SweepPlan:
             self._img_host[:] = 0.
             in_dev = torch.empty_like(self._in_host, device=dev)
 
+            # the results a caller downloads are views of ONE device buffer, so the kernels write the packed image themselves
+            n_test = split_rows(T, test_size)[1]
+            n_oos, n_pre = n_test - window - 1, n_test - 2
+            epochs = _lib.fit_cfg(E=E, T=self.n_train, n_fit=1, **{k: v for k, v in fit_kw.items() if k != "shuffle_seeds"}).max_epochs
+            fields = [("ante", torch.float64, (n, n_oos, F)), ("post", torch.float64, (n, n_oos, F)), ("turnover", torch.float64, (n, F)),
+                      ("metrics", torch.float64, (n, 2, _lib.N_STATS, F)), ("quality", torch.float64, (n, 2 + 2 * n_pre)),
+                      ("eval_status", torch.int32, (n,)), ("ints", torch.int32, (2, n)), ("hist", torch.float32, (2, n, epochs)),
+                      ("W", torch.float32, (n, self.w_stride))]
+            carve, off = {}, 0
+            for name, dt, shape in fields:
+                off += (-off) & 15
+                carve[name] = (off, dt, shape)
+                off += int(np.prod(shape)) * torch.empty((), dtype=dt).element_size()
+            out_dev = torch.zeros(off, dtype=torch.uint8, device=dev)
+            views = {k: out_dev[o:o + int(np.prod(sh)) * torch.empty((), dtype=dt).element_size()].view(dt).reshape(sh)
+                     for k, (o, dt, sh) in carve.items()}
+            self._out_host = torch.empty(off, dtype=torch.uint8, pin_memory=True)
+            eb = 4 * n * epochs                                  # bytes of one history
+            o_i, o_h = carve["ints"][0], carve["hist"][0]
+            self._layout = [carve["ante"], carve["post"], carve["turnover"], carve["metrics"], carve["quality"], carve["eval_status"],
+                            (o_i, torch.int32, (n,)), (o_i + 4 * n, torch.int32, (n,)),
+                            (o_h, torch.float32, (n, epochs)), (o_h + eb, torch.float32, (n, epochs)), carve["W"]]
+
             def body():
                 in_dev.copy_(self._in_host, non_blocking=True)
                 data = ReplicationData.from_packed(in_dev[:8 * n_img].view(torch.float64), T, E, F, window, test_size)
                 W0d = in_dev[8 * n_img:].view(torch.float32).reshape(n, self.w_stride)
-                fit, ev = fit_and_score(data, task_L, W0d, want_oos=want_oos, **fit_kw)
-                return [ev.ante, ev.post, ev.turnover, ev.metrics, ev.quality, ev.status, fit.epochs_run, fit.status,
-                        fit.loss, fit.val_loss, fit.W]
+                fit, ev = fit_and_score(data, task_L, W0d, want_oos=want_oos, out=views, **fit_kw)
+                assert fit.W.data_ptr() == views["W"].data_ptr() and fit.loss.data_ptr() == views["hist"].data_ptr() \
+                    and ev.ante.data_ptr() == views["ante"].data_ptr(), "results not written in place"
+                self._out_host.copy_(out_dev, non_blocking=True)
 
             # once eagerly on a well-formed image: fills the small caches (schedules, index tables), loads the kernels
             rng = np.random.default_rng(0)
@@ -598,23 +628,11 @@ class SweepPlan:
             side = torch.cuda.Stream(device=dev)
             side.wait_stream(torch.cuda.current_stream(dev))
             with torch.cuda.stream(side):
-                outs = body()
+                body()
             side.synchronize()
-            self._layout, off = [], 0
-            for t in outs:
-                off += (-off) & 15
-                self._layout.append((off, t.dtype, tuple(t.shape)))
-                off += t.numel() * t.element_size()
-            self._out_host = torch.empty(off, dtype=torch.uint8, pin_memory=True)
-            out_dev = torch.zeros(off, dtype=torch.uint8, device=dev)
-            del outs
             self._graph = torch.cuda.CUDAGraph()
             with torch.cuda.graph(self._graph, stream=side, capture_error_mode="thread_local"):
-                outs = body()
-                for t, (o, _, _) in zip(outs, self._layout):
-                    nb = t.numel() * t.element_size()
-                    out_dev[o:o + nb].copy_(t.contiguous().reshape(-1).view(torch.uint8))
-                self._out_host.copy_(out_dev, non_blocking=True)
+                body()
             self._stream = side
         self.h2d_bytes, self.d2h_bytes = self._in_host.numel(), off
 
